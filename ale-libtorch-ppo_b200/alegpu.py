@@ -1,0 +1,462 @@
+"""alegpu.py — host-side mirror of the reference's learner interfaces over libalegpu.so.
+
+The reference (cemlyn007/ale-libtorch-ppo) exposes its learner path as C++ functions over
+torch::Tensor (src/ai/gae.h, src/ai/buffer.h, src/ai/vision.h, src/ai/ppo/losses.h,
+src/ai/ppo/train.h).  This module gives the same operations, with the same names, argument
+order and error behaviour, over the C ABI in include/alegpu.h: `gae`, `Buffer`
+(`add`/`get` -> `Batch`), `losses.compute`/`normalize_logits`, `Learner` (= Network +
+torch::optim::Adam + train()), `Metrics`, `Hyperparameters`.  std::invalid_argument maps to
+ValueError, std::runtime_error to RuntimeError, std::out_of_range to IndexError.
+
+Device memory is owned by the library (cudaMalloc through the ABI); numpy arrays are staged
+with explicit copies.  There is NO CPU fallback: if libalegpu.so is missing or no CUDA
+device is present every call raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "libalegpu.so")
+_lib = None
+
+MATH_FP32, MATH_BF16 = 0, 1
+FRAME_BYTES = 210 * 160 * 3
+STACK_BYTES = 4 * 84 * 84
+
+
+class CudaError(RuntimeError):
+    pass
+
+
+def lib():
+    """Load libalegpu.so (built by `make -C ale-libtorch-ppo_b200`); fail loudly if absent."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise ImportError(
+                f"{SO_PATH} is missing: build it with __graft_entry__.build() "
+                "(there is no CPU fallback for the learner path)")
+        _lib = C.CDLL(SO_PATH)
+        _lib.alegpu_last_error.restype = C.c_char_p
+        _lib.alegpu_version.restype = C.c_char_p
+        _lib.alegpu_learner_param_count.restype = C.c_int64
+        _lib.alegpu_learner_param_count.argtypes = [C.c_void_p]
+        _lib.alegpu_learner_stream.restype = C.c_void_p
+        _lib.alegpu_learner_stream.argtypes = [C.c_void_p]
+        _lib.alegpu_learner_last_launch_count.restype = C.c_int64
+        _lib.alegpu_learner_last_launch_count.argtypes = [C.c_void_p]
+        _lib.alegpu_launch_count.restype = C.c_int64
+    return _lib
+
+
+def _check(rc):
+    if rc == 0:
+        return
+    msg = lib().alegpu_last_error().decode()
+    if rc == 1:
+        raise ValueError(msg)       # std::invalid_argument
+    if rc == 2:
+        raise RuntimeError(msg)     # std::runtime_error
+    if rc == 3:
+        raise IndexError(msg)       # std::out_of_range
+    raise CudaError(msg)
+
+
+def device_count():
+    n = C.c_int(0)
+    try:
+        _check(lib().alegpu_device_count(C.byref(n)))
+    except CudaError:
+        return 0
+    return n.value
+
+
+def launch_count():
+    return int(lib().alegpu_launch_count())
+
+
+def synchronize(stream=None):
+    _check(lib().alegpu_stream_synchronize(C.c_void_p(stream)))
+
+
+class DeviceArray:
+    """A typed view of library-owned device memory."""
+
+    def __init__(self, shape, dtype, ptr=None, owner=None):
+        self.shape = tuple(int(s) for s in (shape if hasattr(shape, "__len__") else (shape,)))
+        self.dtype = np.dtype(dtype)
+        self.nbytes = int(np.prod(self.shape, dtype=np.int64)) * self.dtype.itemsize
+        self._owned = ptr is None
+        self._owner = owner
+        if ptr is None:
+            p = C.c_void_p()
+            _check(lib().alegpu_malloc(C.byref(p), C.c_size_t(max(self.nbytes, 1))))
+            ptr = p.value
+        self.ptr = ptr
+
+    @classmethod
+    def from_numpy(cls, a, dtype=None, stream=None):
+        a = np.ascontiguousarray(a, dtype=dtype)
+        d = cls(a.shape, a.dtype)
+        d.copy_from(a, stream)
+        return d
+
+    @classmethod
+    def zeros(cls, shape, dtype):
+        d = cls(shape, dtype)
+        _check(lib().alegpu_memset(C.c_void_p(d.ptr), 0, C.c_size_t(d.nbytes), None))
+        return d
+
+    def copy_from(self, a, stream=None):
+        a = np.ascontiguousarray(a, dtype=self.dtype)
+        assert a.nbytes == self.nbytes, (a.shape, self.shape)
+        _check(lib().alegpu_memcpy_h2d(C.c_void_p(self.ptr), a.ctypes.data_as(C.c_void_p),
+                                       C.c_size_t(self.nbytes), C.c_void_p(stream)))
+        synchronize(stream)
+
+    def numpy(self, stream=None):
+        out = np.empty(self.shape, self.dtype)
+        if self.nbytes:
+            _check(lib().alegpu_memcpy_d2h(out.ctypes.data_as(C.c_void_p), C.c_void_p(self.ptr),
+                                           C.c_size_t(self.nbytes), C.c_void_p(stream)))
+            synchronize(stream)
+        return out
+
+    def view(self, offset_elems, shape):
+        """Sub-view starting `offset_elems` elements in (no copy)."""
+        return DeviceArray(shape, self.dtype, self.ptr + offset_elems * self.dtype.itemsize, self)
+
+    def __del__(self):
+        if getattr(self, "_owned", False) and self.ptr and _lib is not None:
+            _lib.alegpu_free(C.c_void_p(self.ptr))
+            self.ptr = None
+
+
+def _p(x):
+    if x is None:
+        return C.c_void_p(None)
+    return C.c_void_p(x.ptr if isinstance(x, DeviceArray) else int(x))
+
+
+def _dev(a, dtype):
+    return a if isinstance(a, DeviceArray) else DeviceArray.from_numpy(a, dtype)
+
+
+# ---- ai::gae::gae — src/ai/gae.h:4-7 ---------------------------------------------------------
+def gae(advantages, rewards, values, next_values, terminals, truncations, episode_starts, gamma,
+        lambda_, stream=None):
+    """Writes `advantages` (DeviceArray [E,T]) in place, like the reference's out-parameter."""
+    E, T = rewards.shape
+    _check(lib().alegpu_gae(_p(advantages), _p(rewards), _p(values), _p(next_values),
+                            _p(terminals), _p(truncations), _p(episode_starts), C.c_int64(E),
+                            C.c_int64(T), C.c_float(gamma), C.c_float(lambda_),
+                            C.c_void_p(stream)))
+
+
+def gae_numpy(rewards, values, next_values, terminals, truncations, episode_starts, gamma, lam):
+    r, v, nv = (_dev(x, np.float32) for x in (rewards, values, next_values))
+    te, tr, st = (_dev(x, np.uint8) for x in (terminals, truncations, episode_starts))
+    adv = DeviceArray.zeros(r.shape, np.float32)
+    gae(adv, r, v, nv, te, tr, st, gamma, lam)
+    return adv.numpy()
+
+
+def buffer_get_numpy(rewards, values, next_values, terminals, truncations, episode_starts, gamma,
+                     lam, write_index=0):
+    """Buffer::get in pointer form (src/ai/buffer.cc:58-77) on numpy inputs."""
+    r, v, nv = (DeviceArray.from_numpy(x, np.float32) for x in (rewards, values, next_values))
+    te, tr, st = (_dev(x, np.uint8) for x in (terminals, truncations, episode_starts))
+    E, T = r.shape
+    adv, ret = DeviceArray.zeros((E, T), np.float32), DeviceArray.zeros((E, T), np.float32)
+    mk = DeviceArray.zeros((E, T), np.uint8)
+    _check(lib().alegpu_buffer_get(_p(r), _p(v), _p(nv), _p(te), _p(tr), _p(st), C.c_int64(E),
+                                   C.c_int64(T), C.c_float(gamma), C.c_float(lam),
+                                   C.c_int64(write_index), _p(adv), _p(ret), _p(mk), 0, None,
+                                   None))
+    return dict(rewards=r.numpy(), advantages=adv.numpy(), returns=ret.numpy(), masks=mk.numpy())
+
+
+# ---- preprocessing (max_and_skip.cc:33-42 + vision.cc:38-84 + rollout.cc:184-196) -----------
+def preprocess_step(frames_a, frames_b, starts, src_stack, dst_stack, gray_f32=None,
+                    starts_stride=1, src_env_stride=STACK_BYTES, dst_env_stride=STACK_BYTES,
+                    E=None, stream=None):
+    E = frames_a.shape[0] if E is None else E
+    _check(lib().alegpu_preprocess_step(_p(frames_a), _p(frames_b), _p(starts),
+                                        C.c_int64(starts_stride), _p(src_stack),
+                                        C.c_int64(src_env_stride), _p(dst_stack),
+                                        C.c_int64(dst_env_stride), _p(gray_f32), C.c_int64(E),
+                                        C.c_void_p(stream)))
+
+
+def preprocess_rollout(frames, episode_starts, carry_in, carry_out, obs, E, T, stream=None):
+    _check(lib().alegpu_preprocess_rollout(_p(frames), _p(episode_starts), _p(carry_in),
+                                           _p(carry_out), _p(obs), C.c_int64(E), C.c_int64(T),
+                                           C.c_void_p(stream)))
+
+
+# ---- ai::ppo::losses — src/ai/ppo/losses.h:6-37 ----------------------------------------------
+class losses:
+    @staticmethod
+    def normalize_logits(logits):
+        z = _dev(logits, np.float32)
+        out = DeviceArray(z.shape, np.float32)
+        _check(lib().alegpu_normalize_logits(_p(z), C.c_int64(z.shape[0]), C.c_int64(z.shape[1]),
+                                             _p(out), None))
+        return out.numpy()
+
+    @staticmethod
+    def compute(logits, old_log_probabilities, actions, advantages, values, returns, masks,
+                clip_param, value_loss_coef, entropy_coef):
+        """losses::compute on RAW logits + the autograd gradient w.r.t. (logits, values)."""
+        z, ol = _dev(logits, np.float32), _dev(old_log_probabilities, np.float32)
+        a = _dev(actions, np.int64)
+        adv, v, ret = (_dev(x, np.float32) for x in (advantages, values, returns))
+        mk = _dev(masks, np.uint8)
+        n, A = z.shape
+        out = {k: DeviceArray.zeros(n, np.float32) for k in
+               ("clipped_losses", "value_losses", "entropies", "total_losses", "ratio", "dvalues")}
+        out["dlogits"] = DeviceArray.zeros((n, A), np.float32)
+        loss = DeviceArray.zeros(1, np.float32)
+        _check(lib().alegpu_loss(_p(z), _p(ol), _p(a), _p(adv), _p(v), _p(ret), _p(mk),
+                                 C.c_int64(n), C.c_int64(A), C.c_float(clip_param),
+                                 C.c_float(value_loss_coef), C.c_float(entropy_coef), _p(loss),
+                                 _p(out["clipped_losses"]), _p(out["value_losses"]),
+                                 _p(out["entropies"]), _p(out["total_losses"]), _p(out["ratio"]),
+                                 _p(out["dlogits"]), _p(out["dvalues"]), None))
+        res = {k: d.numpy() for k, d in out.items()}
+        res["loss"] = float(loss.numpy()[0])
+        return res
+
+
+# ---- structs ----------------------------------------------------------------------------------
+class _LearnerConfig(C.Structure):
+    _fields_ = [("hidden_size", C.c_int64), ("action_size", C.c_int64),
+                ("max_minibatch", C.c_int64), ("math", C.c_int), ("learning_rate", C.c_double),
+                ("device", C.c_int), ("world_size", C.c_int), ("rank", C.c_int),
+                ("nccl_unique_id", C.c_void_p)]
+
+
+class Hyperparameters(C.Structure):
+    """ai::ppo::train::Hyperparameters — src/ai/ppo/train.h:27-32."""
+    _fields_ = [("clip_param", C.c_float), ("value_loss_coef", C.c_float),
+                ("entropy_coef", C.c_float), ("max_gradient_norm", C.c_float)]
+
+
+class _Batch(C.Structure):
+    _fields_ = [("observations", C.c_void_p), ("actions", C.c_void_p),
+                ("log_probabilities", C.c_void_p), ("advantages", C.c_void_p),
+                ("returns", C.c_void_p), ("masks", C.c_void_p), ("size", C.c_int64)]
+
+
+class _Metrics(C.Structure):
+    _fields_ = [(k, C.c_void_p) for k in
+                ("loss", "clipped_losses", "value_losses", "entropies", "ratio", "total_losses",
+                 "advantages", "returns", "masks", "clipped_gradients")]
+
+
+class _RolloutView(C.Structure):
+    _fields_ = [("E", C.c_int64), ("T", C.c_int64), ("A", C.c_int64)] + [
+        (k, C.c_void_p) for k in
+        ("observations", "carry", "actions", "rewards", "values", "advantages", "returns",
+         "logits", "log_probabilities", "terminals", "truncations", "episode_starts", "masks")]
+
+
+class Batch:
+    """ai::ppo::train::Batch — src/ai/ppo/train.h:34-57 (device arrays, N rows)."""
+
+    def __init__(self, observations, actions, log_probabilities, advantages, returns, masks):
+        self.observations = _dev(observations, np.uint8)
+        self.actions = _dev(actions, np.int64)
+        self.log_probabilities = _dev(log_probabilities, np.float32)
+        self.advantages = _dev(advantages, np.float32)
+        self.returns = _dev(returns, np.float32)
+        self.masks = _dev(masks, np.uint8)
+        self.size = int(self.actions.shape[0])
+
+    def slice(self, start, end):
+        n = end - start
+        A = self.log_probabilities.shape[-1]
+        return Batch(self.observations.view(start * STACK_BYTES, (n, 4, 84, 84)),
+                     self.actions.view(start, (n,)),
+                     self.log_probabilities.view(start * A, (n, A)),
+                     self.advantages.view(start, (n,)), self.returns.view(start, (n,)),
+                     self.masks.view(start, (n,)))
+
+    def _c(self):
+        return _Batch(self.observations.ptr, self.actions.ptr, self.log_probabilities.ptr,
+                      self.advantages.ptr, self.returns.ptr, self.masks.ptr, self.size)
+
+
+class Metrics:
+    """ai::ppo::train::Metrics — src/ai/ppo/train.h:64-109 ([epochs,nmb,mb] device arrays)."""
+    FIELDS = ("loss", "clipped_losses", "value_losses", "entropies", "ratio", "total_losses",
+              "advantages", "returns")
+
+    def __init__(self, num_epochs, num_mini_batches, mini_batch_size):
+        shape = (num_epochs, num_mini_batches, mini_batch_size)
+        for k in self.FIELDS:
+            setattr(self, k, DeviceArray.zeros(shape, np.float32))
+        self.masks = DeviceArray.zeros(shape, np.uint8)
+        self.clipped_gradients = DeviceArray.zeros((num_epochs, num_mini_batches), np.float32)
+
+    def _c(self):
+        return _Metrics(*[getattr(self, k).ptr for k in
+                          ("loss", "clipped_losses", "value_losses", "entropies", "ratio",
+                           "total_losses", "advantages", "returns", "masks",
+                           "clipped_gradients")])
+
+    def numpy(self):
+        return {k: getattr(self, k).numpy() for k in self.FIELDS + ("masks", "clipped_gradients")}
+
+
+class Buffer:
+    """ai::buffer::Buffer — src/ai/buffer.h:27-58."""
+
+    def __init__(self, total_environments, capacity, action_size=4, device=0):
+        h = C.c_void_p()
+        _check(lib().alegpu_rollout_create(C.c_int64(total_environments), C.c_int64(capacity),
+                                           C.c_int64(action_size), C.c_int(device), C.byref(h)))
+        self.h = h
+        v = _RolloutView()
+        _check(lib().alegpu_rollout_get_view(self.h, C.byref(v)))
+        E, T, A = total_environments, capacity, action_size
+        self.E, self.T, self.A = E, T, A
+        mk = lambda ptr, shape, dt: DeviceArray(shape, dt, ptr, self)
+        self.observations = mk(v.observations, (E, T, 4, 84, 84), np.uint8)
+        self.carry = mk(v.carry, (2, E, 4, 84, 84), np.uint8)
+        self.actions = mk(v.actions, (E, T), np.int64)
+        self.rewards = mk(v.rewards, (E, T), np.float32)
+        self.values = mk(v.values, (E, T), np.float32)
+        self.advantages = mk(v.advantages, (E, T), np.float32)
+        self.returns = mk(v.returns, (E, T), np.float32)
+        self.logits = mk(v.logits, (E, T, A), np.float32)
+        self.log_probabilities = mk(v.log_probabilities, (E, T, A), np.float32)
+        self.terminals = mk(v.terminals, (E, T), np.uint8)
+        self.truncations = mk(v.truncations, (E, T), np.uint8)
+        self.episode_starts = mk(v.episode_starts, (E, T), np.uint8)
+        self.masks = mk(v.masks, (E, T), np.uint8)
+
+    def __del__(self):
+        if getattr(self, "h", None) and _lib is not None:
+            _lib.alegpu_rollout_destroy(self.h)
+            self.h = None
+
+    def add(self, observations, actions, rewards, terminals, truncations, episode_starts, logits,
+            values, stream=None):
+        """Buffer::add — src/ai/buffer.cc:41-56 (per-step [E,...] arrays)."""
+        o = None if observations is None else _dev(observations, np.uint8)
+        args = (o, _dev(actions, np.int64), _dev(rewards, np.float32), _dev(terminals, np.uint8),
+                _dev(truncations, np.uint8), _dev(episode_starts, np.uint8),
+                _dev(logits, np.float32), _dev(values, np.float32))
+        _check(lib().alegpu_rollout_add(self.h, *[_p(x) for x in args], C.c_void_p(stream)))
+        synchronize(stream)  # staged temporaries must outlive the copy
+
+    def get(self, next_values, discount, lambda_, check=True, stream=None):
+        """Buffer::get + prepare_batch -> flat train Batch (views of the storage)."""
+        nv = _dev(next_values, np.float32)
+        b = _Batch()
+        _check(lib().alegpu_rollout_get(self.h, _p(nv), C.c_float(discount), C.c_float(lambda_),
+                                        C.byref(b), 0 if check else 1, C.c_void_p(stream)))
+        synchronize(stream)
+        N = self.E * self.T
+        return Batch(self.observations.view(0, (N, 4, 84, 84)), self.actions.view(0, (N,)),
+                     self.log_probabilities.view(0, (N, self.A)), self.advantages.view(0, (N,)),
+                     self.returns.view(0, (N,)), self.masks.view(0, (N,)))
+
+
+class Learner:
+    """Network (src/bin/train.cc:230-269) + Adam (:360-362) + ai::ppo::train::train."""
+
+    def __init__(self, hidden_size=512, action_size=4, max_minibatch=256, math=MATH_FP32,
+                 learning_rate=2.5e-4, device=0, world_size=1, rank=0, nccl_unique_id=None):
+        self._uid = None
+        if nccl_unique_id is not None:
+            self._uid = C.create_string_buffer(bytes(nccl_unique_id), 128)
+        cfg = _LearnerConfig(hidden_size, action_size, max_minibatch, math, learning_rate, device,
+                             world_size, rank,
+                             C.cast(self._uid, C.c_void_p) if self._uid is not None else None)
+        h = C.c_void_p()
+        _check(lib().alegpu_learner_create(C.byref(cfg), C.byref(h)))
+        self.h = h
+        self.hidden_size, self.action_size, self.max_minibatch = hidden_size, action_size, max_minibatch
+        self.P = int(lib().alegpu_learner_param_count(self.h))
+        self.stream = lib().alegpu_learner_stream(self.h)
+
+    def __del__(self):
+        if getattr(self, "h", None) and _lib is not None:
+            _lib.alegpu_learner_destroy(self.h)
+            self.h = None
+
+    def set_params(self, params):
+        p = np.ascontiguousarray(params, np.float32)
+        assert p.size == self.P
+        _check(lib().alegpu_learner_set_params(self.h, p.ctypes.data_as(C.c_void_p)))
+
+    def get_params(self):
+        p = np.zeros(self.P, np.float32)
+        _check(lib().alegpu_learner_get_params(self.h, p.ctypes.data_as(C.c_void_p)))
+        return p
+
+    def get_adam(self):
+        m, v = np.zeros(self.P, np.float32), np.zeros(self.P, np.float32)
+        st = C.c_int64(0)
+        _check(lib().alegpu_learner_get_adam(self.h, m.ctypes.data_as(C.c_void_p),
+                                             v.ctypes.data_as(C.c_void_p), C.byref(st)))
+        return m, v, int(st.value)
+
+    def set_lr(self, lr):
+        _check(lib().alegpu_learner_set_lr(self.h, C.c_double(lr)))
+
+    def forward(self, observations):
+        o = _dev(observations, np.uint8)
+        n = o.shape[0]
+        lg = DeviceArray.zeros((n, self.action_size), np.float32)
+        v = DeviceArray.zeros(n, np.float32)
+        _check(lib().alegpu_learner_forward(self.h, _p(o), C.c_int64(n), _p(lg), _p(v)))
+        synchronize(self.stream)
+        return lg.numpy(), v.numpy()
+
+    def activations(self, n):
+        c1 = np.zeros((n, 32, 20, 20), np.float32)
+        c2 = np.zeros((n, 64, 9, 9), np.float32)
+        c3 = np.zeros((n, 64, 7, 7), np.float32)
+        fc = np.zeros((n, self.hidden_size), np.float32)
+        _check(lib().alegpu_learner_get_activations(
+            self.h, C.c_int64(n), *[x.ctypes.data_as(C.c_void_p) for x in (c1, c2, c3, fc)]))
+        return c1, c2, c3, fc
+
+    def grads(self, batch, hp):
+        g = np.zeros(self.P, np.float32)
+        loss = C.c_float(0)
+        n = batch.size
+        lg = DeviceArray.zeros((n, self.action_size), np.float32)
+        v = DeviceArray.zeros(n, np.float32)
+        cb = batch._c()
+        _check(lib().alegpu_learner_grads(self.h, C.byref(cb), C.byref(hp),
+                                          g.ctypes.data_as(C.c_void_p), C.byref(loss), _p(lg),
+                                          _p(v)))
+        return g, float(loss.value), lg.numpy(), v.numpy()
+
+    def apply_grads(self, grads, max_norm):
+        g = np.ascontiguousarray(grads, np.float32)
+        tn = C.c_float(0)
+        _check(lib().alegpu_learner_apply_grads(self.h, g.ctypes.data_as(C.c_void_p),
+                                                C.c_double(max_norm), C.byref(tn)))
+        return float(tn.value)
+
+    def train(self, batch, metrics, num_epochs, num_mini_batches, hp, cuda_graph=False,
+              sync=True):
+        """ai::ppo::train::train — src/ai/ppo/train.h:133-157."""
+        cb = batch._c()
+        cm = metrics._c() if metrics is not None else None
+        _check(lib().alegpu_learner_train(self.h, C.byref(cb),
+                                          C.byref(cm) if cm is not None else None,
+                                          C.c_int64(num_epochs), C.c_int64(num_mini_batches),
+                                          C.byref(hp), 1 if cuda_graph else 0))
+        if sync:
+            synchronize(self.stream)
+
+    def last_launch_count(self):
+        return int(lib().alegpu_learner_last_launch_count(self.h))

@@ -1,0 +1,273 @@
+// heads.cu — policy/value heads fused with the PPO loss.
+//
+// One warp per sample: the (A+1) x H head weights sit in shared memory, the warp forms the
+// A logits and the value with shuffle reductions (src/bin/train.cc:262-264), evaluates the
+// loss and its analytic gradient (loss.cuh == src/ai/ppo/losses.cc:4-47 + autograd), writes
+// the per-sample metrics straight to their final [epoch,k,:] offsets (Metrics::set,
+// src/ai/ppo/train.h:93-108) and back-propagates through the heads into dfc — so logits,
+// values, dlogits and dvalues never round-trip through HBM between separate kernels.
+#include "loss.cuh"
+#include "net.h"
+
+namespace alegpu {
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+
+template <int kMaxA, bool kLoss>
+__global__ void __launch_bounds__(kThreads)
+    heads_kernel(const float *__restrict__ piw, const float *__restrict__ pib,
+                 const float *__restrict__ vw, const float *__restrict__ vb,
+                 const float *__restrict__ fc, int64_t n, int H, int A,
+                 float *__restrict__ logits, float *__restrict__ values,
+                 float *__restrict__ dfc, float *__restrict__ dout, LossArgs L,
+                 float *__restrict__ partials) {
+  extern __shared__ float sw[]; // [(A+1)][H] head weights, row A = value head
+  __shared__ float red[kWarps];
+  for (int i = threadIdx.x; i < (A + 1) * H; i += kThreads)
+    sw[i] = i < A * H ? piw[i] : vw[i - A * H];
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float inv = 0.0f;
+  if (kLoss)
+    inv = 1.0f / L.count[0];
+  float contrib = 0.0f;
+  for (int64_t i = (int64_t)blockIdx.x * kWarps + warp; i < n; i += (int64_t)gridDim.x * kWarps) {
+    const float *h = fc + i * H;
+    float acc[kMaxA + 1];
+#pragma unroll
+    for (int a = 0; a <= kMaxA; ++a)
+      acc[a] = 0.0f;
+    for (int j = lane; j < H; j += 32) {
+      const float x = h[j];
+#pragma unroll
+      for (int a = 0; a <= kMaxA; ++a)
+        if (a <= A)
+          acc[a] = fmaf(x, sw[a * H + j], acc[a]);
+    }
+    float z[kMaxA];
+    float v = 0.0f;
+#pragma unroll
+    for (int a = 0; a <= kMaxA; ++a)
+      if (a <= A) {
+        const float t = warp_sum(acc[a]);
+        if (a < A) {
+          if (a < kMaxA)
+            z[a] = t + pib[a];
+        } else {
+          v = t + vb[0];
+        }
+      }
+    if (lane == 0) {
+      if (logits)
+        for (int a = 0; a < A; ++a)
+          logits[i * A + a] = z[a];
+      if (values)
+        values[i] = v;
+    }
+    if (kLoss) {
+      float ol[kMaxA], dz[kMaxA], dv;
+#pragma unroll
+      for (int a = 0; a < kMaxA; ++a)
+        if (a < A)
+          ol[a] = L.old_log_probs[i * A + a];
+      const bool m = L.masks[i] != 0;
+      const float adv = L.advantages[i], ret = L.returns[i];
+      const PpoSample s = ppo_sample<kMaxA>(z, ol, A, (int)L.actions[i], adv, v, ret, L.clip,
+                                            L.vcoef, L.ecoef, m ? inv : 0.0f, dz, &dv);
+      if (lane == 0) {
+        if (L.m_clipped) L.m_clipped[i] = s.surr;
+        if (L.m_value) L.m_value[i] = s.value_loss;
+        if (L.m_entropy) L.m_entropy[i] = s.entropy;
+        if (L.m_total) L.m_total[i] = s.total;
+        if (L.m_ratio) L.m_ratio[i] = s.ratio;
+        if (L.m_adv) L.m_adv[i] = adv;
+        if (L.m_ret) L.m_ret[i] = ret;
+        if (L.m_masks) L.m_masks[i] = m ? 1 : 0;
+        for (int a = 0; a < A; ++a)
+          dout[i * (A + 1) + a] = dz[a];
+        dout[i * (A + 1) + A] = dv;
+        contrib += m ? s.total : 0.0f;
+      }
+      // dfc = dlogits . piw + dvalue * vw
+      for (int j = lane; j < H; j += 32) {
+        float g = dv * sw[A * H + j];
+#pragma unroll
+        for (int a = 0; a < kMaxA; ++a)
+          if (a < A)
+            g = fmaf(dz[a], sw[a * H + j], g);
+        dfc[i * H + j] = g;
+      }
+    }
+  }
+  if (kLoss) {
+    if (lane == 0)
+      red[warp] = contrib;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float t = 0.0f;
+      for (int w = 0; w < kWarps; ++w)
+        t += red[w];
+      partials[blockIdx.x] = t;
+    }
+  }
+}
+
+// partial[z][a][j] = sum_{m in split z} dout[m][a] * (j < H ? fc[m][j] : 1)
+template <int kMaxA1>
+__global__ void __launch_bounds__(128)
+    heads_wgrad_kernel(const float *__restrict__ dout, const float *__restrict__ fc, int64_t n,
+                       int H, int A1, int rows_per_split, float *__restrict__ ws) {
+  __shared__ float sd[64 * kMaxA1];
+  const int j = blockIdx.x * 128 + threadIdx.x;
+  const int64_t m0 = (int64_t)blockIdx.y * rows_per_split;
+  const int64_t m1 = min(n, m0 + rows_per_split);
+  float acc[kMaxA1];
+#pragma unroll
+  for (int a = 0; a < kMaxA1; ++a)
+    acc[a] = 0.0f;
+  for (int64_t mb = m0; mb < m1; mb += 64) {
+    const int cnt = (int)min((int64_t)64, m1 - mb);
+    __syncthreads();
+    for (int i = threadIdx.x; i < cnt * A1; i += 128)
+      sd[i] = dout[mb * A1 + i];
+    __syncthreads();
+    if (j <= H)
+      for (int r = 0; r < cnt; ++r) {
+        const float x = j < H ? fc[(mb + r) * H + j] : 1.0f;
+#pragma unroll
+        for (int a = 0; a < kMaxA1; ++a)
+          if (a < A1)
+            acc[a] = fmaf(sd[r * A1 + a], x, acc[a]);
+      }
+  }
+  if (j <= H)
+#pragma unroll
+    for (int a = 0; a < kMaxA1; ++a)
+      if (a < A1)
+        ws[((size_t)blockIdx.y * A1 + a) * (H + 1) + j] = acc[a];
+}
+
+__global__ void heads_reduce_kernel(const float *__restrict__ ws, int splits, int H, int A,
+                                    float *__restrict__ gpiw, float *__restrict__ gpib,
+                                    float *__restrict__ gvw, float *__restrict__ gvb) {
+  const int total = (A + 1) * (H + 1);
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += gridDim.x * blockDim.x) {
+    float s = 0.0f;
+    for (int z = 0; z < splits; ++z)
+      s += ws[(size_t)z * total + idx];
+    const int a = idx / (H + 1), j = idx - a * (H + 1);
+    if (a < A) {
+      if (j < H) gpiw[a * H + j] = s; else gpib[a] = s;
+    } else {
+      if (j < H) gvw[j] = s; else gvb[0] = s;
+    }
+  }
+}
+
+__global__ void finalize_metrics_kernel(const float *__restrict__ partials, int nparts,
+                                        const float *__restrict__ count, float *__restrict__ m_loss,
+                                        int64_t mb, float *__restrict__ loss_out) {
+  __shared__ float s_loss;
+  if (threadIdx.x < 32) {
+    float s = 0.0f;
+    for (int i = threadIdx.x; i < nparts; i += 32)
+      s += partials[i];
+    s = warp_sum(s);
+    if (threadIdx.x == 0)
+      s_loss = s / count[0]; // losses.cc:19
+  }
+  __syncthreads();
+  const float loss = s_loss;
+  if (blockIdx.x == 0 && threadIdx.x == 0 && loss_out)
+    loss_out[0] = loss;
+  if (m_loss) // Metrics.loss[epoch,k,:] is the scalar broadcast over mb (train.h:98)
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < mb;
+         i += (int64_t)gridDim.x * blockDim.x)
+      m_loss[i] = loss;
+}
+
+int heads_grid(int64_t n) {
+  return (int)std::max<int64_t>(1, std::min<int64_t>(ceil_div(n, kWarps), kNumSMs * 4));
+}
+
+template <bool kLoss>
+int launch_heads(const NetParams &P, const float *fc, int64_t n, float *logits, float *values,
+                 float *dfc, float *dout, const LossArgs &L, float *partials, int grid,
+                 cudaStream_t s) {
+  const int H = (int)P.hidden, A = (int)P.actions;
+  const size_t smem = (size_t)(A + 1) * H * sizeof(float);
+  ALEGPU_REQUIRE(smem <= 200 * 1024, ALEGPU_INVALID_ARGUMENT, "heads: (A+1)*H too large");
+  if (A <= 4) {
+    auto k = heads_kernel<4, kLoss>;
+    if (smem > 48 * 1024)
+      ALEGPU_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k<<<grid, kThreads, smem, s>>>(P.piw, P.pib, P.vw, P.vb, fc, n, H, A, logits, values, dfc,
+                                   dout, L, partials);
+  } else {
+    auto k = heads_kernel<18, kLoss>;
+    if (smem > 48 * 1024)
+      ALEGPU_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k<<<grid, kThreads, smem, s>>>(P.piw, P.pib, P.vw, P.vb, fc, n, H, A, logits, values, dfc,
+                                   dout, L, partials);
+  }
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}
+
+} // namespace
+
+int heads_forward(const NetParams &P, const float *fc, int64_t n, float *logits, float *values,
+                  cudaStream_t s) {
+  if (n == 0)
+    return ALEGPU_OK;
+  LossArgs L{};
+  return launch_heads<false>(P, fc, n, logits, values, nullptr, nullptr, L, nullptr,
+                             heads_grid(n), s);
+}
+
+int heads_loss_backward(const NetParams &P, NetActs &A, int64_t n, const LossArgs &L,
+                        float *loss_partials, int *nparts, cudaStream_t s) {
+  const int grid = heads_grid(n);
+  *nparts = grid;
+  return launch_heads<true>(P, A.fc, n, A.logits, A.values, A.dfc, A.dout, L, loss_partials,
+                            grid, s);
+}
+
+int heads_wgrad(const NetParams &G, const NetActs &A, int64_t n, float *ws, size_t ws_floats,
+                cudaStream_t s) {
+  const int H = (int)G.hidden, Ac = (int)G.actions, A1 = Ac + 1;
+  const size_t per = (size_t)A1 * (H + 1);
+  int splits = (int)std::max<int64_t>(1, std::min<int64_t>(n / 64, 2 * kNumSMs));
+  splits = (int)std::min<size_t>(splits, ws_floats / per);
+  ALEGPU_REQUIRE(splits >= 1, ALEGPU_RUNTIME_ERROR, "heads_wgrad: workspace too small");
+  const int rps = (int)ceil_div(n, splits);
+  splits = (int)ceil_div(n, rps);
+  dim3 grid((unsigned)ceil_div(H + 1, 128), (unsigned)splits);
+  if (A1 <= 5)
+    heads_wgrad_kernel<5><<<grid, 128, 0, s>>>(A.dout, A.fc, n, H, A1, rps, ws);
+  else
+    heads_wgrad_kernel<19><<<grid, 128, 0, s>>>(A.dout, A.fc, n, H, A1, rps, ws);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  heads_reduce_kernel<<<(unsigned)ceil_div((int64_t)per, 256), 256, 0, s>>>(
+      ws, splits, H, Ac, G.piw, G.pib, G.vw, G.vb);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}
+
+int finalize_metrics(const float *loss_partials, int nparts, const float *count, float *m_loss,
+                     int64_t mb, float *loss_out, cudaStream_t s) {
+  const int blocks = m_loss ? (int)std::min<int64_t>(ceil_div(mb, 256), 64) : 1;
+  finalize_metrics_kernel<<<blocks, 256, 0, s>>>(loss_partials, nparts, count, m_loss, mb,
+                                                 loss_out);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}
+
+} // namespace alegpu

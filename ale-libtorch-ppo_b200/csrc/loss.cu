@@ -1,0 +1,190 @@
+// loss.cu — stateless PPO loss operators (mirror of src/ai/ppo/losses.{h,cc}).
+//
+// Replaces ~25 ATen elementwise/reduction kernels forward + their autograd backward with one
+// fused kernel: log-softmax, action gather, ratio, clamp, min, value loss, entropy, masked
+// sum, per-sample metrics, dlogits, dvalues.  102 algorithmic bytes per sample.
+// Reductions are deterministic: warp shuffles, a fixed tree per block, block partials summed
+// in index order by one warp.
+#include "loss.cuh"
+
+namespace alegpu {
+namespace {
+
+constexpr int kThreads = 256;
+
+__global__ void normalize_logits_kernel(const float *__restrict__ z, float *__restrict__ out,
+                                        int64_t n, int A) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n)
+    return;
+  const float *zi = z + i * A;
+  float mx = zi[0];
+  for (int j = 1; j < A; ++j)
+    mx = fmaxf(mx, zi[j]);
+  float se = 0.0f;
+  for (int j = 0; j < A; ++j)
+    se += expf(zi[j] - mx);
+  const float lse = mx + logf(se);
+  for (int j = 0; j < A; ++j)
+    out[i * A + j] = zi[j] - lse;
+}
+
+// count[b] = sum(masks[b*n .. (b+1)*n)) as float (exact up to 2^24 rows per minibatch)
+__global__ void __launch_bounds__(kThreads)
+    mask_count_kernel(const uint8_t *__restrict__ masks, int64_t n, float *__restrict__ count) {
+  __shared__ float red[kThreads / 32];
+  const uint8_t *mk = masks + (int64_t)blockIdx.x * n;
+  float c = 0.0f;
+  for (int64_t i = threadIdx.x; i < n; i += kThreads)
+    c += mk[i] ? 1.0f : 0.0f;
+  c = block_sum<float, kThreads>(c, red);
+  if (threadIdx.x == 0)
+    count[blockIdx.x] = c;
+}
+
+template <int kMaxA>
+__global__ void __launch_bounds__(kThreads)
+    loss_kernel(const float *__restrict__ logits, const float *__restrict__ old_lp,
+                const int64_t *__restrict__ actions, const float *__restrict__ adv,
+                const float *__restrict__ values, const float *__restrict__ returns,
+                const uint8_t *__restrict__ masks, int64_t n, int A, float clip, float vcoef,
+                float ecoef, const float *__restrict__ count, float *__restrict__ partials,
+                float *__restrict__ o_clipped, float *__restrict__ o_value,
+                float *__restrict__ o_entropy, float *__restrict__ o_total,
+                float *__restrict__ o_ratio, float *__restrict__ dlogits,
+                float *__restrict__ dvalues) {
+  __shared__ float red[kThreads / 32];
+  const int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+  float contrib = 0.0f;
+  if (i < n) {
+    const float inv = 1.0f / count[0];
+    float z[kMaxA], ol[kMaxA], dz[kMaxA];
+#pragma unroll
+    for (int j = 0; j < kMaxA; ++j)
+      if (j < A) {
+        z[j] = logits[i * A + j];
+        ol[j] = old_lp[i * A + j];
+      }
+    const bool m = masks[i] != 0;
+    float dv;
+    const PpoSample s =
+        ppo_sample<kMaxA>(z, ol, A, (int)actions[i], adv[i], values[i], returns[i], clip, vcoef,
+                          ecoef, m ? inv : 0.0f, dz, &dv);
+    if (o_clipped) o_clipped[i] = s.surr;
+    if (o_value) o_value[i] = s.value_loss;
+    if (o_entropy) o_entropy[i] = s.entropy;
+    if (o_total) o_total[i] = s.total;
+    if (o_ratio) o_ratio[i] = s.ratio;
+    if (dlogits) {
+#pragma unroll
+      for (int j = 0; j < kMaxA; ++j)
+        if (j < A)
+          dlogits[i * A + j] = dz[j];
+    }
+    if (dvalues) dvalues[i] = dv;
+    contrib = m ? s.total : 0.0f;
+  }
+  contrib = block_sum<float, kThreads>(contrib, red);
+  if (threadIdx.x == 0)
+    partials[blockIdx.x] = contrib;
+}
+
+// loss = (sum of block partials, index order) / count   — one warp, fixed order
+__global__ void loss_finalize_kernel(const float *__restrict__ partials, int nparts,
+                                     const float *__restrict__ count, float *__restrict__ loss) {
+  float s = 0.0f;
+  for (int i = threadIdx.x; i < nparts; i += 32)
+    s += partials[i];
+  s = warp_sum(s);
+  if (threadIdx.x == 0)
+    loss[0] = s / count[0];
+}
+
+struct Scratch {
+  float *buf = nullptr;
+  size_t cap = 0;
+};
+Scratch g_scratch;
+
+int ensure_scratch(size_t floats) {
+  if (g_scratch.cap < floats) {
+    if (g_scratch.buf)
+      cudaFree(g_scratch.buf);
+    g_scratch.buf = nullptr;
+    g_scratch.cap = 0;
+    ALEGPU_CUDA_CHECK(cudaMalloc(&g_scratch.buf, floats * sizeof(float)));
+    g_scratch.cap = floats;
+  }
+  return ALEGPU_OK;
+}
+
+} // namespace
+
+// shared with learner.cu ------------------------------------------------------------------
+int launch_mask_count(const uint8_t *masks, int64_t n, int64_t groups, float *count,
+                      cudaStream_t s) {
+  mask_count_kernel<<<(unsigned)groups, kThreads, 0, s>>>(masks, n, count);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}
+
+int launch_normalize_logits(const float *logits, int64_t n, int64_t A, float *out,
+                            cudaStream_t s) {
+  if (n == 0)
+    return ALEGPU_OK;
+  normalize_logits_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(logits, out, n, (int)A);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}
+
+} // namespace alegpu
+
+using namespace alegpu;
+
+extern "C" int alegpu_normalize_logits(const float *logits, int64_t n, int64_t A, float *out,
+                                       void *stream) {
+  ALEGPU_REQUIRE(n >= 0 && A >= 1, ALEGPU_INVALID_ARGUMENT, "normalize_logits: bad shape");
+  ALEGPU_REQUIRE(n == 0 || (logits && out), ALEGPU_INVALID_ARGUMENT,
+                 "normalize_logits: null pointer");
+  return launch_normalize_logits(logits, n, A, out, as_stream(stream));
+}
+
+extern "C" int alegpu_loss(const float *logits, const float *old_log_probs,
+                           const int64_t *actions, const float *advantages, const float *values,
+                           const float *returns, const uint8_t *masks, int64_t n, int64_t A,
+                           float clip_param, float value_loss_coef, float entropy_coef,
+                           float *loss, float *clipped_losses, float *value_losses,
+                           float *entropies, float *total_losses, float *ratio, float *dlogits,
+                           float *dvalues, void *stream) {
+  ALEGPU_REQUIRE(n >= 1 && A >= 1 && A <= 32, ALEGPU_INVALID_ARGUMENT,
+                 "loss: need n >= 1 and 1 <= A <= 32");
+  ALEGPU_REQUIRE(logits && old_log_probs && actions && advantages && values && returns && masks,
+                 ALEGPU_INVALID_ARGUMENT, "loss: null input pointer");
+  cudaStream_t s = as_stream(stream);
+  const int blocks = (int)ceil_div(n, kThreads);
+  if (int rc = ensure_scratch((size_t)blocks + 2))
+    return rc;
+  float *count = g_scratch.buf, *lossbuf = g_scratch.buf + 1, *partials = g_scratch.buf + 2;
+  if (int rc = launch_mask_count(masks, n, 1, count, s))
+    return rc;
+  if (A <= 4)
+    loss_kernel<4><<<blocks, kThreads, 0, s>>>(logits, old_log_probs, actions, advantages,
+                                               values, returns, masks, n, (int)A, clip_param,
+                                               value_loss_coef, entropy_coef, count, partials,
+                                               clipped_losses, value_losses, entropies,
+                                               total_losses, ratio, dlogits, dvalues);
+  else
+    loss_kernel<32><<<blocks, kThreads, 0, s>>>(logits, old_log_probs, actions, advantages,
+                                                values, returns, masks, n, (int)A, clip_param,
+                                                value_loss_coef, entropy_coef, count, partials,
+                                                clipped_losses, value_losses, entropies,
+                                                total_losses, ratio, dlogits, dvalues);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  loss_finalize_kernel<<<1, 32, 0, s>>>(partials, blocks, count, loss ? loss : lossbuf);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}

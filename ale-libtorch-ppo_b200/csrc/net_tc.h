@@ -1,0 +1,27 @@
+// net_tc.h — tcgen05/TMEM tensor-core Nature-CNN path (net_tc.cu).
+#pragma once
+#include "net.h"
+
+namespace alegpu {
+
+struct TcState {
+  int64_t hidden = 0, actions = 0, cap = 0, Ppad = 0;
+  void *w_shadow = nullptr;  // bf16 copy of the flat parameter buffer (written by Adam)
+  void *act1 = nullptr, *act2 = nullptr, *act3 = nullptr;    // bf16 NHWC activations
+  void *dact1 = nullptr, *dact2 = nullptr, *dact3 = nullptr; // bf16 NHWC activation grads
+  void *fc16 = nullptr, *dfc16 = nullptr;                    // bf16 copies of fc in/out grads
+  void *wt = nullptr;        // bf16 re-laid-out weights for dgrad
+  float *stage = nullptr;    // fp32 staging for get_activations
+};
+
+int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_t Ppad,
+                cudaStream_t s);
+void net_tc_destroy(TcState &T);
+int net_tc_refresh_weights(TcState &T, const float *params, int64_t Ppad, cudaStream_t s);
+int net_tc_forward(const NetParams &P, TcState &T, const uint8_t *obs, int64_t n, NetActs &A,
+                   cudaStream_t s);
+int net_tc_backward(const NetParams &P, const NetParams &G, TcState &T, const uint8_t *obs,
+                    int64_t n, NetActs &A, float *ws, size_t ws_floats, cudaStream_t s);
+int net_tc_fetch_activation(TcState &T, int which, int64_t n, float *host, cudaStream_t s);
+
+} // namespace alegpu

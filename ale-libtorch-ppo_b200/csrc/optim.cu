@@ -1,0 +1,140 @@
+// optim.cu — global-norm gradient clip + Adam over one flat parameter buffer.
+//
+// Replaces clip_grad_norm_ (src/ai/ppo/train.cc:12-46: 10 norm kernels + stack + norm +
+// clamp + 10 mul_) and torch::optim::Adam(lr, eps=1e-5) as configured at
+// src/bin/train.cc:360-362 (betas 0.9/0.999, no weight decay, no amsgrad) with two launches:
+//   grad_sumsq : deterministic per-block partial sums of g^2 (sqrt(sum_i ||g_i||^2) over the
+//                per-tensor norms == the L2 norm of the flat gradient)
+//   adam_clip  : every block re-reduces the partials in index order, forms
+//                coef = min(1, max_norm/(total+1e-6)) (train.cc:39-41), and applies
+//                g*=coef; m=b1 m+(1-b1)g; v=b2 v+(1-b2)g^2;
+//                p -= (lr/(1-b1^t)) m / (sqrt(v)/sqrt(1-b2^t) + eps)      (torch's form)
+// with 16-byte vector loads/stores: 28 B per parameter per step (+2 B for the bf16 shadow the
+// tensor-core path consumes, + 4 B for the norm pass).  lr and the step counter live in a
+// device struct so a captured CUDA graph stays correct across lr anneals.
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "optim.h"
+
+namespace alegpu {
+namespace {
+
+constexpr int kThreads = 256;
+
+__global__ void __launch_bounds__(kThreads)
+    grad_sumsq_kernel(const float *__restrict__ g, int64_t n4, float *__restrict__ partials,
+                      OptState *__restrict__ st) {
+  __shared__ float red[kThreads / 32];
+  float acc = 0.0f;
+  const float4 *g4 = reinterpret_cast<const float4 *>(g);
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n4;
+       i += (int64_t)gridDim.x * kThreads) {
+    const float4 x = g4[i];
+    acc += x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
+  }
+  acc = block_sum<float, kThreads>(acc, red);
+  if (threadIdx.x == 0) {
+    partials[blockIdx.x] = acc;
+    if (blockIdx.x == 0)
+      st->step += 1; // Adam's step counter counts minibatch updates (train.h:129)
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+    adam_clip_kernel(float *__restrict__ p, float *__restrict__ g, float *__restrict__ m,
+                     float *__restrict__ v, __nv_bfloat16 *__restrict__ shadow, int64_t n4,
+                     const float *__restrict__ partials, int nparts,
+                     const OptState *__restrict__ st, float max_norm,
+                     float *__restrict__ total_norm_out) {
+  __shared__ float s_coef, s_step_size, s_bc2_sqrt;
+  if (threadIdx.x < 32) {
+    double s = 0.0;
+    for (int i = threadIdx.x; i < nparts; i += 32)
+      s += (double)partials[i];
+    s = warp_sum(s);
+    if (threadIdx.x == 0) {
+      const float total = (float)sqrt(s);
+      float coef = (float)((double)max_norm / ((double)total + 1e-6)); // train.cc:39
+      s_coef = fminf(coef, 1.0f);                                      // train.cc:40-41
+      const double t = (double)st->step;
+      const double bc1 = 1.0 - pow(0.9, t), bc2 = 1.0 - pow(0.999, t);
+      s_step_size = (float)(st->lr / bc1);
+      s_bc2_sqrt = (float)sqrt(bc2);
+      if (blockIdx.x == 0 && total_norm_out)
+        *total_norm_out = total; // the PRE-clip norm (train.h:104)
+    }
+  }
+  __syncthreads();
+  const float coef = s_coef, step_size = s_step_size, bc2_sqrt = s_bc2_sqrt;
+  const float b1 = 0.9f, b2 = 0.999f, omb1 = (float)(1.0 - 0.9), omb2 = (float)(1.0 - 0.999);
+  const float eps = 1e-5f;
+  float4 *p4 = reinterpret_cast<float4 *>(p);
+  float4 *g4 = reinterpret_cast<float4 *>(g);
+  float4 *m4 = reinterpret_cast<float4 *>(m);
+  float4 *v4 = reinterpret_cast<float4 *>(v);
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n4;
+       i += (int64_t)gridDim.x * kThreads) {
+    float4 pp = p4[i], gg = g4[i], mm = m4[i], vv = v4[i];
+    float *pa = &pp.x, *ga = &gg.x, *ma = &mm.x, *va = &vv.x;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float gc = ga[k] * coef; // train.cc:42-44
+      ga[k] = gc;
+      ma[k] = ma[k] * b1 + gc * omb1;
+      va[k] = va[k] * b2 + (gc * gc) * omb2;
+      const float denom = sqrtf(va[k]) / bc2_sqrt + eps;
+      pa[k] = pa[k] - step_size * (ma[k] / denom);
+    }
+    p4[i] = pp;
+    g4[i] = gg;
+    m4[i] = mm;
+    v4[i] = vv;
+    if (shadow) {
+      __nv_bfloat162 lo = __floats2bfloat162_rn(pp.x, pp.y), hi = __floats2bfloat162_rn(pp.z, pp.w);
+      uint2 pk;
+      pk.x = *reinterpret_cast<uint32_t *>(&lo);
+      pk.y = *reinterpret_cast<uint32_t *>(&hi);
+      reinterpret_cast<uint2 *>(shadow)[i] = pk;
+    }
+  }
+}
+
+__global__ void f32_to_bf16_kernel(const float *__restrict__ src, __nv_bfloat16 *__restrict__ dst,
+                                   int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    dst[i] = __float2bfloat16_rn(src[i]);
+}
+
+} // namespace
+
+int launch_grad_sumsq(const float *grads, int64_t n_padded, float *partials, OptState *st,
+                      cudaStream_t s) {
+  grad_sumsq_kernel<<<kNormBlocks, kThreads, 0, s>>>(grads, n_padded / 4, partials, st);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}
+
+int launch_adam_clip(float *params, float *grads, float *m, float *v, void *bf16_shadow,
+                     int64_t n_padded, const float *partials, const OptState *st,
+                     float max_norm, float *total_norm_out, cudaStream_t s) {
+  const int blocks = (int)std::min<int64_t>(ceil_div(n_padded / 4, kThreads), kNumSMs * 8);
+  adam_clip_kernel<<<blocks, kThreads, 0, s>>>(params, grads, m, v,
+                                               static_cast<__nv_bfloat16 *>(bf16_shadow),
+                                               n_padded / 4, partials, kNormBlocks, st, max_norm,
+                                               total_norm_out);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}
+
+int launch_f32_to_bf16(const float *src, void *dst, int64_t n, cudaStream_t s) {
+  f32_to_bf16_kernel<<<kNumSMs * 2, 256, 0, s>>>(src, static_cast<__nv_bfloat16 *>(dst), n);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}
+
+} // namespace alegpu

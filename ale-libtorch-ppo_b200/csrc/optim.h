@@ -1,0 +1,22 @@
+// optim.h — clip + Adam launchers (optim.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+namespace alegpu {
+
+struct OptState {
+  double lr;      // src/bin/train.cc:424-428 writes it once per rollout
+  long long step; // torch Adam's per-parameter step (identical for all parameters)
+};
+
+constexpr int kNormBlocks = 296; // 2 CTAs per SM, fixed => bit-reproducible partial order
+
+int launch_grad_sumsq(const float *grads, int64_t n_padded, float *partials, OptState *st,
+                      cudaStream_t s);
+int launch_adam_clip(float *params, float *grads, float *m, float *v, void *bf16_shadow,
+                     int64_t n_padded, const float *partials, const OptState *st,
+                     float max_norm, float *total_norm_out, cudaStream_t s);
+int launch_f32_to_bf16(const float *src, void *dst, int64_t n, cudaStream_t s);
+
+} // namespace alegpu

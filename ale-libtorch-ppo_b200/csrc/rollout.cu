@@ -1,0 +1,172 @@
+// rollout.cu — the rollout buffer behind the C ABI: mirror of ai::buffer::Buffer
+// (src/ai/buffer.h:27-58, src/ai/buffer.cc:5-77) plus prepare_batch (src/bin/train.cc:272-283).
+//
+// Storage is the reference's: env-major [E,T,...] device arrays (obs u8 [E,T,4,84,84], actions
+// i64, f32 scalars, 1-byte flags, logits [E,T,A]).  `add` is ONE scatter kernel + one strided
+// 2-D copy instead of 8 strided copy_ kernels (buffer.cc:47-54); producers that can write in
+// place (alegpu_preprocess_step -> slot t+1) get the raw pointers through alegpu_rollout_view.
+// `get` = fused clamp + GAE + returns + masks (gae.cu) + log-softmax of the stored logits.
+#include "net.h"
+
+using namespace alegpu;
+
+struct alegpu_rollout {
+  int64_t E = 0, T = 0, A = 0;
+  int device = 0;
+  int64_t write_index = 0; // Buffer::indices_
+  uint8_t *obs = nullptr, *carry = nullptr;
+  int64_t *actions = nullptr;
+  float *rewards = nullptr, *values = nullptr, *advantages = nullptr, *returns = nullptr;
+  float *logits = nullptr, *log_probs = nullptr;
+  uint8_t *terminals = nullptr, *truncations = nullptr, *starts = nullptr, *masks = nullptr;
+  int *error_flag = nullptr;
+};
+
+namespace {
+
+__global__ void rollout_add_kernel(int64_t E, int64_t T, int64_t A, int64_t t,
+                                   const int64_t *__restrict__ actions,
+                                   const float *__restrict__ rewards,
+                                   const uint8_t *__restrict__ terminals,
+                                   const uint8_t *__restrict__ truncations,
+                                   const uint8_t *__restrict__ starts,
+                                   const float *__restrict__ logits,
+                                   const float *__restrict__ values, int64_t *__restrict__ o_actions,
+                                   float *__restrict__ o_rewards, uint8_t *__restrict__ o_terminals,
+                                   uint8_t *__restrict__ o_truncations, uint8_t *__restrict__ o_starts,
+                                   float *__restrict__ o_logits, float *__restrict__ o_values) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= E)
+    return;
+  const int64_t o = e * T + t; // buffer.cc:47-54: column t of every [E,T,...] array
+  o_actions[o] = actions[e];
+  o_rewards[o] = rewards[e];
+  o_terminals[o] = terminals[e] ? 1 : 0;
+  o_truncations[o] = truncations[e] ? 1 : 0;
+  o_starts[o] = starts[e] ? 1 : 0;
+  o_values[o] = values[e];
+  for (int64_t a = 0; a < A; ++a)
+    o_logits[o * A + a] = logits[e * A + a];
+}
+
+template <typename T> int dmalloc(T **p, size_t n) {
+  ALEGPU_CUDA_CHECK(cudaMalloc(p, sizeof(T) * (n ? n : 1)));
+  ALEGPU_CUDA_CHECK(cudaMemset(*p, 0, sizeof(T) * (n ? n : 1)));
+  return ALEGPU_OK;
+}
+
+} // namespace
+
+extern "C" int alegpu_rollout_create(int64_t E, int64_t T, int64_t A, int device,
+                                     alegpu_rollout **out) {
+  ALEGPU_REQUIRE(out && E >= 1 && T >= 1 && A >= 1, ALEGPU_INVALID_ARGUMENT,
+                 "rollout_create: bad arguments");
+  ALEGPU_CUDA_CHECK(cudaSetDevice(device));
+  auto *r = new alegpu_rollout();
+  r->E = E; r->T = T; r->A = A; r->device = device;
+  const size_t n = (size_t)E * T;
+  int rc = 0;
+  if ((rc = dmalloc(&r->obs, n * 28224)) || (rc = dmalloc(&r->carry, (size_t)2 * E * 28224)) ||
+      (rc = dmalloc(&r->actions, n)) || (rc = dmalloc(&r->rewards, n)) ||
+      (rc = dmalloc(&r->values, n)) || (rc = dmalloc(&r->advantages, n)) ||
+      (rc = dmalloc(&r->returns, n)) || (rc = dmalloc(&r->logits, n * A)) ||
+      (rc = dmalloc(&r->log_probs, n * A)) || (rc = dmalloc(&r->terminals, n)) ||
+      (rc = dmalloc(&r->truncations, n)) || (rc = dmalloc(&r->starts, n)) ||
+      (rc = dmalloc(&r->masks, n)) || (rc = dmalloc(&r->error_flag, 1))) {
+    alegpu_rollout_destroy(r);
+    return rc;
+  }
+  *out = r;
+  return ALEGPU_OK;
+}
+
+extern "C" int alegpu_rollout_destroy(alegpu_rollout *r) {
+  if (!r)
+    return ALEGPU_OK;
+  cudaSetDevice(r->device);
+  for (void *p : {(void *)r->obs, (void *)r->carry, (void *)r->actions, (void *)r->rewards,
+                  (void *)r->values, (void *)r->advantages, (void *)r->returns,
+                  (void *)r->logits, (void *)r->log_probs, (void *)r->terminals,
+                  (void *)r->truncations, (void *)r->starts, (void *)r->masks,
+                  (void *)r->error_flag})
+    if (p)
+      cudaFree(p);
+  delete r;
+  return ALEGPU_OK;
+}
+
+extern "C" int alegpu_rollout_get_view(alegpu_rollout *r, alegpu_rollout_view *v) {
+  ALEGPU_REQUIRE(r && v, ALEGPU_INVALID_ARGUMENT, "rollout_get_view: null argument");
+  v->E = r->E; v->T = r->T; v->A = r->A;
+  v->observations = r->obs; v->carry = r->carry; v->actions = r->actions;
+  v->rewards = r->rewards; v->values = r->values; v->advantages = r->advantages;
+  v->returns = r->returns; v->logits = r->logits; v->log_probabilities = r->log_probs;
+  v->terminals = r->terminals; v->truncations = r->truncations;
+  v->episode_starts = r->starts; v->masks = r->masks;
+  return ALEGPU_OK;
+}
+
+extern "C" int alegpu_rollout_add(alegpu_rollout *r, const uint8_t *observations,
+                                  const int64_t *actions, const float *rewards,
+                                  const uint8_t *terminals, const uint8_t *truncations,
+                                  const uint8_t *episode_starts, const float *logits,
+                                  const float *values, void *stream) {
+  ALEGPU_REQUIRE(r && actions && rewards && terminals && truncations && episode_starts && logits &&
+                     values,
+                 ALEGPU_INVALID_ARGUMENT, "rollout_add: null argument");
+  ALEGPU_CUDA_CHECK(cudaSetDevice(r->device));
+  cudaStream_t s = as_stream(stream);
+  const int64_t t = r->write_index;
+  if (observations) // null = the producer already wrote slot t in place
+    ALEGPU_CUDA_CHECK(cudaMemcpy2DAsync(r->obs + t * 28224, (size_t)r->T * 28224, observations,
+                                        28224, 28224, (size_t)r->E, cudaMemcpyDeviceToDevice, s));
+  rollout_add_kernel<<<(unsigned)ceil_div(r->E, 128), 128, 0, s>>>(
+      r->E, r->T, r->A, t, actions, rewards, terminals, truncations, episode_starts, logits,
+      values, r->actions, r->rewards, r->terminals, r->truncations, r->starts, r->logits,
+      r->values);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  r->write_index = (r->write_index + 1) % r->T; // buffer.cc:55
+  return ALEGPU_OK;
+}
+
+extern "C" int alegpu_rollout_set_write_index(alegpu_rollout *r, int64_t index) {
+  ALEGPU_REQUIRE(r && index >= 0 && index < r->T, ALEGPU_INVALID_ARGUMENT,
+                 "rollout_set_write_index: out of range");
+  r->write_index = index;
+  return ALEGPU_OK;
+}
+
+extern "C" int alegpu_rollout_get(alegpu_rollout *r, const float *next_values, float gamma,
+                                  float lambda, alegpu_batch *flat, int flags, void *stream) {
+  ALEGPU_REQUIRE(r && next_values, ALEGPU_INVALID_ARGUMENT, "rollout_get: null argument");
+  ALEGPU_CUDA_CHECK(cudaSetDevice(r->device));
+  cudaStream_t s = as_stream(stream);
+  ALEGPU_CUDA_CHECK(cudaMemsetAsync(r->error_flag, 0, sizeof(int), s));
+  // the flag check (if requested) happens after BOTH kernels are enqueued
+  if (int rc = alegpu_buffer_get(r->rewards, r->values, next_values, r->terminals, r->truncations,
+                                 r->starts, r->E, r->T, gamma, lambda, r->write_index,
+                                 r->advantages, r->returns, r->masks, 1, r->error_flag, stream))
+    return rc;
+  // prepare_batch: old log-probs = log_softmax(stored logits) (src/bin/train.cc:279)
+  if (int rc = launch_normalize_logits(r->logits, r->E * r->T, r->A, r->log_probs, s))
+    return rc;
+  if (flat) { // flatten(0,1) / ravel views (src/bin/train.cc:274-282)
+    flat->observations = r->obs;
+    flat->actions = r->actions;
+    flat->log_probabilities = r->log_probs;
+    flat->advantages = r->advantages;
+    flat->returns = r->returns;
+    flat->masks = r->masks;
+    flat->size = r->E * r->T;
+  }
+  if (!(flags & 1)) {
+    int h = 0;
+    ALEGPU_CUDA_CHECK(cudaMemcpyAsync(&h, r->error_flag, sizeof(int), cudaMemcpyDeviceToHost, s));
+    ALEGPU_CUDA_CHECK(cudaStreamSynchronize(s));
+    if (h)
+      return fail(ALEGPU_INVALID_ARGUMENT,
+                  "Episode starts, terminals, and truncations must be mutually exclusive.");
+  }
+  return ALEGPU_OK;
+}

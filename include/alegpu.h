@@ -1,0 +1,273 @@
+/* alegpu.h — C ABI of the B200-native PPO learner hot path (libalegpu.so).
+ *
+ * Drop-in boundary for cemlyn007/ale-libtorch-ppo's learner path.  The reference has no FFI:
+ * its "operator API" is the C++ signatures in src/ai/{gae,buffer,vision}.h and
+ * src/ai/ppo/{losses,train}.h, all over torch::Tensor.  Each entry point below replaces one
+ * of them (cited file:line) with raw device pointers + explicit sizes + a cudaStream_t
+ * (passed as void*; NULL = the library's own stream for ctx calls / the legacy default
+ * stream for stateless calls).  No torch types cross this boundary; the library links only
+ * cudart (+ NCCL when built with ALEGPU_WITH_NCCL).
+ *
+ * Conventions
+ *   - every function returns an alegpu_status; alegpu_last_error() gives the message
+ *     (thread-local).  The status codes map 1:1 onto the C++ exception types the reference
+ *     throws for the same condition (SURVEY.md §8b "Error convention"); the C++ shim in
+ *     include/ai/ re-throws them.
+ *   - all pointers are DEVICE pointers unless the name ends in _host.
+ *   - layouts are the reference's: rollout storage env-major [E,T,...] (row = e*T + t), bools
+ *     are 1 byte, actions int64, observations [.,4,84,84] u8 with plane 0 = newest,
+ *     parameters flat in `parameters()` order, each tensor OIHW / [out,in].
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point fails with
+ *     ALEGPU_CUDA_ERROR.
+ */
+#ifndef ALEGPU_H_
+#define ALEGPU_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  ALEGPU_OK = 0,
+  ALEGPU_INVALID_ARGUMENT = 1, /* std::invalid_argument (gae.cc:11,19,24-46,52; rollout.cc:46-63) */
+  ALEGPU_RUNTIME_ERROR = 2,    /* std::runtime_error    (buffer.cc:65; train.h:141)             */
+  ALEGPU_OUT_OF_RANGE = 3,     /* std::out_of_range     (rollout.cc:315)                        */
+  ALEGPU_CUDA_ERROR = 4        /* a CUDA runtime / NCCL failure (no reference counterpart)       */
+} alegpu_status;
+
+const char *alegpu_last_error(void);
+/* library / build identification, e.g. "alegpu 0.1 sm_100a nccl=1" */
+const char *alegpu_version(void);
+
+/* ---- device memory helpers (so a host without torch can drive the library) ------------ */
+int alegpu_device_count(int *count);
+int alegpu_set_device(int device);
+int alegpu_malloc(void **dptr, size_t bytes);
+int alegpu_free(void *dptr);
+int alegpu_host_alloc(void **hptr, size_t bytes); /* pinned */
+int alegpu_host_free(void *hptr);
+int alegpu_memcpy_h2d(void *dst, const void *src_host, size_t bytes, void *stream);
+int alegpu_memcpy_d2h(void *dst_host, const void *src, size_t bytes, void *stream);
+int alegpu_memcpy_d2d(void *dst, const void *src, size_t bytes, void *stream);
+int alegpu_memset(void *dst, int value, size_t bytes, void *stream);
+int alegpu_stream_synchronize(void *stream);
+
+/* ---- stateless operators ---------------------------------------------------------------- */
+
+/* ai::gae::gae — src/ai/gae.h:4-7, src/ai/gae.cc:4-80.
+ * advantages[E,T] (out), rewards/values [E,T] f32, next_values [E] f32, flags [E,T] 1-byte
+ * bools.  Returns ALEGPU_INVALID_ARGUMENT if two flags co-occur anywhere (gae.cc:49-53);
+ * like the reference this check synchronises the stream. */
+int alegpu_gae(float *advantages, const float *rewards, const float *values,
+               const float *next_values, const uint8_t *terminals, const uint8_t *truncations,
+               const uint8_t *episode_starts, int64_t E, int64_t T, float gamma, float lambda,
+               void *stream);
+
+/* ai::buffer::Buffer::get — src/ai/buffer.cc:58-77, in pointer form: clamps rewards to
+ * [-1,1] IN PLACE (:67), runs the GAE scan (:68), returns = advantages + values (:70-71),
+ * masks = !episode_starts (:74).  write_index != 0 -> ALEGPU_RUNTIME_ERROR (:64-65).
+ * One fused kernel.  flags: bit0 = skip the flag-exclusivity host sync (error then surfaces
+ * through *device_error_flag if non-NULL). */
+int alegpu_buffer_get(float *rewards_inout, const float *values, const float *next_values,
+                      const uint8_t *terminals, const uint8_t *truncations,
+                      const uint8_t *episode_starts, int64_t E, int64_t T, float gamma,
+                      float lambda, int64_t write_index, float *advantages, float *returns,
+                      uint8_t *masks, int flags, int *device_error_flag, void *stream);
+
+/* Observation preprocessing for ONE env step of E environments.
+ * Replaces MaxAndSkipEnvironment's 2-frame max (src/ai/environment/max_and_skip.cc:33-42),
+ * the libtorch vision path resize_frame_stacked_rgb_images + rgb_to_grayscale_frame_stacked_images
+ * (src/ai/vision.cc:38-48, 71-84; weights :51; area mode :8-10) and
+ * Rollout::update_observations (src/ai/rollout.cc:184-196) with one fused kernel:
+ *   frames_a/frames_b [E,210,160,3] u8 HWC (the last two frames of the skip window)
+ *   -> max -> area-resize to 84x84 per channel -> 0.2125R+0.7154G+0.0721B -> floor(x+.5) u8
+ *   -> dst stack[e] = starts[e] ? {new,new,new,new} : {new, src[e][0], src[e][1], src[e][2]}.
+ * src/dst are [.,4,84,84] u8 stacks addressed as base + e*stride (bytes); they must not
+ * alias.  starts[e*starts_stride] is env e's flag (stride T reads the buffer's [E,T] array).  gray_f32 (optional, [E,84,84]) receives the un-quantised grayscale for parity. */
+int alegpu_preprocess_step(const uint8_t *frames_a, const uint8_t *frames_b,
+                           const uint8_t *starts, int64_t starts_stride, const uint8_t *src_stack,
+                           int64_t src_env_stride, uint8_t *dst_stack, int64_t dst_env_stride,
+                           float *gray_f32, int64_t E, void *stream);
+
+/* The same operator over a whole rollout whose raw frames are resident:
+ *   frames [T,E,2,210,160,3] u8 (time-major, as the ring delivers them),
+ *   episode_starts [E,T] (env-major, the buffer's own array: starts[e,t] != 0 means step t
+ *   of env e was a reset, so the update after step t fills all four planes),
+ *   obs [E,T,4,84,84] u8 rollout storage; carry_in [E,4,84,84] is the stack before step 0
+ *   (it becomes slot 0), carry_out receives the stack after step T-1.  carry_in != carry_out.
+ * Equivalent to T calls of alegpu_preprocess_step with dst = slot t+1. */
+int alegpu_preprocess_rollout(const uint8_t *frames, const uint8_t *episode_starts,
+                              const uint8_t *carry_in, uint8_t *carry_out, uint8_t *obs,
+                              int64_t E, int64_t T, void *stream);
+
+/* ai::ppo::losses::normalize_logits — src/ai/ppo/losses.cc:45-47. [n,A] -> [n,A]. */
+int alegpu_normalize_logits(const float *logits, int64_t n, int64_t A, float *out,
+                            void *stream);
+
+/* ai::ppo::losses::compute — src/ai/ppo/losses.h:6-37, losses.cc:4-43 — plus the gradient
+ * autograd produces for mini_batch_update (train.h:118-126) w.r.t. the RAW logits and the
+ * values.  logits [n,A] raw network outputs, old_log_probs [n,A] normalised, actions [n]
+ * int64, masks [n] 1-byte.  Outputs (any may be NULL): loss [1], per-sample clipped_losses,
+ * value_losses, entropies, total_losses, ratio [n], dlogits [n,A], dvalues [n]. A <= 32. */
+int alegpu_loss(const float *logits, const float *old_log_probs, const int64_t *actions,
+                const float *advantages, const float *values, const float *returns,
+                const uint8_t *masks, int64_t n, int64_t A, float clip_param,
+                float value_loss_coef, float entropy_coef, float *loss, float *clipped_losses,
+                float *value_losses, float *entropies, float *total_losses, float *ratio,
+                float *dlogits, float *dvalues, void *stream);
+
+/* streams / events for hosts that overlap the frame hand-off with compute */
+int alegpu_stream_create(void **stream);
+int alegpu_stream_destroy(void *stream);
+int alegpu_event_create(void **event);
+int alegpu_event_destroy(void *event);
+int alegpu_event_record(void *event, void *stream);
+int alegpu_stream_wait_event(void *stream, void *event);
+int alegpu_event_synchronize(void *event);
+int alegpu_event_elapsed_ms(void *start, void *stop, float *ms);
+/* kernels launched by this thread through the library so far (bench.py's gpu_launches) */
+int64_t alegpu_launch_count(void);
+/* a fresh 128-byte ncclUniqueId (rank 0 creates it, the host broadcasts it) */
+int alegpu_nccl_unique_id(void *out128);
+
+/* ---- the learner: policy + optimiser + trainer ----------------------------------------- */
+typedef struct alegpu_learner alegpu_learner;
+typedef struct alegpu_rollout alegpu_rollout;
+
+typedef enum {
+  ALEGPU_MATH_FP32 = 0, /* CUDA-core fp32 implicit GEMM: the fp32-faithful parity mode      */
+  ALEGPU_MATH_BF16 = 1  /* tcgen05/TMEM tensor-core implicit GEMM, bf16 operands, fp32 accum */
+} alegpu_math;
+
+typedef struct {
+  int64_t hidden_size;    /* configs/*.yaml hidden_size (src/bin/train.cc:113)               */
+  int64_t action_size;    /* fixed 4 in the reference (src/bin/train.cc:36)                   */
+  int64_t max_minibatch;  /* largest minibatch (rows) any call will use; sizes workspaces    */
+  int math;               /* alegpu_math                                                      */
+  double learning_rate;   /* torch::optim::Adam(lr, eps=1e-5), src/bin/train.cc:360-362       */
+  int device;             /* CUDA device ordinal                                              */
+  int world_size;         /* >1: data-parallel; gradients are summed over ranks (NCCL)        */
+  int rank;
+  const void *nccl_unique_id; /* 128-byte ncclUniqueId shared by all ranks (world_size>1)     */
+} alegpu_learner_config;
+
+/* hyper-parameters — ai::ppo::train::Hyperparameters, src/ai/ppo/train.h:27-32 */
+typedef struct {
+  float clip_param;
+  float value_loss_coef;
+  float entropy_coef;
+  float max_gradient_norm;
+} alegpu_hyperparameters;
+
+/* ai::ppo::train::Batch — src/ai/ppo/train.h:34-57 (device pointers, N rows) */
+typedef struct {
+  const uint8_t *observations;    /* [N,4,84,84] u8 */
+  const int64_t *actions;         /* [N] */
+  const float *log_probabilities; /* [N,A] normalised (prepare_batch, src/bin/train.cc:279) */
+  const float *advantages;        /* [N] */
+  const float *returns;           /* [N] */
+  const uint8_t *masks;           /* [N] */
+  int64_t size;                   /* N */
+} alegpu_batch;
+
+/* ai::ppo::train::Metrics — src/ai/ppo/train.h:64-109: [epochs,nmb,mb] f32 (masks 1-byte),
+ * clipped_gradients [epochs,nmb].  Any pointer may be NULL (that metric is skipped). */
+typedef struct {
+  float *loss;
+  float *clipped_losses;
+  float *value_losses;
+  float *entropies;
+  float *ratio;
+  float *total_losses;
+  float *advantages;
+  float *returns;
+  uint8_t *masks;
+  float *clipped_gradients;
+} alegpu_metrics;
+
+/* ---- rollout buffer: ai::buffer::Buffer — src/ai/buffer.h:27-58, src/ai/buffer.cc:5-77 ---- */
+/* raw device pointers of the [E,T,...] storage (ai::buffer::Batch aliases storage too,
+ * buffer.cc:73-76), so producers can write slots in place.  carry = 2 x [E,4,84,84] ping-pong
+ * stacks for the observation carried across rollouts (Rollout::observations_). */
+typedef struct {
+  int64_t E, T, A;
+  uint8_t *observations;      /* [E,T,4,84,84] */
+  uint8_t *carry;             /* [2,E,4,84,84] */
+  int64_t *actions;           /* [E,T] */
+  float *rewards, *values, *advantages, *returns; /* [E,T] */
+  float *logits, *log_probabilities;              /* [E,T,A] */
+  uint8_t *terminals, *truncations, *episode_starts, *masks; /* [E,T] */
+} alegpu_rollout_view;
+
+/* Buffer::Buffer(total_environments, capacity, {4,84,84}, action_size, device) — buffer.cc:5-39 */
+int alegpu_rollout_create(int64_t E, int64_t T, int64_t A, int device, alegpu_rollout **out);
+int alegpu_rollout_destroy(alegpu_rollout *rollout);
+int alegpu_rollout_get_view(alegpu_rollout *rollout, alegpu_rollout_view *view);
+/* Buffer::add — buffer.cc:41-56: per-step device arrays ([E,...]) go to column `write index`,
+ * which then advances mod T.  observations may be NULL when the producer already wrote the
+ * slot in place (alegpu_preprocess_step with dst = slot t). */
+int alegpu_rollout_add(alegpu_rollout *rollout, const uint8_t *observations,
+                       const int64_t *actions, const float *rewards, const uint8_t *terminals,
+                       const uint8_t *truncations, const uint8_t *episode_starts,
+                       const float *logits, const float *values, void *stream);
+int alegpu_rollout_set_write_index(alegpu_rollout *rollout, int64_t index);
+/* Buffer::get (buffer.cc:58-77) + prepare_batch (src/bin/train.cc:272-283): fills *flat with
+ * the [N = E*T] views train() consumes.  ALEGPU_RUNTIME_ERROR if the buffer is not full
+ * (:64-65); ALEGPU_INVALID_ARGUMENT if flags co-occur (gae.cc:49-53) unless flags bit0. */
+int alegpu_rollout_get(alegpu_rollout *rollout, const float *next_values, float gamma,
+                       float lambda, alegpu_batch *flat, int flags, void *stream);
+
+int alegpu_learner_create(const alegpu_learner_config *config, alegpu_learner **out);
+int alegpu_learner_destroy(alegpu_learner *learner);
+int64_t alegpu_learner_param_count(const alegpu_learner *learner);
+void *alegpu_learner_stream(alegpu_learner *learner);
+
+/* Weights in the reference's `parameters()` order and native tensor layouts (host arrays of
+ * param_count floats) — needed to start from the oracle's orthogonal init
+ * (src/bin/train.cc:212-248) and to compare after training. */
+int alegpu_learner_set_params(alegpu_learner *learner, const float *params_host);
+int alegpu_learner_get_params(alegpu_learner *learner, float *params_host);
+/* Adam moments in the same order/layout, and the optimiser step counter. */
+int alegpu_learner_get_adam(alegpu_learner *learner, float *exp_avg_host, float *exp_avg_sq_host,
+                            int64_t *step);
+/* the per-rollout lr anneal of src/bin/train.cc:424-428 (lr lives in a device scalar so a
+ * captured graph stays correct) */
+int alegpu_learner_set_lr(alegpu_learner *learner, double lr);
+
+/* NetworkImpl::forward — src/bin/train.cc:255-265 — inference on n <= max_minibatch rows. */
+int alegpu_learner_forward(alegpu_learner *learner, const uint8_t *observations, int64_t n,
+                           float *logits, float *values);
+/* Post-ReLU conv activations and the FC output of the last forward, converted to the
+ * reference's NCHW f32 layout (host arrays; parity/debug only). */
+int alegpu_learner_get_activations(alegpu_learner *learner, int64_t n, float *conv1_host,
+                                   float *conv2_host, float *conv3_host, float *fc_host);
+
+/* forward + loss + backward of one minibatch exactly as mini_batch_update does up to (not
+ * including) clip/step — src/ai/ppo/train.h:118-126.  grads_host receives the un-clipped
+ * gradient in reference order/layout; loss_host/logits/values optional. */
+int alegpu_learner_grads(alegpu_learner *learner, const alegpu_batch *minibatch,
+                         const alegpu_hyperparameters *hp, float *grads_host, float *loss_host,
+                         float *logits, float *values);
+/* clip_grad_norm_ (src/ai/ppo/train.cc:12-46) + Adam step on caller-provided gradients
+ * (reference order/layout).  total_norm_host = the PRE-clip norm. */
+int alegpu_learner_apply_grads(alegpu_learner *learner, const float *grads_host,
+                               double max_norm, float *total_norm_host);
+
+/* ai::ppo::train::train — src/ai/ppo/train.h:133-157: epochs x minibatches of
+ * {forward, loss, backward, clip, Adam}, minibatch k = rows [k*mb,(k+1)*mb) (the reference's
+ * randperm at :146 is never consumed).  batch.size % num_mini_batches != 0 ->
+ * ALEGPU_RUNTIME_ERROR (:140-143).  Asynchronous on the learner's stream.
+ * flags: bit0 = replay through a cached CUDA graph of this exact call shape. */
+int alegpu_learner_train(alegpu_learner *learner, const alegpu_batch *batch,
+                         const alegpu_metrics *metrics, int64_t num_epochs,
+                         int64_t num_mini_batches, const alegpu_hyperparameters *hp, int flags);
+/* number of kernels the last alegpu_learner_train call launched (or replayed) */
+int64_t alegpu_learner_last_launch_count(const alegpu_learner *learner);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ALEGPU_H_ */

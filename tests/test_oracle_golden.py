@@ -1,0 +1,153 @@
+"""CPU: pins the oracle restatement (oracle/restate.c) against
+  (1) the reference's own known-answer tests (test/ai/gae-test.cc x6, test/ai/vision-test.cc x2),
+  (2) fixtures produced by the reference's own code (tools/make_golden.py -> tests/golden/).
+If oracle/_ref (the reference compiled unmodified) is present it is cross-checked too."""
+import os
+
+import numpy as np
+import pytest
+
+import cases
+from oracle import ref, restate
+
+G = os.path.join(os.path.dirname(__file__), "golden")
+load = lambda n: np.load(os.path.join(G, n))
+
+
+@pytest.mark.parametrize("name", list(cases.GAE_KATS))
+def test_gae_known_answers(name):
+    c = cases.GAE_KATS[name]
+    got = restate.gae(c["rewards"], c["values"], c["next_values"], c["terminals"], c["truncations"],
+                      c["episode_starts"], cases.GAMMA, cases.LAMBDA)
+    np.testing.assert_allclose(got, cases.gae_kat_expected(c), atol=1e-5, rtol=0)  # EXPECT_NEAR 1e-5
+    np.testing.assert_allclose(got, load("gae_kats.npz")[name], atol=1e-6, rtol=0)
+
+
+def test_gae_simple_values():
+    # the reference's gae() reproduced (2.8109, 1.9308, 0.9950) on the first KAT
+    c = cases.GAE_KATS["SimpleNoTerminalsNoTruncations"]
+    got = restate.gae(c["rewards"], c["values"], c["next_values"], c["terminals"], c["truncations"],
+                      c["episode_starts"], cases.GAMMA, cases.LAMBDA)
+    np.testing.assert_allclose(got[0], [2.8109, 1.9308, 0.9950], atol=1e-4)
+
+
+def test_gae_flag_exclusivity_throws():
+    c = dict(cases.GAE_KATS["TerminalHandling"])
+    c["episode_starts"] = c["terminals"].copy()
+    with pytest.raises(ValueError):  # std::invalid_argument, gae.cc:49-53
+        restate.gae(c["rewards"], c["values"], c["next_values"], c["terminals"], c["truncations"],
+                    c["episode_starts"], cases.GAMMA, cases.LAMBDA)
+
+
+def test_buffer_get_golden():
+    s, g = cases.gae_case(), load("buffer_get.npz")
+    got = restate.buffer_get(s["rewards"], s["values"], s["next_values"], s["terminals"],
+                             s["truncations"], s["episode_starts"], cases.GAMMA, cases.LAMBDA)
+    assert np.array_equal(got["rewards"], g["rewards"])  # clamp: exact
+    assert np.array_equal(got["masks"], g["masks"])
+    np.testing.assert_allclose(got["advantages"], g["advantages"], atol=1e-5, rtol=1e-5)
+    np.testing.assert_allclose(got["returns"], g["returns"], atol=1e-5, rtol=1e-5)
+    with pytest.raises(RuntimeError):  # buffer.cc:64-65
+        restate.buffer_get(s["rewards"], s["values"], s["next_values"], s["terminals"],
+                           s["truncations"], s["episode_starts"], cases.GAMMA, cases.LAMBDA, 3)
+
+
+def test_vision_constant_images():
+    # vision-test.cc:5-30: constant in -> the same constant out, exactly
+    for val in (0, 1, 2, 3, 255):
+        f = np.full((1, 210, 160, 3), val, np.uint8)
+        g, q = restate.preprocess(f, f)
+        assert np.all(q == val)
+        np.testing.assert_allclose(g, val, atol=2e-4 * max(val, 1))  # weights sum to 1 +- ulp
+
+
+def test_preprocess_golden():
+    fr, g = cases.frames_case(), load("preprocess.npz")
+    gray, q = restate.preprocess(fr[:, 0], fr[:, 1])
+    np.testing.assert_allclose(gray, g["gray_f32"], atol=1e-3, rtol=0)
+    diff = q.astype(int) - g["gray_u8"].astype(int)
+    assert np.abs(diff).max() <= 1 and (diff != 0).mean() <= 1e-3  # +-1 LSB at .5 boundaries only
+    stack = np.zeros((1, 4, 84, 84), np.uint8)
+    for i, st in enumerate([1, 0, 0, 1, 0]):
+        stack = restate.stack_update(stack, g["gray_u8"][i:i + 1], np.array([st], np.uint8))
+        assert np.array_equal(stack[0], g["stacks"][i])  # frame-stack: bit-exact
+
+
+def test_loss_golden():
+    lc, g = cases.loss_case(), load("loss.npz")
+    got = restate.loss(lc["logits"], lc["old_log_probs"], lc["actions"], lc["advantages"],
+                       lc["values"], lc["returns"], lc["masks"], cases.CLIP, cases.VCOEF, cases.ECOEF)
+    for k in ("clipped_losses", "value_losses", "entropies", "total_losses", "ratio", "dlogits",
+              "dvalues"):
+        np.testing.assert_allclose(got[k], g[k], rtol=1e-5, atol=1e-6, err_msg=k)
+    assert abs(got["loss"] - float(g["loss"])) <= 1e-5 * abs(float(g["loss"])) + 1e-6
+    np.testing.assert_allclose(restate.log_softmax(lc["logits"]), g["log_softmax"], atol=1e-6)
+
+
+def _restate_grads(params, tc, H=32):
+    logits, values, acts = restate.net_forward(params, H, tc["obs"], keep_acts=True)
+    lo = restate.loss(logits, tc["log_probs"], tc["actions"], tc["advantages"], values,
+                      tc["returns"], tc["masks"], cases.CLIP, cases.VCOEF, cases.ECOEF)
+    return restate.net_backward(params, H, acts, lo["dlogits"], lo["dvalues"]), lo["loss"]
+
+
+def test_network_golden():
+    H, g = 32, load("net_h32.npz")
+    params, tc = cases.net_params(H), cases.train_case()
+    logits, values = restate.net_forward(params, H, tc["obs"][:6])
+    np.testing.assert_allclose(logits, g["logits"], rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(values, g["values"], rtol=1e-4, atol=1e-5)
+    grads, loss = _restate_grads(params, tc)
+    assert abs(loss - float(g["loss"])) <= 1e-5 * abs(float(g["loss"])) + 1e-6
+    offs, idx = cases.param_offsets(H), cases.sample_idx(params.size)
+    norms = [np.linalg.norm(grads[offs[i]:offs[i + 1]].astype(np.float64)) for i in range(12)]
+    np.testing.assert_allclose(norms, g["grad_norms"], rtol=1e-4)
+    np.testing.assert_allclose(grads[idx], g["grad_samples"], rtol=1e-3, atol=1e-6)
+    # clip + Adam, two steps (clipped, then un-clipped)
+    m, v = np.zeros_like(params), np.zeros_like(params)
+    p1, _, m, v, tn1 = restate.clip_adam(params, grads, m, v, H, 1, cases.LR, cases.MAX_NORM)
+    p2, _, m, v, tn2 = restate.clip_adam(p1, grads * np.float32(0.01), m, v, H, 2, cases.LR, cases.MAX_NORM)
+    np.testing.assert_allclose([tn1, tn2], g["total_norm"], rtol=1e-5)
+    np.testing.assert_allclose(p1[idx], g["p1"], rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(p2[idx], g["p2"], rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(m[idx], g["m2"], rtol=1e-5, atol=1e-9)
+    np.testing.assert_allclose(v[idx], g["v2"], rtol=1e-5, atol=1e-12)
+    assert int(g["step"]) == 2
+
+
+def test_train_golden():
+    H, g = 32, load("train_h32.npz")
+    params, tc = cases.net_params(H), cases.train_case()
+    z = np.zeros_like(params)
+    p, m, v, step, met = restate.train(params, z, z, 0, H, tc["obs"], tc["actions"], tc["log_probs"],
+                                       tc["advantages"], tc["returns"], tc["masks"], 2, 2,
+                                       cases.CLIP, cases.VCOEF, cases.ECOEF, cases.MAX_NORM, cases.LR)
+    assert step == 4
+    idx = cases.sample_idx(params.size)
+    np.testing.assert_allclose(p[idx], g["params"], rtol=1e-4, atol=1e-6)
+    for k in ("loss", "clipped_losses", "value_losses", "entropies", "ratio", "total_losses",
+              "clipped_gradients"):
+        np.testing.assert_allclose(met[k], g[k], rtol=1e-3, atol=1e-5, err_msg=k)
+    for k in ("advantages", "returns", "masks"):
+        assert np.array_equal(met[k], g[k]), k
+    with pytest.raises(RuntimeError):  # train.h:140-143
+        restate.train(params, z, z, 0, H, tc["obs"], tc["actions"], tc["log_probs"],
+                      tc["advantages"], tc["returns"], tc["masks"], 1, 5, cases.CLIP, cases.VCOEF,
+                      cases.ECOEF, cases.MAX_NORM, cases.LR)
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref not built (needs /root/reference)")
+def test_restatement_matches_compiled_reference():
+    s = cases.gae_case(8, 128, seed=21)
+    a = ref.gae(s["rewards"], s["values"], s["next_values"], s["terminals"], s["truncations"],
+                s["episode_starts"], cases.GAMMA, cases.LAMBDA)
+    b = restate.gae(s["rewards"], s["values"], s["next_values"], s["terminals"], s["truncations"],
+                    s["episode_starts"], cases.GAMMA, cases.LAMBDA)
+    np.testing.assert_allclose(a, b, atol=1e-6, rtol=1e-6)
+    lc = cases.loss_case(257, seed=77)
+    ra = ref.loss(lc["logits"], lc["old_log_probs"], lc["actions"], lc["advantages"], lc["values"],
+                  lc["returns"], lc["masks"], 0.2, 0.5, 0.01)
+    rb = restate.loss(lc["logits"], lc["old_log_probs"], lc["actions"], lc["advantages"],
+                      lc["values"], lc["returns"], lc["masks"], 0.2, 0.5, 0.01)
+    for k in ("total_losses", "ratio", "dlogits", "dvalues"):
+        np.testing.assert_allclose(ra[k], rb[k], rtol=1e-5, atol=1e-6, err_msg=k)
