@@ -129,7 +129,7 @@ class DeviceArray:
         return DeviceArray(shape, self.dtype, self.ptr + offset_elems * self.dtype.itemsize, self)
 
     def __del__(self):
-        if getattr(self, "_owned", False) and self.ptr and _lib is not None:
+        if getattr(self, "_owned", False) and getattr(self, "ptr", None) and _lib is not None:
             _lib.alegpu_free(C.c_void_p(self.ptr))
             self.ptr = None
 

@@ -128,7 +128,7 @@ __device__ __forceinline__ void store_tile(uint8_t *__restrict__ plane, int g,
 // ---- one env step -----------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads)
     preprocess_step_kernel(const uint8_t *__restrict__ frames_a,
-                           const uint8_t *__restrict__ frames_b,
+                           const uint8_t *__restrict__ frames_b, int64_t frame_stride,
                            const uint8_t *__restrict__ starts, int64_t starts_stride,
                            const uint8_t *__restrict__ src, int64_t src_stride,
                            uint8_t *__restrict__ dst, int64_t dst_stride,
@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(kThreads)
   __shared__ GroupSmem sm;
   const int g = blockIdx.x;
   const int64_t e = blockIdx.y;
-  gray_tile(frames_a + e * kFrameBytes, frames_b + e * kFrameBytes, g, sm,
+  gray_tile(frames_a + e * frame_stride, frames_b + e * frame_stride, g, sm,
             gray_f32 ? gray_f32 + e * kPlane : nullptr);
   uint8_t *d = dst + e * dst_stride;
   const int tid = threadIdx.x;
@@ -218,11 +218,12 @@ __global__ void __launch_bounds__(kThreads)
 
 using namespace alegpu;
 
-extern "C" int alegpu_preprocess_step(const uint8_t *frames_a, const uint8_t *frames_b,
-                                      const uint8_t *starts, int64_t starts_stride,
-                                      const uint8_t *src_stack, int64_t src_env_stride,
-                                      uint8_t *dst_stack, int64_t dst_env_stride,
-                                      float *gray_f32, int64_t E, void *stream) {
+static int preprocess_step_impl(const uint8_t *frames_a, const uint8_t *frames_b,
+                                int64_t frame_stride, const uint8_t *starts,
+                                int64_t starts_stride, const uint8_t *src_stack,
+                                int64_t src_env_stride, uint8_t *dst_stack,
+                                int64_t dst_env_stride, float *gray_f32, int64_t E,
+                                void *stream) {
   ALEGPU_REQUIRE(E >= 0 && E <= 65535, ALEGPU_INVALID_ARGUMENT,
                  "preprocess_step: E must be in [0, 65535]");
   if (E == 0)
@@ -232,17 +233,37 @@ extern "C" int alegpu_preprocess_step(const uint8_t *frames_a, const uint8_t *fr
   ALEGPU_REQUIRE(src_stack != dst_stack, ALEGPU_INVALID_ARGUMENT,
                  "preprocess_step: src and dst stacks must not alias");
   ALEGPU_REQUIRE(((uintptr_t)frames_a % 16 == 0) && ((uintptr_t)frames_b % 16 == 0) &&
-                     ((uintptr_t)src_stack % 8 == 0) && ((uintptr_t)dst_stack % 8 == 0) &&
+                     (frame_stride % 16 == 0) && ((uintptr_t)src_stack % 8 == 0) &&
+                     ((uintptr_t)dst_stack % 8 == 0) &&
                      (src_env_stride % 8 == 0) && (dst_env_stride % 8 == 0),
                  ALEGPU_INVALID_ARGUMENT,
                  "preprocess_step: frames need 16-byte, stacks/strides 8-byte alignment");
   dim3 grid(kGroups, (unsigned)E);
   preprocess_step_kernel<<<grid, kThreads, 0, as_stream(stream)>>>(
-      frames_a, frames_b, starts, starts_stride, src_stack, src_env_stride, dst_stack,
-      dst_env_stride, gray_f32);
+      frames_a, frames_b, frame_stride, starts, starts_stride, src_stack, src_env_stride,
+      dst_stack, dst_env_stride, gray_f32);
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
   return ALEGPU_OK;
+}
+
+extern "C" int alegpu_preprocess_step(const uint8_t *frames_a, const uint8_t *frames_b,
+                                      const uint8_t *starts, int64_t starts_stride,
+                                      const uint8_t *src_stack, int64_t src_env_stride,
+                                      uint8_t *dst_stack, int64_t dst_env_stride,
+                                      float *gray_f32, int64_t E, void *stream) {
+  return preprocess_step_impl(frames_a, frames_b, kFrameBytes, starts, starts_stride, src_stack,
+                              src_env_stride, dst_stack, dst_env_stride, gray_f32, E, stream);
+}
+
+extern "C" int alegpu_preprocess_step_strided(const uint8_t *frames_a, const uint8_t *frames_b,
+                                              int64_t frame_env_stride, const uint8_t *starts,
+                                              int64_t starts_stride, const uint8_t *src_stack,
+                                              int64_t src_env_stride, uint8_t *dst_stack,
+                                              int64_t dst_env_stride, int64_t E, void *stream) {
+  return preprocess_step_impl(frames_a, frames_b, frame_env_stride, starts, starts_stride,
+                              src_stack, src_env_stride, dst_stack, dst_env_stride, nullptr, E,
+                              stream);
 }
 
 extern "C" int alegpu_preprocess_rollout(const uint8_t *frames, const uint8_t *episode_starts,

@@ -20,6 +20,11 @@ struct alegpu_rollout {
   float *logits = nullptr, *log_probs = nullptr;
   uint8_t *terminals = nullptr, *truncations = nullptr, *starts = nullptr, *masks = nullptr;
   int *error_flag = nullptr;
+  // hand-off state (alegpu_rollout_ingest)
+  static constexpr int kRing = 4;
+  cudaStream_t copy_stream = nullptr;
+  uint8_t *ring = nullptr;
+  cudaEvent_t copied[kRing] = {}, consumed[kRing] = {}, start = nullptr;
 };
 
 namespace {
@@ -91,6 +96,16 @@ extern "C" int alegpu_rollout_destroy(alegpu_rollout *r) {
                   (void *)r->error_flag})
     if (p)
       cudaFree(p);
+  if (r->copy_stream) {
+    cudaStreamSynchronize(r->copy_stream);
+    cudaStreamDestroy(r->copy_stream);
+    cudaFree(r->ring);
+    for (int i = 0; i < alegpu_rollout::kRing; ++i) {
+      cudaEventDestroy(r->copied[i]);
+      cudaEventDestroy(r->consumed[i]);
+    }
+    cudaEventDestroy(r->start);
+  }
   delete r;
   return ALEGPU_OK;
 }
@@ -127,6 +142,59 @@ extern "C" int alegpu_rollout_add(alegpu_rollout *r, const uint8_t *observations
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
   r->write_index = (r->write_index + 1) % r->T; // buffer.cc:55
+  return ALEGPU_OK;
+}
+
+// ---- the hand-off: pinned host ring -> side-stream cudaMemcpyAsync -> fused preprocess --------
+// Replaces screen_buffers_ + torch::stack + per-env scalar device writes
+// (src/ai/rollout.cc:83-93, 184-196, 216-218).  frames_host is PINNED memory laid out
+// [T,E,2,210,160,3] (what the emulator threads fill, one [E,...] slab per env step).  Step t's
+// slab is copied on the copy stream into one of kRing device slots while the compute stream
+// is still preprocessing step t-1; events chain copy -> preprocess -> slot reuse.
+// carry_index selects which of the two carry stacks holds the stack before step 0; the stack
+// after step T-1 lands in the other one.
+extern "C" int alegpu_rollout_ingest(alegpu_rollout *r, const uint8_t *frames_host,
+                                     int carry_index, void *stream) {
+  ALEGPU_REQUIRE(r && frames_host && (carry_index == 0 || carry_index == 1),
+                 ALEGPU_INVALID_ARGUMENT, "rollout_ingest: bad argument");
+  ALEGPU_CUDA_CHECK(cudaSetDevice(r->device));
+  cudaStream_t s = as_stream(stream);
+  const int64_t E = r->E, T = r->T;
+  const size_t slab = (size_t)E * 2 * 100800;
+  if (!r->copy_stream) {
+    ALEGPU_CUDA_CHECK(cudaStreamCreateWithFlags(&r->copy_stream, cudaStreamNonBlocking));
+    ALEGPU_CUDA_CHECK(cudaMalloc(&r->ring, slab * alegpu_rollout::kRing));
+    for (int i = 0; i < alegpu_rollout::kRing; ++i) {
+      ALEGPU_CUDA_CHECK(cudaEventCreateWithFlags(&r->copied[i], cudaEventDisableTiming));
+      ALEGPU_CUDA_CHECK(cudaEventCreateWithFlags(&r->consumed[i], cudaEventDisableTiming));
+    }
+    ALEGPU_CUDA_CHECK(cudaEventCreateWithFlags(&r->start, cudaEventDisableTiming));
+  }
+  uint8_t *carry_in = r->carry + (size_t)carry_index * E * 28224;
+  uint8_t *carry_out = r->carry + (size_t)(1 - carry_index) * E * 28224;
+  // slot 0 <- the carried stack (Rollout::observations_ persists across rollouts)
+  ALEGPU_CUDA_CHECK(cudaMemcpy2DAsync(r->obs, (size_t)T * 28224, carry_in, 28224, 28224,
+                                      (size_t)E, cudaMemcpyDeviceToDevice, s));
+  ALEGPU_CUDA_CHECK(cudaEventRecord(r->start, s));
+  ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(r->copy_stream, r->start, 0));
+  for (int64_t t = 0; t < T; ++t) {
+    const int slot = (int)(t % alegpu_rollout::kRing);
+    uint8_t *dev = r->ring + slab * slot;
+    if (t >= alegpu_rollout::kRing) // the kernel that last read this slot must be done
+      ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(r->copy_stream, r->consumed[slot], 0));
+    ALEGPU_CUDA_CHECK(cudaMemcpyAsync(dev, frames_host + slab * t, slab, cudaMemcpyHostToDevice,
+                                      r->copy_stream));
+    ALEGPU_CUDA_CHECK(cudaEventRecord(r->copied[slot], r->copy_stream));
+    ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(s, r->copied[slot], 0));
+    const bool last = t + 1 == T;
+    // ring slab layout is [E,2,210,160,3]: frame a of env e at e*201600, frame b 100800 later,
+    // so both frame arrays are the same base with a 2-frame env stride
+    if (int rc = alegpu_preprocess_step_strided(
+            dev, dev + 100800, 2 * 100800, r->starts + t, T, r->obs + t * 28224, T * 28224,
+            last ? carry_out : r->obs + (t + 1) * 28224, last ? 28224 : T * 28224, E, stream))
+      return rc;
+    ALEGPU_CUDA_CHECK(cudaEventRecord(r->consumed[slot], s));
+  }
   return ALEGPU_OK;
 }
 

@@ -48,3 +48,31 @@ def frames(n, seed=42, kind="uniform"):
 
 def observations(n, seed=42):
     return np.random.default_rng(seed).integers(0, 256, (n, 4, 84, 84), dtype=np.uint8)
+
+
+def orthogonal_params(hidden=512, actions=4, seed=42):
+    """Random-init weights of the reference architecture in `parameters()` order: orthogonal
+    rows with gain sqrt(2) (policy head 0.01, value head 1) and zero biases — the scheme of
+    layer_init, src/bin/train.cc:212-228 (torch::nn::init::orthogonal_ flattens to [out, rest]
+    and orthogonalises via QR with sign correction)."""
+    rng = np.random.default_rng(seed)
+
+    def ortho(rows, cols, gain):
+        a = rng.standard_normal((rows, cols))
+        flip = rows < cols
+        if flip:
+            a = a.T
+        q, r = np.linalg.qr(a)
+        q = q * np.sign(np.diag(r))
+        if flip:
+            q = q.T
+        return (gain * q).astype(np.float32).ravel()
+
+    g = np.sqrt(2.0)
+    parts = [ortho(32, 4 * 8 * 8, g), np.zeros(32, np.float32),
+             ortho(64, 32 * 4 * 4, g), np.zeros(64, np.float32),
+             ortho(64, 64 * 3 * 3, g), np.zeros(64, np.float32),
+             ortho(hidden, 3136, g), np.zeros(hidden, np.float32),
+             ortho(actions, hidden, 0.01), np.zeros(actions, np.float32),
+             ortho(1, hidden, 1.0), np.zeros(1, np.float32)]
+    return np.concatenate(parts)

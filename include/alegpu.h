@@ -92,6 +92,13 @@ int alegpu_preprocess_step(const uint8_t *frames_a, const uint8_t *frames_b,
                            int64_t src_env_stride, uint8_t *dst_stack, int64_t dst_env_stride,
                            float *gray_f32, int64_t E, void *stream);
 
+/* as above with frame a/b of env e at frames_x + e*frame_env_stride (interleaved [E,2,...] slabs) */
+int alegpu_preprocess_step_strided(const uint8_t *frames_a, const uint8_t *frames_b,
+                                   int64_t frame_env_stride, const uint8_t *starts,
+                                   int64_t starts_stride, const uint8_t *src_stack,
+                                   int64_t src_env_stride, uint8_t *dst_stack,
+                                   int64_t dst_env_stride, int64_t E, void *stream);
+
 /* The same operator over a whole rollout whose raw frames are resident:
  *   frames [T,E,2,210,160,3] u8 (time-major, as the ring delivers them),
  *   episode_starts [E,T] (env-major, the buffer's own array: starts[e,t] != 0 means step t
@@ -214,6 +221,13 @@ int alegpu_rollout_add(alegpu_rollout *rollout, const uint8_t *observations,
                        const uint8_t *truncations, const uint8_t *episode_starts,
                        const float *logits, const float *values, void *stream);
 int alegpu_rollout_set_write_index(alegpu_rollout *rollout, int64_t index);
+/* The hand-off (replaces screen_buffers_/torch::stack/H2D, src/ai/rollout.cc:83-93,184-196):
+ * frames_host = PINNED [T,E,2,210,160,3]; each step's slab is cudaMemcpyAsync'ed on a side
+ * stream into a 4-slot device ring and preprocessed into slot t+1 on `stream` as it lands.
+ * episode_starts[E,T] must already be in the buffer.  carry_index in {0,1} names the carry
+ * stack holding the observation before step 0; the other one receives the stack after T-1. */
+int alegpu_rollout_ingest(alegpu_rollout *rollout, const uint8_t *frames_host, int carry_index,
+                          void *stream);
 /* Buffer::get (buffer.cc:58-77) + prepare_batch (src/bin/train.cc:272-283): fills *flat with
  * the [N = E*T] views train() consumes.  ALEGPU_RUNTIME_ERROR if the buffer is not full
  * (:64-65); ALEGPU_INVALID_ARGUMENT if flags co-occur (gae.cc:49-53) unless flags bit0. */
