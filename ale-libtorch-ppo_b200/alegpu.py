@@ -460,3 +460,22 @@ class Learner:
 
     def last_launch_count(self):
         return int(lib().alegpu_learner_last_launch_count(self.h))
+
+
+def selftest_tc_gemm(A, B, M, N, R, a_mn=False, b_mn=False, bn=64, splits=1):
+    """C[M,N] = A . B^T through the tcgen05/TMEM engine (alegpu_selftest_tc_gemm).  A is
+    [M,R] (a_mn False) or [R,M] (a_mn True) fp32; likewise B.  Returns [z,M,N] partial
+    products (z == 1 unless splits > 1)."""
+    A = np.ascontiguousarray(A, np.float32)
+    B = np.ascontiguousarray(B, np.float32)
+    z = 1
+    if splits > 1:
+        rps = -(-(-(-R // splits)) // 64) * 64
+        z = -(-R // rps)
+    dA, dB = DeviceArray.from_numpy(A), DeviceArray.from_numpy(B)
+    dC = DeviceArray.zeros((z, M, N), np.float32)
+    _check(lib().alegpu_selftest_tc_gemm(_p(dA), _p(dB), _p(dC), C.c_int64(M), C.c_int64(N),
+                                         C.c_int64(R), C.c_int(int(a_mn)), C.c_int(int(b_mn)),
+                                         C.c_int(bn), C.c_int(splits), None))
+    synchronize()
+    return dC.numpy()

@@ -382,8 +382,8 @@ extern "C" int alegpu_learner_create(const alegpu_learner_config *config, alegpu
   ALEGPU_REQUIRE(config->math == ALEGPU_MATH_FP32 || config->math == ALEGPU_MATH_BF16,
                  ALEGPU_INVALID_ARGUMENT, "learner_create: unknown math mode");
   if (config->math == ALEGPU_MATH_BF16)
-    ALEGPU_REQUIRE(config->hidden_size % 64 == 0, ALEGPU_INVALID_ARGUMENT,
-                   "learner_create: the tensor-core path needs hidden_size % 64 == 0");
+    ALEGPU_REQUIRE(config->hidden_size % 16 == 0, ALEGPU_INVALID_ARGUMENT,
+                   "learner_create: the tensor-core path needs hidden_size % 16 == 0");
   ALEGPU_CUDA_CHECK(cudaSetDevice(config->device));
   auto L = std::make_unique<alegpu_learner>();
   L->cfg = *config;

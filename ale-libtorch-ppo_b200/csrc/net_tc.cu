@@ -1,11 +1,514 @@
-// net_tc.cu — placeholder until the tcgen05 kernels land (next commit).
+// net_tc.cu — tensor-core (tcgen05/TMEM) Nature-CNN forward/backward for sm_100a.
+//
+// Replaces NetworkImpl::forward (src/bin/train.cc:255-265) and its autograd backward
+// (src/ai/ppo/train.h:126) — cuDNN/cuBLAS in the reference — with the implicit-GEMM engine of
+// tc_gemm.cuh.  Every layer, its data gradient and its weight gradient is ONE launch of that
+// engine with a different pair of operand views (16-byte chunk loaders) and a fused epilogue:
+//
+//   layer        M        N     R (reduction)   A view (major)            B view (major)
+//   conv1 fwd    n*400    32    256             im2col(u8 obs)      (K)   c1w [32][256]       (K)
+//   conv2 fwd    n*81     64    512             im2col(act1)        (K)   c2w [64][512]       (K)
+//   conv3 fwd    n*49     64    576             im2col(act2)        (K)   c3w [64][576]       (K)
+//   fc    fwd    n        H     3136            act3                (K)   fcw [H][3136]       (K)
+//   fc    dgrad  n        3136  H               dfc (fp32->bf16)    (K)   fcw^T               (MN)
+//   fc    wgrad  H        3137  n               dfc^T               (MN)  act3^T | ones       (MN)
+//   conv3 dgrad  n*81     64    576             col2im(dact3)       (K)   c3w^T               (MN)
+//   conv3 wgrad  577      64    n*49            im2col(act2)^T|ones (MN)  dact3^T             (MN)
+//   conv2 dgrad  4 x n*100 32   256             col2im(dact2),parity(K)   c2w^T (parity taps) (MN)
+//   conv2 wgrad  513      64    n*81            im2col(act1)^T|ones (MN)  dact2^T             (MN)
+//   conv1 wgrad  257      32    n*400           im2col(obs)^T|ones  (MN)  dact1^T             (MN)
+//
+// Activations and activation gradients are bf16 NHWC; weights are read from the bf16 shadow of
+// the flat parameter buffer that the fused Adam kernel maintains (optim.cu).  u8 pixels are exact
+// in bf16, so the 1/255 of train.cc:258-259 is applied to the fp32 accumulator in the epilogue.
+// Weight gradients are split over the reduction and summed in fixed order (deterministic).
+#include <algorithm>
+#include <vector>
+
 #include "net_tc.h"
+#include "optim.h"
+#include "tc_gemm.cuh"
+
 namespace alegpu {
-static int nyi() { return fail(ALEGPU_RUNTIME_ERROR, "tensor-core path not built yet"); }
-int net_tc_init(TcState &, int64_t, int64_t, int64_t, int64_t, cudaStream_t) { return nyi(); }
-void net_tc_destroy(TcState &) {}
-int net_tc_refresh_weights(TcState &, const float *, int64_t, cudaStream_t) { return nyi(); }
-int net_tc_forward(const NetParams &, TcState &, const uint8_t *, int64_t, NetActs &, cudaStream_t) { return nyi(); }
-int net_tc_backward(const NetParams &, const NetParams &, TcState &, const uint8_t *, int64_t, NetActs &, float *, size_t, cudaStream_t) { return nyi(); }
-int net_tc_fetch_activation(TcState &, int, int64_t, float *, cudaStream_t) { return nyi(); }
+namespace {
+
+using bf16 = __nv_bfloat16;
+using tc::pack_bf16;
+
+__device__ __forceinline__ uint4 ldg16(const void *p) {
+  return __ldg(reinterpret_cast<const uint4 *>(p));
+}
+__device__ __forceinline__ uint4 zero16() { return make_uint4(0u, 0u, 0u, 0u); }
+__device__ __forceinline__ uint4 ones_first16() { return make_uint4(0x00003F80u, 0u, 0u, 0u); }
+__device__ __forceinline__ uint4 f32x8_to_bf16(const float *p) {
+  const float4 a = __ldg(reinterpret_cast<const float4 *>(p));
+  const float4 b = __ldg(reinterpret_cast<const float4 *>(p) + 1);
+  return make_uint4(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w), pack_bf16(b.x, b.y),
+                    pack_bf16(b.z, b.w));
+}
+// four u8 -> four bf16 (exact): bf16(v) = high half of float(v)
+__device__ __forceinline__ void u8x4_to_bf16(uint32_t w, uint32_t &lo, uint32_t &hi) {
+  const uint32_t f0 = __float_as_uint((float)(w & 0xFFu)), f1 = __float_as_uint((float)((w >> 8) & 0xFFu));
+  const uint32_t f2 = __float_as_uint((float)((w >> 16) & 0xFFu)), f3 = __float_as_uint((float)(w >> 24));
+  lo = __byte_perm(f0, f1, 0x7632);
+  hi = __byte_perm(f2, f3, 0x7632);
+}
+
+// ---- im2col / col2im chunk views (each returns the 8 bf16 of one 16-byte chunk) ------------------
+// conv1: row m = (n,oy,ox) of 20x20, k = c*64 + ky*8 + kx ; chunk = the 8 kx of one (c,ky)
+struct Col1 {
+  const uint8_t *obs; // [n,4,84,84] u8
+  __device__ uint4 at(int m, int k) const {
+    const int n = m / 400, pix = m - n * 400, oy = pix / 20, ox = pix - oy * 20;
+    const int c = k >> 6, ky = (k >> 3) & 7;
+    const uint32_t *p = reinterpret_cast<const uint32_t *>(
+        obs + (size_t)n * 28224 + c * 7056 + (oy * 4 + ky) * 84 + ox * 4);
+    const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1);
+    uint4 r;
+    u8x4_to_bf16(w0, r.x, r.y);
+    u8x4_to_bf16(w1, r.z, r.w);
+    return r;
+  }
+};
+// conv2: row m = (n,oy,ox) of 9x9, k = (ky*4+kx)*32 + ci
+struct Col2 {
+  const bf16 *x; // act1 [n,20,20,32]
+  __device__ uint4 at(int m, int k) const {
+    const int n = m / 81, pix = m - n * 81, oy = pix / 9, ox = pix - oy * 9;
+    const int ky = k >> 7, kx = (k >> 5) & 3, ci = k & 31;
+    return ldg16(x + ((size_t)(n * 20 + 2 * oy + ky) * 20 + 2 * ox + kx) * 32 + ci);
+  }
+};
+// conv3: row m = (n,oy,ox) of 7x7, k = (ky*3+kx)*64 + ci
+struct Col3 {
+  const bf16 *x; // act2 [n,9,9,64]
+  __device__ uint4 at(int m, int k) const {
+    const int n = m / 49, pix = m - n * 49, oy = pix / 7, ox = pix - oy * 7;
+    const int t = k >> 6, ky = t / 3, kx = t - ky * 3, ci = k & 63;
+    return ldg16(x + ((size_t)(n * 9 + oy + ky) * 9 + ox + kx) * 64 + ci);
+  }
+};
+
+// K-major A operand of a forward conv: (row m, reduction k..k+7)
+template <class Col> struct ColK {
+  static constexpr bool kMN = false;
+  Col col;
+  __device__ uint4 chunk(int m, int k, int) const { return col.at(m, k); }
+};
+// MN-major A operand of a conv wgrad: rows = k (plus a ones row at k == K for the bias), r = m
+template <class Col, int K> struct ColMN {
+  static constexpr bool kMN = true;
+  Col col;
+  __device__ uint4 chunk(int k0, int m, int) const {
+    return k0 < K ? col.at(m, k0) : ones_first16();
+  }
+};
+// plain bf16 matrix [rows][ld]: K-major view (row, r..r+7)
+struct RowsK {
+  static constexpr bool kMN = false;
+  const bf16 *p;
+  int ld;
+  __device__ uint4 chunk(int i, int r, int) const { return ldg16(p + (size_t)i * ld + r); }
+};
+// fp32 matrix [rows][ld] converted on the fly: K-major view
+struct RowsKF32 {
+  static constexpr bool kMN = false;
+  const float *p;
+  int ld;
+  __device__ uint4 chunk(int i, int r, int) const { return f32x8_to_bf16(p + (size_t)i * ld + r); }
+};
+// transposed view of a bf16 matrix stored [r][ld]: element (i, r) = p[r*ld + i]; MN-major;
+// rows i >= ld (only i == ld is ever requested) give the ones row/column used for bias grads
+struct ColsMN {
+  static constexpr bool kMN = true;
+  const bf16 *p;
+  int ld;
+  __device__ uint4 chunk(int i0, int r, int) const {
+    return i0 < ld ? ldg16(p + (size_t)r * ld + i0) : ones_first16();
+  }
+};
+struct ColsMNF32 {
+  static constexpr bool kMN = true;
+  const float *p;
+  int ld;
+  __device__ uint4 chunk(int i0, int r, int) const { return f32x8_to_bf16(p + (size_t)r * ld + i0); }
+};
+// conv3 dgrad A: rows = act2 pixels (n,iy,ix) of 9x9, r = (ky*3+kx)*64 + co
+struct DCol3 {
+  static constexpr bool kMN = false;
+  const bf16 *dy; // dact3 [n,7,7,64]
+  __device__ uint4 chunk(int i, int r, int) const {
+    const int n = i / 81, pix = i - n * 81, iy = pix / 9, ix = pix - iy * 9;
+    const int t = r >> 6, ky = t / 3, kx = t - ky * 3, co = r & 63;
+    const int oy = iy - ky, ox = ix - kx;
+    if (oy < 0 || oy >= 7 || ox < 0 || ox >= 7)
+      return zero16();
+    return ldg16(dy + ((size_t)(n * 7 + oy) * 7 + ox) * 64 + co);
+  }
+};
+// conv3 dgrad B: (ci0..ci0+7, r = (t,co)) = c3w[co][t*64 + ci]
+struct W3T {
+  static constexpr bool kMN = true;
+  const bf16 *w;
+  __device__ uint4 chunk(int ci0, int r, int) const {
+    const int t = r >> 6, co = r & 63;
+    return ldg16(w + (size_t)co * 576 + t * 64 + ci0);
+  }
+};
+// conv2 dgrad A, parity class z = py*2+px: rows (n,qy,qx) of 10x10, r = (ty*2+tx)*64 + co
+struct DCol2 {
+  static constexpr bool kMN = false;
+  const bf16 *dy; // dact2 [n,9,9,64]
+  __device__ uint4 chunk(int i, int r, int) const {
+    const int n = i / 100, pix = i - n * 100, qy = pix / 10, qx = pix - qy * 10;
+    const int t = r >> 6, ty = t >> 1, tx = t & 1, co = r & 63;
+    const int oy = qy - ty, ox = qx - tx;
+    if (oy < 0 || oy >= 9 || ox < 0 || ox >= 9)
+      return zero16();
+    return ldg16(dy + ((size_t)(n * 9 + oy) * 9 + ox) * 64 + co);
+  }
+};
+// conv2 dgrad B: (ci0.., r=(t,co), z) = c2w[co][(ky*4+kx)*32 + ci], ky = py+2ty, kx = px+2tx
+struct W2T {
+  static constexpr bool kMN = true;
+  const bf16 *w;
+  __device__ uint4 chunk(int ci0, int r, int z) const {
+    const int t = r >> 6, ty = t >> 1, tx = t & 1, co = r & 63;
+    const int ky = (z >> 1) + 2 * ty, kx = (z & 1) + 2 * tx;
+    return ldg16(w + (size_t)co * 512 + (ky * 4 + kx) * 32 + ci0);
+  }
+};
+
+// ---- epilogues (16 consecutive columns of one row per call) --------------------------------------
+__device__ __forceinline__ void store_bf16x16(bf16 *dst, const float (&v)[16]) {
+  uint4 a = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
+                       pack_bf16(v[6], v[7]));
+  uint4 b = make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]),
+                       pack_bf16(v[14], v[15]));
+  reinterpret_cast<uint4 *>(dst)[0] = a;
+  reinterpret_cast<uint4 *>(dst)[1] = b;
+}
+__device__ __forceinline__ void load_bf16x16(const bf16 *src, float (&y)[16]) {
+  const uint4 a = reinterpret_cast<const uint4 *>(src)[0], b = reinterpret_cast<const uint4 *>(src)[1];
+  const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+  for (int t = 0; t < 8; ++t) {
+    y[2 * t] = __uint_as_float(w[t] << 16);
+    y[2 * t + 1] = __uint_as_float(w[t] & 0xFFFF0000u);
+  }
+}
+struct EpiBiasReluBf16 { // out[i][j] = relu(acc*scale + bias[j]) -> bf16, ld % 16 == 0
+  bf16 *out;
+  const float *bias;
+  int ld;
+  float scale;
+  __device__ void operator()(int i, int j0, float (&v)[16], int) const {
+#pragma unroll
+    for (int t = 0; t < 16; ++t)
+      v[t] = fmaxf(fmaf(v[t], scale, __ldg(bias + j0 + t)), 0.0f);
+    store_bf16x16(out + (size_t)i * ld + j0, v);
+  }
+};
+struct EpiBiasF32 { // out[i][j] = acc + bias[j] -> fp32 (the FC layer has no activation)
+  float *out;
+  const float *bias;
+  int ld;
+  __device__ void operator()(int i, int j0, float (&v)[16], int) const {
+    float4 *o = reinterpret_cast<float4 *>(out + (size_t)i * ld + j0);
+#pragma unroll
+    for (int t = 0; t < 4; ++t)
+      o[t] = make_float4(v[4 * t] + __ldg(bias + j0 + 4 * t), v[4 * t + 1] + __ldg(bias + j0 + 4 * t + 1),
+                         v[4 * t + 2] + __ldg(bias + j0 + 4 * t + 2),
+                         v[4 * t + 3] + __ldg(bias + j0 + 4 * t + 3));
+  }
+};
+struct EpiReluMaskBf16 { // out[i][j] = y[i][j] > 0 ? acc : 0 -> bf16
+  bf16 *out;
+  const bf16 *y;
+  int ld;
+  __device__ void operator()(int i, int j0, float (&v)[16], int) const {
+    const size_t o = (size_t)i * ld + j0;
+    float yy[16];
+    load_bf16x16(y + o, yy);
+#pragma unroll
+    for (int t = 0; t < 16; ++t)
+      v[t] = yy[t] > 0.0f ? v[t] : 0.0f;
+    store_bf16x16(out + o, v);
+  }
+};
+struct EpiReluMaskConv2 { // scatter parity class z back into NHWC [n,20,20,32]
+  bf16 *out;
+  const bf16 *y;
+  __device__ void operator()(int i, int j0, float (&v)[16], int z) const {
+    const int n = i / 100, pix = i - n * 100, qy = pix / 10, qx = pix - qy * 10;
+    const size_t o = ((size_t)(n * 20 + 2 * qy + (z >> 1)) * 20 + 2 * qx + (z & 1)) * 32 + j0;
+    float yy[16];
+    load_bf16x16(y + o, yy);
+#pragma unroll
+    for (int t = 0; t < 16; ++t)
+      v[t] = yy[t] > 0.0f ? v[t] : 0.0f;
+    store_bf16x16(out + o, v);
+  }
+};
+struct EpiPartial { // ws[z][i][j] fp32, row length ldn (any), columns >= ldn skipped
+  float *ws;
+  int rows, ldn;
+  __device__ void operator()(int i, int j0, float (&v)[16], int z) const {
+    float *o = ws + ((size_t)z * rows + i) * ldn + j0;
+#pragma unroll
+    for (int t = 0; t < 16; ++t)
+      if (j0 + t < ldn)
+        o[t] = v[t];
+  }
+};
+
+// gw[co*K + k] = scale * sum_z ws[z][k][co] (k < K), gb[co] = sum_z ws[z][K][co]; z ascending
+__global__ void reduce_wgrad_t_kernel(const float *__restrict__ ws, int splits, int K, int C,
+                                      float scale, float *__restrict__ gw, float *__restrict__ gb) {
+  const int64_t per = (int64_t)(K + 1) * C;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < per;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int co = (int)(idx / (K + 1)), k = (int)(idx - (int64_t)co * (K + 1));
+    float s = 0.0f;
+    for (int z = 0; z < splits; ++z)
+      s += ws[(size_t)z * per + (size_t)k * C + co];
+    if (k < K)
+      gw[(size_t)co * K + k] = s * scale;
+    else
+      gb[co] = s;
+  }
+}
+// gw[i*K + j] (j < K) / gb[i] (j == K) = sum_z ws[z][i][j]
+__global__ void reduce_wgrad_kernel(const float *__restrict__ ws, int splits, int rows, int K,
+                                    float *__restrict__ gw, float *__restrict__ gb) {
+  const int ldn = K + 1;
+  const int64_t total = (int64_t)rows * ldn;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    float s = 0.0f;
+    for (int z = 0; z < splits; ++z)
+      s += ws[(size_t)z * total + idx];
+    const int i = (int)(idx / ldn), j = (int)(idx - (int64_t)i * ldn);
+    if (j < K)
+      gw[(size_t)i * K + j] = s;
+    else
+      gb[i] = s;
+  }
+}
+
+// how to split a reduction of length R over CTAs when the output has `tiles` tiles
+void plan_splits(int64_t R, int64_t tiles, size_t per_split_floats, size_t ws_floats, int *splits,
+                 int *r_per_split) {
+  int64_t s = std::max<int64_t>(1, (2 * kNumSMs) / tiles);
+  s = std::min<int64_t>(s, std::max<int64_t>(1, R / (2 * tc::BK)));
+  s = std::min<int64_t>(s, (int64_t)(ws_floats / per_split_floats));
+  s = std::max<int64_t>(s, 1);
+  int64_t rps = ceil_div(ceil_div(R, s), tc::BK) * tc::BK;
+  *r_per_split = (int)rps;
+  *splits = (int)ceil_div(R, rps);
+}
+
+// conv weight gradient: ws[z][k][co] partials of  sum_m col(m,k) * dY[m][co], then fixed-order sum
+template <class Col, int K, int C>
+int conv_wgrad(const Col &col, const bf16 *dy, int64_t Mtot, float scale, float *gw, float *gb,
+               float *ws, size_t ws_floats, cudaStream_t s) {
+  const int64_t mtiles = ceil_div(K + 1, tc::BM);
+  const size_t per = (size_t)(K + 1) * C;
+  ALEGPU_REQUIRE(ws_floats >= per, ALEGPU_RUNTIME_ERROR, "wgrad: workspace too small");
+  int splits, rps;
+  plan_splits(Mtot, mtiles, per, ws_floats, &splits, &rps);
+  if (int rc = tc::launch_gemm_tc<64, 4>(ColMN<Col, K>{col}, ColsMN{dy, C},
+                                         EpiPartial{ws, K + 1, C}, K + 1, C, Mtot, splits, rps, s))
+    return rc;
+  const int blocks = (int)std::min<int64_t>(ceil_div((int64_t)per, 256), 2 * kNumSMs);
+  reduce_wgrad_t_kernel<<<blocks, 256, 0, s>>>(ws, splits, K, C, scale, gw, gb);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}
+
+__global__ void bf16_to_f32_kernel(const bf16 *__restrict__ src, float *__restrict__ dst, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    dst[i] = __bfloat162float(src[i]);
+}
+
+struct Shadow { // bf16 views of the flat parameter buffer (same offsets as NetParams)
+  const bf16 *c1w, *c2w, *c3w, *fcw;
+};
+Shadow shadow_view(const TcState &T, const NetParams &P) {
+  const bf16 *base = static_cast<const bf16 *>(T.w_shadow);
+  Shadow s;
+  s.c1w = base + (P.c1w - P.c1w);
+  s.c2w = base + (P.c2w - P.c1w);
+  s.c3w = base + (P.c3w - P.c1w);
+  s.fcw = base + (P.fcw - P.c1w);
+  return s;
+}
+
+} // namespace
+
+// ---- public (net_tc.h) ----------------------------------------------------------------------------
+int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_t Ppad,
+                cudaStream_t) {
+  ALEGPU_REQUIRE(hidden % 16 == 0, ALEGPU_INVALID_ARGUMENT,
+                 "the tensor-core path needs hidden_size % 16 == 0");
+  T.hidden = hidden;
+  T.actions = actions;
+  T.cap = cap;
+  T.Ppad = Ppad;
+  auto alloc = [](void **p, size_t bytes) -> int {
+    ALEGPU_CUDA_CHECK(cudaMalloc(p, bytes ? bytes : 16));
+    ALEGPU_CUDA_CHECK(cudaMemset(*p, 0, bytes ? bytes : 16));
+    return ALEGPU_OK;
+  };
+  if (int rc = alloc(&T.w_shadow, sizeof(bf16) * (size_t)Ppad)) return rc;
+  if (int rc = alloc(&T.act1, sizeof(bf16) * (size_t)cap * 12800)) return rc;
+  if (int rc = alloc(&T.act2, sizeof(bf16) * (size_t)cap * 5184)) return rc;
+  if (int rc = alloc(&T.act3, sizeof(bf16) * (size_t)cap * 3136)) return rc;
+  if (int rc = alloc(&T.dact1, sizeof(bf16) * (size_t)cap * 12800)) return rc;
+  if (int rc = alloc(&T.dact2, sizeof(bf16) * (size_t)cap * 5184)) return rc;
+  if (int rc = alloc(&T.dact3, sizeof(bf16) * (size_t)cap * 3136)) return rc;
+  return ALEGPU_OK;
+}
+
+void net_tc_destroy(TcState &T) {
+  for (void *p : {T.w_shadow, T.act1, T.act2, T.act3, T.dact1, T.dact2, T.dact3, T.fc16, T.dfc16,
+                  T.wt, (void *)T.stage})
+    if (p)
+      cudaFree(p);
+  T = TcState{};
+}
+
+int net_tc_refresh_weights(TcState &T, const float *params, int64_t Ppad, cudaStream_t s) {
+  return launch_f32_to_bf16(params, T.w_shadow, Ppad, s);
+}
+
+int net_tc_forward(const NetParams &P, TcState &T, const uint8_t *obs, int64_t n, NetActs &A,
+                   cudaStream_t s) {
+  const int H = (int)P.hidden;
+  const Shadow W = shadow_view(T, P);
+  bf16 *act1 = (bf16 *)T.act1, *act2 = (bf16 *)T.act2, *act3 = (bf16 *)T.act3;
+  if (int rc = tc::launch_gemm_tc<32, 4>(ColK<Col1>{Col1{obs}}, RowsK{W.c1w, 256},
+                                         EpiBiasReluBf16{act1, P.c1b, 32, 1.0f / 255.0f}, n * 400,
+                                         32, 256, 1, 0, s))
+    return rc;
+  if (int rc = tc::launch_gemm_tc<64, 4>(ColK<Col2>{Col2{act1}}, RowsK{W.c2w, 512},
+                                         EpiBiasReluBf16{act2, P.c2b, 64, 1.0f}, n * 81, 64, 512,
+                                         1, 0, s))
+    return rc;
+  if (int rc = tc::launch_gemm_tc<64, 4>(ColK<Col3>{Col3{act2}}, RowsK{W.c3w, 576},
+                                         EpiBiasReluBf16{act3, P.c3b, 64, 1.0f}, n * 49, 64, 576,
+                                         1, 0, s))
+    return rc;
+  return tc::launch_gemm_tc<128, 3>(RowsK{act3, 3136}, RowsK{W.fcw, 3136},
+                                    EpiBiasF32{A.fc, P.fcb, H}, n, H, 3136, 1, 0, s);
+}
+
+// A.dfc [n,H] fp32 is d loss / d fc-output (heads.cu).  Fills every gradient except the heads'.
+int net_tc_backward(const NetParams &P, const NetParams &G, TcState &T, const uint8_t *obs,
+                    int64_t n, NetActs &A, float *ws, size_t ws_floats, cudaStream_t s) {
+  const int H = (int)P.hidden;
+  const Shadow W = shadow_view(T, P);
+  bf16 *act1 = (bf16 *)T.act1, *act2 = (bf16 *)T.act2, *act3 = (bf16 *)T.act3;
+  bf16 *dact1 = (bf16 *)T.dact1, *dact2 = (bf16 *)T.dact2, *dact3 = (bf16 *)T.dact3;
+  // FC dgrad: dact3 = (dfc . fcw) * relu'(act3)
+  if (int rc = tc::launch_gemm_tc<128, 3>(RowsKF32{A.dfc, H}, ColsMN{W.fcw, 3136},
+                                          EpiReluMaskBf16{dact3, act3, 3136}, n, 3136, H, 1, 0, s))
+    return rc;
+  // FC wgrad: [H][3136 | bias] = dfc^T . [act3 | 1]
+  {
+    const int64_t tiles = ceil_div(H, tc::BM) * ceil_div(3137, 128);
+    const size_t per = (size_t)H * 3137;
+    ALEGPU_REQUIRE(ws_floats >= per, ALEGPU_RUNTIME_ERROR, "fc wgrad: workspace too small");
+    int splits, rps;
+    plan_splits(n, tiles, per, ws_floats, &splits, &rps);
+    if (int rc = tc::launch_gemm_tc<128, 3>(ColsMNF32{A.dfc, H}, ColsMN{act3, 3136},
+                                            EpiPartial{ws, H, 3137}, H, 3137, n, splits, rps, s))
+      return rc;
+    const int blocks = (int)std::min<int64_t>(ceil_div((int64_t)per, 256), 4 * kNumSMs);
+    reduce_wgrad_kernel<<<blocks, 256, 0, s>>>(ws, splits, H, 3136, G.fcw, G.fcb);
+    ALEGPU_COUNT_LAUNCH();
+    ALEGPU_LAUNCH_CHECK();
+  }
+  // conv3
+  if (int rc = tc::launch_gemm_tc<64, 4>(DCol3{dact3}, W3T{W.c3w}, EpiReluMaskBf16{dact2, act2, 64},
+                                         n * 81, 64, 576, 1, 0, s))
+    return rc;
+  if (int rc = conv_wgrad<Col3, 576, 64>(Col3{act2}, dact3, n * 49, 1.0f, G.c3w, G.c3b, ws,
+                                         ws_floats, s))
+    return rc;
+  // conv2 (4 parity classes of the stride-2 transposed convolution in one launch)
+  if (int rc = tc::launch_gemm_tc<64, 4>(DCol2{dact2}, W2T{W.c2w}, EpiReluMaskConv2{dact1, act1},
+                                         n * 100, 32, 256, 4, 0, s))
+    return rc;
+  if (int rc = conv_wgrad<Col2, 512, 64>(Col2{act1}, dact2, n * 81, 1.0f, G.c2w, G.c2b, ws,
+                                         ws_floats, s))
+    return rc;
+  // conv1 (input needs no gradient); the 1/255 of the input scale lands on the weight gradient
+  return conv_wgrad<Col1, 256, 32>(Col1{obs}, dact1, n * 400, 1.0f / 255.0f, G.c1w, G.c1b, ws,
+                                   ws_floats, s);
+}
+
+int net_tc_fetch_activation(TcState &T, int which, int64_t n, float *host, cudaStream_t s) {
+  const int64_t per = which == 1 ? 12800 : which == 2 ? 5184 : 3136;
+  const bf16 *src = (const bf16 *)(which == 1 ? T.act1 : which == 2 ? T.act2 : T.act3);
+  const int64_t total = n * per;
+  if (!T.stage)
+    ALEGPU_CUDA_CHECK(cudaMalloc(&T.stage, sizeof(float) * (size_t)T.cap * 12800));
+  bf16_to_f32_kernel<<<kNumSMs * 2, 256, 0, s>>>(src, T.stage, total);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  ALEGPU_CUDA_CHECK(cudaMemcpyAsync(host, T.stage, sizeof(float) * total, cudaMemcpyDeviceToHost, s));
+  ALEGPU_CUDA_CHECK(cudaStreamSynchronize(s));
+  return ALEGPU_OK;
+}
+
 } // namespace alegpu
+
+// ---- engine self-test (C ABI, include/alegpu.h) ---------------------------------------------------
+// C[M][N] (fp32) = A . B^T through the tcgen05 engine with fp32 inputs rounded to bf16 on load.
+// a_mn == 0: A is [M][R] row-major (K-major operand); a_mn == 1: A is stored [R][M] (MN-major).
+// Same for B with N.  bn selects the tile width instantiation (32, 64, 128 or 256).
+extern "C" int alegpu_selftest_tc_gemm(const float *A, const float *B, float *C, int64_t M, int64_t N,
+                                       int64_t R, int a_mn, int b_mn, int bn, int splits,
+                                       void *stream) {
+  using namespace alegpu;
+  ALEGPU_REQUIRE(A && B && C && M > 0 && N > 0 && R > 0, ALEGPU_INVALID_ARGUMENT,
+                 "selftest_tc_gemm: bad argument");
+  ALEGPU_REQUIRE(splits >= 1, ALEGPU_INVALID_ARGUMENT, "selftest_tc_gemm: splits >= 1");
+  ALEGPU_REQUIRE((a_mn ? M : R) % 8 == 0 && (b_mn ? N : R) % 8 == 0, ALEGPU_INVALID_ARGUMENT,
+                 "selftest_tc_gemm: the contiguous dimension of each operand must be a multiple of 8");
+  cudaStream_t s = as_stream(stream);
+  int rps = 0;
+  if (splits > 1)
+    rps = (int)(ceil_div(ceil_div(R, splits), tc::BK) * tc::BK);
+  const int z = splits > 1 ? (int)ceil_div(R, rps) : 1;
+  EpiPartial e{C, (int)M, (int)N}; // splits > 1: C must hold z*M*N floats (partials, not summed)
+#define ALEGPU_ST(BN, ST)                                                                          \
+  do {                                                                                             \
+    if (!a_mn && !b_mn)                                                                            \
+      return tc::launch_gemm_tc<BN, ST>(RowsKF32{A, (int)R}, RowsKF32{B, (int)R}, e, M, N, R, z,   \
+                                        rps, s);                                                   \
+    if (a_mn && !b_mn)                                                                             \
+      return tc::launch_gemm_tc<BN, ST>(ColsMNF32{A, (int)M}, RowsKF32{B, (int)R}, e, M, N, R, z,  \
+                                        rps, s);                                                   \
+    if constexpr (BN >= 64) {                                                                      \
+      if (!a_mn && b_mn)                                                                           \
+        return tc::launch_gemm_tc<BN, ST>(RowsKF32{A, (int)R}, ColsMNF32{B, (int)N}, e, M, N, R,   \
+                                          z, rps, s);                                              \
+      return tc::launch_gemm_tc<BN, ST>(ColsMNF32{A, (int)M}, ColsMNF32{B, (int)N}, e, M, N, R, z, \
+                                        rps, s);                                                   \
+    }                                                                                              \
+  } while (0)
+  if (bn == 32)
+    ALEGPU_ST(32, 4);
+  else if (bn == 64)
+    ALEGPU_ST(64, 4);
+  else if (bn == 128)
+    ALEGPU_ST(128, 3);
+  else if (bn == 256)
+    ALEGPU_ST(256, 3);
+#undef ALEGPU_ST
+  return fail(ALEGPU_INVALID_ARGUMENT, "selftest_tc_gemm: unsupported bn / major combination");
+}

@@ -1,0 +1,312 @@
+// tc_gemm.cuh — the tcgen05/TMEM implicit-GEMM engine of the tensor-core Nature-CNN path.
+//
+//   C[i][j] = sum_r A(i,r) * B(j,r)        bf16 operands, fp32 accumulation in tensor memory
+//
+// One CTA computes one 128 x BN tile.  Operands are never materialised in global memory: eight
+// producer warps gather 16-byte chunks (8 bf16) through loader functors (im2col, transposed-conv
+// and weight-gradient views live in net_tc.cu) and store them into shared memory directly in the
+// 128-byte-swizzled canonical layout the UMMA shared-memory descriptors describe.  A ninth warp
+// owns the tensor memory allocation and has one elected thread issue tcgen05.mma (UMMA 128xBNx16,
+// kind::f16, cta_group::1); full/empty mbarriers form a STAGES-deep ring between the producers and
+// the tensor core, tcgen05.commit releases ring slots and finally signals the epilogue.  The same
+// eight warps then read the accumulator with tcgen05.ld (32 lanes x 16 columns per instruction)
+// and run the fused epilogue functor (bias/ReLU, ReLU-mask, scatter, split partials).
+//
+// Shared-memory tile layouts (one k-block = 64 reduction elements):
+//   K-major operand  (reduction index contiguous in the 16-byte chunk):
+//       row i owns 128 contiguous bytes; chunk kc sits at i*128 + ((kc ^ (i&7)) << 4);
+//       8-row groups are 1024 B apart (SBO); one UMMA (K=16) advances the start address by 32 B.
+//   MN-major operand (row index contiguous in the chunk, e.g. transposed weights / wgrad views):
+//       64 rows x 8 reduction indices form a 1024-B atom: chunk c of reduction row kr sits at
+//       kr*128 + ((c ^ kr) << 4); atoms of successive reduction groups are 1024 B apart (SBO),
+//       atoms of successive 64-row blocks 8192 B apart (LBO); one UMMA advances by 2048 B.
+#pragma once
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+
+namespace alegpu {
+namespace tc {
+
+constexpr int BM = 128;          // UMMA M (cta_group::1)
+constexpr int BK = 64;           // reduction elements per pipeline stage (4 UMMAs of K=16)
+constexpr int kProducerWarps = 8;
+constexpr int kThreads = (kProducerWarps + 1) * 32;
+
+// ---- PTX wrappers -------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+  const uint32_t a = smem_u32(bar);
+  asm volatile("{\n\t"
+               ".reg .pred p;\n\t"
+               "WAIT_%=:\n\t"
+               "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+               "@p bra DONE_%=;\n\t"
+               "bra WAIT_%=;\n\t"
+               "DONE_%=:\n\t"
+               "}" ::"r"(a),
+               "r"(parity)
+               : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+// generic-proxy shared-memory writes -> visible to the async proxy (tcgen05.mma operand reads)
+__device__ __forceinline__ void fence_proxy_async_smem() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t *slot, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                   smem_u32(slot)),
+               "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols)
+               : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc]
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                          uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{\n\t"
+               ".reg .pred p;\n\t"
+               "setp.ne.b32 p, %4, 0;\n\t"
+               "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+               "}" ::"r"(tmem_d),
+               "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+               : "memory");
+}
+// arrive on an mbarrier once every tcgen05.mma issued so far by this thread has completed
+__device__ __forceinline__ void umma_commit(uint64_t *bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                   smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
+  uint32_t r[16];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+               "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]),
+                 "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]),
+                 "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+               : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i)
+    v[i] = __uint_as_float(r[i]);
+}
+
+// ---- descriptors ----------------------------------------------------------------------------------
+// UMMA shared-memory descriptor (SWIZZLE_128B): start>>4 [0,14) | LBO>>4 [16,30) | SBO>>4 [32,46)
+// | version=1 [46,48) | layout_type=2 [61,64)
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes,
+                                                   uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFFu);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// UMMA instruction descriptor, kind::f16: D=f32, A=B=bf16, M=128, N=BN, per-operand major bits
+__host__ __device__ constexpr uint32_t make_idesc(int n, bool a_mn, bool b_mn) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn ? 1u : 0u) << 15) |
+         ((b_mn ? 1u : 0u) << 16) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+}
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t *>(&h);
+}
+
+// ---- tile producer ----------------------------------------------------------------------------------
+// Fill one [ROWS x 64] operand tile.  Loader contract:
+//   K-major  (Op::kMN == false): Op::chunk(row, r, z) -> 8 bf16 = elements (row, r..r+7)
+//   MN-major (Op::kMN == true) : Op::chunk(row0, r, z) -> 8 bf16 = elements (row0..row0+7, r)
+// The loader is only called for row < rows_total and r < r_end; everything else is zero-filled.
+template <int ROWS, class Op>
+__device__ __forceinline__ void produce_tile(const Op &op, uint8_t *tile, int row0, int rows_total,
+                                             int r0, int r_end, int z, int ptid) {
+  constexpr int kChunks = ROWS * 8;
+  constexpr int kPer = (kChunks + kProducerWarps * 32 - 1) / (kProducerWarps * 32);
+  uint4 v[kPer];
+  uint32_t off[kPer];
+#pragma unroll
+  for (int it = 0; it < kPer; ++it) {
+    const int q = ptid + it * kProducerWarps * 32;
+    v[it] = make_uint4(0u, 0u, 0u, 0u);
+    off[it] = 0xFFFFFFFFu;
+    if (kChunks % (kProducerWarps * 32) == 0 || q < kChunks) {
+      if constexpr (!Op::kMN) {
+        const int kc = q & 7, il = q >> 3;
+        off[it] = (uint32_t)(il * 128 + ((kc ^ (il & 7)) << 4));
+        const int i = row0 + il, r = r0 + kc * 8;
+        if (i < rows_total && r < r_end)
+          v[it] = op.chunk(i, r, z);
+      } else {
+        constexpr int kRowChunks = ROWS / 8;
+        const int c = q % kRowChunks, k = q / kRowChunks;
+        const int kr = k & 7;
+        off[it] = (uint32_t)((c >> 3) * 8192 + (k >> 3) * 1024 + kr * 128 + (((c & 7) ^ kr) << 4));
+        const int i = row0 + c * 8, r = r0 + k;
+        if (i < rows_total && r < r_end)
+          v[it] = op.chunk(i, r, z);
+      }
+    }
+  }
+#pragma unroll
+  for (int it = 0; it < kPer; ++it)
+    if (off[it] != 0xFFFFFFFFu)
+      *reinterpret_cast<uint4 *>(tile + off[it]) = v[it];
+}
+
+__host__ __device__ constexpr int tile_bytes(int rows) { return rows * 128; }
+__host__ __device__ constexpr int smem_bytes(int bn, int stages) {
+  return stages * (tile_bytes(BM) + tile_bytes(bn < 64 ? 64 : bn)) + 1024;
+}
+__host__ __device__ constexpr uint32_t tmem_cols(int bn) { return bn <= 32 ? 32u : bn <= 64 ? 64u : bn <= 128 ? 128u : 256u; }
+
+// Epilogue contract: epi(i, j0, v, z) receives 16 consecutive columns j0..j0+15 of row i
+// (only for i < M and j0 < N; columns >= N inside the group must be skipped by the functor).
+template <int BN, int STAGES, class AOp, class BOp, class Epi>
+__global__ void __launch_bounds__(kThreads)
+    gemm_tc_kernel(const AOp aop, const BOp bop, const Epi epi, int M, int N, int R,
+                   int r_per_split) {
+  static_assert(BN % 32 == 0 && BN >= 32 && BN <= 256, "BN must be 32..256, multiple of 32");
+  static_assert(!BOp::kMN || BN >= 64, "an MN-major B tile needs at least one 64-row atom");
+  constexpr int kATile = tile_bytes(BM), kBTile = tile_bytes(BN < 64 ? 64 : BN);
+  constexpr int kStage = kATile + kBTile;
+  constexpr uint32_t kIdesc = make_idesc(BN, AOp::kMN, BOp::kMN);
+  constexpr uint32_t kCols = tmem_cols(BN);
+
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], accum_bar;
+  __shared__ uint32_t tmem_slot;
+  // SWIZZLE_128B atoms need 1024-byte alignment
+  uint8_t *tiles = reinterpret_cast<uint8_t *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN, z = blockIdx.z;
+  const int r_begin = r_per_split > 0 ? z * r_per_split : 0;
+  const int r_end = r_per_split > 0 ? min(R, r_begin + r_per_split) : R;
+  const int nkb = (r_end - r_begin + BK - 1) / BK;
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], kProducerWarps);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(&accum_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == kProducerWarps)
+    tmem_alloc(&tmem_slot, kCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  if (warp < kProducerWarps) {
+    // ===== producers: gather -> swizzled smem ==================================================
+    const int ptid = threadIdx.x;
+    for (int kb = 0; kb < nkb; ++kb) {
+      const int s = kb % STAGES;
+      const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+      mbar_wait(&empty_bar[s], ph ^ 1u);
+      uint8_t *st = tiles + s * kStage;
+      const int r0 = r_begin + kb * BK;
+      produce_tile<BM>(aop, st, m0, M, r0, r_end, z, ptid);
+      produce_tile<(BN < 64 ? 64 : BN)>(bop, st + kATile, n0, N, r0, r_end, z, ptid);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0)
+        mbar_arrive(&full_bar[s]);
+    }
+    // ===== epilogue: TMEM -> registers -> fused functor ========================================
+    if (nkb > 0) {
+      mbar_wait(&accum_bar, 0u);
+      tc_fence_after();
+    }
+    const int quarter = warp & 3, half = warp >> 2;
+    const int i = m0 + quarter * 32 + lane;
+    constexpr int kColsPerHalf = BN / 2;
+#pragma unroll
+    for (int c = 0; c < kColsPerHalf; c += 16) {
+      const int col = half * kColsPerHalf + c;
+      float v[16];
+      if (nkb > 0) {
+        tmem_ld16(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)col, v);
+      } else {
+#pragma unroll
+        for (int t = 0; t < 16; ++t)
+          v[t] = 0.0f;
+      }
+      if (i < M && n0 + col < N)
+        epi(i, n0 + col, v, z);
+    }
+  } else if (lane == 0) {
+    // ===== MMA issuer: one thread drives the tensor core =========================================
+    for (int kb = 0; kb < nkb; ++kb) {
+      const int s = kb % STAGES;
+      const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+      mbar_wait(&full_bar[s], ph);
+      tc_fence_after();
+      const uint32_t a_addr = smem_u32(tiles + s * kStage), b_addr = a_addr + kATile;
+      const uint64_t adesc = make_smem_desc(a_addr, AOp::kMN ? 8192u : 16u, 1024u);
+      const uint64_t bdesc = make_smem_desc(b_addr, BOp::kMN ? 8192u : 16u, 1024u);
+#pragma unroll
+      for (int kk = 0; kk < BK / 16; ++kk) {
+        const uint64_t ad = adesc + (uint64_t)(kk * (AOp::kMN ? 128 : 2));
+        const uint64_t bd = bdesc + (uint64_t)(kk * (BOp::kMN ? 128 : 2));
+        umma_bf16(tmem_base, ad, bd, kIdesc, (uint32_t)((kb | kk) != 0));
+      }
+      umma_commit(&empty_bar[s]); // slot reusable once these UMMAs have read it
+    }
+    if (nkb > 0)
+      umma_commit(&accum_bar);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kProducerWarps)
+    tmem_dealloc(tmem_base, kCols);
+}
+
+template <int BN, int STAGES, class AOp, class BOp, class Epi>
+int launch_gemm_tc(const AOp &a, const BOp &b, const Epi &e, int64_t M, int64_t N, int64_t R,
+                   int zdim, int r_per_split, cudaStream_t s) {
+  if (M <= 0 || N <= 0)
+    return ALEGPU_OK;
+  auto kern = gemm_tc_kernel<BN, STAGES, AOp, BOp, Epi>;
+  constexpr int kSmem = smem_bytes(BN, STAGES);
+  static bool configured = false; // per template instantiation
+  if (!configured) {
+    ALEGPU_CUDA_CHECK(
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+    configured = true;
+  }
+  dim3 grid((unsigned)ceil_div(M, BM), (unsigned)ceil_div(N, BN), (unsigned)zdim);
+  kern<<<grid, kThreads, kSmem, s>>>(a, b, e, (int)M, (int)N, (int)R, r_per_split);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}
+
+} // namespace tc
+} // namespace alegpu

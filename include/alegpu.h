@@ -281,6 +281,15 @@ int alegpu_learner_train(alegpu_learner *learner, const alegpu_batch *batch,
 /* number of kernels the last alegpu_learner_train call launched (or replayed) */
 int64_t alegpu_learner_last_launch_count(const alegpu_learner *learner);
 
+/* Self-test of the tcgen05/TMEM implicit-GEMM engine behind ALEGPU_MATH_BF16 (no reference
+ * counterpart: cuBLAS plays this role under libtorch).  C[M][N] fp32 = A . B^T with fp32 inputs
+ * rounded to bf16 on load.  a_mn == 0: A is [M][R] row-major; a_mn == 1: A is stored [R][M];
+ * likewise b_mn for B and N.  bn = tile width (32, 64, 128, 256; an MN-major B needs bn >= 64).
+ * splits > 1: the reduction is cut into ceil(R / rps) parts, rps = R/splits rounded up to 64,
+ * and C receives that many [M][N] partial products back to back (not summed). */
+int alegpu_selftest_tc_gemm(const float *A, const float *B, float *C, int64_t M, int64_t N,
+                            int64_t R, int a_mn, int b_mn, int bn, int splits, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,127 @@
+"""GPU parity tests of the tcgen05/TMEM tensor-core path (ALEGPU_MATH_BF16).
+
+Engine level: alegpu_selftest_tc_gemm against a float64 product of the bf16-rounded inputs
+(the engine accumulates in fp32, so the bound is fp32 summation noise).  Network level: the
+same golden / oracle comparisons as the fp32-faithful mode with the bf16 tolerances SURVEY.md
+§8c states: outputs rel-L2 <= 1e-2, per-tensor gradients rel-L2 <= 3e-2 and cosine >= 0.999.
+"""
+import numpy as np
+import pytest
+
+import alegpu
+import cases
+from oracle import restate
+
+pytestmark = pytest.mark.gpu
+
+
+def bf16_round(x):
+    u = np.ascontiguousarray(x, np.float32).view(np.uint32).astype(np.uint64)
+    u = (u + 0x7FFF + ((u >> 16) & 1)) & 0xFFFF0000
+    return u.astype(np.uint32).view(np.float32)
+
+
+def rel_l2(a, b):
+    a, b = np.asarray(a, np.float64).ravel(), np.asarray(b, np.float64).ravel()
+    return np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30)
+
+
+def cosine(a, b):
+    a, b = np.asarray(a, np.float64).ravel(), np.asarray(b, np.float64).ravel()
+    return float(a @ b / (np.linalg.norm(a) * np.linalg.norm(b) + 1e-300))
+
+
+def hp():
+    return alegpu.Hyperparameters(cases.CLIP, cases.VCOEF, cases.ECOEF, cases.MAX_NORM)
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (True, False), (False, True), (True, True)])
+@pytest.mark.parametrize("M,N,R,bn", [(128, 64, 64, 64), (304, 64, 576, 64), (256, 136, 200, 128),
+                                      (520, 256, 1000, 256), (64, 32, 256, 32)])
+def test_tc_gemm_engine(a_mn, b_mn, M, N, R, bn):
+    if b_mn and bn < 64:
+        pytest.skip("an MN-major B tile needs bn >= 64")
+    rng = np.random.default_rng(M * 7 + N * 3 + R)
+    A = rng.standard_normal((M, R)).astype(np.float32)
+    B = rng.standard_normal((N, R)).astype(np.float32)
+    want = bf16_round(A).astype(np.float64) @ bf16_round(B).astype(np.float64).T
+    got = alegpu.selftest_tc_gemm(A.T if a_mn else A, B.T if b_mn else B, M, N, R, a_mn, b_mn, bn)
+    assert got.shape == (1, M, N)
+    err = np.abs(got[0] - want).max()
+    assert err <= 1e-4 * np.sqrt(R) * 4, (err, a_mn, b_mn)
+
+
+def test_tc_gemm_engine_splits():
+    M, N, R = 264, 64, 1000
+    rng = np.random.default_rng(5)
+    A = rng.standard_normal((M, R)).astype(np.float32)
+    B = rng.standard_normal((N, R)).astype(np.float32)
+    want = bf16_round(A).astype(np.float64) @ bf16_round(B).astype(np.float64).T
+    got = alegpu.selftest_tc_gemm(A.T, B.T, M, N, R, True, True, 64, splits=5)
+    assert got.shape[0] == 4  # rps = 256 -> 4 parts
+    assert np.abs(got.sum(0) - want).max() <= 2e-3
+
+
+def _batch(tc, n=None):
+    sl = slice(0, n)
+    return alegpu.Batch(tc["obs"][sl], tc["actions"][sl], tc["log_probs"][sl], tc["advantages"][sl],
+                        tc["returns"][sl], tc["masks"][sl])
+
+
+# gradient bound: SURVEY.md §8c's bf16 figures (rel-L2 3e-2, cosine 0.999) at the v0 minibatch shape;
+# the 16-sample debug-width case averages bf16 rounding noise over 16x fewer rows, so 6e-2 / 0.998
+@pytest.mark.parametrize("H,n,pseed,dseed,gtol,gcos", [(32, 16, 3, 109, 6e-2, 0.998),
+                                                       (512, 256, 13, 31, 3e-2, 0.999)])
+def test_network_bf16_vs_oracle(H, n, pseed, dseed, gtol, gcos):
+    params = cases.net_params(H, seed=pseed)
+    tc = cases.train_case(n, seed=dseed)
+    L = alegpu.Learner(H, 4, n, alegpu.MATH_BF16, cases.LR)
+    L.set_params(params)
+    grads, loss, logits, values = L.grads(_batch(tc), hp())
+    lg, v, acts = restate.net_forward(params, H, tc["obs"], keep_acts=True)
+    k = min(n, 4)
+    c1, c2, c3, fc = L.activations(k)
+    o1, o2, o3 = 28224, 28224 + 12800, 28224 + 12800 + 5184  # packed [obs|a1|a2|a3|fc], NCHW
+    assert rel_l2(c1, acts[:k, o1:o2]) <= 1e-2, rel_l2(c1, acts[:k, o1:o2])
+    assert rel_l2(c2, acts[:k, o2:o3]) <= 1e-2, rel_l2(c2, acts[:k, o2:o3])
+    assert rel_l2(c3, acts[:k, o3:o3 + 3136]) <= 1e-2, rel_l2(c3, acts[:k, o3:o3 + 3136])
+    assert rel_l2(fc, acts[:k, o3 + 3136:]) <= 2e-2, rel_l2(fc, acts[:k, o3 + 3136:])
+    assert rel_l2(logits, lg) <= 2e-2, rel_l2(logits, lg)
+    assert rel_l2(values, v) <= 2e-2, rel_l2(values, v)
+    lo = restate.loss(lg, tc["log_probs"], tc["actions"], tc["advantages"], v, tc["returns"],
+                      tc["masks"], cases.CLIP, cases.VCOEF, cases.ECOEF)
+    assert abs(loss - lo["loss"]) <= 2e-2 * abs(lo["loss"]) + 1e-3
+    want = restate.net_backward(params, H, acts, lo["dlogits"], lo["dvalues"])
+    offs = cases.param_offsets(H)
+    report = []
+    for i in range(12):
+        a, b = grads[offs[i]:offs[i + 1]], want[offs[i]:offs[i + 1]]
+        report.append((i, rel_l2(a, b), cosine(a, b)))
+    print("bf16 grad report (tensor, rel-L2, cosine):", [(i, round(r, 5), round(c, 6)) for i, r, c in report])
+    for i, r, c in report:
+        assert r <= gtol and c >= gcos, report
+
+
+def test_train_bf16_vs_oracle_and_determinism():
+    H, n = 64, 64
+    params = cases.net_params(H, seed=21)
+    tc = cases.train_case(n, seed=77)
+    z = np.zeros_like(params)
+    p, _, _, _, m = restate.train(params, z, z, 0, H, tc["obs"], tc["actions"], tc["log_probs"],
+                                  tc["advantages"], tc["returns"], tc["masks"], 2, 2, cases.CLIP,
+                                  cases.VCOEF, cases.ECOEF, cases.MAX_NORM, cases.LR)
+    outs = []
+    for graph in (False, True, True):
+        L = alegpu.Learner(H, 4, n // 2, alegpu.MATH_BF16, cases.LR)
+        L.set_params(params)
+        met = alegpu.Metrics(2, 2, n // 2)
+        L.train(_batch(tc), met, 2, 2, hp(), cuda_graph=graph)
+        outs.append(L.get_params())
+        got = met.numpy()
+        np.testing.assert_allclose(got["loss"], m["loss"], rtol=5e-2, atol=2e-3)
+        assert L.get_adam()[2] == 4
+    # parameters moved by 4 Adam steps of size ~lr: compare the UPDATE, not the weights
+    du, dw = outs[0] - params, p - params
+    assert cosine(du, dw) >= 0.98, cosine(du, dw)
+    assert rel_l2(outs[0], p) <= 1e-3
+    assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[1], outs[2])  # bit-reproducible
