@@ -42,7 +42,21 @@ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
 // launch counter (bench.py's gpu_launches claim): every kernel launch goes through COUNT()
 extern thread_local int64_t g_launches;
-#define ALEGPU_COUNT_LAUNCH() (++::alegpu::g_launches)
+// optional launch tracer (alegpu_trace_begin/_end): a CUDA event after every launch site
+void trace_launch(const char *file, int line);
+extern thread_local bool g_trace_on;
+#define ALEGPU_COUNT_LAUNCH_NAMED(name)                                                      \
+  do {                                                                                       \
+    ++::alegpu::g_launches;                                                                  \
+    if (::alegpu::g_trace_on)                                                                \
+      ::alegpu::trace_launch(name, 0);                                                       \
+  } while (0)
+#define ALEGPU_COUNT_LAUNCH()                                                                \
+  do {                                                                                       \
+    ++::alegpu::g_launches;                                                                  \
+    if (::alegpu::g_trace_on)                                                                \
+      ::alegpu::trace_launch(__FILE__, __LINE__);                                            \
+  } while (0)
 
 #ifdef __CUDACC__
 // 16-byte streaming load/store: data touched once goes around L1 -----------------------------

@@ -8,6 +8,7 @@
 // clip coefficient live in device memory, so the whole train() call can be captured once into
 // a CUDA graph and replayed (the reference's capture_train_cuda_graph, train.h:163-195,
 // freezes lr into the graph; this one does not).
+#include <algorithm>
 #include <cstring>
 #include <memory>
 #include <vector>
@@ -57,6 +58,23 @@ static NcclApi &nccl() {
 #endif
 
 thread_local int64_t g_launches = 0;
+thread_local bool g_trace_on = false;
+namespace {
+struct TraceRec {
+  const char *file;
+  int line;
+  cudaEvent_t ev;
+};
+thread_local std::vector<TraceRec> g_trace;
+thread_local cudaStream_t g_trace_stream = nullptr;
+} // namespace
+void trace_launch(const char *file, int line) {
+  cudaEvent_t e;
+  if (cudaEventCreate(&e) != cudaSuccess)
+    return;
+  cudaEventRecord(e, g_trace_stream);
+  g_trace.push_back({file, line, e});
+}
 namespace {
 thread_local std::string g_error;
 }
@@ -353,6 +371,56 @@ extern "C" int alegpu_event_elapsed_ms(void *start, void *stop, float *ms) {
 }
 extern "C" int64_t alegpu_launch_count(void) { return g_launches; }
 
+// Launch tracer: between _begin and _end every kernel launch site on `stream` (this thread) is
+// followed by a CUDA event; _end writes "file:line count total_us" lines (device time from the
+// previous event to this one, i.e. kernel + launch gap) sorted by total time.
+extern "C" int alegpu_trace_begin(void *stream) {
+  for (auto &r : g_trace)
+    cudaEventDestroy(r.ev);
+  g_trace.clear();
+  g_trace_stream = as_stream(stream);
+  g_trace_on = true;
+  trace_launch("begin", 0);
+  return ALEGPU_OK;
+}
+extern "C" int alegpu_trace_end(char *out, size_t out_bytes) {
+  g_trace_on = false;
+  if (g_trace.empty())
+    return ALEGPU_OK;
+  ALEGPU_CUDA_CHECK(cudaEventSynchronize(g_trace.back().ev));
+  struct Agg { std::string key; int n; double us; };
+  std::vector<Agg> agg;
+  for (size_t i = 1; i < g_trace.size(); ++i) {
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, g_trace[i - 1].ev, g_trace[i].ev);
+    std::string f = g_trace[i].file;
+    const size_t slash = f.find_last_of('/');
+    if (slash != std::string::npos)
+      f = f.substr(slash + 1);
+    std::string key = f + ":" + std::to_string(g_trace[i].line);
+    auto it = std::find_if(agg.begin(), agg.end(), [&](const Agg &a) { return a.key == key; });
+    if (it == agg.end())
+      agg.push_back({key, 1, ms * 1e3});
+    else {
+      it->n += 1;
+      it->us += ms * 1e3;
+    }
+  }
+  std::sort(agg.begin(), agg.end(), [](const Agg &a, const Agg &b) { return a.us > b.us; });
+  std::string text;
+  for (auto &a : agg)
+    text += a.key + " " + std::to_string(a.n) + " " + std::to_string(a.us) + "\n";
+  if (out && out_bytes) {
+    const size_t n = std::min(out_bytes - 1, text.size());
+    std::memcpy(out, text.data(), n);
+    out[n] = 0;
+  }
+  for (auto &r : g_trace)
+    cudaEventDestroy(r.ev);
+  g_trace.clear();
+  return ALEGPU_OK;
+}
+
 extern "C" int alegpu_nccl_unique_id(void *out128) {
 #ifdef ALEGPU_WITH_NCCL
   static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
@@ -423,6 +491,10 @@ extern "C" int alegpu_learner_create(const alegpu_learner_config *config, alegpu
   if (int rc = fmalloc(&a.logits, (size_t)cap * A)) return rc;
   if (int rc = fmalloc(&a.values, (size_t)cap)) return rc;
   if (int rc = fmalloc(&a.dout, (size_t)cap * (A + 1))) return rc;
+  if (tc) { // room for 24 reduction splits of up to 1024 rows
+    a.fc_ws_floats = (size_t)std::min<int64_t>(cap, 1024) * H * 24;
+    if (int rc = fmalloc(&a.fc_ws, a.fc_ws_floats)) return rc;
+  }
   L->ws_floats = std::max<size_t>((size_t)4 << 20, (size_t)H * 3137 + 1024);
   if (int rc = fmalloc(&L->ws, L->ws_floats)) return rc;
   if (int rc = fmalloc(&L->norm_partials, kNormBlocks)) return rc;
@@ -468,7 +540,7 @@ extern "C" int alegpu_learner_destroy(alegpu_learner *L) {
     cudaGraphExecDestroy(L->graph_exec);
   NetActs &a = L->acts;
   for (float *p : {L->flat, a.act1, a.act2, a.act3, a.fc, a.dact1, a.dact2, a.dact3, a.dfc,
-                   a.logits, a.values, a.dout, L->ws, L->norm_partials, L->loss_partials,
+                   a.logits, a.values, a.dout, a.fc_ws, L->ws, L->norm_partials, L->loss_partials,
                    L->counts, L->scalars})
     if (p)
       cudaFree(p);

@@ -44,6 +44,8 @@ struct NetActs {
   float *dact1 = nullptr, *dact2 = nullptr, *dact3 = nullptr, *dfc = nullptr;
   float *logits = nullptr, *values = nullptr; // [cap,A], [cap]
   float *dout = nullptr;                      // [cap, A+1] = (dlogits, dvalue)
+  float *fc_ws = nullptr;                     // split-K partials of the FC forward (tensor-core path)
+  size_t fc_ws_floats = 0;
 };
 
 int net_f32_forward(const NetParams &P, const uint8_t *obs, int64_t n, NetActs &A,

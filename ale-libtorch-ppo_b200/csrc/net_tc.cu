@@ -40,40 +40,69 @@ __device__ __forceinline__ uint4 ldg16(const void *p) {
 }
 __device__ __forceinline__ uint4 zero16() { return make_uint4(0u, 0u, 0u, 0u); }
 __device__ __forceinline__ uint4 ones_first16() { return make_uint4(0x00003F80u, 0u, 0u, 0u); }
-__device__ __forceinline__ uint4 f32x8_to_bf16(const float *p) {
-  const float4 a = __ldg(reinterpret_cast<const float4 *>(p));
-  const float4 b = __ldg(reinterpret_cast<const float4 *>(p) + 1);
-  return make_uint4(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w), pack_bf16(b.x, b.y),
-                    pack_bf16(b.z, b.w));
-}
 // four u8 -> four bf16 (exact): bf16(v) = high half of float(v)
 __device__ __forceinline__ void u8x4_to_bf16(uint32_t w, uint32_t &lo, uint32_t &hi) {
-  const uint32_t f0 = __float_as_uint((float)(w & 0xFFu)), f1 = __float_as_uint((float)((w >> 8) & 0xFFu));
-  const uint32_t f2 = __float_as_uint((float)((w >> 16) & 0xFFu)), f3 = __float_as_uint((float)(w >> 24));
+  const uint32_t f0 = __float_as_uint((float)(w & 0xFFu)),
+                 f1 = __float_as_uint((float)((w >> 8) & 0xFFu));
+  const uint32_t f2 = __float_as_uint((float)((w >> 16) & 0xFFu)),
+                 f3 = __float_as_uint((float)(w >> 24));
   lo = __byte_perm(f0, f1, 0x7632);
   hi = __byte_perm(f2, f3, 0x7632);
 }
+struct F32x8 {
+  float4 a, b;
+};
+__device__ __forceinline__ F32x8 ldg_f32x8(const float *p) {
+  F32x8 r;
+  r.a = __ldg(reinterpret_cast<const float4 *>(p));
+  r.b = __ldg(reinterpret_cast<const float4 *>(p) + 1);
+  return r;
+}
+__device__ __forceinline__ uint4 f32x8_to_bf16(const F32x8 &v) {
+  return make_uint4(pack_bf16(v.a.x, v.a.y), pack_bf16(v.a.z, v.a.w), pack_bf16(v.b.x, v.b.y),
+                    pack_bf16(v.b.z, v.b.w));
+}
+// loaders whose raw form already is 8 bf16 / is 8 fp32
+#define ALEGPU_RAW_BF16                                                                          \
+  using Raw = uint4;                                                                             \
+  static __device__ __forceinline__ Raw zero() { return make_uint4(0u, 0u, 0u, 0u); }            \
+  static __device__ __forceinline__ uint4 cvt(const Raw &v) { return v; }
+#define ALEGPU_RAW_F32                                                                           \
+  using Raw = F32x8;                                                                             \
+  static __device__ __forceinline__ Raw zero() {                                                 \
+    F32x8 r;                                                                                     \
+    r.a = r.b = make_float4(0.f, 0.f, 0.f, 0.f);                                                 \
+    return r;                                                                                    \
+  }                                                                                              \
+  static __device__ __forceinline__ uint4 cvt(const Raw &v) { return f32x8_to_bf16(v); }
 
-// ---- im2col / col2im chunk views (each returns the 8 bf16 of one 16-byte chunk) ------------------
-// conv1: row m = (n,oy,ox) of 20x20, k = c*64 + ky*8 + kx ; chunk = the 8 kx of one (c,ky)
+// ---- im2col / col2im chunk views -----------------------------------------------------------------
+// Each view gives the RAW form of one 16-byte operand chunk (8 reduction- or row-contiguous
+// elements); conversion to bf16 happens when the chunk is stored to shared memory.
+// conv1: row m = (n,oy,ox) of 20x20, k = c*64 + ky*8 + kx ; chunk = the 8 kx of one (c,ky), raw u8
 struct Col1 {
+  using Raw = uint2;
+  static __device__ __forceinline__ Raw zero() { return make_uint2(0u, 0u); }
+  static __device__ __forceinline__ uint4 cvt(const Raw &v) {
+    uint4 r;
+    u8x4_to_bf16(v.x, r.x, r.y);
+    u8x4_to_bf16(v.y, r.z, r.w);
+    return r;
+  }
   const uint8_t *obs; // [n,4,84,84] u8
-  __device__ uint4 at(int m, int k) const {
+  __device__ __forceinline__ Raw at(int m, int k) const {
     const int n = m / 400, pix = m - n * 400, oy = pix / 20, ox = pix - oy * 20;
     const int c = k >> 6, ky = (k >> 3) & 7;
     const uint32_t *p = reinterpret_cast<const uint32_t *>(
         obs + (size_t)n * 28224 + c * 7056 + (oy * 4 + ky) * 84 + ox * 4);
-    const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1);
-    uint4 r;
-    u8x4_to_bf16(w0, r.x, r.y);
-    u8x4_to_bf16(w1, r.z, r.w);
-    return r;
+    return make_uint2(__ldg(p), __ldg(p + 1));
   }
 };
 // conv2: row m = (n,oy,ox) of 9x9, k = (ky*4+kx)*32 + ci
 struct Col2 {
+  ALEGPU_RAW_BF16
   const bf16 *x; // act1 [n,20,20,32]
-  __device__ uint4 at(int m, int k) const {
+  __device__ __forceinline__ uint4 at(int m, int k) const {
     const int n = m / 81, pix = m - n * 81, oy = pix / 9, ox = pix - oy * 9;
     const int ky = k >> 7, kx = (k >> 5) & 3, ci = k & 31;
     return ldg16(x + ((size_t)(n * 20 + 2 * oy + ky) * 20 + 2 * ox + kx) * 32 + ci);
@@ -81,8 +110,9 @@ struct Col2 {
 };
 // conv3: row m = (n,oy,ox) of 7x7, k = (ky*3+kx)*64 + ci
 struct Col3 {
+  ALEGPU_RAW_BF16
   const bf16 *x; // act2 [n,9,9,64]
-  __device__ uint4 at(int m, int k) const {
+  __device__ __forceinline__ uint4 at(int m, int k) const {
     const int n = m / 49, pix = m - n * 49, oy = pix / 7, ox = pix - oy * 7;
     const int t = k >> 6, ky = t / 3, kx = t - ky * 3, ci = k & 63;
     return ldg16(x + ((size_t)(n * 9 + oy + ky) * 9 + ox + kx) * 64 + ci);
@@ -92,52 +122,78 @@ struct Col3 {
 // K-major A operand of a forward conv: (row m, reduction k..k+7)
 template <class Col> struct ColK {
   static constexpr bool kMN = false;
+  using Raw = typename Col::Raw;
+  static __device__ __forceinline__ Raw zero() { return Col::zero(); }
+  static __device__ __forceinline__ uint4 cvt(const Raw &v) { return Col::cvt(v); }
   Col col;
-  __device__ uint4 chunk(int m, int k, int) const { return col.at(m, k); }
+  __device__ __forceinline__ Raw load(int m, int k, int) const { return col.at(m, k); }
 };
-// MN-major A operand of a conv wgrad: rows = k (plus a ones row at k == K for the bias), r = m
+// MN-major A operand of a conv wgrad: rows = k (plus a ones row at k == K for the bias), r = m.
+// The ones row is encoded in the raw form as an all-ones first word (never a valid chunk of
+// this operand: raw u8 0xFFFFFFFF|.. pixels or a bf16 NaN pair) and decoded in cvt().
 template <class Col, int K> struct ColMN {
   static constexpr bool kMN = true;
+  struct Raw {
+    typename Col::Raw v;
+    bool ones;
+  };
+  static __device__ __forceinline__ Raw zero() { return Raw{Col::zero(), false}; }
+  static __device__ __forceinline__ uint4 cvt(const Raw &r) {
+    return r.ones ? ones_first16() : Col::cvt(r.v);
+  }
   Col col;
-  __device__ uint4 chunk(int k0, int m, int) const {
-    return k0 < K ? col.at(m, k0) : ones_first16();
+  __device__ __forceinline__ Raw load(int k0, int m, int) const {
+    if (k0 < K)
+      return Raw{col.at(m, k0), false};
+    return Raw{Col::zero(), true};
   }
 };
 // plain bf16 matrix [rows][ld]: K-major view (row, r..r+7)
 struct RowsK {
+  ALEGPU_RAW_BF16
   static constexpr bool kMN = false;
   const bf16 *p;
   int ld;
-  __device__ uint4 chunk(int i, int r, int) const { return ldg16(p + (size_t)i * ld + r); }
+  __device__ __forceinline__ uint4 load(int i, int r, int) const {
+    return ldg16(p + (size_t)i * ld + r);
+  }
 };
 // fp32 matrix [rows][ld] converted on the fly: K-major view
 struct RowsKF32 {
+  ALEGPU_RAW_F32
   static constexpr bool kMN = false;
   const float *p;
   int ld;
-  __device__ uint4 chunk(int i, int r, int) const { return f32x8_to_bf16(p + (size_t)i * ld + r); }
+  __device__ __forceinline__ F32x8 load(int i, int r, int) const {
+    return ldg_f32x8(p + (size_t)i * ld + r);
+  }
 };
 // transposed view of a bf16 matrix stored [r][ld]: element (i, r) = p[r*ld + i]; MN-major;
 // rows i >= ld (only i == ld is ever requested) give the ones row/column used for bias grads
 struct ColsMN {
+  ALEGPU_RAW_BF16
   static constexpr bool kMN = true;
   const bf16 *p;
   int ld;
-  __device__ uint4 chunk(int i0, int r, int) const {
+  __device__ __forceinline__ uint4 load(int i0, int r, int) const {
     return i0 < ld ? ldg16(p + (size_t)r * ld + i0) : ones_first16();
   }
 };
 struct ColsMNF32 {
+  ALEGPU_RAW_F32
   static constexpr bool kMN = true;
   const float *p;
   int ld;
-  __device__ uint4 chunk(int i0, int r, int) const { return f32x8_to_bf16(p + (size_t)r * ld + i0); }
+  __device__ __forceinline__ F32x8 load(int i0, int r, int) const {
+    return ldg_f32x8(p + (size_t)r * ld + i0);
+  }
 };
 // conv3 dgrad A: rows = act2 pixels (n,iy,ix) of 9x9, r = (ky*3+kx)*64 + co
 struct DCol3 {
+  ALEGPU_RAW_BF16
   static constexpr bool kMN = false;
   const bf16 *dy; // dact3 [n,7,7,64]
-  __device__ uint4 chunk(int i, int r, int) const {
+  __device__ __forceinline__ uint4 load(int i, int r, int) const {
     const int n = i / 81, pix = i - n * 81, iy = pix / 9, ix = pix - iy * 9;
     const int t = r >> 6, ky = t / 3, kx = t - ky * 3, co = r & 63;
     const int oy = iy - ky, ox = ix - kx;
@@ -148,18 +204,20 @@ struct DCol3 {
 };
 // conv3 dgrad B: (ci0..ci0+7, r = (t,co)) = c3w[co][t*64 + ci]
 struct W3T {
+  ALEGPU_RAW_BF16
   static constexpr bool kMN = true;
   const bf16 *w;
-  __device__ uint4 chunk(int ci0, int r, int) const {
+  __device__ __forceinline__ uint4 load(int ci0, int r, int) const {
     const int t = r >> 6, co = r & 63;
     return ldg16(w + (size_t)co * 576 + t * 64 + ci0);
   }
 };
 // conv2 dgrad A, parity class z = py*2+px: rows (n,qy,qx) of 10x10, r = (ty*2+tx)*64 + co
 struct DCol2 {
+  ALEGPU_RAW_BF16
   static constexpr bool kMN = false;
   const bf16 *dy; // dact2 [n,9,9,64]
-  __device__ uint4 chunk(int i, int r, int) const {
+  __device__ __forceinline__ uint4 load(int i, int r, int) const {
     const int n = i / 100, pix = i - n * 100, qy = pix / 10, qx = pix - qy * 10;
     const int t = r >> 6, ty = t >> 1, tx = t & 1, co = r & 63;
     const int oy = qy - ty, ox = qx - tx;
@@ -170,9 +228,10 @@ struct DCol2 {
 };
 // conv2 dgrad B: (ci0.., r=(t,co), z) = c2w[co][(ky*4+kx)*32 + ci], ky = py+2ty, kx = px+2tx
 struct W2T {
+  ALEGPU_RAW_BF16
   static constexpr bool kMN = true;
   const bf16 *w;
-  __device__ uint4 chunk(int ci0, int r, int z) const {
+  __device__ __forceinline__ uint4 load(int ci0, int r, int z) const {
     const int t = r >> 6, ty = t >> 1, tx = t & 1, co = r & 63;
     const int ky = (z >> 1) + 2 * ty, kx = (z & 1) + 2 * tx;
     return ldg16(w + (size_t)co * 512 + (ky * 4 + kx) * 32 + ci0);
@@ -255,27 +314,76 @@ struct EpiPartial { // ws[z][i][j] fp32, row length ldn (any), columns >= ldn sk
   int rows, ldn;
   __device__ void operator()(int i, int j0, float (&v)[16], int z) const {
     float *o = ws + ((size_t)z * rows + i) * ldn + j0;
+    if ((ldn & 3) == 0 && j0 + 16 <= ldn) {
 #pragma unroll
-    for (int t = 0; t < 16; ++t)
-      if (j0 + t < ldn)
-        o[t] = v[t];
+      for (int t = 0; t < 4; ++t)
+        reinterpret_cast<float4 *>(o)[t] = make_float4(v[4 * t], v[4 * t + 1], v[4 * t + 2], v[4 * t + 3]);
+    } else {
+#pragma unroll
+      for (int t = 0; t < 16; ++t)
+        if (j0 + t < ldn)
+          o[t] = v[t];
+    }
+  }
+};
+struct EpiWgradDirect { // gw[i*K + j] = acc (j < K), gb[i] = acc (j == K)
+  float *gw, *gb;
+  int K;
+  __device__ void operator()(int i, int j0, float (&v)[16], int) const {
+    if (j0 + 16 <= K) {
+      float4 *o = reinterpret_cast<float4 *>(gw + (size_t)i * K + j0);
+#pragma unroll
+      for (int t = 0; t < 4; ++t)
+        o[t] = make_float4(v[4 * t], v[4 * t + 1], v[4 * t + 2], v[4 * t + 3]);
+    } else {
+#pragma unroll
+      for (int t = 0; t < 16; ++t) {
+        if (j0 + t < K)
+          gw[(size_t)i * K + j0 + t] = v[t];
+        else if (j0 + t == K)
+          gb[i] = v[t];
+      }
+    }
   }
 };
 
-// gw[co*K + k] = scale * sum_z ws[z][k][co] (k < K), gb[co] = sum_z ws[z][K][co]; z ascending
-__global__ void reduce_wgrad_t_kernel(const float *__restrict__ ws, int splits, int K, int C,
-                                      float scale, float *__restrict__ gw, float *__restrict__ gb) {
-  const int64_t per = (int64_t)(K + 1) * C;
-  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < per;
-       idx += (int64_t)gridDim.x * blockDim.x) {
-    const int co = (int)(idx / (K + 1)), k = (int)(idx - (int64_t)co * (K + 1));
-    float s = 0.0f;
-    for (int z = 0; z < splits; ++z)
-      s += ws[(size_t)z * per + (size_t)k * C + co];
+// gw[co*K + k] = scale * sum_z ws[z][k][co] (k < K), gb[co] = sum_z ws[z][K][co].
+// One block per (k, 32 channels); the 8 thread rows sum interleaved z subsets which are then
+// combined in fixed order, so the result is deterministic.  block = (32, 8), grid = (K+1, C/32)
+__global__ void __launch_bounds__(256)
+    reduce_wgrad_t_kernel(const float *__restrict__ ws, int splits, int K, int C, float scale,
+                          float *__restrict__ gw, float *__restrict__ gb) {
+  __shared__ float part[8][32];
+  const int k = blockIdx.x, co = blockIdx.y * 32 + threadIdx.x, ty = threadIdx.y;
+  const size_t per = (size_t)(K + 1) * C;
+  const float *p = ws + (size_t)k * C + co;
+  float s = 0.0f;
+  for (int z = ty; z < splits; z += 8)
+    s += p[(size_t)z * per];
+  part[ty][threadIdx.x] = s;
+  __syncthreads();
+  if (ty == 0) {
+    float t = part[0][threadIdx.x];
+#pragma unroll
+    for (int g = 1; g < 8; ++g)
+      t += part[g][threadIdx.x];
     if (k < K)
-      gw[(size_t)co * K + k] = s * scale;
+      gw[(size_t)co * K + k] = t * scale;
     else
-      gb[co] = s;
+      gb[co] = t;
+  }
+}
+// fc[i][j] = bias[j] + sum_z ws[z][i][j]  (split-K forward of the FC layer at small minibatches)
+__global__ void reduce_fc_kernel(const float4 *__restrict__ ws, int splits, int64_t total4, int H4,
+                                 const float4 *__restrict__ bias, float4 *__restrict__ out) {
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total4;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    float4 s = bias[idx % H4];
+    for (int z = 0; z < splits; ++z) {
+      const float4 v = ws[(size_t)z * total4 + idx];
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    out[idx] = s;
   }
 }
 // gw[i*K + j] (j < K) / gb[i] (j == K) = sum_z ws[z][i][j]
@@ -320,8 +428,9 @@ int conv_wgrad(const Col &col, const bf16 *dy, int64_t Mtot, float scale, float 
   if (int rc = tc::launch_gemm_tc<64, 4>(ColMN<Col, K>{col}, ColsMN{dy, C},
                                          EpiPartial{ws, K + 1, C}, K + 1, C, Mtot, splits, rps, s))
     return rc;
-  const int blocks = (int)std::min<int64_t>(ceil_div((int64_t)per, 256), 2 * kNumSMs);
-  reduce_wgrad_t_kernel<<<blocks, 256, 0, s>>>(ws, splits, K, C, scale, gw, gb);
+  static_assert(C % 32 == 0, "channel count must be a multiple of 32");
+  reduce_wgrad_t_kernel<<<dim3(K + 1, C / 32), dim3(32, 8), 0, s>>>(
+      ws, splits, K, C, scale, gw, gb);
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
   return ALEGPU_OK;
@@ -401,6 +510,26 @@ int net_tc_forward(const NetParams &P, TcState &T, const uint8_t *obs, int64_t n
                                          EpiBiasReluBf16{act3, P.c3b, 64, 1.0f}, n * 49, 64, 576,
                                          1, 0, s))
     return rc;
+  // FC: with few output tiles (small minibatch) the 3136-long reduction is split over CTAs and
+  // summed in fixed order; otherwise one pass with the bias fused in the epilogue
+  const int64_t tiles64 = ceil_div(n, tc::BM) * ceil_div(H, 64);
+  if (tiles64 * 2 <= kNumSMs && A.fc_ws && (size_t)n * H * 2 <= A.fc_ws_floats) {
+    int splits = (int)std::min<int64_t>({(int64_t)(2 * kNumSMs) / tiles64, (int64_t)(3136 / (2 * tc::BK)),
+                                         (int64_t)(A.fc_ws_floats / ((size_t)n * H))});
+    splits = std::max(splits, 1);
+    const int rps = (int)(ceil_div(ceil_div(3136, splits), tc::BK) * tc::BK);
+    splits = (int)ceil_div(3136, rps);
+    if (int rc = tc::launch_gemm_tc<64, 4>(RowsK{act3, 3136}, RowsK{W.fcw, 3136},
+                                           EpiPartial{A.fc_ws, (int)n, H}, n, H, 3136, splits, rps, s))
+      return rc;
+    const int64_t total4 = n * H / 4;
+    reduce_fc_kernel<<<(unsigned)std::min<int64_t>(ceil_div(total4, 256), 2 * kNumSMs), 256, 0, s>>>(
+        reinterpret_cast<const float4 *>(A.fc_ws), splits, total4, H / 4,
+        reinterpret_cast<const float4 *>(P.fcb), reinterpret_cast<float4 *>(A.fc));
+    ALEGPU_COUNT_LAUNCH();
+    ALEGPU_LAUNCH_CHECK();
+    return ALEGPU_OK;
+  }
   return tc::launch_gemm_tc<128, 3>(RowsK{act3, 3136}, RowsK{W.fcw, 3136},
                                     EpiBiasF32{A.fc, P.fcb, H}, n, H, 3136, 1, 0, s);
 }
@@ -413,8 +542,13 @@ int net_tc_backward(const NetParams &P, const NetParams &G, TcState &T, const ui
   bf16 *act1 = (bf16 *)T.act1, *act2 = (bf16 *)T.act2, *act3 = (bf16 *)T.act3;
   bf16 *dact1 = (bf16 *)T.dact1, *dact2 = (bf16 *)T.dact2, *dact3 = (bf16 *)T.dact3;
   // FC dgrad: dact3 = (dfc . fcw) * relu'(act3)
-  if (int rc = tc::launch_gemm_tc<128, 3>(RowsKF32{A.dfc, H}, ColsMN{W.fcw, 3136},
-                                          EpiReluMaskBf16{dact3, act3, 3136}, n, 3136, H, 1, 0, s))
+  if (ceil_div(n, tc::BM) * 25 < kNumSMs) { // small minibatch: narrower tiles, twice the CTAs
+    if (int rc = tc::launch_gemm_tc<64, 4>(RowsKF32{A.dfc, H}, ColsMN{W.fcw, 3136},
+                                           EpiReluMaskBf16{dact3, act3, 3136}, n, 3136, H, 1, 0, s))
+      return rc;
+  } else if (int rc = tc::launch_gemm_tc<128, 3>(RowsKF32{A.dfc, H}, ColsMN{W.fcw, 3136},
+                                                 EpiReluMaskBf16{dact3, act3, 3136}, n, 3136, H, 1,
+                                                 0, s))
     return rc;
   // FC wgrad: [H][3136 | bias] = dfc^T . [act3 | 1]
   {
@@ -423,13 +557,21 @@ int net_tc_backward(const NetParams &P, const NetParams &G, TcState &T, const ui
     ALEGPU_REQUIRE(ws_floats >= per, ALEGPU_RUNTIME_ERROR, "fc wgrad: workspace too small");
     int splits, rps;
     plan_splits(n, tiles, per, ws_floats, &splits, &rps);
-    if (int rc = tc::launch_gemm_tc<128, 3>(ColsMNF32{A.dfc, H}, ColsMN{act3, 3136},
-                                            EpiPartial{ws, H, 3137}, H, 3137, n, splits, rps, s))
-      return rc;
-    const int blocks = (int)std::min<int64_t>(ceil_div((int64_t)per, 256), 4 * kNumSMs);
-    reduce_wgrad_kernel<<<blocks, 256, 0, s>>>(ws, splits, H, 3136, G.fcw, G.fcb);
-    ALEGPU_COUNT_LAUNCH();
-    ALEGPU_LAUNCH_CHECK();
+    if (n <= 1024)
+      splits = 1, rps = 0; // 100 output tiles already fill the chip; skip the partial round trip
+    if (splits == 1) {
+      if (int rc = tc::launch_gemm_tc<128, 3>(ColsMNF32{A.dfc, H}, ColsMN{act3, 3136},
+                                              EpiWgradDirect{G.fcw, G.fcb, 3136}, H, 3137, n, 1, 0, s))
+        return rc;
+    } else {
+      if (int rc = tc::launch_gemm_tc<128, 3>(ColsMNF32{A.dfc, H}, ColsMN{act3, 3136},
+                                              EpiPartial{ws, H, 3137}, H, 3137, n, splits, rps, s))
+        return rc;
+      const int blocks = (int)std::min<int64_t>(ceil_div((int64_t)per, 256), 4 * kNumSMs);
+      reduce_wgrad_kernel<<<blocks, 256, 0, s>>>(ws, splits, H, 3136, G.fcw, G.fcb);
+      ALEGPU_COUNT_LAUNCH();
+      ALEGPU_LAUNCH_CHECK();
+    }
   }
   // conv3
   if (int rc = tc::launch_gemm_tc<64, 4>(DCol3{dact3}, W3T{W.c3w}, EpiReluMaskBf16{dact2, act2, 64},

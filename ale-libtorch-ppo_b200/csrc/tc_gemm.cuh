@@ -136,45 +136,65 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 }
 
 // ---- tile producer ----------------------------------------------------------------------------------
-// Fill one [ROWS x 64] operand tile.  Loader contract:
-//   K-major  (Op::kMN == false): Op::chunk(row, r, z) -> 8 bf16 = elements (row, r..r+7)
-//   MN-major (Op::kMN == true) : Op::chunk(row0, r, z) -> 8 bf16 = elements (row0..row0+7, r)
+// One thread's share of a [ROWS x 64] operand tile, held in registers between the global gather
+// and the swizzled shared-memory store so that the loads of k-block kb+1 are in flight while
+// k-block kb is stored and consumed.  Loader contract:
+//   K-major  (Op::kMN == false): Op::load(row, r, z)  -> Raw of elements (row, r..r+7)
+//   MN-major (Op::kMN == true) : Op::load(row0, r, z) -> Raw of elements (row0..row0+7, r)
+//   Op::cvt(Raw) -> uint4 of 8 bf16; Op::zero() -> the Raw that converts to eight zeros
 // The loader is only called for row < rows_total and r < r_end; everything else is zero-filled.
-template <int ROWS, class Op>
-__device__ __forceinline__ void produce_tile(const Op &op, uint8_t *tile, int row0, int rows_total,
-                                             int r0, int r_end, int z, int ptid) {
-  constexpr int kChunks = ROWS * 8;
-  constexpr int kPer = (kChunks + kProducerWarps * 32 - 1) / (kProducerWarps * 32);
-  uint4 v[kPer];
-  uint32_t off[kPer];
+__device__ __forceinline__ void sts16(uint32_t addr, const uint4 &v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
+}
+template <int ROWS, class Op> struct TileRegs {
+  static constexpr int kChunks = ROWS * 8;
+  static constexpr int kProducers = kProducerWarps * 32;
+  static constexpr int kPer = (kChunks + kProducers - 1) / kProducers;
+  typename Op::Raw v[kPer]; // as loaded; converted to 8 bf16 only when stored (keeps loads in flight)
+
+  __device__ __forceinline__ void load(const Op &op, int row0, int rows_total, int r0, int r_end,
+                                       int z, int ptid) {
 #pragma unroll
-  for (int it = 0; it < kPer; ++it) {
-    const int q = ptid + it * kProducerWarps * 32;
-    v[it] = make_uint4(0u, 0u, 0u, 0u);
-    off[it] = 0xFFFFFFFFu;
-    if (kChunks % (kProducerWarps * 32) == 0 || q < kChunks) {
-      if constexpr (!Op::kMN) {
-        const int kc = q & 7, il = q >> 3;
-        off[it] = (uint32_t)(il * 128 + ((kc ^ (il & 7)) << 4));
-        const int i = row0 + il, r = r0 + kc * 8;
-        if (i < rows_total && r < r_end)
-          v[it] = op.chunk(i, r, z);
-      } else {
-        constexpr int kRowChunks = ROWS / 8;
-        const int c = q % kRowChunks, k = q / kRowChunks;
-        const int kr = k & 7;
-        off[it] = (uint32_t)((c >> 3) * 8192 + (k >> 3) * 1024 + kr * 128 + (((c & 7) ^ kr) << 4));
-        const int i = row0 + c * 8, r = r0 + k;
-        if (i < rows_total && r < r_end)
-          v[it] = op.chunk(i, r, z);
+    for (int it = 0; it < kPer; ++it) {
+      const int q = ptid + it * kProducers;
+      v[it] = Op::zero();
+      if (kChunks % kProducers == 0 || q < kChunks) {
+        if constexpr (!Op::kMN) {
+          const int kc = q & 7, il = q >> 3;
+          const int i = row0 + il, r = r0 + kc * 8;
+          if (i < rows_total && r < r_end)
+            v[it] = op.load(i, r, z);
+        } else {
+          constexpr int kRowChunks = ROWS / 8;
+          const int c = q % kRowChunks, k = q / kRowChunks;
+          const int i = row0 + c * 8, r = r0 + k;
+          if (i < rows_total && r < r_end)
+            v[it] = op.load(i, r, z);
+        }
       }
     }
   }
+  __device__ __forceinline__ void store(uint32_t tile, int ptid) const {
 #pragma unroll
-  for (int it = 0; it < kPer; ++it)
-    if (off[it] != 0xFFFFFFFFu)
-      *reinterpret_cast<uint4 *>(tile + off[it]) = v[it];
-}
+    for (int it = 0; it < kPer; ++it) {
+      const int q = ptid + it * kProducers;
+      if (kChunks % kProducers == 0 || q < kChunks) {
+        uint32_t off;
+        if constexpr (!Op::kMN) {
+          const int kc = q & 7, il = q >> 3;
+          off = (uint32_t)(il * 128 + ((kc ^ (il & 7)) << 4));
+        } else {
+          constexpr int kRowChunks = ROWS / 8;
+          const int c = q % kRowChunks, k = q / kRowChunks, kr = k & 7;
+          off = (uint32_t)((c >> 3) * 8192 + (k >> 3) * 1024 + kr * 128 + (((c & 7) ^ kr) << 4));
+        }
+        sts16(tile + off, Op::cvt(v[it]));
+      }
+    }
+  }
+};
 
 __host__ __device__ constexpr int tile_bytes(int rows) { return rows * 128; }
 __host__ __device__ constexpr int smem_bytes(int bn, int stages) {
@@ -185,7 +205,7 @@ __host__ __device__ constexpr uint32_t tmem_cols(int bn) { return bn <= 32 ? 32u
 // Epilogue contract: epi(i, j0, v, z) receives 16 consecutive columns j0..j0+15 of row i
 // (only for i < M and j0 < N; columns >= N inside the group must be skipped by the functor).
 template <int BN, int STAGES, class AOp, class BOp, class Epi>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, BN <= 128 ? 2 : 1)
     gemm_tc_kernel(const AOp aop, const BOp bop, const Epi epi, int M, int N, int R,
                    int r_per_split) {
   static_assert(BN % 32 == 0 && BN >= 32 && BN <= 256, "BN must be 32..256, multiple of 32");
@@ -224,20 +244,43 @@ __global__ void __launch_bounds__(kThreads)
   const uint32_t tmem_base = tmem_slot;
 
   if (warp < kProducerWarps) {
-    // ===== producers: gather -> swizzled smem ==================================================
+    // ===== producers: gather -> registers -> swizzled smem (loads run one k-block ahead) ========
     const int ptid = threadIdx.x;
-    for (int kb = 0; kb < nkb; ++kb) {
+    constexpr int kBRows = BN < 64 ? 64 : BN;
+    const uint32_t tiles_s = smem_u32(tiles);
+    constexpr int kPF = 2; // register buffers: loads run kPF-1 k-blocks ahead of the smem stores
+    TileRegs<BM, AOp> ra[kPF];
+    TileRegs<kBRows, BOp> rb[kPF];
+    auto stage_out = [&](int kb, const TileRegs<BM, AOp> &a, const TileRegs<kBRows, BOp> &b) {
       const int s = kb % STAGES;
       const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
       mbar_wait(&empty_bar[s], ph ^ 1u);
-      uint8_t *st = tiles + s * kStage;
-      const int r0 = r_begin + kb * BK;
-      produce_tile<BM>(aop, st, m0, M, r0, r_end, z, ptid);
-      produce_tile<(BN < 64 ? 64 : BN)>(bop, st + kATile, n0, N, r0, r_end, z, ptid);
+      const uint32_t st = tiles_s + (uint32_t)(s * kStage);
+      a.store(st, ptid);
+      b.store(st + kATile, ptid);
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0)
         mbar_arrive(&full_bar[s]);
+    };
+#pragma unroll
+    for (int u = 0; u < kPF - 1; ++u)
+      if (u < nkb) {
+        ra[u].load(aop, m0, M, r_begin + u * BK, r_end, z, ptid);
+        rb[u].load(bop, n0, N, r_begin + u * BK, r_end, z, ptid);
+      }
+    for (int kb0 = 0; kb0 < nkb; kb0 += kPF) {
+#pragma unroll
+      for (int u = 0; u < kPF; ++u) {
+        const int kb = kb0 + u;
+        if (kb < nkb) {
+          if (kb + kPF - 1 < nkb) {
+            ra[(u + kPF - 1) % kPF].load(aop, m0, M, r_begin + (kb + kPF - 1) * BK, r_end, z, ptid);
+            rb[(u + kPF - 1) % kPF].load(bop, n0, N, r_begin + (kb + kPF - 1) * BK, r_end, z, ptid);
+          }
+          stage_out(kb, ra[u], rb[u]);
+        }
+      }
     }
     // ===== epilogue: TMEM -> registers -> fused functor ========================================
     if (nkb > 0) {
@@ -303,7 +346,7 @@ int launch_gemm_tc(const AOp &a, const BOp &b, const Epi &e, int64_t M, int64_t 
   }
   dim3 grid((unsigned)ceil_div(M, BM), (unsigned)ceil_div(N, BN), (unsigned)zdim);
   kern<<<grid, kThreads, kSmem, s>>>(a, b, e, (int)M, (int)N, (int)R, r_per_split);
-  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_COUNT_LAUNCH_NAMED(__PRETTY_FUNCTION__);
   ALEGPU_LAUNCH_CHECK();
   return ALEGPU_OK;
 }

@@ -170,7 +170,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="v0", choices=list(WORKLOADS))
-    ap.add_argument("--math", default=os.environ.get("ALEGPU_MATH", "fp32"), choices=["fp32", "bf16"])
+    ap.add_argument("--math", default=os.environ.get("ALEGPU_MATH", "bf16"), choices=["fp32", "bf16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
     args = ap.parse_args()

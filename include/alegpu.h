@@ -137,6 +137,10 @@ int alegpu_event_synchronize(void *event);
 int alegpu_event_elapsed_ms(void *start, void *stop, float *ms);
 /* kernels launched by this thread through the library so far (bench.py's gpu_launches) */
 int64_t alegpu_launch_count(void);
+/* launch tracer (profiling aid): between _begin and _end a CUDA event follows every kernel launch
+ * this thread makes on `stream`; _end writes "site count total_us" lines, sorted, into out. */
+int alegpu_trace_begin(void *stream);
+int alegpu_trace_end(char *out, size_t out_bytes);
 /* a fresh 128-byte ncclUniqueId (rank 0 creates it, the host broadcasts it) */
 int alegpu_nccl_unique_id(void *out128);
 
