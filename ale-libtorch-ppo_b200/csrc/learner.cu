@@ -183,10 +183,10 @@ int forward(alegpu_learner *L, const uint8_t *obs, int64_t n) {
 }
 
 int backward(alegpu_learner *L, const uint8_t *obs, int64_t n) {
+  if (use_tc(L)) // launches the heads' weight gradients itself, on its side branch
+    return net_tc_backward(L->Pv, L->Gv, L->tc, obs, n, L->acts, L->stream);
   if (int rc = heads_wgrad(L->Gv, L->acts, n, L->ws, L->ws_floats, L->stream))
     return rc;
-  if (use_tc(L))
-    return net_tc_backward(L->Pv, L->Gv, L->tc, obs, n, L->acts, L->ws, L->ws_floats, L->stream);
   return net_f32_backward(L->Pv, L->Gv, obs, n, L->acts, L->ws, L->ws_floats, L->stream);
 }
 

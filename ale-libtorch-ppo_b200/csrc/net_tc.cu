@@ -23,6 +23,7 @@
 // in bf16, so the 1/255 of train.cc:258-259 is applied to the fp32 accumulator in the epilogue.
 // Weight gradients are split over the reduction and summed in fixed order (deterministic).
 #include <algorithm>
+#include <cstdlib>
 #include <vector>
 
 #include "net_tc.h"
@@ -478,14 +479,35 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
   if (int rc = alloc(&T.dact1, sizeof(bf16) * (size_t)cap * 12800)) return rc;
   if (int rc = alloc(&T.dact2, sizeof(bf16) * (size_t)cap * 5184)) return rc;
   if (int rc = alloc(&T.dact3, sizeof(bf16) * (size_t)cap * 3136)) return rc;
+  T.ws_heads_n = (size_t)(actions + 1) * (hidden + 1) * 2 * kNumSMs;
+  T.ws_fc_n = (size_t)hidden * 3137 * 2;
+  T.ws_c3_n = (size_t)577 * 64 * 64;
+  T.ws_c2_n = (size_t)513 * 64 * 64;
+  T.ws_c1_n = (size_t)257 * 32 * 128;
+  if (int rc = alloc((void **)&T.ws_heads, sizeof(float) * T.ws_heads_n)) return rc;
+  if (int rc = alloc((void **)&T.ws_fc, sizeof(float) * T.ws_fc_n)) return rc;
+  if (int rc = alloc((void **)&T.ws_c3, sizeof(float) * T.ws_c3_n)) return rc;
+  if (int rc = alloc((void **)&T.ws_c2, sizeof(float) * T.ws_c2_n)) return rc;
+  if (int rc = alloc((void **)&T.ws_c1, sizeof(float) * T.ws_c1_n)) return rc;
+  ALEGPU_CUDA_CHECK(cudaStreamCreateWithFlags(&T.side, cudaStreamNonBlocking));
+  for (cudaEvent_t *e : {&T.ev_fork, &T.ev_d3, &T.ev_d2, &T.ev_join})
+    ALEGPU_CUDA_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+  const char *env = getenv("ALEGPU_TC_SERIAL");
+  T.serial = env && env[0] == '1';
   return ALEGPU_OK;
 }
 
 void net_tc_destroy(TcState &T) {
   for (void *p : {T.w_shadow, T.act1, T.act2, T.act3, T.dact1, T.dact2, T.dact3, T.fc16, T.dfc16,
-                  T.wt, (void *)T.stage})
+                  T.wt, (void *)T.stage, (void *)T.ws_heads, (void *)T.ws_fc, (void *)T.ws_c3,
+                  (void *)T.ws_c2, (void *)T.ws_c1})
     if (p)
       cudaFree(p);
+  for (cudaEvent_t e : {T.ev_fork, T.ev_d3, T.ev_d2, T.ev_join})
+    if (e)
+      cudaEventDestroy(e);
+  if (T.side)
+    cudaStreamDestroy(T.side);
   T = TcState{};
 }
 
@@ -534,14 +556,45 @@ int net_tc_forward(const NetParams &P, TcState &T, const uint8_t *obs, int64_t n
                                     EpiBiasF32{A.fc, P.fcb, H}, n, H, 3136, 1, 0, s);
 }
 
-// A.dfc [n,H] fp32 is d loss / d fc-output (heads.cu).  Fills every gradient except the heads'.
+// A.dfc [n,H] fp32 is d loss / d fc-output and A.dout the head gradients (heads.cu).  Fills every
+// gradient.  Two branches: the data-gradient chain fc -> conv3 -> conv2 (+ conv1's weight gradient)
+// on `s`, and the other weight gradients on T.side as soon as their inputs exist.
 int net_tc_backward(const NetParams &P, const NetParams &G, TcState &T, const uint8_t *obs,
-                    int64_t n, NetActs &A, float *ws, size_t ws_floats, cudaStream_t s) {
+                    int64_t n, NetActs &A, cudaStream_t s) {
   const int H = (int)P.hidden;
   const Shadow W = shadow_view(T, P);
   bf16 *act1 = (bf16 *)T.act1, *act2 = (bf16 *)T.act2, *act3 = (bf16 *)T.act3;
   bf16 *dact1 = (bf16 *)T.dact1, *dact2 = (bf16 *)T.dact2, *dact3 = (bf16 *)T.dact3;
-  // FC dgrad: dact3 = (dfc . fcw) * relu'(act3)
+  cudaStream_t w = T.serial ? s : T.side;
+  if (!T.serial) {
+    ALEGPU_CUDA_CHECK(cudaEventRecord(T.ev_fork, s));
+    ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(w, T.ev_fork, 0));
+  }
+  // ---- side: heads + FC weight gradients (need only dout / dfc / act3)
+  if (int rc = heads_wgrad(G, A, n, T.ws_heads, T.ws_heads_n, w))
+    return rc;
+  {
+    const int64_t tiles = ceil_div(H, tc::BM) * ceil_div(3137, 128);
+    const size_t per = (size_t)H * 3137;
+    int splits, rps;
+    plan_splits(n, tiles, per, T.ws_fc_n, &splits, &rps);
+    if (n <= 1024)
+      splits = 1, rps = 0; // 100 output tiles already fill the chip; skip the partial round trip
+    if (splits == 1) { // [H][3136 | bias] = dfc^T . [act3 | 1]
+      if (int rc = tc::launch_gemm_tc<128, 3>(ColsMNF32{A.dfc, H}, ColsMN{act3, 3136},
+                                              EpiWgradDirect{G.fcw, G.fcb, 3136}, H, 3137, n, 1, 0, w))
+        return rc;
+    } else {
+      if (int rc = tc::launch_gemm_tc<128, 3>(ColsMNF32{A.dfc, H}, ColsMN{act3, 3136},
+                                              EpiPartial{T.ws_fc, H, 3137}, H, 3137, n, splits, rps, w))
+        return rc;
+      const int blocks = (int)std::min<int64_t>(ceil_div((int64_t)per, 256), 4 * kNumSMs);
+      reduce_wgrad_kernel<<<blocks, 256, 0, w>>>(T.ws_fc, splits, H, 3136, G.fcw, G.fcb);
+      ALEGPU_COUNT_LAUNCH();
+      ALEGPU_LAUNCH_CHECK();
+    }
+  }
+  // ---- main: FC dgrad: dact3 = (dfc . fcw) * relu'(act3)
   if (ceil_div(n, tc::BM) * 25 < kNumSMs) { // small minibatch: narrower tiles, twice the CTAs
     if (int rc = tc::launch_gemm_tc<64, 4>(RowsKF32{A.dfc, H}, ColsMN{W.fcw, 3136},
                                            EpiReluMaskBf16{dact3, act3, 3136}, n, 3136, H, 1, 0, s))
@@ -550,46 +603,39 @@ int net_tc_backward(const NetParams &P, const NetParams &G, TcState &T, const ui
                                                  EpiReluMaskBf16{dact3, act3, 3136}, n, 3136, H, 1,
                                                  0, s))
     return rc;
-  // FC wgrad: [H][3136 | bias] = dfc^T . [act3 | 1]
-  {
-    const int64_t tiles = ceil_div(H, tc::BM) * ceil_div(3137, 128);
-    const size_t per = (size_t)H * 3137;
-    ALEGPU_REQUIRE(ws_floats >= per, ALEGPU_RUNTIME_ERROR, "fc wgrad: workspace too small");
-    int splits, rps;
-    plan_splits(n, tiles, per, ws_floats, &splits, &rps);
-    if (n <= 1024)
-      splits = 1, rps = 0; // 100 output tiles already fill the chip; skip the partial round trip
-    if (splits == 1) {
-      if (int rc = tc::launch_gemm_tc<128, 3>(ColsMNF32{A.dfc, H}, ColsMN{act3, 3136},
-                                              EpiWgradDirect{G.fcw, G.fcb, 3136}, H, 3137, n, 1, 0, s))
-        return rc;
-    } else {
-      if (int rc = tc::launch_gemm_tc<128, 3>(ColsMNF32{A.dfc, H}, ColsMN{act3, 3136},
-                                              EpiPartial{ws, H, 3137}, H, 3137, n, splits, rps, s))
-        return rc;
-      const int blocks = (int)std::min<int64_t>(ceil_div((int64_t)per, 256), 4 * kNumSMs);
-      reduce_wgrad_kernel<<<blocks, 256, 0, s>>>(ws, splits, H, 3136, G.fcw, G.fcb);
-      ALEGPU_COUNT_LAUNCH();
-      ALEGPU_LAUNCH_CHECK();
-    }
+  if (!T.serial) {
+    ALEGPU_CUDA_CHECK(cudaEventRecord(T.ev_d3, s));
+    ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(w, T.ev_d3, 0));
   }
-  // conv3
+  // ---- side: conv3 wgrad (needs dact3)
+  if (int rc = conv_wgrad<Col3, 576, 64>(Col3{act2}, dact3, n * 49, 1.0f, G.c3w, G.c3b, T.ws_c3,
+                                         T.ws_c3_n, w))
+    return rc;
+  // ---- main: conv3 dgrad
   if (int rc = tc::launch_gemm_tc<64, 4>(DCol3{dact3}, W3T{W.c3w}, EpiReluMaskBf16{dact2, act2, 64},
                                          n * 81, 64, 576, 1, 0, s))
     return rc;
-  if (int rc = conv_wgrad<Col3, 576, 64>(Col3{act2}, dact3, n * 49, 1.0f, G.c3w, G.c3b, ws,
-                                         ws_floats, s))
+  if (!T.serial) {
+    ALEGPU_CUDA_CHECK(cudaEventRecord(T.ev_d2, s));
+    ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(w, T.ev_d2, 0));
+  }
+  // ---- side: conv2 wgrad (needs dact2)
+  if (int rc = conv_wgrad<Col2, 512, 64>(Col2{act1}, dact2, n * 81, 1.0f, G.c2w, G.c2b, T.ws_c2,
+                                         T.ws_c2_n, w))
     return rc;
-  // conv2 (4 parity classes of the stride-2 transposed convolution in one launch)
+  if (!T.serial)
+    ALEGPU_CUDA_CHECK(cudaEventRecord(T.ev_join, w));
+  // ---- main: conv2 dgrad (4 parity classes of the stride-2 transposed convolution in one launch)
   if (int rc = tc::launch_gemm_tc<64, 4>(DCol2{dact2}, W2T{W.c2w}, EpiReluMaskConv2{dact1, act1},
                                          n * 100, 32, 256, 4, 0, s))
     return rc;
-  if (int rc = conv_wgrad<Col2, 512, 64>(Col2{act1}, dact2, n * 81, 1.0f, G.c2w, G.c2b, ws,
-                                         ws_floats, s))
-    return rc;
   // conv1 (input needs no gradient); the 1/255 of the input scale lands on the weight gradient
-  return conv_wgrad<Col1, 256, 32>(Col1{obs}, dact1, n * 400, 1.0f / 255.0f, G.c1w, G.c1b, ws,
-                                   ws_floats, s);
+  if (int rc = conv_wgrad<Col1, 256, 32>(Col1{obs}, dact1, n * 400, 1.0f / 255.0f, G.c1w, G.c1b,
+                                         T.ws_c1, T.ws_c1_n, s))
+    return rc;
+  if (!T.serial)
+    ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(s, T.ev_join, 0));
+  return ALEGPU_OK;
 }
 
 int net_tc_fetch_activation(TcState &T, int which, int64_t n, float *host, cudaStream_t s) {

@@ -12,6 +12,14 @@ struct TcState {
   void *fc16 = nullptr, *dfc16 = nullptr;                    // bf16 copies of fc in/out grads
   void *wt = nullptr;        // bf16 re-laid-out weights for dgrad
   float *stage = nullptr;    // fp32 staging for get_activations
+  // weight-gradient branch: runs on its own stream next to the data-gradient chain (fork/join
+  // with events, so it also becomes a parallel branch of a captured CUDA graph); every wgrad
+  // has its own split-partials workspace because they may be in flight together
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_d3 = nullptr, ev_d2 = nullptr, ev_join = nullptr;
+  float *ws_heads = nullptr, *ws_fc = nullptr, *ws_c3 = nullptr, *ws_c2 = nullptr, *ws_c1 = nullptr;
+  size_t ws_heads_n = 0, ws_fc_n = 0, ws_c3_n = 0, ws_c2_n = 0, ws_c1_n = 0;
+  bool serial = false;       // ALEGPU_TC_SERIAL=1: keep everything on one stream (profiling)
 };
 
 int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_t Ppad,
@@ -20,8 +28,9 @@ void net_tc_destroy(TcState &T);
 int net_tc_refresh_weights(TcState &T, const float *params, int64_t Ppad, cudaStream_t s);
 int net_tc_forward(const NetParams &P, TcState &T, const uint8_t *obs, int64_t n, NetActs &A,
                    cudaStream_t s);
+// includes the heads' weight gradients (heads_wgrad) — the caller must not launch them again
 int net_tc_backward(const NetParams &P, const NetParams &G, TcState &T, const uint8_t *obs,
-                    int64_t n, NetActs &A, float *ws, size_t ws_floats, cudaStream_t s);
+                    int64_t n, NetActs &A, cudaStream_t s);
 int net_tc_fetch_activation(TcState &T, int which, int64_t n, float *host, cudaStream_t s);
 
 } // namespace alegpu
