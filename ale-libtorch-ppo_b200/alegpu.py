@@ -128,6 +128,13 @@ class DeviceArray:
         """Sub-view starting `offset_elems` elements in (no copy)."""
         return DeviceArray(shape, self.dtype, self.ptr + offset_elems * self.dtype.itemsize, self)
 
+    def close(self):
+        """Destroy the learner now (NCCL communicator included); with world_size > 1 every rank
+        must call this at the same point of the program."""
+        if getattr(self, "h", None) and _lib is not None:
+            _lib.alegpu_learner_destroy(self.h)
+            self.h = None
+
     def __del__(self):
         if getattr(self, "_owned", False) and getattr(self, "ptr", None) and _lib is not None:
             _lib.alegpu_free(C.c_void_p(self.ptr))

@@ -15,6 +15,8 @@
 // 35 input rows = one contiguous 16 800 B span of each frame, read with 16-byte streaming
 // loads (10 in flight per thread), max'ed with vmaxu4, column-summed with packed-u16
 // arithmetic in registers and staged in shared memory for the horizontal pass.
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace alegpu {
@@ -154,37 +156,192 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
-// ---- whole rollout, frames resident ---------------------------------------------------------
-// plane p of slot s holds the frame of step s-1-p unless a reset-fill happened in between;
-// so the tile of step t goes to slot t+1+d plane d (d = 0..3) until a later reset overwrites
-// the stack, and if step t itself was a reset it also fills the older planes d..3.
-__global__ void __launch_bounds__(kThreads)
-    preprocess_rollout_kernel(const uint8_t *__restrict__ frames,
-                              const uint8_t *__restrict__ starts, uint8_t *__restrict__ carry_out,
-                              uint8_t *__restrict__ obs, int64_t E, int64_t T) {
-  __shared__ GroupSmem sm;
-  const int64_t lin = blockIdx.x;
-  const int g = (int)(lin % kGroups);
-  const int64_t et = lin / kGroups; // time-major frame index t*E + e
-  const int64_t t = et / E, e = et - t * E;
-  const uint8_t *fa = frames + (size_t)et * 2 * kFrameBytes;
-  gray_tile(fa, fa + kFrameBytes, g, sm, nullptr);
-  const uint8_t *st = starts + e * T;
-  const bool reset_t = st[t] != 0;
+// ---- whole rollout, persistent + bulk-async pipeline ----------------------------------------------
+// plane p of slot s holds the frame of step s-1-p unless a reset-fill happened in between; so the
+// tile of step t goes to slot t+1+d plane d (d = 0..3) until a later reset overwrites the stack,
+// and if step t itself was a reset it also fills the older planes d..3.
+// Work items = (frame pair, band group), as in the step kernel, but each CTA stays
+// resident and walks items blockIdx.x, +gridDim.x, ...: one thread streams the two contiguous
+// 16 800-byte input spans of the NEXT item into shared memory with cp.async.bulk (TMA bulk copy,
+// completion on an mbarrier) while all threads reduce the current one, so HBM reads never wait for
+// the arithmetic and cost no registers.  2 CTAs per SM x 2 stages = 134 KB of loads in flight per SM.
+constexpr int kSpan = 35 * kRowBytes; // 16 800 bytes of one frame per band group
+
+struct PipeSmem {
+  alignas(128) uint8_t in[2][2][kSpan]; // [stage][frame a|b]
+  alignas(16) uint16_t sums[kOutRowsPerGroup][kRowBytes];
+  alignas(16) uint8_t out[kGroupOut + 8];
+  alignas(8) uint64_t full[2];
+};
+
+__device__ __forceinline__ uint32_t smem_addr(const void *p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void bulk_load(uint32_t dst, const void *src, uint32_t bytes,
+                                          uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ uint4 lds16(uint32_t addr) {
+  uint4 r;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "r"(addr));
+  return r;
+}
+// x / 3 correctly rounded for the finite operand set of this kernel (integer sums <= 2295 and their
+// thirds): q0 = x*(1/3), one residual correction; verified exhaustively against IEEE division.
+__device__ __forceinline__ float div3_exact(float x) {
+  const float r3 = 0.333333343267440796f; // fl(1/3)
+  const float q0 = __fmul_rn(x, r3);
+  return __fmaf_rn(__fmaf_rn(-3.0f, q0, x), r3, q0);
+}
+
+__global__ void __launch_bounds__(kThreads, 2)
+    preprocess_rollout_pipe_kernel(const uint8_t *__restrict__ frames,
+                                   const uint8_t *__restrict__ starts,
+                                   uint8_t *__restrict__ carry_out, uint8_t *__restrict__ obs,
+                                   int64_t E, int64_t T) {
+  extern __shared__ __align__(128) uint8_t pipe_raw[];
+  PipeSmem &sm = *reinterpret_cast<PipeSmem *>(pipe_raw);
   const int tid = threadIdx.x;
-  for (int d = 0; d < 4; ++d) {
-    const int64_t s = t + 1 + d;
-    if (s > T)
-      break;
-    if (d >= 1 && st[t + d])
-      break;
-    uint8_t *base = (s == T) ? carry_out + e * kStack : obs + (size_t)(e * T + s) * kStack;
-    if (reset_t) {
-      for (int i = tid; i < (4 - d) * 147; i += kThreads)
-        store_tile(base + (d + i / 147) * kPlane, g, sm, i % 147);
-    } else {
-      store_tile(base + d * kPlane, g, sm, tid);
+  const int64_t nitems = E * T * kGroups;
+  if (tid == 0) {
+    for (int i = 0; i < 2; ++i)
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&sm.full[i])));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  auto issue = [&](int64_t item, int stage) {
+    const int g = (int)(item % kGroups);
+    const int64_t et = item / kGroups;
+    const uint8_t *fa = frames + (size_t)et * 2 * kFrameBytes + (size_t)g * kSpan;
+    const uint32_t bar = smem_addr(&sm.full[stage]);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar),
+                 "r"(2u * kSpan)
+                 : "memory");
+    bulk_load(smem_addr(&sm.in[stage][0][0]), fa, kSpan, bar);
+    bulk_load(smem_addr(&sm.in[stage][1][0]), fa + kFrameBytes, kSpan, bar);
+  };
+  int64_t item = blockIdx.x;
+  if (tid == 0 && item < nitems)
+    issue(item, 0);
+  // phase-2 geometry of this thread: one output column, rows rg, rg+3, ...
+  const int ox = tid % 84, rg = tid / 84;
+  const int x0 = (ox * 160) / 84, x1 = ((ox + 1) * 160 + 83) / 84;
+  const bool three = (x1 - x0) == 3;
+  for (int k = 0; item < nitems; ++k, item += gridDim.x) {
+    const int stage = k & 1;
+    const int64_t next = item + gridDim.x;
+    if (tid == 0 && next < nitems)
+      issue(next, stage ^ 1); // that stage was fully consumed before the barriers of iteration k-1
+    {
+      const uint32_t bar = smem_addr(&sm.full[stage]), parity = (uint32_t)(k >> 1) & 1u;
+      asm volatile("{\n\t.reg .pred p;\n\tW_%=:\n\t"
+                   "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+                   "@p bra D_%=;\n\tbra W_%=;\n\tD_%=:\n\t}" ::"r"(bar),
+                   "r"(parity)
+                   : "memory");
     }
+    // ---- phase 1: 2-frame max + vertical 3-row sums, 16 bytes of one band per thread
+    if (tid < kBandsPerGroup * 30) {
+      const int band = tid / 30, chunk = tid % 30;
+      const uint32_t off = (uint32_t)(5 * band * kRowBytes + 16 * chunk);
+      const uint32_t pa = smem_addr(&sm.in[stage][0][0]) + off, pb = smem_addr(&sm.in[stage][1][0]) + off;
+      uint32_t top_lo[4], top_hi[4], bot_lo[4], bot_hi[4];
+#pragma unroll
+      for (int w = 0; w < 4; ++w)
+        top_lo[w] = top_hi[w] = bot_lo[w] = bot_hi[w] = 0u;
+#pragma unroll
+      for (int r = 0; r < 5; ++r) {
+        const uint4 a = lds16(pa + r * kRowBytes), b = lds16(pb + r * kRowBytes);
+        const uint32_t wa[4] = {a.x, a.y, a.z, a.w};
+        const uint32_t wb[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+          const uint32_t m = __vmaxu4(wa[w], wb[w]); // max_and_skip.cc:36-38, exact
+          const uint32_t lo = m & 0x00FF00FFu, hi = (m >> 8) & 0x00FF00FFu;
+          if (r <= 2) {
+            top_lo[w] += lo;
+            top_hi[w] += hi;
+          }
+          if (r >= 2) {
+            bot_lo[w] += lo;
+            bot_hi[w] += hi;
+          }
+        }
+      }
+      uint32_t t[8], bt[8];
+#pragma unroll
+      for (int w = 0; w < 4; ++w) {
+        t[2 * w] = __byte_perm(top_lo[w], top_hi[w], 0x5410);
+        t[2 * w + 1] = __byte_perm(top_lo[w], top_hi[w], 0x7632);
+        bt[2 * w] = __byte_perm(bot_lo[w], bot_hi[w], 0x5410);
+        bt[2 * w + 1] = __byte_perm(bot_lo[w], bot_hi[w], 0x7632);
+      }
+      uint4 *dt = reinterpret_cast<uint4 *>(&sm.sums[2 * band][16 * chunk]);
+      uint4 *db = reinterpret_cast<uint4 *>(&sm.sums[2 * band + 1][16 * chunk]);
+      dt[0] = make_uint4(t[0], t[1], t[2], t[3]);
+      dt[1] = make_uint4(t[4], t[5], t[6], t[7]);
+      db[0] = make_uint4(bt[0], bt[1], bt[2], bt[3]);
+      db[1] = make_uint4(bt[4], bt[5], bt[6], bt[7]);
+    }
+    __syncthreads();
+    // ---- phase 2: horizontal bins, mean, luminance, round to u8 (bit-identical to the oracle)
+    if (tid < 252) {
+      for (int orow = rg; orow < kOutRowsPerGroup; orow += 3) {
+        const uint16_t *row = &sm.sums[orow][3 * x0];
+        uint32_t s0 = (uint32_t)row[0] + row[3], s1 = (uint32_t)row[1] + row[4],
+                 s2 = (uint32_t)row[2] + row[5];
+        if (three) {
+          s0 += row[6];
+          s1 += row[7];
+          s2 += row[8];
+        }
+        float m0 = div3_exact((float)s0), m1 = div3_exact((float)s1), m2 = div3_exact((float)s2);
+        if (three) {
+          m0 = div3_exact(m0);
+          m1 = div3_exact(m1);
+          m2 = div3_exact(m2);
+        } else {
+          m0 = __fmul_rn(m0, 0.5f);
+          m1 = __fmul_rn(m1, 0.5f);
+          m2 = __fmul_rn(m2, 0.5f);
+        }
+        float gr = __fmul_rn(0.2125f, m0);
+        gr = __fadd_rn(gr, __fmul_rn(0.7154f, m1));
+        gr = __fadd_rn(gr, __fmul_rn(0.0721f, m2)); // vision.cc:80, no fma contraction
+        float q = floorf(__fadd_rn(gr, 0.5f));
+        q = fminf(fmaxf(q, 0.0f), 255.0f);
+        sm.out[orow * 84 + ox] = (uint8_t)q;
+      }
+    }
+    __syncthreads();
+    // ---- phase 3: the tile of step t is plane d of slot t+1+d until a reset overwrites the stack
+    {
+      const int g = (int)(item % kGroups);
+      const int64_t et = item / kGroups;
+      const int64_t t = et / E, e = et - t * E;
+      const uint8_t *st = starts + e * T;
+      const bool reset_t = st[t] != 0;
+      for (int d = 0; d < 4; ++d) {
+        const int64_t slot = t + 1 + d;
+        if (slot > T)
+          break;
+        if (d >= 1 && st[t + d])
+          break;
+        uint8_t *base = (slot == T) ? carry_out + e * kStack : obs + (size_t)(e * T + slot) * kStack;
+        const int nplanes = reset_t ? 4 - d : 1;
+        for (int i = tid; i < nplanes * 147; i += kThreads) {
+          const int pl = d + i / 147, l = i % 147;
+          const uint2 v = *reinterpret_cast<const uint2 *>(&sm.out[8 * l]);
+          st_stream_u2(base + pl * kPlane + kGroupOut * g + 8 * l, v);
+        }
+      }
+    }
+    // the next iteration's phase 1 only writes sm.sums (last read before the barrier above) and its
+    // phase 2 writes sm.out after another barrier, so no extra synchronisation is needed here
   }
 }
 
@@ -286,8 +443,19 @@ extern "C" int alegpu_preprocess_rollout(const uint8_t *frames, const uint8_t *e
       carry_in, episode_starts, carry_out, obs, T);
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
-  preprocess_rollout_kernel<<<(unsigned)(E * T * kGroups), kThreads, 0, as_stream(stream)>>>(
-      frames, episode_starts, carry_out, obs, E, T);
+  {
+    constexpr int kPipeSmem = (int)sizeof(PipeSmem) + 128;
+    static bool configured = false;
+    if (!configured) {
+      ALEGPU_CUDA_CHECK(cudaFuncSetAttribute(preprocess_rollout_pipe_kernel,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, kPipeSmem));
+      configured = true;
+    }
+    const int64_t items = E * T * kGroups;
+    const unsigned grid = (unsigned)std::min<int64_t>(items, 2 * kNumSMs);
+    preprocess_rollout_pipe_kernel<<<grid, kThreads, kPipeSmem, as_stream(stream)>>>(
+        frames, episode_starts, carry_out, obs, E, T);
+  }
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
   return ALEGPU_OK;

@@ -352,10 +352,16 @@ def main():
     d2h = loss_host.nbytes + gn_host.nbytes
     assert np.isfinite(loss_host).all() and np.isfinite(gn_host).all(), "non-finite metrics"
 
+    # tear the communicators down on every rank at the same point, before rank 0 goes on alone
+    if dist is not None:
+        alegpu.synchronize(stream)
+        dist.barrier()
+        L.close()
+        dist.barrier()
+        dist.destroy_process_group()
     if rank != 0:
-        if dist is not None:
-            dist.destroy_process_group()
-        return
+        sys.stdout.flush()
+        os._exit(0)
     hbm, tflops, which = peaks()
     pre = float(np.median(pre_ms)) if pre_ms else None
     roof = None
@@ -386,8 +392,9 @@ def main():
             line["cpu_baseline"] = {"value": None, "unit": "agent-steps/s", "cores": threads,
                                     "kind": "reference", "sample": desc}
     print(json.dumps(line))
-    if dist is not None:
-        dist.destroy_process_group()
+    sys.stdout.flush()
+    if world > 1:
+        os._exit(0)  # never linger in interpreter teardown with NCCL state around
 
 
 if __name__ == "__main__":
