@@ -163,15 +163,16 @@ __global__ void __launch_bounds__(kThreads)
 // Work items = (frame pair, band group), as in the step kernel, but each CTA stays
 // resident and walks items blockIdx.x, +gridDim.x, ...: one thread streams the two contiguous
 // 16 800-byte input spans of the NEXT item into shared memory with cp.async.bulk (TMA bulk copy,
-// completion on an mbarrier) while all threads reduce the current one, so HBM reads never wait for
-// the arithmetic and cost no registers.  2 CTAs per SM x 2 stages = 134 KB of loads in flight per SM.
+// completion on an mbarrier) as soon as the current one has been reduced to column sums, so the
+// copy overlaps the horizontal pass and the stores and costs no registers.  4 CTAs per SM keep up to
+// 134 KB of loads in flight per SM and 32 warps to hide the shared-memory latencies.
 constexpr int kSpan = 35 * kRowBytes; // 16 800 bytes of one frame per band group
 
 struct PipeSmem {
-  alignas(128) uint8_t in[2][2][kSpan]; // [stage][frame a|b]
+  alignas(128) uint8_t in[2][kSpan]; // [frame a|b]
   alignas(16) uint16_t sums[kOutRowsPerGroup][kRowBytes];
   alignas(16) uint8_t out[kGroupOut + 8];
-  alignas(8) uint64_t full[2];
+  alignas(8) uint64_t full;
 };
 
 __device__ __forceinline__ uint32_t smem_addr(const void *p) {
@@ -198,46 +199,68 @@ __device__ __forceinline__ float div3_exact(float x) {
   return __fmaf_rn(__fmaf_rn(-3.0f, q0, x), r3, q0);
 }
 
-__global__ void __launch_bounds__(kThreads, 2)
+// slots 0..3 inherit planes from the stack carried over from the previous rollout (task = (env, group))
+__device__ __forceinline__ void carry_in_task(const uint8_t *__restrict__ carry_in,
+                                              const uint8_t *__restrict__ starts,
+                                              uint8_t *__restrict__ carry_out,
+                                              uint8_t *__restrict__ obs, int64_t T, int64_t e, int g,
+                                              int tid) {
+  const uint8_t *src = carry_in + e * kStack + kGroupOut * g;
+  const uint8_t *st = starts + e * T;
+  for (int s = 0; s < 4; ++s) {
+    if (s > T)
+      break;
+    if (s >= 1 && st[s - 1])
+      break;
+    uint8_t *base =
+        ((s == T) ? carry_out + e * kStack : obs + (size_t)(e * T + s) * kStack) + kGroupOut * g;
+    for (int i = tid; i < (4 - s) * 147; i += kThreads) {
+      const int p = s + i / 147, l = i % 147;
+      const uint2 v = ld_stream_u2(src + (p - s) * kPlane + 8 * l);
+      st_stream_u2(base + p * kPlane + 8 * l, v);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 4)
     preprocess_rollout_pipe_kernel(const uint8_t *__restrict__ frames,
                                    const uint8_t *__restrict__ starts,
+                                   const uint8_t *__restrict__ carry_in,
                                    uint8_t *__restrict__ carry_out, uint8_t *__restrict__ obs,
                                    int64_t E, int64_t T) {
   extern __shared__ __align__(128) uint8_t pipe_raw[];
   PipeSmem &sm = *reinterpret_cast<PipeSmem *>(pipe_raw);
   const int tid = threadIdx.x;
-  const int64_t nitems = E * T * kGroups;
+  const uint32_t nitems = (uint32_t)(E * T * kGroups), E32 = (uint32_t)E; // < 2^31 (checked by the host)
   if (tid == 0) {
-    for (int i = 0; i < 2; ++i)
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&sm.full[i])));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&sm.full)));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  auto issue = [&](int64_t item, int stage) {
-    const int g = (int)(item % kGroups);
-    const int64_t et = item / kGroups;
+  auto issue = [&](uint32_t item) {
+    const uint32_t et = item / kGroups, g = item - et * kGroups;
     const uint8_t *fa = frames + (size_t)et * 2 * kFrameBytes + (size_t)g * kSpan;
-    const uint32_t bar = smem_addr(&sm.full[stage]);
+    const uint32_t bar = smem_addr(&sm.full);
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar),
                  "r"(2u * kSpan)
                  : "memory");
-    bulk_load(smem_addr(&sm.in[stage][0][0]), fa, kSpan, bar);
-    bulk_load(smem_addr(&sm.in[stage][1][0]), fa + kFrameBytes, kSpan, bar);
+    bulk_load(smem_addr(&sm.in[0][0]), fa, kSpan, bar);
+    bulk_load(smem_addr(&sm.in[1][0]), fa + kFrameBytes, kSpan, bar);
   };
-  int64_t item = blockIdx.x;
+  uint32_t item = blockIdx.x;
   if (tid == 0 && item < nitems)
-    issue(item, 0);
+    issue(item);
+  // while the first item streams in: the planes inherited from the previous rollout (they never
+  // coincide with a plane written from this rollout's frames, so no ordering is needed)
+  for (uint32_t task = blockIdx.x; task < E32 * kGroups; task += gridDim.x)
+    carry_in_task(carry_in, starts, carry_out, obs, T, task / kGroups, (int)(task % kGroups), tid);
   // phase-2 geometry of this thread: one output column, rows rg, rg+3, ...
   const int ox = tid % 84, rg = tid / 84;
   const int x0 = (ox * 160) / 84, x1 = ((ox + 1) * 160 + 83) / 84;
   const bool three = (x1 - x0) == 3;
   for (int k = 0; item < nitems; ++k, item += gridDim.x) {
-    const int stage = k & 1;
-    const int64_t next = item + gridDim.x;
-    if (tid == 0 && next < nitems)
-      issue(next, stage ^ 1); // that stage was fully consumed before the barriers of iteration k-1
     {
-      const uint32_t bar = smem_addr(&sm.full[stage]), parity = (uint32_t)(k >> 1) & 1u;
+      const uint32_t bar = smem_addr(&sm.full), parity = (uint32_t)k & 1u;
       asm volatile("{\n\t.reg .pred p;\n\tW_%=:\n\t"
                    "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
                    "@p bra D_%=;\n\tbra W_%=;\n\tD_%=:\n\t}" ::"r"(bar),
@@ -248,7 +271,8 @@ __global__ void __launch_bounds__(kThreads, 2)
     if (tid < kBandsPerGroup * 30) {
       const int band = tid / 30, chunk = tid % 30;
       const uint32_t off = (uint32_t)(5 * band * kRowBytes + 16 * chunk);
-      const uint32_t pa = smem_addr(&sm.in[stage][0][0]) + off, pb = smem_addr(&sm.in[stage][1][0]) + off;
+      const uint32_t pa = smem_addr(&sm.in[0][0]) + off, pb = smem_addr(&sm.in[1][0]) + off;
+      // packed u16 column sums in natural byte order: lo = (b0,b1), hi = (b2,b3) of each word
       uint32_t top_lo[4], top_hi[4], bot_lo[4], bot_hi[4];
 #pragma unroll
       for (int w = 0; w < 4; ++w)
@@ -261,7 +285,7 @@ __global__ void __launch_bounds__(kThreads, 2)
 #pragma unroll
         for (int w = 0; w < 4; ++w) {
           const uint32_t m = __vmaxu4(wa[w], wb[w]); // max_and_skip.cc:36-38, exact
-          const uint32_t lo = m & 0x00FF00FFu, hi = (m >> 8) & 0x00FF00FFu;
+          const uint32_t lo = __byte_perm(m, 0u, 0x4140), hi = __byte_perm(m, 0u, 0x4342);
           if (r <= 2) {
             top_lo[w] += lo;
             top_hi[w] += hi;
@@ -272,57 +296,53 @@ __global__ void __launch_bounds__(kThreads, 2)
           }
         }
       }
-      uint32_t t[8], bt[8];
-#pragma unroll
-      for (int w = 0; w < 4; ++w) {
-        t[2 * w] = __byte_perm(top_lo[w], top_hi[w], 0x5410);
-        t[2 * w + 1] = __byte_perm(top_lo[w], top_hi[w], 0x7632);
-        bt[2 * w] = __byte_perm(bot_lo[w], bot_hi[w], 0x5410);
-        bt[2 * w + 1] = __byte_perm(bot_lo[w], bot_hi[w], 0x7632);
-      }
       uint4 *dt = reinterpret_cast<uint4 *>(&sm.sums[2 * band][16 * chunk]);
       uint4 *db = reinterpret_cast<uint4 *>(&sm.sums[2 * band + 1][16 * chunk]);
-      dt[0] = make_uint4(t[0], t[1], t[2], t[3]);
-      dt[1] = make_uint4(t[4], t[5], t[6], t[7]);
-      db[0] = make_uint4(bt[0], bt[1], bt[2], bt[3]);
-      db[1] = make_uint4(bt[4], bt[5], bt[6], bt[7]);
+      dt[0] = make_uint4(top_lo[0], top_hi[0], top_lo[1], top_hi[1]);
+      dt[1] = make_uint4(top_lo[2], top_hi[2], top_lo[3], top_hi[3]);
+      db[0] = make_uint4(bot_lo[0], bot_hi[0], bot_lo[1], bot_hi[1]);
+      db[1] = make_uint4(bot_lo[2], bot_hi[2], bot_lo[3], bot_hi[3]);
     }
     __syncthreads();
+    { // the input buffer is consumed: stream the next item in while phases 2-3 run
+      const uint32_t next = item + gridDim.x;
+      if (tid == 0 && next < nitems)
+        issue(next);
+    }
     // ---- phase 2: horizontal bins, mean, luminance, round to u8 (bit-identical to the oracle)
     if (tid < 252) {
-      for (int orow = rg; orow < kOutRowsPerGroup; orow += 3) {
-        const uint16_t *row = &sm.sums[orow][3 * x0];
-        uint32_t s0 = (uint32_t)row[0] + row[3], s1 = (uint32_t)row[1] + row[4],
-                 s2 = (uint32_t)row[2] + row[5];
-        if (three) {
-          s0 += row[6];
-          s1 += row[7];
-          s2 += row[8];
+      // branch-free in the bin width (2 or 3 columns) so that a warp never diverges
+      const uint16_t *col = &sm.sums[rg][3 * x0];
+      const int o3 = three ? 6 : 0; // a 2-wide bin re-reads column 0 and masks it out
+      const uint32_t keep = three ? 0xFFFFFFFFu : 0u;
+#pragma unroll
+      for (int j = 0; j < 5; ++j) {
+        const int orow = rg + 3 * j;
+        if (orow < kOutRowsPerGroup) {
+          const uint16_t *row = col + j * 3 * kRowBytes;
+          const uint32_t s0 = (uint32_t)row[0] + row[3] + (row[o3] & keep);
+          const uint32_t s1 = (uint32_t)row[1] + row[4] + (row[o3 + 1] & keep);
+          const uint32_t s2 = (uint32_t)row[2] + row[5] + (row[o3 + 2] & keep);
+          float m0 = div3_exact((float)s0), m1 = div3_exact((float)s1), m2 = div3_exact((float)s2);
+          const float h0 = __fmul_rn(m0, 0.5f), h1 = __fmul_rn(m1, 0.5f), h2 = __fmul_rn(m2, 0.5f);
+          const float t0 = div3_exact(m0), t1 = div3_exact(m1), t2 = div3_exact(m2);
+          m0 = three ? t0 : h0;
+          m1 = three ? t1 : h1;
+          m2 = three ? t2 : h2;
+          float gr = __fmul_rn(0.2125f, m0);
+          gr = __fadd_rn(gr, __fmul_rn(0.7154f, m1));
+          gr = __fadd_rn(gr, __fmul_rn(0.0721f, m2)); // vision.cc:80, no fma contraction
+          // 0 <= gr <= 255 (the weights sum to 1), so floor(gr + .5) needs no clamp
+          sm.out[orow * 84 + ox] = (uint8_t)__float2uint_rd(__fadd_rn(gr, 0.5f));
         }
-        float m0 = div3_exact((float)s0), m1 = div3_exact((float)s1), m2 = div3_exact((float)s2);
-        if (three) {
-          m0 = div3_exact(m0);
-          m1 = div3_exact(m1);
-          m2 = div3_exact(m2);
-        } else {
-          m0 = __fmul_rn(m0, 0.5f);
-          m1 = __fmul_rn(m1, 0.5f);
-          m2 = __fmul_rn(m2, 0.5f);
-        }
-        float gr = __fmul_rn(0.2125f, m0);
-        gr = __fadd_rn(gr, __fmul_rn(0.7154f, m1));
-        gr = __fadd_rn(gr, __fmul_rn(0.0721f, m2)); // vision.cc:80, no fma contraction
-        float q = floorf(__fadd_rn(gr, 0.5f));
-        q = fminf(fmaxf(q, 0.0f), 255.0f);
-        sm.out[orow * 84 + ox] = (uint8_t)q;
       }
     }
     __syncthreads();
     // ---- phase 3: the tile of step t is plane d of slot t+1+d until a reset overwrites the stack
     {
-      const int g = (int)(item % kGroups);
-      const int64_t et = item / kGroups;
-      const int64_t t = et / E, e = et - t * E;
+      const uint32_t et = item / kGroups, g = item - et * kGroups;
+      const uint32_t t32 = et / E32;
+      const int64_t t = t32, e = et - t32 * E32;
       const uint8_t *st = starts + e * T;
       const bool reset_t = st[t] != 0;
       for (int d = 0; d < 4; ++d) {
@@ -342,31 +362,6 @@ __global__ void __launch_bounds__(kThreads, 2)
     }
     // the next iteration's phase 1 only writes sm.sums (last read before the barrier above) and its
     // phase 2 writes sm.out after another barrier, so no extra synchronisation is needed here
-  }
-}
-
-// slots 0..3 inherit planes from the stack carried over from the previous rollout
-__global__ void __launch_bounds__(kThreads)
-    preprocess_carry_in_kernel(const uint8_t *__restrict__ carry_in,
-                               const uint8_t *__restrict__ starts, uint8_t *__restrict__ carry_out,
-                               uint8_t *__restrict__ obs, int64_t T) {
-  const int g = blockIdx.x;
-  const int64_t e = blockIdx.y;
-  const uint8_t *src = carry_in + e * kStack + kGroupOut * g;
-  const uint8_t *st = starts + e * T;
-  const int tid = threadIdx.x;
-  for (int s = 0; s < 4; ++s) {
-    if (s > T)
-      break;
-    if (s >= 1 && st[s - 1])
-      break;
-    uint8_t *base =
-        ((s == T) ? carry_out + e * kStack : obs + (size_t)(e * T + s) * kStack) + kGroupOut * g;
-    for (int i = tid; i < (4 - s) * 147; i += kThreads) {
-      const int p = s + i / 147, l = i % 147;
-      const uint2 v = ld_stream_u2(src + (p - s) * kPlane + 8 * l);
-      st_stream_u2(base + p * kPlane + 8 * l, v);
-    }
   }
 }
 
@@ -439,10 +434,6 @@ extern "C" int alegpu_preprocess_rollout(const uint8_t *frames, const uint8_t *e
                  ALEGPU_INVALID_ARGUMENT, "preprocess_rollout: misaligned pointer");
   ALEGPU_REQUIRE(E * T * kGroups < (int64_t)2147483647, ALEGPU_INVALID_ARGUMENT,
                  "preprocess_rollout: E*T too large for one launch");
-  preprocess_carry_in_kernel<<<dim3(kGroups, (unsigned)E), kThreads, 0, as_stream(stream)>>>(
-      carry_in, episode_starts, carry_out, obs, T);
-  ALEGPU_COUNT_LAUNCH();
-  ALEGPU_LAUNCH_CHECK();
   {
     constexpr int kPipeSmem = (int)sizeof(PipeSmem) + 128;
     static bool configured = false;
@@ -452,9 +443,9 @@ extern "C" int alegpu_preprocess_rollout(const uint8_t *frames, const uint8_t *e
       configured = true;
     }
     const int64_t items = E * T * kGroups;
-    const unsigned grid = (unsigned)std::min<int64_t>(items, 2 * kNumSMs);
+    const unsigned grid = (unsigned)std::min<int64_t>(items, 4 * kNumSMs);
     preprocess_rollout_pipe_kernel<<<grid, kThreads, kPipeSmem, as_stream(stream)>>>(
-        frames, episode_starts, carry_out, obs, E, T);
+        frames, episode_starts, carry_in, carry_out, obs, E, T);
   }
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();

@@ -367,7 +367,7 @@ def main():
     roof = None
     if pre:
         ach = N * PREPROCESS_BYTES_PER_STEP / (pre * 1e-3) / 1e9
-        roof = {"kernel": "preprocess_rollout_kernel", "bound": "hbm", "achieved": ach, "peak": hbm,
+        roof = {"kernel": "preprocess_rollout_pipe_kernel", "bound": "hbm", "achieved": ach, "peak": hbm,
                 "unit": "GB/s", "frac": ach / hbm, "traffic": None, "peak_source": which,
                 "ms_per_launch": pre, "algorithmic_bytes_per_launch": N * PREPROCESS_BYTES_PER_STEP}
     line = {"metric": METRIC, "value": value, "unit": "agent-steps/s", "n_gpus": world,
