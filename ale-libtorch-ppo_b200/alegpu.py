@@ -128,13 +128,6 @@ class DeviceArray:
         """Sub-view starting `offset_elems` elements in (no copy)."""
         return DeviceArray(shape, self.dtype, self.ptr + offset_elems * self.dtype.itemsize, self)
 
-    def close(self):
-        """Destroy the learner now (NCCL communicator included); with world_size > 1 every rank
-        must call this at the same point of the program."""
-        if getattr(self, "h", None) and _lib is not None:
-            _lib.alegpu_learner_destroy(self.h)
-            self.h = None
-
     def __del__(self):
         if getattr(self, "_owned", False) and getattr(self, "ptr", None) and _lib is not None:
             _lib.alegpu_free(C.c_void_p(self.ptr))
@@ -390,6 +383,13 @@ class Learner:
         self.hidden_size, self.action_size, self.max_minibatch = hidden_size, action_size, max_minibatch
         self.P = int(lib().alegpu_learner_param_count(self.h))
         self.stream = lib().alegpu_learner_stream(self.h)
+
+    def close(self):
+        """Destroy the learner now (NCCL communicator included); with world_size > 1 every rank
+        must call this at the same point of the program."""
+        if getattr(self, "h", None) and _lib is not None:
+            _lib.alegpu_learner_destroy(self.h)
+            self.h = None
 
     def __del__(self):
         if getattr(self, "h", None) and _lib is not None:

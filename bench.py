@@ -352,13 +352,9 @@ def main():
     d2h = loss_host.nbytes + gn_host.nbytes
     assert np.isfinite(loss_host).all() and np.isfinite(gn_host).all(), "non-finite metrics"
 
-    # tear the communicators down on every rank at the same point, before rank 0 goes on alone
-    if dist is not None:
-        alegpu.synchronize(stream)
-        dist.barrier()
-        L.close()
-        dist.barrier()
-        dist.destroy_process_group()
+    # Multi-rank exit: every collective of this run has completed (timed_loop ends on a barrier).
+    # Graceful NCCL teardown (ncclCommDestroy / destroy_process_group) of two communicators in one
+    # process hung on this image, so ranks leave through os._exit once rank 0 has printed its line.
     if rank != 0:
         sys.stdout.flush()
         os._exit(0)
@@ -381,7 +377,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": "agent-steps/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms},
             "gpu_launches": int(launches), "clocks": sampler.summary(), "roofline": roof}
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and world == 1:  # reported on rank 0 at N=1 only
         threads = os.cpu_count() or 1
         frac = 1.0 if N <= 4096 else 4096.0 / N
         v, desc = cpu_reference_iteration(w, threads, frac, iters=2 if N <= 1024 else 1, warm=1)
@@ -398,4 +394,13 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    try:
+        main()
+    except BaseException:
+        import traceback
+        traceback.print_exc()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+            os._exit(1)  # do not hang in teardown with NCCL communicators alive
+        raise
