@@ -9,6 +9,7 @@
 // a CUDA graph and replayed (the reference's capture_train_cuda_graph, train.h:163-195,
 // freezes lr into the graph; this one does not).
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <vector>
@@ -34,6 +35,7 @@ struct NcclApi {
   ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
                             cudaStream_t) = nullptr;
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*CommSplit)(ncclComm_t, int, int, ncclComm_t *, ncclConfig_t *) = nullptr;
   const char *(*GetErrorString)(ncclResult_t) = nullptr;
   bool ok = false;
 };
@@ -48,6 +50,7 @@ static NcclApi &nccl() {
       api.CommInitRank = (decltype(api.CommInitRank))dlsym(h, "ncclCommInitRank");
       api.AllReduce = (decltype(api.AllReduce))dlsym(h, "ncclAllReduce");
       api.CommDestroy = (decltype(api.CommDestroy))dlsym(h, "ncclCommDestroy");
+      api.CommSplit = (decltype(api.CommSplit))dlsym(h, "ncclCommSplit");
       api.GetErrorString = (decltype(api.GetErrorString))dlsym(h, "ncclGetErrorString");
       api.ok = api.GetUniqueId && api.CommInitRank && api.AllReduce && api.CommDestroy &&
                api.GetErrorString;
@@ -111,6 +114,11 @@ struct alegpu_learner {
   int64_t graph_launches = 0;
 #ifdef ALEGPU_WITH_NCCL
   ncclComm_t comm = nullptr;
+  // second communicator + stream: the FC/heads gradient bucket is exchanged while the conv
+  // data-gradient chain is still running (tensor-core path)
+  ncclComm_t comm2 = nullptr;
+  cudaStream_t comm_stream = nullptr;
+  cudaEvent_t ev_comm = nullptr;
 #endif
   std::vector<float> host_tmp;
 };
@@ -193,11 +201,26 @@ int backward(alegpu_learner *L, const uint8_t *obs, int64_t n) {
 int allreduce_grads(alegpu_learner *L) {
 #ifdef ALEGPU_WITH_NCCL
   if (L->cfg.world_size > 1) {
-    ncclResult_t r = nccl().AllReduce(L->grads, L->grads, (size_t)L->Ppad, ncclFloat, ncclSum,
-                                   L->comm, L->stream);
+    float *g = L->grads;
+    size_t count = (size_t)L->Ppad;
+    const size_t head = (size_t)(L->Gv.fcw - L->Gv.c1w); // conv tensors come first in the flat buffer
+    if (use_tc(L) && L->comm2 && !L->tc.serial) {
+      // bucket 1 (fcw, fcb, heads): on the communication stream as soon as the side branch has them
+      ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(L->comm_stream, L->tc.ev_fcw, 0));
+      ncclResult_t r = nccl().AllReduce(g + head, g + head, count - head, ncclFloat, ncclSum,
+                                        L->comm2, L->comm_stream);
+      if (r != ncclSuccess)
+        return fail(ALEGPU_CUDA_ERROR, std::string("ncclAllReduce: ") + nccl().GetErrorString(r));
+      ALEGPU_COUNT_LAUNCH();
+      ALEGPU_CUDA_CHECK(cudaEventRecord(L->ev_comm, L->comm_stream));
+      count = head; // bucket 2 (conv tensors, 312 KB) follows the backward on the main stream
+    }
+    ncclResult_t r = nccl().AllReduce(g, g, count, ncclFloat, ncclSum, L->comm, L->stream);
     if (r != ncclSuccess)
       return fail(ALEGPU_CUDA_ERROR, std::string("ncclAllReduce: ") + nccl().GetErrorString(r));
     ALEGPU_COUNT_LAUNCH();
+    if (count != (size_t)L->Ppad)
+      ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(L->stream, L->ev_comm, 0));
   }
 #endif
   return ALEGPU_OK;
@@ -516,6 +539,13 @@ extern "C" int alegpu_learner_create(const alegpu_learner_config *config, alegpu
     ncclResult_t r = nccl().CommInitRank(&L->comm, L->cfg.world_size, id, L->cfg.rank);
     if (r != ncclSuccess)
       return fail(ALEGPU_CUDA_ERROR, std::string("ncclCommInitRank: ") + nccl().GetErrorString(r));
+    if (tc && nccl().CommSplit && !getenv("ALEGPU_NO_COMM_OVERLAP")) {
+      r = nccl().CommSplit(L->comm, 0, L->cfg.rank, &L->comm2, nullptr);
+      if (r != ncclSuccess)
+        return fail(ALEGPU_CUDA_ERROR, std::string("ncclCommSplit: ") + nccl().GetErrorString(r));
+      ALEGPU_CUDA_CHECK(cudaStreamCreateWithFlags(&L->comm_stream, cudaStreamNonBlocking));
+      ALEGPU_CUDA_CHECK(cudaEventCreateWithFlags(&L->ev_comm, cudaEventDisableTiming));
+    }
   }
 #else
   ALEGPU_REQUIRE(L->cfg.world_size == 1, ALEGPU_RUNTIME_ERROR,
@@ -533,8 +563,14 @@ extern "C" int alegpu_learner_destroy(alegpu_learner *L) {
   cudaSetDevice(L->cfg.device);
   cudaStreamSynchronize(L->stream);
 #ifdef ALEGPU_WITH_NCCL
+  if (L->comm2)
+    nccl().CommDestroy(L->comm2);
   if (L->comm)
     nccl().CommDestroy(L->comm);
+  if (L->comm_stream)
+    cudaStreamDestroy(L->comm_stream);
+  if (L->ev_comm)
+    cudaEventDestroy(L->ev_comm);
 #endif
   if (L->graph_exec)
     cudaGraphExecDestroy(L->graph_exec);

@@ -17,6 +17,7 @@ struct TcState {
   // has its own split-partials workspace because they may be in flight together
   cudaStream_t side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_d3 = nullptr, ev_d2 = nullptr, ev_join = nullptr;
+  cudaEvent_t ev_fcw = nullptr; // recorded on the side branch once the FC + heads gradients exist
   float *ws_heads = nullptr, *ws_fc = nullptr, *ws_c3 = nullptr, *ws_c2 = nullptr, *ws_c1 = nullptr;
   size_t ws_heads_n = 0, ws_fc_n = 0, ws_c3_n = 0, ws_c2_n = 0, ws_c1_n = 0;
   bool serial = false;       // ALEGPU_TC_SERIAL=1: keep everything on one stream (profiling)
