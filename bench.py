@@ -361,10 +361,16 @@ def main():
     hbm, tflops, which = peaks()
     pre = float(np.median(pre_ms)) if pre_ms else None
     roof = None
+    traffic = None
+    try:  # measured DRAM bytes per launch of this kernel (one ncu --set full capture, see profiles/)
+        with open(os.path.join(ROOT, "profiles", "r01_roofline_traffic.json")) as f:
+            traffic = json.load(f).get(args.workload)
+    except Exception:
+        pass
     if pre:
         ach = N * PREPROCESS_BYTES_PER_STEP / (pre * 1e-3) / 1e9
         roof = {"kernel": "preprocess_rollout_pipe_kernel", "bound": "hbm", "achieved": ach, "peak": hbm,
-                "unit": "GB/s", "frac": ach / hbm, "traffic": None, "peak_source": which,
+                "unit": "GB/s", "frac": ach / hbm, "traffic": traffic, "peak_source": which,
                 "ms_per_launch": pre, "algorithmic_bytes_per_launch": N * PREPROCESS_BYTES_PER_STEP}
     line = {"metric": METRIC, "value": value, "unit": "agent-steps/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
