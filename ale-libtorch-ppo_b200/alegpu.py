@@ -469,7 +469,7 @@ class Learner:
         return int(lib().alegpu_learner_last_launch_count(self.h))
 
 
-def selftest_tc_gemm(A, B, M, N, R, a_mn=False, b_mn=False, bn=64, splits=1):
+def selftest_tc_gemm(A, B, M, N, R, a_mn=False, b_mn=False, bn=64, splits=1, use_async=False):
     """C[M,N] = A . B^T through the tcgen05/TMEM engine (alegpu_selftest_tc_gemm).  A is
     [M,R] (a_mn False) or [R,M] (a_mn True) fp32; likewise B.  Returns [z,M,N] partial
     products (z == 1 unless splits > 1)."""
@@ -481,8 +481,8 @@ def selftest_tc_gemm(A, B, M, N, R, a_mn=False, b_mn=False, bn=64, splits=1):
         z = -(-R // rps)
     dA, dB = DeviceArray.from_numpy(A), DeviceArray.from_numpy(B)
     dC = DeviceArray.zeros((z, M, N), np.float32)
-    _check(lib().alegpu_selftest_tc_gemm(_p(dA), _p(dB), _p(dC), C.c_int64(M), C.c_int64(N),
-                                         C.c_int64(R), C.c_int(int(a_mn)), C.c_int(int(b_mn)),
-                                         C.c_int(bn), C.c_int(splits), None))
+    fn = lib().alegpu_selftest_tc_gemm_async if use_async else lib().alegpu_selftest_tc_gemm
+    _check(fn(_p(dA), _p(dB), _p(dC), C.c_int64(M), C.c_int64(N), C.c_int64(R),
+              C.c_int(int(a_mn)), C.c_int(int(b_mn)), C.c_int(bn), C.c_int(splits), None))
     synchronize()
     return dC.numpy()

@@ -529,6 +529,7 @@ extern "C" int alegpu_learner_create(const alegpu_learner_config *config, alegpu
   if (tc)
     if (int rc = net_tc_init(L->tc, H, A, cap, L->Ppad, L->stream))
       return rc;
+  a.dfc16 = L->tc.dfc16; // the heads kernel also emits dfc in bf16 for the tensor-core backward
 #ifdef ALEGPU_WITH_NCCL
   if (L->cfg.world_size > 1) {
     ALEGPU_REQUIRE(config->nccl_unique_id, ALEGPU_INVALID_ARGUMENT,

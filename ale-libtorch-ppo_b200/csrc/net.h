@@ -44,6 +44,7 @@ struct NetActs {
   float *dact1 = nullptr, *dact2 = nullptr, *dact3 = nullptr, *dfc = nullptr;
   float *logits = nullptr, *values = nullptr; // [cap,A], [cap]
   float *dout = nullptr;                      // [cap, A+1] = (dlogits, dvalue)
+  void *dfc16 = nullptr;                      // optional bf16 copy of dfc (tensor-core path)
   float *fc_ws = nullptr;                     // split-K partials of the FC forward (tensor-core path)
   size_t fc_ws_floats = 0;
 };

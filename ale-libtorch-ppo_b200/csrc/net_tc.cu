@@ -40,6 +40,9 @@ __device__ __forceinline__ uint4 ldg16(const void *p) {
   return __ldg(reinterpret_cast<const uint4 *>(p));
 }
 __device__ __forceinline__ uint4 zero16() { return make_uint4(0u, 0u, 0u, 0u); }
+// the chunk (1, 0, 0, 0, 0, 0, 0, 0) in bf16: source of the "ones" row/column that turns a weight
+// gradient GEMM into weight + bias gradient, for the cp.async producers
+__device__ const uint4 g_ones_chunk = {0x00003F80u, 0u, 0u, 0u};
 __device__ __forceinline__ uint4 ones_first16() { return make_uint4(0x00003F80u, 0u, 0u, 0u); }
 // four u8 -> four bf16 (exact): bf16(v) = high half of float(v)
 __device__ __forceinline__ void u8x4_to_bf16(uint32_t w, uint32_t &lo, uint32_t &hi) {
@@ -82,6 +85,7 @@ __device__ __forceinline__ uint4 f32x8_to_bf16(const F32x8 &v) {
 // elements); conversion to bf16 happens when the chunk is stored to shared memory.
 // conv1: row m = (n,oy,ox) of 20x20, k = c*64 + ky*8 + kx ; chunk = the 8 kx of one (c,ky), raw u8
 struct Col1 {
+  static constexpr bool kAsyncSrc = false; // u8 pixels need the register path (convert at store)
   using Raw = uint2;
   static __device__ __forceinline__ Raw zero() { return make_uint2(0u, 0u); }
   static __device__ __forceinline__ uint4 cvt(const Raw &v) {
@@ -91,6 +95,7 @@ struct Col1 {
     return r;
   }
   const uint8_t *obs; // [n,4,84,84] u8
+  __device__ __forceinline__ const void *ptr_at(int, int) const { return nullptr; } // never async
   __device__ __forceinline__ Raw at(int m, int k) const {
     const int n = m / 400, pix = m - n * 400, oy = pix / 20, ox = pix - oy * 20;
     const int c = k >> 6, ky = (k >> 3) & 7;
@@ -102,22 +107,26 @@ struct Col1 {
 // conv2: row m = (n,oy,ox) of 9x9, k = (ky*4+kx)*32 + ci
 struct Col2 {
   ALEGPU_RAW_BF16
+  static constexpr bool kAsyncSrc = true;
   const bf16 *x; // act1 [n,20,20,32]
-  __device__ __forceinline__ uint4 at(int m, int k) const {
+  __device__ __forceinline__ const bf16 *ptr_at(int m, int k) const {
     const int n = m / 81, pix = m - n * 81, oy = pix / 9, ox = pix - oy * 9;
     const int ky = k >> 7, kx = (k >> 5) & 3, ci = k & 31;
-    return ldg16(x + ((size_t)(n * 20 + 2 * oy + ky) * 20 + 2 * ox + kx) * 32 + ci);
+    return x + ((size_t)(n * 20 + 2 * oy + ky) * 20 + 2 * ox + kx) * 32 + ci;
   }
+  __device__ __forceinline__ uint4 at(int m, int k) const { return ldg16(ptr_at(m, k)); }
 };
 // conv3: row m = (n,oy,ox) of 7x7, k = (ky*3+kx)*64 + ci
 struct Col3 {
   ALEGPU_RAW_BF16
+  static constexpr bool kAsyncSrc = true;
   const bf16 *x; // act2 [n,9,9,64]
-  __device__ __forceinline__ uint4 at(int m, int k) const {
+  __device__ __forceinline__ const bf16 *ptr_at(int m, int k) const {
     const int n = m / 49, pix = m - n * 49, oy = pix / 7, ox = pix - oy * 7;
     const int t = k >> 6, ky = t / 3, kx = t - ky * 3, ci = k & 63;
-    return ldg16(x + ((size_t)(n * 9 + oy + ky) * 9 + ox + kx) * 64 + ci);
+    return x + ((size_t)(n * 9 + oy + ky) * 9 + ox + kx) * 64 + ci;
   }
+  __device__ __forceinline__ uint4 at(int m, int k) const { return ldg16(ptr_at(m, k)); }
 };
 
 // K-major A operand of a forward conv: (row m, reduction k..k+7)
@@ -126,8 +135,10 @@ template <class Col> struct ColK {
   using Raw = typename Col::Raw;
   static __device__ __forceinline__ Raw zero() { return Col::zero(); }
   static __device__ __forceinline__ uint4 cvt(const Raw &v) { return Col::cvt(v); }
+  static constexpr bool kAsync = Col::kAsyncSrc;
   Col col;
   __device__ __forceinline__ Raw load(int m, int k, int) const { return col.at(m, k); }
+  __device__ __forceinline__ const void *ptr(int m, int k, int) const { return col.ptr_at(m, k); }
 };
 // MN-major A operand of a conv wgrad: rows = k (plus a ones row at k == K for the bias), r = m.
 // The ones row is encoded in the raw form as an all-ones first word (never a valid chunk of
@@ -142,21 +153,31 @@ template <class Col, int K> struct ColMN {
   static __device__ __forceinline__ uint4 cvt(const Raw &r) {
     return r.ones ? ones_first16() : Col::cvt(r.v);
   }
+  static constexpr bool kAsync = Col::kAsyncSrc;
   Col col;
   __device__ __forceinline__ Raw load(int k0, int m, int) const {
     if (k0 < K)
       return Raw{col.at(m, k0), false};
     return Raw{Col::zero(), true};
   }
+  __device__ __forceinline__ const void *ptr(int k0, int m, int) const {
+    if (k0 < K)
+      return col.ptr_at(m, k0);
+    return &g_ones_chunk;
+  }
 };
 // plain bf16 matrix [rows][ld]: K-major view (row, r..r+7)
 struct RowsK {
   ALEGPU_RAW_BF16
   static constexpr bool kMN = false;
+  static constexpr bool kAsync = true;
   const bf16 *p;
   int ld;
   __device__ __forceinline__ uint4 load(int i, int r, int) const {
     return ldg16(p + (size_t)i * ld + r);
+  }
+  __device__ __forceinline__ const void *ptr(int i, int r, int) const {
+    return p + (size_t)i * ld + r;
   }
 };
 // fp32 matrix [rows][ld] converted on the fly: K-major view
@@ -176,8 +197,12 @@ struct ColsMN {
   static constexpr bool kMN = true;
   const bf16 *p;
   int ld;
+  static constexpr bool kAsync = true;
   __device__ __forceinline__ uint4 load(int i0, int r, int) const {
     return i0 < ld ? ldg16(p + (size_t)r * ld + i0) : ones_first16();
+  }
+  __device__ __forceinline__ const void *ptr(int i0, int r, int) const {
+    return i0 < ld ? (const void *)(p + (size_t)r * ld + i0) : (const void *)&g_ones_chunk;
   }
 };
 struct ColsMNF32 {
@@ -202,6 +227,15 @@ struct DCol3 {
       return zero16();
     return ldg16(dy + ((size_t)(n * 7 + oy) * 7 + ox) * 64 + co);
   }
+  static constexpr bool kAsync = true;
+  __device__ __forceinline__ const void *ptr(int i, int r, int) const {
+    const int n = i / 81, pix = i - n * 81, iy = pix / 9, ix = pix - iy * 9;
+    const int t = r >> 6, ky = t / 3, kx = t - ky * 3, co = r & 63;
+    const int oy = iy - ky, ox = ix - kx;
+    if (oy < 0 || oy >= 7 || ox < 0 || ox >= 7)
+      return nullptr;
+    return dy + ((size_t)(n * 7 + oy) * 7 + ox) * 64 + co;
+  }
 };
 // conv3 dgrad B: (ci0..ci0+7, r = (t,co)) = c3w[co][t*64 + ci]
 struct W3T {
@@ -211,6 +245,11 @@ struct W3T {
   __device__ __forceinline__ uint4 load(int ci0, int r, int) const {
     const int t = r >> 6, co = r & 63;
     return ldg16(w + (size_t)co * 576 + t * 64 + ci0);
+  }
+  static constexpr bool kAsync = true;
+  __device__ __forceinline__ const void *ptr(int ci0, int r, int) const {
+    const int t = r >> 6, co = r & 63;
+    return w + (size_t)co * 576 + t * 64 + ci0;
   }
 };
 // conv2 dgrad A, parity class z = py*2+px: rows (n,qy,qx) of 10x10, r = (ty*2+tx)*64 + co
@@ -226,6 +265,15 @@ struct DCol2 {
       return zero16();
     return ldg16(dy + ((size_t)(n * 9 + oy) * 9 + ox) * 64 + co);
   }
+  static constexpr bool kAsync = true;
+  __device__ __forceinline__ const void *ptr(int i, int r, int) const {
+    const int n = i / 100, pix = i - n * 100, qy = pix / 10, qx = pix - qy * 10;
+    const int t = r >> 6, ty = t >> 1, tx = t & 1, co = r & 63;
+    const int oy = qy - ty, ox = qx - tx;
+    if (oy < 0 || oy >= 9 || ox < 0 || ox >= 9)
+      return nullptr;
+    return dy + ((size_t)(n * 9 + oy) * 9 + ox) * 64 + co;
+  }
 };
 // conv2 dgrad B: (ci0.., r=(t,co), z) = c2w[co][(ky*4+kx)*32 + ci], ky = py+2ty, kx = px+2tx
 struct W2T {
@@ -236,6 +284,12 @@ struct W2T {
     const int t = r >> 6, ty = t >> 1, tx = t & 1, co = r & 63;
     const int ky = (z >> 1) + 2 * ty, kx = (z & 1) + 2 * tx;
     return ldg16(w + (size_t)co * 512 + (ky * 4 + kx) * 32 + ci0);
+  }
+  static constexpr bool kAsync = true;
+  __device__ __forceinline__ const void *ptr(int ci0, int r, int z) const {
+    const int t = r >> 6, ty = t >> 1, tx = t & 1, co = r & 63;
+    const int ky = (z >> 1) + 2 * ty, kx = (z & 1) + 2 * tx;
+    return w + (size_t)co * 512 + (ky * 4 + kx) * 32 + ci0;
   }
 };
 
@@ -479,6 +533,7 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
   if (int rc = alloc(&T.dact1, sizeof(bf16) * (size_t)cap * 12800)) return rc;
   if (int rc = alloc(&T.dact2, sizeof(bf16) * (size_t)cap * 5184)) return rc;
   if (int rc = alloc(&T.dact3, sizeof(bf16) * (size_t)cap * 3136)) return rc;
+  if (int rc = alloc(&T.dfc16, sizeof(bf16) * (size_t)cap * hidden)) return rc;
   T.ws_heads_n = (size_t)(actions + 1) * (hidden + 1) * 2 * kNumSMs;
   T.ws_fc_n = (size_t)hidden * 3137 * 2;
   T.ws_c3_n = (size_t)577 * 64 * 64;
@@ -535,7 +590,7 @@ int net_tc_forward(const NetParams &P, TcState &T, const uint8_t *obs, int64_t n
   // FC: with few output tiles (small minibatch) the 3136-long reduction is split over CTAs and
   // summed in fixed order; otherwise one pass with the bias fused in the epilogue
   const int64_t tiles64 = ceil_div(n, tc::BM) * ceil_div(H, 64);
-  if (tiles64 * 2 <= kNumSMs && A.fc_ws && (size_t)n * H * 2 <= A.fc_ws_floats) {
+  if (tiles64 <= kNumSMs && A.fc_ws && (size_t)n * H * 2 <= A.fc_ws_floats) {
     int splits = (int)std::min<int64_t>({(int64_t)(2 * kNumSMs) / tiles64, (int64_t)(3136 / (2 * tc::BK)),
                                          (int64_t)(A.fc_ws_floats / ((size_t)n * H))});
     splits = std::max(splits, 1);
@@ -565,6 +620,7 @@ int net_tc_backward(const NetParams &P, const NetParams &G, TcState &T, const ui
   const Shadow W = shadow_view(T, P);
   bf16 *act1 = (bf16 *)T.act1, *act2 = (bf16 *)T.act2, *act3 = (bf16 *)T.act3;
   bf16 *dact1 = (bf16 *)T.dact1, *dact2 = (bf16 *)T.dact2, *dact3 = (bf16 *)T.dact3;
+  const bf16 *dfc16 = (const bf16 *)T.dfc16; // bf16 copy of A.dfc written by the heads kernel
   cudaStream_t w = T.serial ? s : T.side;
   if (!T.serial) {
     ALEGPU_CUDA_CHECK(cudaEventRecord(T.ev_fork, s));
@@ -581,11 +637,11 @@ int net_tc_backward(const NetParams &P, const NetParams &G, TcState &T, const ui
     if (n <= 1024)
       splits = 1, rps = 0; // 100 output tiles already fill the chip; skip the partial round trip
     if (splits == 1) { // [H][3136 | bias] = dfc^T . [act3 | 1]
-      if (int rc = tc::launch_gemm_tc<128, 3>(ColsMNF32{A.dfc, H}, ColsMN{act3, 3136},
+      if (int rc = tc::launch_gemm_tc<128, 3>(ColsMN{dfc16, H}, ColsMN{act3, 3136},
                                               EpiWgradDirect{G.fcw, G.fcb, 3136}, H, 3137, n, 1, 0, w))
         return rc;
     } else {
-      if (int rc = tc::launch_gemm_tc<128, 3>(ColsMNF32{A.dfc, H}, ColsMN{act3, 3136},
+      if (int rc = tc::launch_gemm_tc<128, 3>(ColsMN{dfc16, H}, ColsMN{act3, 3136},
                                               EpiPartial{T.ws_fc, H, 3137}, H, 3137, n, splits, rps, w))
         return rc;
       const int blocks = (int)std::min<int64_t>(ceil_div((int64_t)per, 256), 4 * kNumSMs);
@@ -598,10 +654,10 @@ int net_tc_backward(const NetParams &P, const NetParams &G, TcState &T, const ui
     ALEGPU_CUDA_CHECK(cudaEventRecord(T.ev_fcw, w));
   // ---- main: FC dgrad: dact3 = (dfc . fcw) * relu'(act3)
   if (ceil_div(n, tc::BM) * 25 < kNumSMs) { // small minibatch: narrower tiles, twice the CTAs
-    if (int rc = tc::launch_gemm_tc<64, 4>(RowsKF32{A.dfc, H}, ColsMN{W.fcw, 3136},
+    if (int rc = tc::launch_gemm_tc<64, 4>(RowsK{dfc16, H}, ColsMN{W.fcw, 3136},
                                            EpiReluMaskBf16{dact3, act3, 3136}, n, 3136, H, 1, 0, s))
       return rc;
-  } else if (int rc = tc::launch_gemm_tc<128, 3>(RowsKF32{A.dfc, H}, ColsMN{W.fcw, 3136},
+  } else if (int rc = tc::launch_gemm_tc<128, 3>(RowsK{dfc16, H}, ColsMN{W.fcw, 3136},
                                                  EpiReluMaskBf16{dact3, act3, 3136}, n, 3136, H, 1,
                                                  0, s))
     return rc;
@@ -657,38 +713,28 @@ int net_tc_fetch_activation(TcState &T, int which, int64_t n, float *host, cudaS
 } // namespace alegpu
 
 // ---- engine self-test (C ABI, include/alegpu.h) ---------------------------------------------------
-// C[M][N] (fp32) = A . B^T through the tcgen05 engine with fp32 inputs rounded to bf16 on load.
+// C[M][N] (fp32) = A . B^T through the tcgen05 engine with fp32 inputs rounded to bf16.
 // a_mn == 0: A is [M][R] row-major (K-major operand); a_mn == 1: A is stored [R][M] (MN-major).
 // Same for B with N.  bn selects the tile width instantiation (32, 64, 128 or 256).
-extern "C" int alegpu_selftest_tc_gemm(const float *A, const float *B, float *C, int64_t M, int64_t N,
-                                       int64_t R, int a_mn, int b_mn, int bn, int splits,
-                                       void *stream) {
-  using namespace alegpu;
-  ALEGPU_REQUIRE(A && B && C && M > 0 && N > 0 && R > 0, ALEGPU_INVALID_ARGUMENT,
-                 "selftest_tc_gemm: bad argument");
-  ALEGPU_REQUIRE(splits >= 1, ALEGPU_INVALID_ARGUMENT, "selftest_tc_gemm: splits >= 1");
-  ALEGPU_REQUIRE((a_mn ? M : R) % 8 == 0 && (b_mn ? N : R) % 8 == 0, ALEGPU_INVALID_ARGUMENT,
-                 "selftest_tc_gemm: the contiguous dimension of each operand must be a multiple of 8");
-  cudaStream_t s = as_stream(stream);
-  int rps = 0;
-  if (splits > 1)
-    rps = (int)(ceil_div(ceil_div(R, splits), tc::BK) * tc::BK);
-  const int z = splits > 1 ? (int)ceil_div(R, rps) : 1;
+// async == 0: fp32 loaders (register path: load -> convert -> swizzled st.shared);
+// async == 1: the inputs are first rounded to bf16 buffers and read by the cp.async producers.
+namespace alegpu {
+namespace {
+template <class AOpK, class AOpMN, class BOpK, class BOpMN>
+int selftest_dispatch(const AOpK &ak, const AOpMN &am, const BOpK &bk, const BOpMN &bm, float *C,
+                      int64_t M, int64_t N, int64_t R, int a_mn, int b_mn, int bn, int z, int rps,
+                      cudaStream_t s) {
   EpiPartial e{C, (int)M, (int)N}; // splits > 1: C must hold z*M*N floats (partials, not summed)
 #define ALEGPU_ST(BN, ST)                                                                          \
   do {                                                                                             \
     if (!a_mn && !b_mn)                                                                            \
-      return tc::launch_gemm_tc<BN, ST>(RowsKF32{A, (int)R}, RowsKF32{B, (int)R}, e, M, N, R, z,   \
-                                        rps, s);                                                   \
+      return tc::launch_gemm_tc<BN, ST>(ak, bk, e, M, N, R, z, rps, s);                            \
     if (a_mn && !b_mn)                                                                             \
-      return tc::launch_gemm_tc<BN, ST>(ColsMNF32{A, (int)M}, RowsKF32{B, (int)R}, e, M, N, R, z,  \
-                                        rps, s);                                                   \
+      return tc::launch_gemm_tc<BN, ST>(am, bk, e, M, N, R, z, rps, s);                            \
     if constexpr (BN >= 64) {                                                                      \
       if (!a_mn && b_mn)                                                                           \
-        return tc::launch_gemm_tc<BN, ST>(RowsKF32{A, (int)R}, ColsMNF32{B, (int)N}, e, M, N, R,   \
-                                          z, rps, s);                                              \
-      return tc::launch_gemm_tc<BN, ST>(ColsMNF32{A, (int)M}, ColsMNF32{B, (int)N}, e, M, N, R, z, \
-                                        rps, s);                                                   \
+        return tc::launch_gemm_tc<BN, ST>(ak, bm, e, M, N, R, z, rps, s);                          \
+      return tc::launch_gemm_tc<BN, ST>(am, bm, e, M, N, R, z, rps, s);                            \
     }                                                                                              \
   } while (0)
   if (bn == 32)
@@ -701,4 +747,48 @@ extern "C" int alegpu_selftest_tc_gemm(const float *A, const float *B, float *C,
     ALEGPU_ST(256, 3);
 #undef ALEGPU_ST
   return fail(ALEGPU_INVALID_ARGUMENT, "selftest_tc_gemm: unsupported bn / major combination");
+}
+} // namespace
+} // namespace alegpu
+
+static int selftest_impl(const float *A, const float *B, float *C, int64_t M, int64_t N, int64_t R,
+                         int a_mn, int b_mn, int bn, int splits, int async, void *stream) {
+  using namespace alegpu;
+  ALEGPU_REQUIRE(A && B && C && M > 0 && N > 0 && R > 0, ALEGPU_INVALID_ARGUMENT,
+                 "selftest_tc_gemm: bad argument");
+  ALEGPU_REQUIRE(splits >= 1, ALEGPU_INVALID_ARGUMENT, "selftest_tc_gemm: splits >= 1");
+  ALEGPU_REQUIRE((a_mn ? M : R) % 8 == 0 && (b_mn ? N : R) % 8 == 0, ALEGPU_INVALID_ARGUMENT,
+                 "selftest_tc_gemm: the contiguous dimension of each operand must be a multiple of 8");
+  cudaStream_t s = as_stream(stream);
+  int rps = 0;
+  if (splits > 1)
+    rps = (int)(ceil_div(ceil_div(R, splits), tc::BK) * tc::BK);
+  const int z = splits > 1 ? (int)ceil_div(R, rps) : 1;
+  if (!async)
+    return selftest_dispatch(RowsKF32{A, (int)R}, ColsMNF32{A, (int)M}, RowsKF32{B, (int)R},
+                             ColsMNF32{B, (int)N}, C, M, N, R, a_mn, b_mn, bn, z, rps, s);
+  bf16 *a16 = nullptr, *b16 = nullptr;
+  ALEGPU_CUDA_CHECK(cudaMalloc(&a16, sizeof(bf16) * (size_t)M * R));
+  ALEGPU_CUDA_CHECK(cudaMalloc(&b16, sizeof(bf16) * (size_t)N * R));
+  int rc = launch_f32_to_bf16(A, a16, M * R, s);
+  if (!rc)
+    rc = launch_f32_to_bf16(B, b16, N * R, s);
+  if (!rc) // ColsMN's ones row (i0 >= ld) is never requested here: rows < M == ld
+    rc = selftest_dispatch(RowsK{a16, (int)R}, ColsMN{a16, (int)M}, RowsK{b16, (int)R},
+                           ColsMN{b16, (int)N}, C, M, N, R, a_mn, b_mn, bn, z, rps, s);
+  cudaStreamSynchronize(s);
+  cudaFree(a16);
+  cudaFree(b16);
+  return rc;
+}
+
+extern "C" int alegpu_selftest_tc_gemm(const float *A, const float *B, float *C, int64_t M, int64_t N,
+                                       int64_t R, int a_mn, int b_mn, int bn, int splits,
+                                       void *stream) {
+  return selftest_impl(A, B, C, M, N, R, a_mn, b_mn, bn, splits, 0, stream);
+}
+extern "C" int alegpu_selftest_tc_gemm_async(const float *A, const float *B, float *C, int64_t M,
+                                             int64_t N, int64_t R, int a_mn, int b_mn, int bn,
+                                             int splits, void *stream) {
+  return selftest_impl(A, B, C, M, N, R, a_mn, b_mn, bn, splits, 1, stream);
 }

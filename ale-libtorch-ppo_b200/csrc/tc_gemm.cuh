@@ -196,6 +196,82 @@ template <int ROWS, class Op> struct TileRegs {
   }
 };
 
+// ---- asynchronous tile producer (cp.async / LDGSTS) -------------------------------------------------
+// Operands that already are bf16 in global memory skip the register round trip: every thread copies
+// its 16-byte chunks global -> swizzled shared memory with cp.async.cg (zero-fill for chunks outside
+// the matrix), so STAGES-1 k-blocks of loads are in flight per thread at no register cost.
+// Loader contract (Op::kAsync == true):
+//   K-major : Op::ptr(row, r, z)  -> address of elements (row, r..r+7), or nullptr = eight zeros
+//   MN-major: Op::ptr(row0, r, z) -> address of elements (row0..row0+7, r), or nullptr
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src) {
+  if (src)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+  else // nothing to copy: plain zero store (ordered with the later fence.proxy.async like the copies)
+    asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" ::"r"(dst), "r"(0u) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() {
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+template <int N> __device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+template <class Op, class = void> struct IsAsync {
+  static constexpr bool value = false;
+};
+template <class Op> struct IsAsync<Op, decltype((void)Op::kAsync)> {
+  static constexpr bool value = Op::kAsync;
+};
+template <int ROWS, class Op>
+__device__ __forceinline__ void tile_issue_async(const Op &op, uint32_t tile, int row0,
+                                                 int rows_total, int r0, int r_end, int z,
+                                                 int ptid) {
+  constexpr int kChunks = ROWS * 8;
+  constexpr int kProducers = kProducerWarps * 32;
+  constexpr int kPer = (kChunks + kProducers - 1) / kProducers;
+#pragma unroll
+  for (int it = 0; it < kPer; ++it) {
+    const int q = ptid + it * kProducers;
+    if (kChunks % kProducers == 0 || q < kChunks) {
+      const void *src = nullptr;
+      uint32_t off;
+      if constexpr (!Op::kMN) {
+        const int kc = q & 7, il = q >> 3;
+        const int i = row0 + il, r = r0 + kc * 8;
+        off = (uint32_t)(il * 128 + ((kc ^ (il & 7)) << 4));
+        if (i < rows_total && r < r_end)
+          src = op.ptr(i, r, z);
+      } else {
+        constexpr int kRowChunks = ROWS / 8;
+        const int c = q % kRowChunks, k = q / kRowChunks, kr = k & 7;
+        const int i = row0 + c * 8, r = r0 + k;
+        off = (uint32_t)((c >> 3) * 8192 + (k >> 3) * 1024 + kr * 128 + (((c & 7) ^ kr) << 4));
+        if (i < rows_total && r < r_end)
+          src = op.ptr(i, r, z);
+      }
+      cp_async16(tile + off, src);
+    }
+  }
+}
+// register-path tile that compiles to nothing for asynchronous operands
+template <int ROWS, class Op, bool kAsyncOp = IsAsync<Op>::value> struct TileStage {
+  TileRegs<ROWS, Op> t;
+  __device__ __forceinline__ void load(const Op &op, int row0, int rows_total, int r0, int r_end,
+                                       int z, int ptid) {
+    t.load(op, row0, rows_total, r0, r_end, z, ptid);
+  }
+  __device__ __forceinline__ void put(const Op &, uint32_t tile, int, int, int, int, int,
+                                      int ptid) const {
+    t.store(tile, ptid);
+  }
+};
+template <int ROWS, class Op> struct TileStage<ROWS, Op, true> {
+  __device__ __forceinline__ void load(const Op &, int, int, int, int, int, int) {}
+  __device__ __forceinline__ void put(const Op &op, uint32_t tile, int row0, int rows_total, int r0,
+                                      int r_end, int z, int ptid) const {
+    tile_issue_async<ROWS>(op, tile, row0, rows_total, r0, r_end, z, ptid);
+  }
+};
+
 __host__ __device__ constexpr int tile_bytes(int rows) { return rows * 128; }
 __host__ __device__ constexpr int smem_bytes(int bn, int stages) {
   return stages * (tile_bytes(BM) + tile_bytes(bn < 64 ? 64 : bn)) + 1024;
@@ -248,40 +324,61 @@ __global__ void __launch_bounds__(kThreads, BN <= 128 ? 2 : 1)
     const int ptid = threadIdx.x;
     constexpr int kBRows = BN < 64 ? 64 : BN;
     const uint32_t tiles_s = smem_u32(tiles);
-    constexpr int kPF = 2; // register buffers: loads run kPF-1 k-blocks ahead of the smem stores
-    TileRegs<BM, AOp> ra[kPF];
-    TileRegs<kBRows, BOp> rb[kPF];
-    auto stage_out = [&](int kb, const TileRegs<BM, AOp> &a, const TileRegs<kBRows, BOp> &b) {
-      const int s = kb % STAGES;
-      const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
-      mbar_wait(&empty_bar[s], ph ^ 1u);
-      const uint32_t st = tiles_s + (uint32_t)(s * kStage);
-      a.store(st, ptid);
-      b.store(st + kATile, ptid);
+    // Register-path operands (u8 / fp32 sources) are loaded one k-block ahead and converted when
+    // stored; asynchronous operands are copied straight into the stage.  A stage is handed to the
+    // tensor core kLag k-blocks after it was issued, when its cp.async group has landed, so up to
+    // STAGES-1 k-blocks of loads are in flight per thread.
+    constexpr int kPF = 2;
+    constexpr int kLag = STAGES - 2; // k-blocks between issuing a stage and signalling it
+    TileStage<BM, AOp> ra[kPF];
+    TileStage<kBRows, BOp> rb[kPF];
+    auto signal = [&](int kb) {
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0)
-        mbar_arrive(&full_bar[s]);
+        mbar_arrive(&full_bar[kb % STAGES]);
     };
-#pragma unroll
-    for (int u = 0; u < kPF - 1; ++u)
-      if (u < nkb) {
-        ra[u].load(aop, m0, M, r_begin + u * BK, r_end, z, ptid);
-        rb[u].load(bop, n0, N, r_begin + u * BK, r_end, z, ptid);
-      }
+    if (nkb > 0) {
+      ra[0].load(aop, m0, M, r_begin, r_end, z, ptid);
+      rb[0].load(bop, n0, N, r_begin, r_end, z, ptid);
+    }
     for (int kb0 = 0; kb0 < nkb; kb0 += kPF) {
 #pragma unroll
       for (int u = 0; u < kPF; ++u) {
         const int kb = kb0 + u;
         if (kb < nkb) {
-          if (kb + kPF - 1 < nkb) {
-            ra[(u + kPF - 1) % kPF].load(aop, m0, M, r_begin + (kb + kPF - 1) * BK, r_end, z, ptid);
-            rb[(u + kPF - 1) % kPF].load(bop, n0, N, r_begin + (kb + kPF - 1) * BK, r_end, z, ptid);
+          if (kb + 1 < nkb) {
+            ra[(u + 1) % kPF].load(aop, m0, M, r_begin + (kb + 1) * BK, r_end, z, ptid);
+            rb[(u + 1) % kPF].load(bop, n0, N, r_begin + (kb + 1) * BK, r_end, z, ptid);
           }
-          stage_out(kb, ra[u], rb[u]);
+          const int s = kb % STAGES;
+          const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+          mbar_wait(&empty_bar[s], ph ^ 1u);
+          const uint32_t st = tiles_s + (uint32_t)(s * kStage);
+          ra[u].put(aop, st, m0, M, r_begin + kb * BK, r_end, z, ptid);
+          rb[u].put(bop, st + kATile, n0, N, r_begin + kb * BK, r_end, z, ptid);
+          cp_async_commit();
+          if (kb >= kLag) {
+            cp_async_wait<kLag>();
+            signal(kb - kLag);
+          }
         }
       }
     }
+    // drain: the last kLag stages
+    static_assert(kLag >= 0 && kLag <= 4, "drain below is unrolled for kLag <= 4");
+#define ALEGPU_TC_DRAIN(T)                                                                         \
+  if constexpr (kLag > (T)) {                                                                      \
+    if (nkb - 1 - (T) >= 0) {                                                                      \
+      cp_async_wait<(T)>();                                                                        \
+      signal(nkb - 1 - (T));                                                                       \
+    }                                                                                              \
+  }
+    ALEGPU_TC_DRAIN(3)
+    ALEGPU_TC_DRAIN(2)
+    ALEGPU_TC_DRAIN(1)
+    ALEGPU_TC_DRAIN(0)
+#undef ALEGPU_TC_DRAIN
     // ===== epilogue: TMEM -> registers -> fused functor ========================================
     if (nkb > 0) {
       mbar_wait(&accum_bar, 0u);

@@ -293,6 +293,11 @@ int64_t alegpu_learner_last_launch_count(const alegpu_learner *learner);
  * and C receives that many [M][N] partial products back to back (not summed). */
 int alegpu_selftest_tc_gemm(const float *A, const float *B, float *C, int64_t M, int64_t N,
                             int64_t R, int a_mn, int b_mn, int bn, int splits, void *stream);
+/* the same product with A and B first rounded to bf16 device buffers and read by the engine's
+ * cp.async (global -> swizzled shared memory, no register staging) producers — the path every bf16
+ * operand of the network takes; the fp32 entry point above exercises the register producers. */
+int alegpu_selftest_tc_gemm_async(const float *A, const float *B, float *C, int64_t M, int64_t N,
+                                  int64_t R, int a_mn, int b_mn, int bn, int splits, void *stream);
 
 #ifdef __cplusplus
 }

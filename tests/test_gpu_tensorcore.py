@@ -35,29 +35,32 @@ def hp():
     return alegpu.Hyperparameters(cases.CLIP, cases.VCOEF, cases.ECOEF, cases.MAX_NORM)
 
 
+@pytest.mark.parametrize("use_async", [False, True])
 @pytest.mark.parametrize("a_mn,b_mn", [(False, False), (True, False), (False, True), (True, True)])
 @pytest.mark.parametrize("M,N,R,bn", [(128, 64, 64, 64), (304, 64, 576, 64), (256, 136, 200, 128),
-                                      (520, 256, 1000, 256), (64, 32, 256, 32)])
-def test_tc_gemm_engine(a_mn, b_mn, M, N, R, bn):
+                                      (520, 256, 1000, 256), (64, 32, 256, 32), (128, 64, 128, 64)])
+def test_tc_gemm_engine(a_mn, b_mn, M, N, R, bn, use_async):
     if b_mn and bn < 64:
         pytest.skip("an MN-major B tile needs bn >= 64")
     rng = np.random.default_rng(M * 7 + N * 3 + R)
     A = rng.standard_normal((M, R)).astype(np.float32)
     B = rng.standard_normal((N, R)).astype(np.float32)
     want = bf16_round(A).astype(np.float64) @ bf16_round(B).astype(np.float64).T
-    got = alegpu.selftest_tc_gemm(A.T if a_mn else A, B.T if b_mn else B, M, N, R, a_mn, b_mn, bn)
+    got = alegpu.selftest_tc_gemm(A.T if a_mn else A, B.T if b_mn else B, M, N, R, a_mn, b_mn, bn,
+                                  use_async=use_async)
     assert got.shape == (1, M, N)
     err = np.abs(got[0] - want).max()
     assert err <= 1e-4 * np.sqrt(R) * 4, (err, a_mn, b_mn)
 
 
-def test_tc_gemm_engine_splits():
+@pytest.mark.parametrize("use_async", [False, True])
+def test_tc_gemm_engine_splits(use_async):
     M, N, R = 264, 64, 1000
     rng = np.random.default_rng(5)
     A = rng.standard_normal((M, R)).astype(np.float32)
     B = rng.standard_normal((N, R)).astype(np.float32)
     want = bf16_round(A).astype(np.float64) @ bf16_round(B).astype(np.float64).T
-    got = alegpu.selftest_tc_gemm(A.T, B.T, M, N, R, True, True, 64, splits=5)
+    got = alegpu.selftest_tc_gemm(A.T, B.T, M, N, R, True, True, 64, splits=5, use_async=use_async)
     assert got.shape[0] == 4  # rps = 256 -> 4 parts
     assert np.abs(got.sum(0) - want).max() <= 2e-3
 

@@ -6,7 +6,7 @@ nproc >> gpurun_out/gpus.txt
 timeout 900 python -m pytest tests -m gpu -q -s --timeout 300 > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
 timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" | tee -a gpurun_out/smoke.log
 for w in v0 v1; do
-  for m in bf16 fp32; do
+  for m in ${BENCH_MATHS:-bf16}; do
     timeout 600 python bench.py --workload $w --math $m --steps 10 --warmup 3 > gpurun_out/bench_${w}_${m}.json 2> gpurun_out/bench_${w}_${m}.err; echo "bench $w $m rc=$?"
   done
 done
