@@ -45,11 +45,13 @@ __device__ __forceinline__ uint4 zero16() { return make_uint4(0u, 0u, 0u, 0u); }
 __device__ const uint4 g_ones_chunk = {0x00003F80u, 0u, 0u, 0u};
 __device__ __forceinline__ uint4 ones_first16() { return make_uint4(0x00003F80u, 0u, 0u, 0u); }
 // four u8 -> four bf16 (exact): bf16(v) = high half of float(v)
+// (byte k dropped into the mantissa of 2^23, minus 2^23: PRMT + FADD instead of the slow I2F pipe)
 __device__ __forceinline__ void u8x4_to_bf16(uint32_t w, uint32_t &lo, uint32_t &hi) {
-  const uint32_t f0 = __float_as_uint((float)(w & 0xFFu)),
-                 f1 = __float_as_uint((float)((w >> 8) & 0xFFu));
-  const uint32_t f2 = __float_as_uint((float)((w >> 16) & 0xFFu)),
-                 f3 = __float_as_uint((float)(w >> 24));
+  constexpr uint32_t kMagic = 0x4B000000u; // 8388608.0f
+  const uint32_t f0 = __float_as_uint(__uint_as_float(__byte_perm(w, kMagic, 0x7540)) - 8388608.0f);
+  const uint32_t f1 = __float_as_uint(__uint_as_float(__byte_perm(w, kMagic, 0x7541)) - 8388608.0f);
+  const uint32_t f2 = __float_as_uint(__uint_as_float(__byte_perm(w, kMagic, 0x7542)) - 8388608.0f);
+  const uint32_t f3 = __float_as_uint(__uint_as_float(__byte_perm(w, kMagic, 0x7543)) - 8388608.0f);
   lo = __byte_perm(f0, f1, 0x7632);
   hi = __byte_perm(f2, f3, 0x7632);
 }
@@ -86,6 +88,7 @@ __device__ __forceinline__ uint4 f32x8_to_bf16(const F32x8 &v) {
 // conv1: row m = (n,oy,ox) of 20x20, k = c*64 + ky*8 + kx ; chunk = the 8 kx of one (c,ky), raw u8
 struct Col1 {
   static constexpr bool kAsyncSrc = false; // u8 pixels need the register path (convert at store)
+  static constexpr int kPrefetch = 4;      // 8-byte raw chunks: loads run 3 k-blocks ahead
   using Raw = uint2;
   static __device__ __forceinline__ Raw zero() { return make_uint2(0u, 0u); }
   static __device__ __forceinline__ uint4 cvt(const Raw &v) {
@@ -95,7 +98,9 @@ struct Col1 {
     return r;
   }
   const uint8_t *obs; // [n,4,84,84] u8
-  __device__ __forceinline__ const void *ptr_at(int, int) const { return nullptr; } // never async
+  using PosPtr = const uint8_t *;
+  __device__ __forceinline__ PosPtr pos_ptr(int) const { return nullptr; } // never async
+  __device__ __forceinline__ int k_off(int) const { return 0; }
   __device__ __forceinline__ Raw at(int m, int k) const {
     const int n = m / 400, pix = m - n * 400, oy = pix / 20, ox = pix - oy * 20;
     const int c = k >> 6, ky = (k >> 3) & 7;
@@ -108,25 +113,36 @@ struct Col1 {
 struct Col2 {
   ALEGPU_RAW_BF16
   static constexpr bool kAsyncSrc = true;
+  static constexpr int kPrefetch = 2;
   const bf16 *x; // act1 [n,20,20,32]
-  __device__ __forceinline__ const bf16 *ptr_at(int m, int k) const {
+  // address of element (m, k) = pos_ptr(m) + k_off(k): the position part and the tap part
+  using PosPtr = const bf16 *;
+  __device__ __forceinline__ const bf16 *pos_ptr(int m) const {
     const int n = m / 81, pix = m - n * 81, oy = pix / 9, ox = pix - oy * 9;
-    const int ky = k >> 7, kx = (k >> 5) & 3, ci = k & 31;
-    return x + ((size_t)(n * 20 + 2 * oy + ky) * 20 + 2 * ox + kx) * 32 + ci;
+    return x + ((size_t)(n * 20 + 2 * oy) * 20 + 2 * ox) * 32;
   }
-  __device__ __forceinline__ uint4 at(int m, int k) const { return ldg16(ptr_at(m, k)); }
+  __device__ __forceinline__ int k_off(int k) const {
+    const int ky = k >> 7, kx = (k >> 5) & 3, ci = k & 31;
+    return (ky * 20 + kx) * 32 + ci;
+  }
+  __device__ __forceinline__ uint4 at(int m, int k) const { return ldg16(pos_ptr(m) + k_off(k)); }
 };
 // conv3: row m = (n,oy,ox) of 7x7, k = (ky*3+kx)*64 + ci
 struct Col3 {
   ALEGPU_RAW_BF16
   static constexpr bool kAsyncSrc = true;
+  static constexpr int kPrefetch = 2;
   const bf16 *x; // act2 [n,9,9,64]
-  __device__ __forceinline__ const bf16 *ptr_at(int m, int k) const {
+  using PosPtr = const bf16 *;
+  __device__ __forceinline__ const bf16 *pos_ptr(int m) const {
     const int n = m / 49, pix = m - n * 49, oy = pix / 7, ox = pix - oy * 7;
-    const int t = k >> 6, ky = t / 3, kx = t - ky * 3, ci = k & 63;
-    return x + ((size_t)(n * 9 + oy + ky) * 9 + ox + kx) * 64 + ci;
+    return x + ((size_t)(n * 9 + oy) * 9 + ox) * 64;
   }
-  __device__ __forceinline__ uint4 at(int m, int k) const { return ldg16(ptr_at(m, k)); }
+  __device__ __forceinline__ int k_off(int k) const {
+    const int t = k >> 6, ky = t / 3, kx = t - ky * 3, ci = k & 63;
+    return (ky * 9 + kx) * 64 + ci;
+  }
+  __device__ __forceinline__ uint4 at(int m, int k) const { return ldg16(pos_ptr(m) + k_off(k)); }
 };
 
 // K-major A operand of a forward conv: (row m, reduction k..k+7)
@@ -136,9 +152,14 @@ template <class Col> struct ColK {
   static __device__ __forceinline__ Raw zero() { return Col::zero(); }
   static __device__ __forceinline__ uint4 cvt(const Raw &v) { return Col::cvt(v); }
   static constexpr bool kAsync = Col::kAsyncSrc;
-  Col col;
-  __device__ __forceinline__ Raw load(int m, int k, int) const { return col.at(m, k); }
-  __device__ __forceinline__ const void *ptr(int m, int k, int) const { return col.ptr_at(m, k); }
+  static constexpr int kPrefetch = Col::kPrefetch;
+  Col src;
+  __device__ __forceinline__ Raw load(int m, int k, int) const { return src.at(m, k); }
+  using RowCtx = typename Col::PosPtr; // position part of the address
+  using ColCtx = int;                                           // tap part (element offset)
+  __device__ __forceinline__ RowCtx row(int m) const { return src.pos_ptr(m); }
+  __device__ __forceinline__ ColCtx col(int k, int) const { return src.k_off(k); }
+  __device__ __forceinline__ const void *at(RowCtx rc, ColCtx cc) const { return rc + cc; }
 };
 // MN-major A operand of a conv wgrad: rows = k (plus a ones row at k == K for the bias), r = m.
 // The ones row is encoded in the raw form as an all-ones first word (never a valid chunk of
@@ -154,16 +175,20 @@ template <class Col, int K> struct ColMN {
     return r.ones ? ones_first16() : Col::cvt(r.v);
   }
   static constexpr bool kAsync = Col::kAsyncSrc;
-  Col col;
+  static constexpr int kPrefetch = Col::kPrefetch;
+  static constexpr bool kPosFastest = !Col::kAsyncSrc; // register path (conv1): see tc_gemm.cuh
+  Col src;
   __device__ __forceinline__ Raw load(int k0, int m, int) const {
     if (k0 < K)
-      return Raw{col.at(m, k0), false};
+      return Raw{src.at(m, k0), false};
     return Raw{Col::zero(), true};
   }
-  __device__ __forceinline__ const void *ptr(int k0, int m, int) const {
-    if (k0 < K)
-      return col.ptr_at(m, k0);
-    return &g_ones_chunk;
+  using RowCtx = int; // tap offset of k0, or -1 for the ones row
+  using ColCtx = typename Col::PosPtr;
+  __device__ __forceinline__ RowCtx row(int k0) const { return k0 < K ? src.k_off(k0) : -1; }
+  __device__ __forceinline__ ColCtx col(int m, int) const { return src.pos_ptr(m); }
+  __device__ __forceinline__ const void *at(RowCtx rc, ColCtx cc) const {
+    return rc >= 0 ? (const void *)(cc + rc) : (const void *)&g_ones_chunk;
   }
 };
 // plain bf16 matrix [rows][ld]: K-major view (row, r..r+7)
@@ -176,9 +201,11 @@ struct RowsK {
   __device__ __forceinline__ uint4 load(int i, int r, int) const {
     return ldg16(p + (size_t)i * ld + r);
   }
-  __device__ __forceinline__ const void *ptr(int i, int r, int) const {
-    return p + (size_t)i * ld + r;
-  }
+  using RowCtx = const bf16 *;
+  using ColCtx = int;
+  __device__ __forceinline__ RowCtx row(int i) const { return p + (size_t)i * ld; }
+  __device__ __forceinline__ ColCtx col(int r, int) const { return r; }
+  __device__ __forceinline__ const void *at(RowCtx rc, ColCtx cc) const { return rc + cc; }
 };
 // fp32 matrix [rows][ld] converted on the fly: K-major view
 struct RowsKF32 {
@@ -201,8 +228,12 @@ struct ColsMN {
   __device__ __forceinline__ uint4 load(int i0, int r, int) const {
     return i0 < ld ? ldg16(p + (size_t)r * ld + i0) : ones_first16();
   }
-  __device__ __forceinline__ const void *ptr(int i0, int r, int) const {
-    return i0 < ld ? (const void *)(p + (size_t)r * ld + i0) : (const void *)&g_ones_chunk;
+  using RowCtx = int; // i0, or -1 for the ones row
+  using ColCtx = const bf16 *;
+  __device__ __forceinline__ RowCtx row(int i0) const { return i0 < ld ? i0 : -1; }
+  __device__ __forceinline__ ColCtx col(int r, int) const { return p + (size_t)r * ld; }
+  __device__ __forceinline__ const void *at(RowCtx rc, ColCtx cc) const {
+    return rc >= 0 ? (const void *)(cc + rc) : (const void *)&g_ones_chunk;
   }
 };
 struct ColsMNF32 {
@@ -228,13 +259,24 @@ struct DCol3 {
     return ldg16(dy + ((size_t)(n * 7 + oy) * 7 + ox) * 64 + co);
   }
   static constexpr bool kAsync = true;
-  __device__ __forceinline__ const void *ptr(int i, int r, int) const {
+  struct RowCtx {
+    const bf16 *base; // dy element of (n, oy = iy, ox = ix), channel 0 (may lie outside: only offset)
+    int iy, ix;
+  };
+  struct ColCtx {
+    int off, ky, kx; // off = co - (ky*7 + kx)*64
+  };
+  __device__ __forceinline__ RowCtx row(int i) const {
     const int n = i / 81, pix = i - n * 81, iy = pix / 9, ix = pix - iy * 9;
+    return RowCtx{dy + ((ptrdiff_t)(n * 7 + iy) * 7 + ix) * 64, iy, ix};
+  }
+  __device__ __forceinline__ ColCtx col(int r, int) const {
     const int t = r >> 6, ky = t / 3, kx = t - ky * 3, co = r & 63;
-    const int oy = iy - ky, ox = ix - kx;
-    if (oy < 0 || oy >= 7 || ox < 0 || ox >= 7)
-      return nullptr;
-    return dy + ((size_t)(n * 7 + oy) * 7 + ox) * 64 + co;
+    return ColCtx{co - (ky * 7 + kx) * 64, ky, kx};
+  }
+  __device__ __forceinline__ const void *at(const RowCtx &rc, const ColCtx &cc) const {
+    const unsigned oy = (unsigned)(rc.iy - cc.ky), ox = (unsigned)(rc.ix - cc.kx);
+    return (oy < 7u && ox < 7u) ? (const void *)(rc.base + cc.off) : nullptr;
   }
 };
 // conv3 dgrad B: (ci0..ci0+7, r = (t,co)) = c3w[co][t*64 + ci]
@@ -247,10 +289,14 @@ struct W3T {
     return ldg16(w + (size_t)co * 576 + t * 64 + ci0);
   }
   static constexpr bool kAsync = true;
-  __device__ __forceinline__ const void *ptr(int ci0, int r, int) const {
+  using RowCtx = int;
+  using ColCtx = const bf16 *;
+  __device__ __forceinline__ RowCtx row(int ci0) const { return ci0; }
+  __device__ __forceinline__ ColCtx col(int r, int) const {
     const int t = r >> 6, co = r & 63;
-    return w + (size_t)co * 576 + t * 64 + ci0;
+    return w + (size_t)co * 576 + t * 64;
   }
+  __device__ __forceinline__ const void *at(RowCtx rc, ColCtx cc) const { return cc + rc; }
 };
 // conv2 dgrad A, parity class z = py*2+px: rows (n,qy,qx) of 10x10, r = (ty*2+tx)*64 + co
 struct DCol2 {
@@ -266,13 +312,24 @@ struct DCol2 {
     return ldg16(dy + ((size_t)(n * 9 + oy) * 9 + ox) * 64 + co);
   }
   static constexpr bool kAsync = true;
-  __device__ __forceinline__ const void *ptr(int i, int r, int) const {
+  struct RowCtx {
+    const bf16 *base; // dy element of (n, oy = qy, ox = qx), channel 0 (only an offset base)
+    int qy, qx;
+  };
+  struct ColCtx {
+    int off, ty, tx; // off = co - (ty*9 + tx)*64
+  };
+  __device__ __forceinline__ RowCtx row(int i) const {
     const int n = i / 100, pix = i - n * 100, qy = pix / 10, qx = pix - qy * 10;
+    return RowCtx{dy + ((ptrdiff_t)(n * 9 + qy) * 9 + qx) * 64, qy, qx};
+  }
+  __device__ __forceinline__ ColCtx col(int r, int) const {
     const int t = r >> 6, ty = t >> 1, tx = t & 1, co = r & 63;
-    const int oy = qy - ty, ox = qx - tx;
-    if (oy < 0 || oy >= 9 || ox < 0 || ox >= 9)
-      return nullptr;
-    return dy + ((size_t)(n * 9 + oy) * 9 + ox) * 64 + co;
+    return ColCtx{co - (ty * 9 + tx) * 64, ty, tx};
+  }
+  __device__ __forceinline__ const void *at(const RowCtx &rc, const ColCtx &cc) const {
+    const unsigned oy = (unsigned)(rc.qy - cc.ty), ox = (unsigned)(rc.qx - cc.tx);
+    return (oy < 9u && ox < 9u) ? (const void *)(rc.base + cc.off) : nullptr;
   }
 };
 // conv2 dgrad B: (ci0.., r=(t,co), z) = c2w[co][(ky*4+kx)*32 + ci], ky = py+2ty, kx = px+2tx
@@ -286,11 +343,15 @@ struct W2T {
     return ldg16(w + (size_t)co * 512 + (ky * 4 + kx) * 32 + ci0);
   }
   static constexpr bool kAsync = true;
-  __device__ __forceinline__ const void *ptr(int ci0, int r, int z) const {
+  using RowCtx = int;
+  using ColCtx = const bf16 *;
+  __device__ __forceinline__ RowCtx row(int ci0) const { return ci0; }
+  __device__ __forceinline__ ColCtx col(int r, int z) const {
     const int t = r >> 6, ty = t >> 1, tx = t & 1, co = r & 63;
     const int ky = (z >> 1) + 2 * ty, kx = (z & 1) + 2 * tx;
-    return w + (size_t)co * 512 + (ky * 4 + kx) * 32 + ci0;
+    return w + (size_t)co * 512 + (ky * 4 + kx) * 32;
   }
+  __device__ __forceinline__ const void *at(RowCtx rc, ColCtx cc) const { return cc + rc; }
 };
 
 // ---- epilogues (16 consecutive columns of one row per call) --------------------------------------

@@ -148,6 +148,16 @@ __device__ __forceinline__ void sts16(uint32_t addr, const uint4 &v) {
                "r"(v.w)
                : "memory");
 }
+// MN-major register-path tiles: which index runs fastest over the threads.  Default: the 8-row
+// chunks of one reduction index (contiguous 16-byte pieces of a plain matrix row).  With
+// Op::kPosFastest the 64 reduction indices (im2col positions) run fastest instead: a thread keeps
+// ONE position per k-block (one div/mod chain) and a warp reads neighbouring, overlapping windows.
+template <class Op, class = void> struct PosFastest {
+  static constexpr bool value = false;
+};
+template <class Op> struct PosFastest<Op, decltype((void)Op::kPosFastest)> {
+  static constexpr bool value = Op::kPosFastest;
+};
 template <int ROWS, class Op> struct TileRegs {
   static constexpr int kChunks = ROWS * 8;
   static constexpr int kProducers = kProducerWarps * 32;
@@ -168,7 +178,8 @@ template <int ROWS, class Op> struct TileRegs {
             v[it] = op.load(i, r, z);
         } else {
           constexpr int kRowChunks = ROWS / 8;
-          const int c = q % kRowChunks, k = q / kRowChunks;
+          const int c = PosFastest<Op>::value ? q / BK : q % kRowChunks;
+          const int k = PosFastest<Op>::value ? q % BK : q / kRowChunks;
           const int i = row0 + c * 8, r = r0 + k;
           if (i < rows_total && r < r_end)
             v[it] = op.load(i, r, z);
@@ -187,7 +198,9 @@ template <int ROWS, class Op> struct TileRegs {
           off = (uint32_t)(il * 128 + ((kc ^ (il & 7)) << 4));
         } else {
           constexpr int kRowChunks = ROWS / 8;
-          const int c = q % kRowChunks, k = q / kRowChunks, kr = k & 7;
+          const int c = PosFastest<Op>::value ? q / BK : q % kRowChunks;
+          const int k = PosFastest<Op>::value ? q % BK : q / kRowChunks;
+          const int kr = k & 7;
           off = (uint32_t)((c >> 3) * 8192 + (k >> 3) * 1024 + kr * 128 + (((c & 7) ^ kr) << 4));
         }
         sts16(tile + off, Op::cvt(v[it]));
@@ -200,9 +213,7 @@ template <int ROWS, class Op> struct TileRegs {
 // Operands that already are bf16 in global memory skip the register round trip: every thread copies
 // its 16-byte chunks global -> swizzled shared memory with cp.async.cg (zero-fill for chunks outside
 // the matrix), so STAGES-1 k-blocks of loads are in flight per thread at no register cost.
-// Loader contract (Op::kAsync == true):
-//   K-major : Op::ptr(row, r, z)  -> address of elements (row, r..r+7), or nullptr = eight zeros
-//   MN-major: Op::ptr(row0, r, z) -> address of elements (row0..row0+7, r), or nullptr
+// Loader contract (Op::kAsync == true): see AsyncCtx below.
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void *src) {
   if (src)
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
@@ -221,37 +232,83 @@ template <class Op, class = void> struct IsAsync {
 template <class Op> struct IsAsync<Op, decltype((void)Op::kAsync)> {
   static constexpr bool value = Op::kAsync;
 };
-template <int ROWS, class Op>
-__device__ __forceinline__ void tile_issue_async(const Op &op, uint32_t tile, int row0,
-                                                 int rows_total, int r0, int r_end, int z,
-                                                 int ptid) {
-  constexpr int kChunks = ROWS * 8;
-  constexpr int kProducers = kProducerWarps * 32;
-  constexpr int kPer = (kChunks + kProducers - 1) / kProducers;
+// register buffers a register-path operand wants (Op::kPrefetch, default 2): small raw forms
+// (u8 pixels) can afford to run their loads several k-blocks ahead
+template <class Op, class = void> struct PrefetchDepth {
+  static constexpr int value = 2;
+};
+template <class Op> struct PrefetchDepth<Op, decltype((void)Op::kPrefetch)> {
+  static constexpr int value = Op::kPrefetch;
+};
+// Per-thread state of an asynchronous operand, set up once before the k-loop.  The address of a
+// chunk is split into a ROW part and a REDUCTION part so the div/mod of the im2col views is not
+// repeated for every chunk:
+//   Op::row(i)      -> RowCtx   (i = matrix row; for MN-major operands the first of 8 rows)
+//   Op::col(r, z)   -> ColCtx   (r = reduction index; K-major: first of 8)
+//   Op::at(rc, cc)  -> address of the 16-byte chunk, or nullptr for eight zeros
+// K-major tiles: a thread always serves reduction chunk kc = ptid & 7 of rows il = ptid/8 + 32*it,
+// so its kPer row contexts are fixed and ONE column context per k-block serves all of them.
+// MN-major tiles: a thread always serves row chunk c = ptid % (ROWS/8); only r changes.
+template <int ROWS, class Op, bool kAsyncOp = IsAsync<Op>::value> struct AsyncCtx {
+  __device__ __forceinline__ void init(const Op &, int, int, int) {}
+};
+template <int ROWS, class Op> struct AsyncCtx<ROWS, Op, true> {
+  static constexpr int kChunks = ROWS * 8;
+  static constexpr int kProducers = kProducerWarps * 32;
+  static_assert(kChunks % kProducers == 0, "tile rows must be a multiple of 32");
+  static constexpr int kPer = kChunks / kProducers;
+  static constexpr int kRowChunks = ROWS / 8;
+  static_assert(Op::kMN ? kProducers % kRowChunks == 0 : true, "row chunks must divide 256");
+  static constexpr int kCtx = Op::kMN ? 1 : kPer;
+  typename Op::RowCtx rc[kCtx];
+  uint32_t valid; // bit it: row of chunk `it` is inside the matrix
+  uint32_t off0;  // swizzled offset of chunk 0 inside the tile
+
+  __device__ __forceinline__ void init(const Op &op, int row0, int rows_total, int ptid) {
+    valid = 0u;
+    if constexpr (!Op::kMN) {
+      const int kc = ptid & 7, il0 = ptid >> 3;
+      off0 = (uint32_t)(il0 * 128 + ((kc ^ (il0 & 7)) << 4));
 #pragma unroll
-  for (int it = 0; it < kPer; ++it) {
-    const int q = ptid + it * kProducers;
-    if (kChunks % kProducers == 0 || q < kChunks) {
-      const void *src = nullptr;
-      uint32_t off;
-      if constexpr (!Op::kMN) {
-        const int kc = q & 7, il = q >> 3;
-        const int i = row0 + il, r = r0 + kc * 8;
-        off = (uint32_t)(il * 128 + ((kc ^ (il & 7)) << 4));
-        if (i < rows_total && r < r_end)
-          src = op.ptr(i, r, z);
-      } else {
-        constexpr int kRowChunks = ROWS / 8;
-        const int c = q % kRowChunks, k = q / kRowChunks, kr = k & 7;
-        const int i = row0 + c * 8, r = r0 + k;
-        off = (uint32_t)((c >> 3) * 8192 + (k >> 3) * 1024 + kr * 128 + (((c & 7) ^ kr) << 4));
-        if (i < rows_total && r < r_end)
-          src = op.ptr(i, r, z);
+      for (int it = 0; it < kPer; ++it) {
+        const int i = row0 + il0 + it * 32;
+        rc[it] = op.row(i < rows_total ? i : row0);
+        valid |= (i < rows_total ? 1u : 0u) << it;
       }
-      cp_async16(tile + off, src);
+    } else {
+      const int c = ptid % kRowChunks;
+      const int i = row0 + c * 8;
+      rc[0] = op.row(i < rows_total ? i : row0);
+      valid = i < rows_total ? 1u : 0u;
+      off0 = (uint32_t)((c >> 3) * 8192);
     }
   }
-}
+  __device__ __forceinline__ void issue(const Op &op, uint32_t tile, int r0, int r_end, int z,
+                                        int ptid) const {
+    if constexpr (!Op::kMN) {
+      const int r = r0 + (ptid & 7) * 8;
+      const bool rv = r < r_end;
+      const typename Op::ColCtx cc = op.col(rv ? r : r0, z);
+#pragma unroll
+      for (int it = 0; it < kPer; ++it) {
+        const void *src = (rv && ((valid >> it) & 1u)) ? op.at(rc[it], cc) : nullptr;
+        cp_async16(tile + off0 + (uint32_t)(it * 32 * 128), src);
+      }
+    } else {
+      const int c = ptid % kRowChunks, k0 = ptid / kRowChunks;
+#pragma unroll
+      for (int it = 0; it < kPer; ++it) {
+        const int k = k0 + it * (kProducers / kRowChunks), kr = k & 7;
+        const int r = r0 + k;
+        const uint32_t off = off0 + (uint32_t)((k >> 3) * 1024 + kr * 128 + (((c & 7) ^ kr) << 4));
+        const void *src = nullptr;
+        if (valid && r < r_end)
+          src = op.at(rc[0], op.col(r, z));
+        cp_async16(tile + off, src);
+      }
+    }
+  }
+};
 // register-path tile that compiles to nothing for asynchronous operands
 template <int ROWS, class Op, bool kAsyncOp = IsAsync<Op>::value> struct TileStage {
   TileRegs<ROWS, Op> t;
@@ -259,16 +316,16 @@ template <int ROWS, class Op, bool kAsyncOp = IsAsync<Op>::value> struct TileSta
                                        int z, int ptid) {
     t.load(op, row0, rows_total, r0, r_end, z, ptid);
   }
-  __device__ __forceinline__ void put(const Op &, uint32_t tile, int, int, int, int, int,
-                                      int ptid) const {
+  __device__ __forceinline__ void put(const Op &, const AsyncCtx<ROWS, Op> &, uint32_t tile, int,
+                                      int, int, int ptid) const {
     t.store(tile, ptid);
   }
 };
 template <int ROWS, class Op> struct TileStage<ROWS, Op, true> {
   __device__ __forceinline__ void load(const Op &, int, int, int, int, int, int) {}
-  __device__ __forceinline__ void put(const Op &op, uint32_t tile, int row0, int rows_total, int r0,
-                                      int r_end, int z, int ptid) const {
-    tile_issue_async<ROWS>(op, tile, row0, rows_total, r0, r_end, z, ptid);
+  __device__ __forceinline__ void put(const Op &op, const AsyncCtx<ROWS, Op> &ctx, uint32_t tile,
+                                      int r0, int r_end, int z, int ptid) const {
+    ctx.issue(op, tile, r0, r_end, z, ptid);
   }
 };
 
@@ -328,35 +385,43 @@ __global__ void __launch_bounds__(kThreads, BN <= 128 ? 2 : 1)
     // stored; asynchronous operands are copied straight into the stage.  A stage is handed to the
     // tensor core kLag k-blocks after it was issued, when its cp.async group has landed, so up to
     // STAGES-1 k-blocks of loads are in flight per thread.
-    constexpr int kPF = 2;
+    constexpr int kPF = PrefetchDepth<AOp>::value > PrefetchDepth<BOp>::value
+                            ? PrefetchDepth<AOp>::value
+                            : PrefetchDepth<BOp>::value; // register buffers (loads run kPF-1 ahead)
     constexpr int kLag = STAGES - 2; // k-blocks between issuing a stage and signalling it
     TileStage<BM, AOp> ra[kPF];
     TileStage<kBRows, BOp> rb[kPF];
+    AsyncCtx<BM, AOp> ca;
+    AsyncCtx<kBRows, BOp> cb;
+    ca.init(aop, m0, M, ptid);
+    cb.init(bop, n0, N, ptid);
     auto signal = [&](int kb) {
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0)
         mbar_arrive(&full_bar[kb % STAGES]);
     };
-    if (nkb > 0) {
-      ra[0].load(aop, m0, M, r_begin, r_end, z, ptid);
-      rb[0].load(bop, n0, N, r_begin, r_end, z, ptid);
-    }
+#pragma unroll
+    for (int u = 0; u < kPF - 1; ++u)
+      if (u < nkb) {
+        ra[u].load(aop, m0, M, r_begin + u * BK, r_end, z, ptid);
+        rb[u].load(bop, n0, N, r_begin + u * BK, r_end, z, ptid);
+      }
     for (int kb0 = 0; kb0 < nkb; kb0 += kPF) {
 #pragma unroll
       for (int u = 0; u < kPF; ++u) {
         const int kb = kb0 + u;
         if (kb < nkb) {
-          if (kb + 1 < nkb) {
-            ra[(u + 1) % kPF].load(aop, m0, M, r_begin + (kb + 1) * BK, r_end, z, ptid);
-            rb[(u + 1) % kPF].load(bop, n0, N, r_begin + (kb + 1) * BK, r_end, z, ptid);
+          if (kb + kPF - 1 < nkb) {
+            ra[(u + kPF - 1) % kPF].load(aop, m0, M, r_begin + (kb + kPF - 1) * BK, r_end, z, ptid);
+            rb[(u + kPF - 1) % kPF].load(bop, n0, N, r_begin + (kb + kPF - 1) * BK, r_end, z, ptid);
           }
           const int s = kb % STAGES;
           const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
           mbar_wait(&empty_bar[s], ph ^ 1u);
           const uint32_t st = tiles_s + (uint32_t)(s * kStage);
-          ra[u].put(aop, st, m0, M, r_begin + kb * BK, r_end, z, ptid);
-          rb[u].put(bop, st + kATile, n0, N, r_begin + kb * BK, r_end, z, ptid);
+          ra[u].put(aop, ca, st, r_begin + kb * BK, r_end, z, ptid);
+          rb[u].put(bop, cb, st + kATile, r_begin + kb * BK, r_end, z, ptid);
           cp_async_commit();
           if (kb >= kLag) {
             cp_async_wait<kLag>();
