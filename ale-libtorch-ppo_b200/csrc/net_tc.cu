@@ -99,6 +99,7 @@ struct Col1 {
   }
   const uint8_t *obs; // [n,4,84,84] u8
   using PosPtr = const uint8_t *;
+  __device__ __forceinline__ const void *anchor() const { return obs; }
   __device__ __forceinline__ PosPtr pos_ptr(int) const { return nullptr; } // never async
   __device__ __forceinline__ int k_off(int) const { return 0; }
   __device__ __forceinline__ Raw at(int m, int k) const {
@@ -117,6 +118,7 @@ struct Col2 {
   const bf16 *x; // act1 [n,20,20,32]
   // address of element (m, k) = pos_ptr(m) + k_off(k): the position part and the tap part
   using PosPtr = const bf16 *;
+  __device__ __forceinline__ const void *anchor() const { return x; }
   __device__ __forceinline__ const bf16 *pos_ptr(int m) const {
     const int n = m / 81, pix = m - n * 81, oy = pix / 9, ox = pix - oy * 9;
     return x + ((size_t)(n * 20 + 2 * oy) * 20 + 2 * ox) * 32;
@@ -134,6 +136,7 @@ struct Col3 {
   static constexpr int kPrefetch = 2;
   const bf16 *x; // act2 [n,9,9,64]
   using PosPtr = const bf16 *;
+  __device__ __forceinline__ const void *anchor() const { return x; }
   __device__ __forceinline__ const bf16 *pos_ptr(int m) const {
     const int n = m / 49, pix = m - n * 49, oy = pix / 7, ox = pix - oy * 7;
     return x + ((size_t)(n * 9 + oy) * 9 + ox) * 64;
@@ -159,6 +162,7 @@ template <class Col> struct ColK {
   using ColCtx = int;                                           // tap part (element offset)
   __device__ __forceinline__ RowCtx row(int m) const { return src.pos_ptr(m); }
   __device__ __forceinline__ ColCtx col(int k, int) const { return src.k_off(k); }
+  __device__ __forceinline__ const void *anchor() const { return src.anchor(); }
   __device__ __forceinline__ const void *at(RowCtx rc, ColCtx cc) const { return rc + cc; }
 };
 // MN-major A operand of a conv wgrad: rows = k (plus a ones row at k == K for the bias), r = m.
@@ -187,6 +191,7 @@ template <class Col, int K> struct ColMN {
   using ColCtx = typename Col::PosPtr;
   __device__ __forceinline__ RowCtx row(int k0) const { return k0 < K ? src.k_off(k0) : -1; }
   __device__ __forceinline__ ColCtx col(int m, int) const { return src.pos_ptr(m); }
+  __device__ __forceinline__ const void *anchor() const { return src.anchor(); }
   __device__ __forceinline__ const void *at(RowCtx rc, ColCtx cc) const {
     return rc >= 0 ? (const void *)(cc + rc) : (const void *)&g_ones_chunk;
   }
@@ -205,6 +210,7 @@ struct RowsK {
   using ColCtx = int;
   __device__ __forceinline__ RowCtx row(int i) const { return p + (size_t)i * ld; }
   __device__ __forceinline__ ColCtx col(int r, int) const { return r; }
+  __device__ __forceinline__ const void *anchor() const { return p; }
   __device__ __forceinline__ const void *at(RowCtx rc, ColCtx cc) const { return rc + cc; }
 };
 // fp32 matrix [rows][ld] converted on the fly: K-major view
@@ -232,6 +238,7 @@ struct ColsMN {
   using ColCtx = const bf16 *;
   __device__ __forceinline__ RowCtx row(int i0) const { return i0 < ld ? i0 : -1; }
   __device__ __forceinline__ ColCtx col(int r, int) const { return p + (size_t)r * ld; }
+  __device__ __forceinline__ const void *anchor() const { return p; }
   __device__ __forceinline__ const void *at(RowCtx rc, ColCtx cc) const {
     return rc >= 0 ? (const void *)(cc + rc) : (const void *)&g_ones_chunk;
   }
@@ -274,6 +281,7 @@ struct DCol3 {
     const int t = r >> 6, ky = t / 3, kx = t - ky * 3, co = r & 63;
     return ColCtx{co - (ky * 7 + kx) * 64, ky, kx};
   }
+  __device__ __forceinline__ const void *anchor() const { return dy; }
   __device__ __forceinline__ const void *at(const RowCtx &rc, const ColCtx &cc) const {
     const unsigned oy = (unsigned)(rc.iy - cc.ky), ox = (unsigned)(rc.ix - cc.kx);
     return (oy < 7u && ox < 7u) ? (const void *)(rc.base + cc.off) : nullptr;
@@ -296,6 +304,7 @@ struct W3T {
     const int t = r >> 6, co = r & 63;
     return w + (size_t)co * 576 + t * 64;
   }
+  __device__ __forceinline__ const void *anchor() const { return w; }
   __device__ __forceinline__ const void *at(RowCtx rc, ColCtx cc) const { return cc + rc; }
 };
 // conv2 dgrad A, parity class z = py*2+px: rows (n,qy,qx) of 10x10, r = (ty*2+tx)*64 + co
@@ -327,6 +336,7 @@ struct DCol2 {
     const int t = r >> 6, ty = t >> 1, tx = t & 1, co = r & 63;
     return ColCtx{co - (ty * 9 + tx) * 64, ty, tx};
   }
+  __device__ __forceinline__ const void *anchor() const { return dy; }
   __device__ __forceinline__ const void *at(const RowCtx &rc, const ColCtx &cc) const {
     const unsigned oy = (unsigned)(rc.qy - cc.ty), ox = (unsigned)(rc.qx - cc.tx);
     return (oy < 9u && ox < 9u) ? (const void *)(rc.base + cc.off) : nullptr;
@@ -351,6 +361,7 @@ struct W2T {
     const int ky = (z >> 1) + 2 * ty, kx = (z & 1) + 2 * tx;
     return w + (size_t)co * 512 + (ky * 4 + kx) * 32;
   }
+  __device__ __forceinline__ const void *anchor() const { return w; }
   __device__ __forceinline__ const void *at(RowCtx rc, ColCtx cc) const { return cc + rc; }
 };
 

@@ -23,6 +23,8 @@
 #pragma once
 #include <cuda_bf16.h>
 
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace alegpu {
@@ -43,17 +45,18 @@ __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+constexpr uint32_t kSuspendHintNs = 20000u;
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
   const uint32_t a = smem_u32(bar);
   asm volatile("{\n\t"
                ".reg .pred p;\n\t"
                "WAIT_%=:\n\t"
-               "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+               "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
                "@p bra DONE_%=;\n\t"
                "bra WAIT_%=;\n\t"
                "DONE_%=:\n\t"
                "}" ::"r"(a),
-               "r"(parity)
+               "r"(parity), "r"(kSuspendHintNs) // the wait sleeps in hardware instead of spinning
                : "memory");
 }
 __device__ __forceinline__ void fence_barrier_init() {
@@ -214,11 +217,13 @@ template <int ROWS, class Op> struct TileRegs {
 // its 16-byte chunks global -> swizzled shared memory with cp.async.cg (zero-fill for chunks outside
 // the matrix), so STAGES-1 k-blocks of loads are in flight per thread at no register cost.
 // Loader contract (Op::kAsync == true): see AsyncCtx below.
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src) {
-  if (src)
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
-  else // nothing to copy: plain zero store (ordered with the later fence.proxy.async like the copies)
-    asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" ::"r"(dst), "r"(0u) : "memory");
+// `fallback` is any mapped global address: with src-size 0 nothing is read and the 16 bytes are
+// zero-filled, so chunks outside the matrix need no branch
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src, const void *fallback) {
+  const uint32_t bytes = src ? 16u : 0u;
+  const void *p = src ? src : fallback;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(p), "r"(bytes)
+               : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() {
   asm volatile("cp.async.commit_group;" ::: "memory");
@@ -292,7 +297,7 @@ template <int ROWS, class Op> struct AsyncCtx<ROWS, Op, true> {
 #pragma unroll
       for (int it = 0; it < kPer; ++it) {
         const void *src = (rv && ((valid >> it) & 1u)) ? op.at(rc[it], cc) : nullptr;
-        cp_async16(tile + off0 + (uint32_t)(it * 32 * 128), src);
+        cp_async16(tile + off0 + (uint32_t)(it * 32 * 128), src, op.anchor());
       }
     } else {
       const int c = ptid % kRowChunks, k0 = ptid / kRowChunks;
@@ -304,7 +309,7 @@ template <int ROWS, class Op> struct AsyncCtx<ROWS, Op, true> {
         const void *src = nullptr;
         if (valid && r < r_end)
           src = op.at(rc[0], op.col(r, z));
-        cp_async16(tile + off, src);
+        cp_async16(tile + off, src, op.anchor());
       }
     }
   }
@@ -337,6 +342,13 @@ __host__ __device__ constexpr uint32_t tmem_cols(int bn) { return bn <= 32 ? 32u
 
 // Epilogue contract: epi(i, j0, v, z) receives 16 consecutive columns j0..j0+15 of row i
 // (only for i < M and j0 < N; columns >= N inside the group must be skipped by the functor).
+//
+// A CTA owns one (n-tile, split z) and walks the m-tiles blockIdx.x, blockIdx.x + gridDim.x, ...
+// (gridDim.x == number of m-tiles gives the plain one-tile-per-CTA kernel).  Tiles are software
+// pipelined: the accumulator is double-buffered in tensor memory, the operand ring keeps running
+// across tile boundaries, and the producer warps issue the loads of tile t+1 BEFORE they run the
+// epilogue of tile t, so for the short-reduction layers (4 k-blocks per tile) load latency, MMA
+// and epilogue of neighbouring tiles overlap instead of adding up per CTA.
 template <int BN, int STAGES, class AOp, class BOp, class Epi>
 __global__ void __launch_bounds__(kThreads, BN <= 128 ? 2 : 1)
     gemm_tc_kernel(const AOp aop, const BOp bop, const Epi epi, int M, int N, int R,
@@ -346,16 +358,17 @@ __global__ void __launch_bounds__(kThreads, BN <= 128 ? 2 : 1)
   constexpr int kATile = tile_bytes(BM), kBTile = tile_bytes(BN < 64 ? 64 : BN);
   constexpr int kStage = kATile + kBTile;
   constexpr uint32_t kIdesc = make_idesc(BN, AOp::kMN, BOp::kMN);
-  constexpr uint32_t kCols = tmem_cols(BN);
+  constexpr uint32_t kCols = tmem_cols(BN); // per accumulator buffer; two are allocated
 
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], accum_bar;
+  __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], acc_full[2], acc_empty[2];
   __shared__ uint32_t tmem_slot;
   // SWIZZLE_128B atoms need 1024-byte alignment
   uint8_t *tiles = reinterpret_cast<uint8_t *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN, z = blockIdx.z;
+  const int n0 = blockIdx.y * BN, z = blockIdx.z;
+  const int m_tiles = (M + BM - 1) / BM;
   const int r_begin = r_per_split > 0 ? z * r_per_split : 0;
   const int r_end = r_per_split > 0 ? min(R, r_begin + r_per_split) : R;
   const int nkb = (r_end - r_begin + BK - 1) / BK;
@@ -366,136 +379,175 @@ __global__ void __launch_bounds__(kThreads, BN <= 128 ? 2 : 1)
       mbar_init(&full_bar[s], kProducerWarps);
       mbar_init(&empty_bar[s], 1);
     }
-    mbar_init(&accum_bar, 1);
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&acc_full[b], 1);
+      mbar_init(&acc_empty[b], kProducerWarps);
+    }
     fence_barrier_init();
   }
   if (warp == kProducerWarps)
-    tmem_alloc(&tmem_slot, kCols);
+    tmem_alloc(&tmem_slot, 2 * kCols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
 
   if (warp < kProducerWarps) {
-    // ===== producers: gather -> registers -> swizzled smem (loads run one k-block ahead) ========
+    // ===== producers (and epilogue) ================================================================
     const int ptid = threadIdx.x;
     constexpr int kBRows = BN < 64 ? 64 : BN;
     const uint32_t tiles_s = smem_u32(tiles);
-    // Register-path operands (u8 / fp32 sources) are loaded one k-block ahead and converted when
+    // Register-path operands (u8 / fp32 sources) are loaded kPF-1 k-blocks ahead and converted when
     // stored; asynchronous operands are copied straight into the stage.  A stage is handed to the
     // tensor core kLag k-blocks after it was issued, when its cp.async group has landed, so up to
     // STAGES-1 k-blocks of loads are in flight per thread.
     constexpr int kPF = PrefetchDepth<AOp>::value > PrefetchDepth<BOp>::value
                             ? PrefetchDepth<AOp>::value
-                            : PrefetchDepth<BOp>::value; // register buffers (loads run kPF-1 ahead)
+                            : PrefetchDepth<BOp>::value;
     constexpr int kLag = STAGES - 2; // k-blocks between issuing a stage and signalling it
+    static_assert(kLag >= 0 && kLag <= 4, "drain below is unrolled for kLag <= 4");
     TileStage<BM, AOp> ra[kPF];
     TileStage<kBRows, BOp> rb[kPF];
     AsyncCtx<BM, AOp> ca;
     AsyncCtx<kBRows, BOp> cb;
-    ca.init(aop, m0, M, ptid);
     cb.init(bop, n0, N, ptid);
-    auto signal = [&](int kb) {
+    auto signal = [&](int g) { // g = k-block number counted over all tiles of this CTA
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0)
-        mbar_arrive(&full_bar[kb % STAGES]);
+        mbar_arrive(&full_bar[g % STAGES]);
     };
+    // issue every k-block of m-tile mt (global k-block numbers gbase..); signals all but the last
+    // kLag of them
+    auto issue_tile = [&](int mt, int gbase) {
+      const int m0 = mt * BM;
+      ca.init(aop, m0, M, ptid);
 #pragma unroll
-    for (int u = 0; u < kPF - 1; ++u)
-      if (u < nkb) {
-        ra[u].load(aop, m0, M, r_begin + u * BK, r_end, z, ptid);
-        rb[u].load(bop, n0, N, r_begin + u * BK, r_end, z, ptid);
-      }
-    for (int kb0 = 0; kb0 < nkb; kb0 += kPF) {
+      for (int u = 0; u < kPF - 1; ++u)
+        if (u < nkb) {
+          ra[u].load(aop, m0, M, r_begin + u * BK, r_end, z, ptid);
+          rb[u].load(bop, n0, N, r_begin + u * BK, r_end, z, ptid);
+        }
+      for (int kb0 = 0; kb0 < nkb; kb0 += kPF) {
 #pragma unroll
-      for (int u = 0; u < kPF; ++u) {
-        const int kb = kb0 + u;
-        if (kb < nkb) {
-          if (kb + kPF - 1 < nkb) {
-            ra[(u + kPF - 1) % kPF].load(aop, m0, M, r_begin + (kb + kPF - 1) * BK, r_end, z, ptid);
-            rb[(u + kPF - 1) % kPF].load(bop, n0, N, r_begin + (kb + kPF - 1) * BK, r_end, z, ptid);
-          }
-          const int s = kb % STAGES;
-          const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
-          mbar_wait(&empty_bar[s], ph ^ 1u);
-          const uint32_t st = tiles_s + (uint32_t)(s * kStage);
-          ra[u].put(aop, ca, st, r_begin + kb * BK, r_end, z, ptid);
-          rb[u].put(bop, cb, st + kATile, r_begin + kb * BK, r_end, z, ptid);
-          cp_async_commit();
-          if (kb >= kLag) {
-            cp_async_wait<kLag>();
-            signal(kb - kLag);
+        for (int u = 0; u < kPF; ++u) {
+          const int kb = kb0 + u;
+          if (kb < nkb) {
+            if (kb + kPF - 1 < nkb) {
+              ra[(u + kPF - 1) % kPF].load(aop, m0, M, r_begin + (kb + kPF - 1) * BK, r_end, z, ptid);
+              rb[(u + kPF - 1) % kPF].load(bop, n0, N, r_begin + (kb + kPF - 1) * BK, r_end, z, ptid);
+            }
+            const int g = gbase + kb, s = g % STAGES;
+            const uint32_t ph = (uint32_t)(g / STAGES) & 1u;
+            mbar_wait(&empty_bar[s], ph ^ 1u);
+            const uint32_t st = tiles_s + (uint32_t)(s * kStage);
+            ra[u].put(aop, ca, st, r_begin + kb * BK, r_end, z, ptid);
+            rb[u].put(bop, cb, st + kATile, r_begin + kb * BK, r_end, z, ptid);
+            cp_async_commit();
+            if (kb >= kLag) {
+              cp_async_wait<kLag>();
+              signal(g - kLag);
+            }
           }
         }
       }
-    }
-    // drain: the last kLag stages
-    static_assert(kLag >= 0 && kLag <= 4, "drain below is unrolled for kLag <= 4");
+    };
+    auto drain_tile = [&](int gbase) { // the last kLag stages of the tile
 #define ALEGPU_TC_DRAIN(T)                                                                         \
   if constexpr (kLag > (T)) {                                                                      \
     if (nkb - 1 - (T) >= 0) {                                                                      \
       cp_async_wait<(T)>();                                                                        \
-      signal(nkb - 1 - (T));                                                                       \
+      signal(gbase + nkb - 1 - (T));                                                               \
     }                                                                                              \
   }
-    ALEGPU_TC_DRAIN(3)
-    ALEGPU_TC_DRAIN(2)
-    ALEGPU_TC_DRAIN(1)
-    ALEGPU_TC_DRAIN(0)
+      ALEGPU_TC_DRAIN(3)
+      ALEGPU_TC_DRAIN(2)
+      ALEGPU_TC_DRAIN(1)
+      ALEGPU_TC_DRAIN(0)
 #undef ALEGPU_TC_DRAIN
-    // ===== epilogue: TMEM -> registers -> fused functor ========================================
-    if (nkb > 0) {
-      mbar_wait(&accum_bar, 0u);
-      tc_fence_after();
-    }
-    const int quarter = warp & 3, half = warp >> 2;
-    const int i = m0 + quarter * 32 + lane;
-    constexpr int kColsPerHalf = BN / 2;
-#pragma unroll
-    for (int c = 0; c < kColsPerHalf; c += 16) {
-      const int col = half * kColsPerHalf + c;
-      float v[16];
+    };
+    // TMEM -> registers -> fused functor, for the tile whose accumulator sits in buffer it & 1
+    auto epilogue = [&](int mt, int it) {
+      const int buf = it & 1;
       if (nkb > 0) {
-        tmem_ld16(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)col, v);
-      } else {
-#pragma unroll
-        for (int t = 0; t < 16; ++t)
-          v[t] = 0.0f;
+        mbar_wait(&acc_full[buf], (uint32_t)(it >> 1) & 1u);
+        tc_fence_after();
       }
-      if (i < M && n0 + col < N)
-        epi(i, n0 + col, v, z);
+      const int quarter = warp & 3, half = warp >> 2;
+      const int i = mt * BM + quarter * 32 + lane;
+      constexpr int kColsPerHalf = BN / 2;
+#pragma unroll
+      for (int c = 0; c < kColsPerHalf; c += 16) {
+        const int col = half * kColsPerHalf + c;
+        float v[16];
+        if (nkb > 0) {
+          tmem_ld16(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * kCols + col), v);
+        } else {
+#pragma unroll
+          for (int t = 0; t < 16; ++t)
+            v[t] = 0.0f;
+        }
+        if (i < M && n0 + col < N)
+          epi(i, n0 + col, v, z);
+      }
+      if (nkb > 0) { // this warp has read its part of the accumulator buffer: hand it back
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0)
+          mbar_arrive(&acc_empty[buf]);
+      }
+    };
+    int mt = blockIdx.x, it = 0;
+    if (mt < m_tiles) {
+      issue_tile(mt, 0);
+      drain_tile(0);
+    }
+    for (; mt < m_tiles; mt += gridDim.x, ++it) {
+      const int nxt = mt + gridDim.x;
+      if (nxt < m_tiles)
+        issue_tile(nxt, (it + 1) * nkb);
+      epilogue(mt, it);
+      if (nxt < m_tiles)
+        drain_tile((it + 1) * nkb);
     }
   } else if (lane == 0) {
     // ===== MMA issuer: one thread drives the tensor core =========================================
-    for (int kb = 0; kb < nkb; ++kb) {
-      const int s = kb % STAGES;
-      const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
-      mbar_wait(&full_bar[s], ph);
+    int g = 0, it = 0;
+    for (int mt = blockIdx.x; mt < m_tiles && nkb > 0; mt += gridDim.x, ++it) {
+      const int buf = it & 1;
+      if (it >= 2) // the epilogue of tile it-2 has drained this accumulator buffer
+        mbar_wait(&acc_empty[buf], ((uint32_t)(it >> 1) & 1u) ^ 1u);
       tc_fence_after();
-      const uint32_t a_addr = smem_u32(tiles + s * kStage), b_addr = a_addr + kATile;
-      const uint64_t adesc = make_smem_desc(a_addr, AOp::kMN ? 8192u : 16u, 1024u);
-      const uint64_t bdesc = make_smem_desc(b_addr, BOp::kMN ? 8192u : 16u, 1024u);
+      const uint32_t tmem_d = tmem_base + (uint32_t)(buf * kCols);
+      for (int kb = 0; kb < nkb; ++kb, ++g) {
+        const int s = g % STAGES;
+        const uint32_t ph = (uint32_t)(g / STAGES) & 1u;
+        mbar_wait(&full_bar[s], ph);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(tiles + s * kStage), b_addr = a_addr + kATile;
+        const uint64_t adesc = make_smem_desc(a_addr, AOp::kMN ? 8192u : 16u, 1024u);
+        const uint64_t bdesc = make_smem_desc(b_addr, BOp::kMN ? 8192u : 16u, 1024u);
 #pragma unroll
-      for (int kk = 0; kk < BK / 16; ++kk) {
-        const uint64_t ad = adesc + (uint64_t)(kk * (AOp::kMN ? 128 : 2));
-        const uint64_t bd = bdesc + (uint64_t)(kk * (BOp::kMN ? 128 : 2));
-        umma_bf16(tmem_base, ad, bd, kIdesc, (uint32_t)((kb | kk) != 0));
+        for (int kk = 0; kk < BK / 16; ++kk) {
+          const uint64_t ad = adesc + (uint64_t)(kk * (AOp::kMN ? 128 : 2));
+          const uint64_t bd = bdesc + (uint64_t)(kk * (BOp::kMN ? 128 : 2));
+          umma_bf16(tmem_d, ad, bd, kIdesc, (uint32_t)((kb | kk) != 0));
+        }
+        umma_commit(&empty_bar[s]); // slot reusable once these UMMAs have read it
       }
-      umma_commit(&empty_bar[s]); // slot reusable once these UMMAs have read it
+      umma_commit(&acc_full[buf]);
     }
-    if (nkb > 0)
-      umma_commit(&accum_bar);
   }
   tc_fence_before();
   __syncthreads();
   if (warp == kProducerWarps)
-    tmem_dealloc(tmem_base, kCols);
+    tmem_dealloc(tmem_base, 2 * kCols);
 }
 
 template <int BN, int STAGES, class AOp, class BOp, class Epi>
 int launch_gemm_tc(const AOp &a, const BOp &b, const Epi &e, int64_t M, int64_t N, int64_t R,
-                   int zdim, int r_per_split, cudaStream_t s) {
+                   int zdim, int r_per_split, cudaStream_t s, bool persistent = true) {
   if (M <= 0 || N <= 0)
     return ALEGPU_OK;
   auto kern = gemm_tc_kernel<BN, STAGES, AOp, BOp, Epi>;
@@ -506,7 +558,12 @@ int launch_gemm_tc(const AOp &a, const BOp &b, const Epi &e, int64_t M, int64_t 
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
     configured = true;
   }
-  dim3 grid((unsigned)ceil_div(M, BM), (unsigned)ceil_div(N, BN), (unsigned)zdim);
+  // more tiles than resident CTA slots: each CTA walks several m-tiles (pipelined across tiles)
+  int64_t gx = ceil_div(M, BM);
+  const int64_t gy = ceil_div(N, BN), slots = (int64_t)kNumSMs * (BN <= 128 ? 2 : 1);
+  if (persistent && gx * gy * zdim > slots)
+    gx = std::max<int64_t>(1, std::min<int64_t>(gx, slots / (gy * zdim)));
+  dim3 grid((unsigned)gx, (unsigned)gy, (unsigned)zdim);
   kern<<<grid, kThreads, kSmem, s>>>(a, b, e, (int)M, (int)N, (int)R, r_per_split);
   ALEGPU_COUNT_LAUNCH_NAMED(__PRETTY_FUNCTION__);
   ALEGPU_LAUNCH_CHECK();
