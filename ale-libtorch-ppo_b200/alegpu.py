@@ -366,6 +366,10 @@ class Buffer:
                      self.returns.view(0, (N,)), self.masks.view(0, (N,)))
 
 
+class _TrainOptions(C.Structure):
+    _fields_ = [("indices", C.c_void_p), ("normalize_advantages", C.c_int)]
+
+
 class Learner:
     """Network (src/bin/train.cc:230-269) + Adam (:360-362) + ai::ppo::train::train."""
 
@@ -425,6 +429,31 @@ class Learner:
         synchronize(self.stream)
         return lg.numpy(), v.numpy()
 
+    def act(self, observations, uniforms=None, seed=0, step=0, buffer=None, t=None):
+        """The action selector of src/bin/train.cc:367-379 (alegpu_learner_act): returns
+        (actions [E] i64, logits [E,A], values [E]).  With buffer/t the three outputs are ALSO
+        written into column t of the rollout storage (Buffer::add's job, buffer.cc:41-56)."""
+        o = _dev(observations, np.uint8)
+        E, A = o.shape[0], self.action_size
+        u = _dev(uniforms, np.float32) if uniforms is not None else None
+        dense = DeviceArray.zeros(E, np.int64)
+        if buffer is not None:
+            T = buffer.T
+            lg, v, ac = buffer.logits, buffer.values, buffer.actions
+            lp, vp, ap = lg.ptr + 4 * t * A, v.ptr + 4 * t, ac.ptr + 8 * t
+            ls, vs, as_ = T * A, T, T
+        else:
+            lg, v = DeviceArray.zeros((E, A), np.float32), DeviceArray.zeros(E, np.float32)
+            lp, vp, ap, ls, vs, as_ = lg.ptr, v.ptr, None, A, 1, 0
+        _check(lib().alegpu_learner_act(self.h, _p(o), C.c_int64(E), _p(u) if u is not None else None,
+                                        C.c_uint64(seed), C.c_uint64(step), C.c_void_p(lp),
+                                        C.c_int64(ls), C.c_void_p(vp), C.c_int64(vs),
+                                        C.c_void_p(ap), C.c_int64(as_), _p(dense), None))
+        synchronize(self.stream)
+        if buffer is not None:
+            return (dense.numpy(), lg.numpy().reshape(E, T, A)[:, t], v.numpy().reshape(E, T)[:, t])
+        return dense.numpy(), lg.numpy(), v.numpy()
+
     def activations(self, n):
         c1 = np.zeros((n, 32, 20, 20), np.float32)
         c2 = np.zeros((n, 64, 9, 9), np.float32)
@@ -454,14 +483,18 @@ class Learner:
         return float(tn.value)
 
     def train(self, batch, metrics, num_epochs, num_mini_batches, hp, cuda_graph=False,
-              sync=True):
-        """ai::ppo::train::train — src/ai/ppo/train.h:133-157."""
+              sync=True, indices=None, normalize_advantages=False):
+        """ai::ppo::train::train — src/ai/ppo/train.h:133-157.  indices ([epochs*N] int64 row
+        order) and normalize_advantages are the opt-in extras of alegpu_train_options."""
         cb = batch._c()
         cm = metrics._c() if metrics is not None else None
-        _check(lib().alegpu_learner_train(self.h, C.byref(cb),
-                                          C.byref(cm) if cm is not None else None,
-                                          C.c_int64(num_epochs), C.c_int64(num_mini_batches),
-                                          C.byref(hp), 1 if cuda_graph else 0))
+        self._idx = _dev(indices, np.int64) if indices is not None else None
+        opt = _TrainOptions(self._idx.ptr if self._idx is not None else None,
+                            1 if normalize_advantages else 0)
+        _check(lib().alegpu_learner_train_ex(self.h, C.byref(cb),
+                                             C.byref(cm) if cm is not None else None,
+                                             C.c_int64(num_epochs), C.c_int64(num_mini_batches),
+                                             C.byref(hp), C.byref(opt), 1 if cuda_graph else 0))
         if sync:
             synchronize(self.stream)
 

@@ -75,7 +75,14 @@ __global__ void __launch_bounds__(kThreads)
         if (a < A)
           ol[a] = L.old_log_probs[i * A + a];
       const bool m = L.masks[i] != 0;
-      const float adv = L.advantages[i], ret = L.returns[i];
+      const float adv_raw = L.advantages[i];
+      float adv = adv_raw;
+      const float ret = L.returns[i];
+      if (L.adv_stats) { // every thread derives the same (mean, 1/(std+eps)) from the 3 doubles
+        const double c = L.adv_stats[0], mean = L.adv_stats[1] / c;
+        const double var = (L.adv_stats[2] - c * mean * mean) / (c - 1.0);
+        adv = (float)(((double)adv - mean) / (sqrt(fmax(var, 0.0)) + 1e-8));
+      }
       const PpoSample s = ppo_sample<kMaxA>(z, ol, A, (int)L.actions[i], adv, v, ret, L.clip,
                                             L.vcoef, L.ecoef, m ? inv : 0.0f, dz, &dv);
       if (lane == 0) {
@@ -84,7 +91,7 @@ __global__ void __launch_bounds__(kThreads)
         if (L.m_entropy) L.m_entropy[i] = s.entropy;
         if (L.m_total) L.m_total[i] = s.total;
         if (L.m_ratio) L.m_ratio[i] = s.ratio;
-        if (L.m_adv) L.m_adv[i] = adv;
+        if (L.m_adv) L.m_adv[i] = adv_raw;
         if (L.m_ret) L.m_ret[i] = ret;
         if (L.m_masks) L.m_masks[i] = m ? 1 : 0;
         for (int a = 0; a < A; ++a)
@@ -222,7 +229,73 @@ int launch_heads(const NetParams &P, const float *fc, int64_t n, float *logits, 
   return ALEGPU_OK;
 }
 
+// ---- rollout-side action selection ------------------------------------------------------------
+// The reference's action selector (src/bin/train.cc:367-379): probabilities = softmax(logits),
+// actions = multinomial(probabilities, 1).  One thread per env draws by inverse CDF: the action is
+// the first a with cumsum(p)[a] > u, u in [0,1) either supplied per env (parity runs) or generated
+// from a counter-based hash of (seed, step, env) — libtorch's Philox stream cannot be reproduced,
+// so parity with the reference is distributional (tests: chi-square against softmax).
+__device__ __forceinline__ float act_uniform(uint64_t seed, uint64_t step, uint64_t env) {
+  uint64_t x = seed ^ (step * 0x9E3779B97F4A7C15ull) ^ (env * 0xD1B54A32D192ED03ull);
+  x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull; // splitmix64 finaliser
+  x ^= x >> 27; x *= 0x94D049BB133111EBull;
+  x ^= x >> 31;
+  return (float)(x >> 40) * (1.0f / 16777216.0f); // 24 random bits -> [0,1)
+}
+__global__ void act_sample_kernel(const float *__restrict__ logits_in,
+                                  const float *__restrict__ values_in, int64_t n, int A,
+                                  const float *__restrict__ uniforms, uint64_t seed, uint64_t step,
+                                  float *__restrict__ logits_out, int64_t logits_stride,
+                                  float *__restrict__ values_out, int64_t values_stride,
+                                  int64_t *__restrict__ actions_out, int64_t actions_stride,
+                                  int64_t *__restrict__ actions_dense) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n)
+    return;
+  const float *z = logits_in + i * A;
+  float mx = z[0];
+  for (int a = 1; a < A; ++a)
+    mx = fmaxf(mx, z[a]);
+  float sum = 0.0f;
+  for (int a = 0; a < A; ++a)
+    sum += expf(z[a] - mx);
+  const float u = uniforms ? uniforms[i] : act_uniform(seed, step, (uint64_t)i);
+  float cum = 0.0f;
+  int act = A - 1;
+  for (int a = 0; a < A; ++a) {
+    cum += expf(z[a] - mx) / sum;
+    if (cum > u) {
+      act = a;
+      break;
+    }
+  }
+  if (logits_out)
+    for (int a = 0; a < A; ++a)
+      logits_out[i * logits_stride + a] = z[a];
+  if (values_out)
+    values_out[i * values_stride] = values_in[i];
+  if (actions_out)
+    actions_out[i * actions_stride] = act;
+  if (actions_dense)
+    actions_dense[i] = act;
+}
+
 } // namespace
+
+int launch_act_sample(const float *logits, const float *values, int64_t n, int A,
+                      const float *uniforms, uint64_t seed, uint64_t step, float *logits_out,
+                      int64_t logits_stride, float *values_out, int64_t values_stride,
+                      int64_t *actions_out, int64_t actions_stride, int64_t *actions_dense,
+                      cudaStream_t s) {
+  if (n == 0)
+    return ALEGPU_OK;
+  act_sample_kernel<<<(unsigned)ceil_div(n, 128), 128, 0, s>>>(
+      logits, values, n, A, uniforms, seed, step, logits_out, logits_stride, values_out,
+      values_stride, actions_out, actions_stride, actions_dense);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}
 
 int heads_forward(const NetParams &P, const float *fc, int64_t n, float *logits, float *values,
                   cudaStream_t s) {

@@ -14,6 +14,7 @@
 #include <memory>
 #include <vector>
 
+#include "minibatch.h"
 #include "net.h"
 #include "net_tc.h"
 #include "optim.h"
@@ -104,6 +105,10 @@ struct alegpu_learner {
   size_t ws_floats = 0;
   float *norm_partials = nullptr, *loss_partials = nullptr, *counts = nullptr, *scalars = nullptr;
   int64_t counts_cap = 0;
+  // opt-in minibatch preparation (alegpu_train_options): gather staging, advantage statistics
+  StagedBatch staged;
+  double *adv_stats = nullptr;
+  int *gather_error = nullptr;
   OptState *opt = nullptr;
   int64_t host_step = 0;
   double lr = 0.0;
@@ -235,13 +240,32 @@ int clip_and_step(alegpu_learner *L, float max_norm, float *total_norm_out) {
 }
 
 // the body of train(): everything is stream-ordered, nothing synchronises
+int ensure_staging(alegpu_learner *L) {
+  if (L->staged.obs)
+    return ALEGPU_OK;
+  const size_t cap = (size_t)L->cap, A = (size_t)L->cfg.action_size;
+  ALEGPU_CUDA_CHECK(cudaMalloc(&L->staged.obs, cap * 28224));
+  ALEGPU_CUDA_CHECK(cudaMalloc(&L->staged.actions, cap * sizeof(int64_t)));
+  ALEGPU_CUDA_CHECK(cudaMalloc(&L->staged.logp, cap * A * sizeof(float)));
+  ALEGPU_CUDA_CHECK(cudaMalloc(&L->staged.adv, cap * sizeof(float)));
+  ALEGPU_CUDA_CHECK(cudaMalloc(&L->staged.ret, cap * sizeof(float)));
+  ALEGPU_CUDA_CHECK(cudaMalloc(&L->staged.masks, cap));
+  ALEGPU_CUDA_CHECK(cudaMalloc(&L->gather_error, sizeof(int)));
+  ALEGPU_CUDA_CHECK(cudaMemset(L->gather_error, 0, sizeof(int)));
+  return ALEGPU_OK;
+}
+
 int enqueue_train(alegpu_learner *L, const alegpu_batch &b, const alegpu_metrics &mt,
-                  int64_t epochs, int64_t nmb, const alegpu_hyperparameters &hp) {
+                  int64_t epochs, int64_t nmb, const alegpu_hyperparameters &hp,
+                  const alegpu_train_options &opt) {
   const int64_t mb = b.size / nmb, A = L->cfg.action_size;
-  if (int rc = launch_mask_count(b.masks, mb, nmb, L->counts, L->stream))
-    return rc;
+  const bool shuffled = opt.indices != nullptr;
+  // contiguous slices: the per-minibatch unmasked counts are known up front; shuffled: per step
+  if (!shuffled)
+    if (int rc = launch_mask_count(b.masks, mb, nmb, L->counts, L->stream))
+      return rc;
 #ifdef ALEGPU_WITH_NCCL
-  if (L->cfg.world_size > 1) { // the loss normaliser is the GLOBAL unmasked count (losses.cc:19)
+  if (L->cfg.world_size > 1 && !shuffled) { // the loss normaliser is the GLOBAL unmasked count (losses.cc:19)
     ncclResult_t r = nccl().AllReduce(L->counts, L->counts, (size_t)nmb, ncclFloat, ncclSum, L->comm,
                                    L->stream);
     if (r != ncclSuccess)
@@ -253,18 +277,57 @@ int enqueue_train(alegpu_learner *L, const alegpu_batch &b, const alegpu_metrics
     for (int64_t k = 0; k < nmb; ++k) {
       const int64_t s = k * mb, o = (ep * nmb + k) * mb; // train.h:149-151 contiguous slice
       const uint8_t *obs = b.observations + s * 28224;
-      if (int rc = forward(L, obs, mb))
-        return rc;
       LossArgs la{};
       la.actions = b.actions + s;
       la.old_log_probs = b.log_probabilities + s * A;
       la.advantages = b.advantages + s;
       la.returns = b.returns + s;
       la.masks = b.masks + s;
+      float *count = L->counts + k;
+      if (shuffled) { // minibatch k of epoch ep = rows indices[ep*N + k*mb ...], gathered once
+        if (int rc = launch_gather_rows(opt.indices + ep * b.size + s, mb, b.size, (int)A,
+                                        b.observations, b.actions, b.log_probabilities,
+                                        b.advantages, b.returns, b.masks, L->staged,
+                                        L->gather_error, L->stream))
+          return rc;
+        obs = L->staged.obs;
+        la.actions = L->staged.actions;
+        la.old_log_probs = L->staged.logp;
+        la.advantages = L->staged.adv;
+        la.returns = L->staged.ret;
+        la.masks = L->staged.masks;
+        count = L->counts + (ep * nmb + k) % L->counts_cap;
+        if (int rc = launch_mask_count(la.masks, mb, 1, count, L->stream))
+          return rc;
+#ifdef ALEGPU_WITH_NCCL
+        if (L->cfg.world_size > 1) {
+          ncclResult_t r = nccl().AllReduce(count, count, 1, ncclFloat, ncclSum, L->comm, L->stream);
+          if (r != ncclSuccess)
+            return fail(ALEGPU_CUDA_ERROR, std::string("ncclAllReduce: ") + nccl().GetErrorString(r));
+          ALEGPU_COUNT_LAUNCH();
+        }
+#endif
+      }
+      if (opt.normalize_advantages) {
+        double *st = L->adv_stats + 3 * ((ep * nmb + k) % L->counts_cap);
+        if (int rc = launch_adv_stats(la.advantages, la.masks, mb, st, L->stream))
+          return rc;
+#ifdef ALEGPU_WITH_NCCL
+        if (L->cfg.world_size > 1) { // global statistics: the minibatch spans all ranks
+          ncclResult_t r = nccl().AllReduce(st, st, 3, ncclDouble, ncclSum, L->comm, L->stream);
+          if (r != ncclSuccess)
+            return fail(ALEGPU_CUDA_ERROR, std::string("ncclAllReduce: ") + nccl().GetErrorString(r));
+          ALEGPU_COUNT_LAUNCH();
+        }
+#endif
+        la.adv_stats = st;
+      }
+      if (int rc = forward(L, obs, mb))
+        return rc;
       la.clip = hp.clip_param;
       la.vcoef = hp.value_loss_coef;
       la.ecoef = hp.entropy_coef;
-      la.count = L->counts + k;
+      la.count = count;
       la.m_clipped = mt.clipped_losses ? mt.clipped_losses + o : nullptr;
       la.m_value = mt.value_losses ? mt.value_losses + o : nullptr;
       la.m_entropy = mt.entropies ? mt.entropies + o : nullptr;
@@ -285,7 +348,7 @@ int enqueue_train(alegpu_learner *L, const alegpu_batch &b, const alegpu_metrics
                                                       : L->scalars))
         return rc;
       if (mt.loss)
-        if (int rc = finalize_metrics(L->loss_partials, nparts, L->counts + k, mt.loss + o, mb,
+        if (int rc = finalize_metrics(L->loss_partials, nparts, count, mt.loss + o, mb,
                                       nullptr, L->stream))
           return rc;
     }
@@ -524,6 +587,7 @@ extern "C" int alegpu_learner_create(const alegpu_learner_config *config, alegpu
   if (int rc = fmalloc(&L->loss_partials, kNumSMs * 4 + 8)) return rc;
   L->counts_cap = 4096;
   if (int rc = fmalloc(&L->counts, L->counts_cap)) return rc;
+  ALEGPU_CUDA_CHECK(cudaMalloc(&L->adv_stats, sizeof(double) * 3 * (size_t)L->counts_cap));
   if (int rc = fmalloc(&L->scalars, 16)) return rc;
   ALEGPU_CUDA_CHECK(cudaMalloc(&L->opt, sizeof(OptState)));
   if (tc)
@@ -584,6 +648,11 @@ extern "C" int alegpu_learner_destroy(alegpu_learner *L) {
   if (L->opt)
     cudaFree(L->opt);
   net_tc_destroy(L->tc);
+  for (void *p : {(void *)L->staged.obs, (void *)L->staged.actions, (void *)L->staged.logp,
+                  (void *)L->staged.adv, (void *)L->staged.ret, (void *)L->staged.masks,
+                  (void *)L->adv_stats, (void *)L->gather_error})
+    if (p)
+      cudaFree(p);
   cudaStreamDestroy(L->stream);
   delete L;
   return ALEGPU_OK;
@@ -651,6 +720,43 @@ extern "C" int alegpu_learner_forward(alegpu_learner *L, const uint8_t *observat
     return rc;
   return heads_forward(L->Pv, L->acts.fc, n, logits ? logits : L->acts.logits,
                        values ? values : L->acts.values, L->stream);
+}
+
+// The rollout-side policy call (action selector lambda, src/bin/train.cc:367-379): forward of the
+// E current observation stacks, softmax, one categorical draw per env; logits / values / actions are
+// written with caller-given strides so they can land directly in column t of the rollout storage
+// (Buffer::add, buffer.cc:41-56), and the actions also go to a dense [E] array (device, optionally
+// mirrored into pinned host memory in ONE copy instead of E `.item()` syncs, rollout.cc:313).
+extern "C" int alegpu_learner_act(alegpu_learner *L, const uint8_t *observations, int64_t E,
+                                  const float *uniforms, uint64_t seed, uint64_t step,
+                                  float *logits, int64_t logits_env_stride, float *values,
+                                  int64_t values_env_stride, int64_t *actions,
+                                  int64_t actions_env_stride, int64_t *actions_dense,
+                                  int64_t *actions_host) {
+  ALEGPU_REQUIRE(L && observations, ALEGPU_INVALID_ARGUMENT, "act: null argument");
+  ALEGPU_REQUIRE(E >= 0, ALEGPU_INVALID_ARGUMENT, "act: negative env count");
+  ALEGPU_REQUIRE(!actions_host || actions_dense, ALEGPU_INVALID_ARGUMENT,
+                 "act: actions_host needs the dense device array it is copied from");
+  ALEGPU_CUDA_CHECK(cudaSetDevice(L->cfg.device));
+  const int A = (int)L->Pv.actions;
+  for (int64_t e0 = 0; e0 < E; e0 += L->cap) { // chunks of at most max_minibatch rows
+    const int64_t n = std::min<int64_t>(L->cap, E - e0);
+    if (int rc = forward(L, observations + (size_t)e0 * 28224, n))
+      return rc;
+    if (int rc = heads_forward(L->Pv, L->acts.fc, n, L->acts.logits, L->acts.values, L->stream))
+      return rc;
+    if (int rc = launch_act_sample(
+            L->acts.logits, L->acts.values, n, A, uniforms ? uniforms + e0 : nullptr, seed,
+            step * 0x100000000ull + (uint64_t)e0, logits ? logits + e0 * logits_env_stride : nullptr,
+            logits_env_stride, values ? values + e0 * values_env_stride : nullptr,
+            values_env_stride, actions ? actions + e0 * actions_env_stride : nullptr,
+            actions_env_stride, actions_dense ? actions_dense + e0 : nullptr, L->stream))
+      return rc;
+  }
+  if (actions_host && E > 0)
+    ALEGPU_CUDA_CHECK(cudaMemcpyAsync(actions_host, actions_dense, sizeof(int64_t) * (size_t)E,
+                                      cudaMemcpyDeviceToHost, L->stream));
+  return ALEGPU_OK;
 }
 
 extern "C" int alegpu_learner_get_activations(alegpu_learner *L, int64_t n, float *c1, float *c2,
@@ -755,6 +861,14 @@ extern "C" int alegpu_learner_train(alegpu_learner *L, const alegpu_batch *batch
                                     const alegpu_metrics *metrics, int64_t num_epochs,
                                     int64_t num_mini_batches, const alegpu_hyperparameters *hp,
                                     int flags) {
+  return alegpu_learner_train_ex(L, batch, metrics, num_epochs, num_mini_batches, hp, nullptr,
+                                 flags);
+}
+
+extern "C" int alegpu_learner_train_ex(alegpu_learner *L, const alegpu_batch *batch,
+                                       const alegpu_metrics *metrics, int64_t num_epochs,
+                                       int64_t num_mini_batches, const alegpu_hyperparameters *hp,
+                                       const alegpu_train_options *options, int flags) {
   ALEGPU_REQUIRE(L && batch && hp, ALEGPU_INVALID_ARGUMENT, "train: null argument");
   ALEGPU_REQUIRE(num_mini_batches >= 1 && num_epochs >= 0, ALEGPU_INVALID_ARGUMENT,
                  "train: bad epoch / minibatch count");
@@ -769,12 +883,27 @@ extern "C" int alegpu_learner_train(alegpu_learner *L, const alegpu_batch *batch
                      batch->advantages && batch->returns && batch->masks,
                  ALEGPU_INVALID_ARGUMENT, "train: null batch pointer");
   ALEGPU_CUDA_CHECK(cudaSetDevice(L->cfg.device));
+  alegpu_train_options opt{};
+  if (options)
+    opt = *options;
+  if (opt.indices) {
+    if (int rc = ensure_staging(L))
+      return rc;
+    int bad = 0; // a previous shuffled train() found an index outside [0, N)
+    ALEGPU_CUDA_CHECK(cudaMemcpyAsync(&bad, L->gather_error, sizeof(int), cudaMemcpyDeviceToHost,
+                                      L->stream));
+    ALEGPU_CUDA_CHECK(cudaStreamSynchronize(L->stream));
+    if (bad) {
+      ALEGPU_CUDA_CHECK(cudaMemsetAsync(L->gather_error, 0, sizeof(int), L->stream));
+      return fail(ALEGPU_OUT_OF_RANGE, "train: a minibatch index was outside [0, batch size)");
+    }
+  }
   alegpu_metrics mt{};
   if (metrics)
     mt = *metrics;
   const int64_t before = g_launches;
   if (!(flags & 1)) {
-    int rc = enqueue_train(L, *batch, mt, num_epochs, num_mini_batches, *hp);
+    int rc = enqueue_train(L, *batch, mt, num_epochs, num_mini_batches, *hp, opt);
     L->last_launches = g_launches - before;
     return rc;
   }
@@ -788,6 +917,7 @@ extern "C" int alegpu_learner_train(alegpu_learner *L, const alegpu_batch *batch
   key_push(key, mt.clipped_gradients); key_push(key, num_epochs); key_push(key, num_mini_batches);
   key_push(key, hp->clip_param); key_push(key, hp->value_loss_coef);
   key_push(key, hp->entropy_coef); key_push(key, hp->max_gradient_norm);
+  key_push(key, opt.indices); key_push(key, opt.normalize_advantages);
   if (!L->graph_exec || key != L->graph_key) {
     if (L->graph_exec) {
       cudaGraphExecDestroy(L->graph_exec);
@@ -795,7 +925,7 @@ extern "C" int alegpu_learner_train(alegpu_learner *L, const alegpu_batch *batch
     }
     const int64_t step_before = L->host_step;
     ALEGPU_CUDA_CHECK(cudaStreamBeginCapture(L->stream, cudaStreamCaptureModeThreadLocal));
-    int rc = enqueue_train(L, *batch, mt, num_epochs, num_mini_batches, *hp);
+    int rc = enqueue_train(L, *batch, mt, num_epochs, num_mini_batches, *hp, opt);
     cudaGraph_t graph = nullptr;
     cudaError_t ce = cudaStreamEndCapture(L->stream, &graph);
     L->host_step = step_before; // capture enqueued nothing; the replay below advances it

@@ -61,6 +61,9 @@ struct LossArgs {
   const uint8_t *masks;
   float clip, vcoef, ecoef;
   const float *count; // device scalar: (global) number of unmasked rows in the minibatch
+  // optional advantage normalisation: (count, sum, sum of squares) of the minibatch's unmasked
+  // advantages in double; adv' = (adv - mean) / (std + 1e-8), unbiased std.  nullptr = off.
+  const double *adv_stats;
   // per-sample metric outputs at their final offsets (any may be null) — Metrics::set, train.h:93-108
   float *m_clipped, *m_value, *m_entropy, *m_total, *m_ratio, *m_adv, *m_ret;
   uint8_t *m_masks;
@@ -68,6 +71,13 @@ struct LossArgs {
 // logits/value heads only (inference; src/bin/train.cc:262-264)
 int heads_forward(const NetParams &P, const float *fc, int64_t n, float *logits, float *values,
                   cudaStream_t s);
+// softmax + categorical draw per row (src/bin/train.cc:373-375) and strided writes of
+// logits/values/actions (e.g. straight into column t of the [E,T,...] rollout storage)
+int launch_act_sample(const float *logits, const float *values, int64_t n, int A,
+                      const float *uniforms, uint64_t seed, uint64_t step, float *logits_out,
+                      int64_t logits_stride, float *values_out, int64_t values_stride,
+                      int64_t *actions_out, int64_t actions_stride, int64_t *actions_dense,
+                      cudaStream_t s);
 // heads forward + PPO loss + d loss/d(logits,value) + dfc, fused; loss_partials[grid] out
 int heads_loss_backward(const NetParams &P, NetActs &A, int64_t n, const LossArgs &L,
                         float *loss_partials, int *nparts, cudaStream_t s);

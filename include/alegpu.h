@@ -258,6 +258,24 @@ int alegpu_learner_set_lr(alegpu_learner *learner, double lr);
 /* NetworkImpl::forward — src/bin/train.cc:255-265 — inference on n <= max_minibatch rows. */
 int alegpu_learner_forward(alegpu_learner *learner, const uint8_t *observations, int64_t n,
                            float *logits, float *values);
+/* The rollout-side policy call — the action-selector lambda of src/bin/train.cc:367-379, called at
+ * src/ai/rollout.cc:207,268: forward of E observation stacks ([E,4,84,84] u8, contiguous; E may
+ * exceed max_minibatch, it is processed in chunks), probabilities = softmax(logits), one
+ * categorical draw per env (torch::multinomial(p, 1)).  The draw is the inverse CDF of u in [0,1):
+ * action = first a with cumsum(p)[a] > u.  uniforms [E] supplies u (parity runs); NULL = a
+ * counter-based generator keyed by (seed, step, env) — libtorch's Philox stream is not
+ * reproducible, so parity with the reference is distributional.
+ * Outputs (any may be NULL) are written at base + e*stride (strides in ELEMENTS) so they can land
+ * in column t of the [E,T,...] rollout storage (Buffer::add, src/ai/buffer.cc:41-56):
+ * logits[e*logits_env_stride + a], values[e*values_env_stride], actions[e*actions_env_stride].
+ * actions_dense [E] (device) also receives the actions; actions_host (pinned, needs actions_dense)
+ * gets them in ONE async copy on the learner's stream — replaces the per-env `.item()` syncs of
+ * src/ai/rollout.cc:313.  Asynchronous on the learner's stream. */
+int alegpu_learner_act(alegpu_learner *learner, const uint8_t *observations, int64_t E,
+                       const float *uniforms, uint64_t seed, uint64_t step, float *logits,
+                       int64_t logits_env_stride, float *values, int64_t values_env_stride,
+                       int64_t *actions, int64_t actions_env_stride, int64_t *actions_dense,
+                       int64_t *actions_host);
 /* Post-ReLU conv activations and the FC output of the last forward, converted to the
  * reference's NCHW f32 layout (host arrays; parity/debug only). */
 int alegpu_learner_get_activations(alegpu_learner *learner, int64_t n, float *conv1_host,
@@ -282,6 +300,25 @@ int alegpu_learner_apply_grads(alegpu_learner *learner, const float *grads_host,
 int alegpu_learner_train(alegpu_learner *learner, const alegpu_batch *batch,
                          const alegpu_metrics *metrics, int64_t num_epochs,
                          int64_t num_mini_batches, const alegpu_hyperparameters *hp, int flags);
+/* Opt-in minibatch preparation that BASELINE.json's north_star lists on the path but the reference
+ * does not perform (src/ai/ppo/train.h:146-151 slices contiguously — its randperm is generated
+ * and never consumed — and nothing normalises advantages).  Zero-initialised = reference semantics.
+ *   indices: DEVICE [num_epochs * N] int64; minibatch k of epoch e trains on rows
+ *            indices[e*N + k*mb .. e*N + (k+1)*mb) (one randperm(N) per epoch gives the usual PPO
+ *            shuffle), gathered by one HBM-bound kernel (2 x 28 224 + 45 B per row).  The per-sample
+ *            metrics at [e,k,:] then describe the gathered rows.  An index outside [0,N) makes the
+ *            NEXT shuffled train call fail with ALEGPU_OUT_OF_RANGE (checked on the device).
+ *   normalize_advantages: A' = (A - mean) / (std + 1e-8) per minibatch, mean and unbiased std over
+ *            the minibatch's UNMASKED rows (over all ranks when world_size > 1); Metrics.advantages
+ *            stays the raw value. */
+typedef struct {
+  const int64_t *indices;
+  int normalize_advantages;
+} alegpu_train_options;
+int alegpu_learner_train_ex(alegpu_learner *learner, const alegpu_batch *batch,
+                            const alegpu_metrics *metrics, int64_t num_epochs,
+                            int64_t num_mini_batches, const alegpu_hyperparameters *hp,
+                            const alegpu_train_options *options, int flags);
 /* number of kernels the last alegpu_learner_train call launched (or replayed) */
 int64_t alegpu_learner_last_launch_count(const alegpu_learner *learner);
 

@@ -189,3 +189,34 @@ def train(params, m, v, step, hidden, obs, actions_taken, log_probs, advantages,
                           _f(met["ratio"]), _f(met["total_losses"]), _f(met["advantages"]),
                           _f(met["returns"]), _u(met["masks"]), _f(met["clipped_gradients"])))
     return p, m_, v_, int(st.value), met
+
+
+def act_sample(logits, uniforms):
+    """The action selector of src/bin/train.cc:373-375 — probabilities = softmax(logits),
+    actions = multinomial(probabilities, 1) — restated as the inverse CDF of a supplied u in
+    [0,1): action = first a with cumsum(p)[a] > u (torch::multinomial's own Philox stream is not
+    reproducible, so the draw is parameterised by u).  Returns (actions, cumsum(p)) in fp32."""
+    z = np.asarray(logits, np.float32)
+    u = np.asarray(uniforms, np.float32)
+    e = np.exp(z - z.max(axis=1, keepdims=True), dtype=np.float32)
+    p = (e / e.sum(axis=1, keepdims=True, dtype=np.float32)).astype(np.float32)
+    cum = np.cumsum(p, axis=1, dtype=np.float32)
+    hit = cum > u[:, None]
+    actions = np.where(hit.any(axis=1), hit.argmax(axis=1), z.shape[1] - 1).astype(np.int64)
+    return actions, cum
+
+
+def normalize_advantages(advantages, masks):
+    """Opt-in extra (not in the reference; BASELINE.json north_star): per-minibatch
+    A' = (A - mean) / (std + 1e-8), mean and UNBIASED std (torch .std()) over the unmasked rows."""
+    a = np.asarray(advantages, np.float64)
+    m = np.asarray(masks).astype(bool)
+    mean, std = a[m].mean(), a[m].std(ddof=1)
+    return ((a - mean) / (std + 1e-8)).astype(np.float32)
+
+
+def gather_minibatches(indices, *arrays):
+    """Opt-in extra: the shuffled row order train() consumes (rows indices[...] of every array)."""
+    idx = np.asarray(indices, np.int64)
+    return tuple(np.ascontiguousarray(np.asarray(x)[idx]) for x in arrays)
+

@@ -315,3 +315,103 @@ def test_buffer_add_get_roundtrip():
             s["truncations"][:, 0], s["episode_starts"][:, 0], s["logits"][:, 0], s["values"][:, 0])
     with pytest.raises(RuntimeError):  # not full: buffer.cc:64-65
         buf.get(s["next_values"], cases.GAMMA, cases.LAMBDA)
+
+
+# ---- N1: rollout-side policy call (action selector, src/bin/train.cc:367-379) -------------------
+def test_act_matches_oracle_given_uniforms():
+    H, E = 32, 24
+    params = cases.net_params(H)
+    obs = cases.train_case(E, seed=77)["obs"]
+    L = alegpu.Learner(H, 4, 16, alegpu.MATH_FP32, cases.LR)  # E > max_minibatch: chunked
+    L.set_params(params)
+    u = np.random.default_rng(3).random(E).astype(np.float32)
+    actions, logits, values = L.act(obs, uniforms=u)
+    want_logits, want_values = restate.net_forward(params, H, obs)[:2]
+    np.testing.assert_allclose(logits, want_logits, rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(values, want_values, rtol=1e-4, atol=1e-5)
+    want_actions, cum = restate.act_sample(logits, u)
+    # identical except where u sits within float noise of a CDF step
+    near = (np.abs(cum - u[:, None]) < 1e-6).any(axis=1)
+    assert np.array_equal(actions[~near], want_actions[~near])
+    assert actions.min() >= 0 and actions.max() < 4
+
+
+def test_act_writes_rollout_column_and_is_categorical():
+    H, E, T, t = 32, 512, 3, 1
+    params = cases.net_params(H)
+    obs = np.repeat(cases.train_case(1, seed=5)["obs"], E, axis=0)  # same state in every env
+    L = alegpu.Learner(H, 4, 256, alegpu.MATH_FP32, cases.LR)
+    L.set_params(params)
+    buf = alegpu.Buffer(E, T, 4)
+    counts = np.zeros(4)
+    for step in range(8):
+        actions, logits, values = L.act(obs, seed=11, step=step, buffer=buf, t=t)
+        assert np.array_equal(buf.actions.numpy()[:, t], actions)  # column t, nothing else
+        assert np.all(buf.actions.numpy()[:, [0, 2]] == 0)
+        np.testing.assert_array_equal(buf.logits.numpy()[:, t], logits)
+        np.testing.assert_array_equal(buf.values.numpy()[:, t], values)
+        counts += np.bincount(actions, minlength=4)
+    p = np.exp(restate.log_softmax(logits[:1]))[0].astype(np.float64)
+    n = counts.sum()
+    chi2 = float(((counts - n * p) ** 2 / (n * p)).sum())
+    assert chi2 < 21.1, (chi2, counts, p)  # 3 dof, p ~ 1e-4
+    # a different step gives a different draw, the same (seed, step) the same draw
+    a0 = L.act(obs, seed=11, step=0)[0]
+    assert np.array_equal(a0, L.act(obs, seed=11, step=0)[0])
+    assert not np.array_equal(a0, L.act(obs, seed=11, step=1)[0])
+
+
+# ---- north_star extras: minibatch shuffle/gather and advantage normalisation (opt-in) ------------
+@pytest.mark.parametrize("shuffle,norm", [(True, False), (False, True), (True, True)])
+def test_train_shuffle_and_advantage_normalisation(shuffle, norm):
+    """train_ex(indices, normalize) on the original rows == the oracle's contiguous train() on rows
+    that were gathered / normalised on the host first (one epoch, so one permutation)."""
+    H, N, nmb = 32, 64, 4
+    mb = N // nmb
+    params = cases.net_params(H)
+    tc = cases.train_case(N, seed=41)
+    perm = np.random.default_rng(9).permutation(N).astype(np.int64) if shuffle else np.arange(N)
+    obs, act, lp, adv, ret, msk = restate.gather_minibatches(
+        perm, tc["obs"], tc["actions"], tc["log_probs"], tc["advantages"], tc["returns"], tc["masks"])
+    adv_used = adv.copy()
+    if norm:
+        for k in range(nmb):
+            sl = slice(k * mb, (k + 1) * mb)
+            adv_used[sl] = restate.normalize_advantages(adv[sl], msk[sl])
+    z = np.zeros_like(params)
+    want_p, _, _, _, want_m = restate.train(params, z, z, 0, H, obs, act, lp, adv_used, ret, msk, 1,
+                                            nmb, cases.CLIP, cases.VCOEF, cases.ECOEF,
+                                            cases.MAX_NORM, cases.LR)
+    met = alegpu.Metrics(1, nmb, mb)
+    batch = alegpu.Batch(tc["obs"], tc["actions"], tc["log_probs"], tc["advantages"], tc["returns"],
+                         tc["masks"])
+    hp = alegpu.Hyperparameters(cases.CLIP, cases.VCOEF, cases.ECOEF, cases.MAX_NORM)
+    for graph in (False, True):
+        L = alegpu.Learner(H, 4, mb, alegpu.MATH_FP32, cases.LR)  # fresh Adam state per mode
+        L.set_params(params)
+        L.train(batch, met, 1, nmb, hp, cuda_graph=graph, indices=perm if shuffle else None,
+                normalize_advantages=norm)
+        got = L.get_params()
+        err = np.linalg.norm((got - want_p).astype(np.float64)) / np.linalg.norm(want_p)
+        assert err < 1e-4, (err, graph)  # fp32-faithful mode, same bound as the plain train() test
+        m = met.numpy()
+        np.testing.assert_allclose(m["loss"], want_m["loss"], rtol=1e-3, atol=1e-5)
+        np.testing.assert_array_equal(m["advantages"].ravel(), adv)  # raw, in gathered order
+        np.testing.assert_array_equal(m["masks"].ravel().astype(bool), msk.astype(bool))
+
+
+def test_train_shuffle_index_out_of_range():
+    H, N = 32, 16
+    tc = cases.train_case(N, seed=2)
+    L = alegpu.Learner(H, 4, N, alegpu.MATH_FP32, cases.LR)
+    L.set_params(cases.net_params(H))
+    batch = alegpu.Batch(tc["obs"], tc["actions"], tc["log_probs"], tc["advantages"], tc["returns"],
+                         tc["masks"])
+    hp = alegpu.Hyperparameters(cases.CLIP, cases.VCOEF, cases.ECOEF, cases.MAX_NORM)
+    bad = np.arange(N, dtype=np.int64)
+    bad[3] = N  # torch index_select would throw (std::out_of_range family)
+    L.train(batch, None, 1, 1, hp, indices=bad)
+    with pytest.raises(IndexError):  # std::out_of_range
+        L.train(batch, None, 1, 1, hp, indices=np.arange(N, dtype=np.int64))
+    L.train(batch, None, 1, 1, hp, indices=np.arange(N, dtype=np.int64))  # flag was cleared
+
