@@ -310,6 +310,30 @@ class Metrics:
     def numpy(self):
         return {k: getattr(self, k).numpy() for k in self.FIELDS + ("masks", "clipped_gradients")}
 
+    def summary(self, stream=None):
+        """The scalars of log_data (src/bin/train.cc:180-190) reduced on the device and fetched in
+        one copy (alegpu_metrics_summarize)."""
+        E, K, mb = self.loss.shape
+        dev = DeviceArray.zeros(8, np.float32)
+        cm = self._c()
+        _check(lib().alegpu_metrics_summarize(C.byref(cm), C.c_int64(E), C.c_int64(K),
+                                              C.c_int64(mb), _p(dev), None, C.c_void_p(stream)))
+        synchronize(stream)
+        v = dev.numpy()
+        return dict(zip(("mean_clipped_gradient", "mean_loss", "mean_clipped_loss",
+                         "mean_value_loss", "mean_entropy", "mean_ratio", "mean_total_loss",
+                         "unmasked"), (float(x) for x in v)))
+
+    def masked(self, field, stream=None):
+        """gather(metrics.<field>, metrics.masks) of src/bin/train.cc:149-155 (alegpu_masked_select)."""
+        x = getattr(self, field)
+        n = int(np.prod(x.shape))
+        out, cnt = DeviceArray.zeros(max(n, 1), np.float32), DeviceArray.zeros(1, np.int64)
+        _check(lib().alegpu_masked_select(_p(x), _p(self.masks), C.c_int64(n), _p(out), _p(cnt),
+                                          C.c_void_p(stream)))
+        synchronize(stream)
+        return out.numpy()[:int(cnt.numpy()[0])]
+
 
 class Buffer:
     """ai::buffer::Buffer — src/ai/buffer.h:27-58."""

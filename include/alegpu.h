@@ -199,6 +199,33 @@ typedef struct {
   float *clipped_gradients;
 } alegpu_metrics;
 
+/* The scalars log_data (src/bin/train.cc:163-210) extracts from Metrics with one `.item()` sync
+ * each: clipped_gradients.mean() (:180-181), loss.mean() (:182), and the means of
+ * clipped_losses / value_losses / entropies / ratio over the UNMASKED samples (mean(tensor, mask),
+ * :144-147, :183-190); plus the unmasked mean of total_losses and the unmasked count. */
+typedef struct {
+  float mean_clipped_gradient;
+  float mean_loss;
+  float mean_clipped_loss;
+  float mean_value_loss;
+  float mean_entropy;
+  float mean_ratio;
+  float mean_total_loss;
+  float unmasked;
+} alegpu_metrics_summary;
+/* One kernel fills *summary (DEVICE); summary_host (optional, pinned for a truly async copy)
+ * receives it with one cudaMemcpyAsync on `stream`.  metrics holds [epochs,nmb,mb] arrays (NULL
+ * members are skipped and reported as 0). */
+int alegpu_metrics_summarize(const alegpu_metrics *metrics, int64_t num_epochs,
+                             int64_t num_mini_batches, int64_t mini_batch_size,
+                             alegpu_metrics_summary *summary, alegpu_metrics_summary *summary_host,
+                             void *stream);
+/* tensor.masked_select(mask) — the histogram feeds gather(tensor, mask) of src/bin/train.cc:149-155,
+ * 194-207: out receives the values[i] with masks[i] != 0 in order (stable), *count (DEVICE int64)
+ * how many.  out must hold n floats.  Not re-entrant (shares one scratch buffer). */
+int alegpu_masked_select(const float *values, const uint8_t *masks, int64_t n, float *out,
+                         int64_t *count, void *stream);
+
 /* ---- rollout buffer: ai::buffer::Buffer — src/ai/buffer.h:27-58, src/ai/buffer.cc:5-77 ---- */
 /* raw device pointers of the [E,T,...] storage (ai::buffer::Batch aliases storage too,
  * buffer.cc:73-76), so producers can write slots in place.  carry = 2 x [E,4,84,84] ping-pong

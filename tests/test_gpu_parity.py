@@ -415,3 +415,33 @@ def test_train_shuffle_index_out_of_range():
         L.train(batch, None, 1, 1, hp, indices=np.arange(N, dtype=np.int64))
     L.train(batch, None, 1, 1, hp, indices=np.arange(N, dtype=np.int64))  # flag was cleared
 
+
+# ---- N3: on-device reduction of Metrics for the logging feed (src/bin/train.cc:163-210) ---------
+@pytest.mark.parametrize("shape", [(2, 4, 64), (1, 3, 5000)])
+def test_metrics_summary_and_masked_select(shape):
+    rng = np.random.default_rng(sum(shape))
+    met = alegpu.Metrics(*shape)
+    host = {}
+    for k in alegpu.Metrics.FIELDS:
+        host[k] = rng.standard_normal(shape).astype(np.float32)
+        getattr(met, k).copy_from(host[k])
+    host["masks"] = (rng.random(shape) > 0.2).astype(np.uint8)
+    met.masks.copy_from(host["masks"])
+    host["clipped_gradients"] = rng.random(shape[:2]).astype(np.float32)
+    met.clipped_gradients.copy_from(host["clipped_gradients"])
+    m = host["masks"].astype(bool)
+    s = met.summary()
+    # the reference's expressions, in float64 (torch's fp32 mean differs by summation order only)
+    want = {"mean_clipped_gradient": host["clipped_gradients"].mean(dtype=np.float64),
+            "mean_loss": host["loss"].mean(dtype=np.float64),
+            "mean_clipped_loss": host["clipped_losses"][m].mean(dtype=np.float64),
+            "mean_value_loss": host["value_losses"][m].mean(dtype=np.float64),
+            "mean_entropy": host["entropies"][m].mean(dtype=np.float64),
+            "mean_ratio": host["ratio"][m].mean(dtype=np.float64),
+            "mean_total_loss": host["total_losses"][m].mean(dtype=np.float64),
+            "unmasked": float(m.sum())}
+    for k, w in want.items():
+        assert abs(s[k] - w) <= 1e-6 + 1e-5 * abs(w), (k, s[k], w)
+    for k in ("total_losses", "advantages"):  # bit-exact, order preserved
+        assert np.array_equal(met.masked(k), host[k][m])
+
