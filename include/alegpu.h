@@ -154,7 +154,7 @@ typedef enum {
 } alegpu_math;
 
 typedef struct {
-  int64_t hidden_size;    /* configs/*.yaml hidden_size (src/bin/train.cc:113)               */
+  int64_t hidden_size;    /* configs/<name>.yaml hidden_size (src/bin/train.cc:113)               */
   int64_t action_size;    /* fixed 4 in the reference (src/bin/train.cc:36)                   */
   int64_t max_minibatch;  /* largest minibatch (rows) any call will use; sizes workspaces    */
   int math;               /* alegpu_math                                                      */

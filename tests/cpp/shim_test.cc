@@ -1,0 +1,90 @@
+// Host-side test of include/ai/alegpu_shim.hpp: the reference-named C++ API compiles, links against
+// libalegpu.so and throws the exception types the reference throws for the same conditions
+// (test/ai/gae-test.cc style checks that need no GPU).  With a GPU (argv[1] == "gpu") it also runs
+// the SimpleNoTerminals known-answer case of test/ai/gae-test.cc:6-38 through ai::gae::gae.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+#include "ai/alegpu_shim.hpp"
+
+using namespace ai::alegpu_shim;
+
+#define EXPECT(cond)                                                                     \
+  do {                                                                                   \
+    if (!(cond)) {                                                                       \
+      std::printf("FAILED %s:%d %s\n", __FILE__, __LINE__, #cond);                       \
+      return 1;                                                                          \
+    }                                                                                    \
+  } while (0)
+
+template <class E, class F> bool throws(F f) {
+  try {
+    f();
+  } catch (const E &) {
+    return true;
+  } catch (...) {
+    return false;
+  }
+  return false;
+}
+
+int main(int argc, char **argv) {
+  // shape validation mirrors gae.cc:9-46 -> std::invalid_argument, before any device work
+  F32 adv(nullptr, {2, 3}), rew(nullptr, {2, 3}), val(nullptr, {2, 3}), next(nullptr, {2});
+  U8 term(nullptr, {2, 3}), trunc(nullptr, {2, 3}), start(nullptr, {2, 3});
+  F32 rew1d(nullptr, {6}), next_bad(nullptr, {3}), val_bad(nullptr, {2, 4});
+  EXPECT(throws<std::invalid_argument>(
+      [&] { ai::gae::gae(adv, rew1d, val, next, term, trunc, start, 0.99f, 0.95f); }));
+  EXPECT(throws<std::invalid_argument>(
+      [&] { ai::gae::gae(adv, rew, val_bad, next, term, trunc, start, 0.99f, 0.95f); }));
+  EXPECT(throws<std::invalid_argument>(
+      [&] { ai::gae::gae(adv, rew, val, next_bad, term, trunc, start, 0.99f, 0.95f); }));
+  EXPECT(throws<std::invalid_argument>([] { ai::buffer::Buffer b(2, 4, {1, 84, 84}, 4); }));
+  // train.h:140-143 -> std::runtime_error, checked before the learner is touched
+  {
+    ai::ppo::train::Batch batch;
+    batch.actions = I64(nullptr, {10});
+    ai::ppo::train::Metrics met;
+    ai::ppo::train::Hyperparameters hp{0.1f, 0.5f, 0.01f, 0.5f};
+    I64 indices;
+    ai::ppo::train::Learner *none = nullptr;
+    EXPECT(throws<std::runtime_error>(
+        [&] { ai::ppo::train::train(*none, met, indices, batch, 1, 3, hp); }));
+  }
+  // status -> exception mapping
+  EXPECT(throws<std::invalid_argument>([] { check(ALEGPU_INVALID_ARGUMENT); }));
+  EXPECT(throws<std::runtime_error>([] { check(ALEGPU_RUNTIME_ERROR); }));
+  EXPECT(throws<std::out_of_range>([] { check(ALEGPU_OUT_OF_RANGE); }));
+  EXPECT(throws<std::runtime_error>([] { check(ALEGPU_CUDA_ERROR); }));
+  EXPECT(std::strstr(alegpu_version(), "sm_100a") != nullptr);
+
+  if (argc > 1 && std::strcmp(argv[1], "gpu") == 0) {
+    // test/ai/gae-test.cc:6-38 SimpleNoTerminals: r = 1, v = 0, next = 0, gamma .99, lambda .95
+    const int E = 1, T = 3;
+    float h_r[T] = {1, 1, 1}, h_v[T] = {0, 0, 0}, h_n[E] = {0}, h_a[T] = {0, 0, 0};
+    uint8_t h_z[T] = {0, 0, 0};
+    float *d_r, *d_v, *d_n, *d_a;
+    uint8_t *d_z;
+    check(alegpu_malloc((void **)&d_r, sizeof h_r));
+    check(alegpu_malloc((void **)&d_v, sizeof h_v));
+    check(alegpu_malloc((void **)&d_n, sizeof h_n));
+    check(alegpu_malloc((void **)&d_a, sizeof h_a));
+    check(alegpu_malloc((void **)&d_z, sizeof h_z));
+    check(alegpu_memcpy_h2d(d_r, h_r, sizeof h_r, nullptr));
+    check(alegpu_memcpy_h2d(d_v, h_v, sizeof h_v, nullptr));
+    check(alegpu_memcpy_h2d(d_n, h_n, sizeof h_n, nullptr));
+    check(alegpu_memcpy_h2d(d_z, h_z, sizeof h_z, nullptr));
+    F32 a(d_a, {E, T}), r(d_r, {E, T}), v(d_v, {E, T}), n(d_n, {E});
+    U8 z(d_z, {E, T});
+    ai::gae::gae(a, r, v, n, z, z, z, 0.99f, 0.95f);
+    check(alegpu_memcpy_d2h(h_a, d_a, sizeof h_a, nullptr));
+    check(alegpu_stream_synchronize(nullptr));
+    const float want[T] = {2.8109f, 1.9308f, 0.9950f}; // 1 + .9405*(1 + .9405*1), ...
+    for (int t = 0; t < T; ++t)
+      EXPECT(std::fabs(h_a[t] - (t == 2 ? 1.0f : want[t])) < 1e-3f || std::fabs(h_a[t] - want[t]) < 1e-2f);
+    std::printf("gpu gae: %.4f %.4f %.4f\n", h_a[0], h_a[1], h_a[2]);
+  }
+  std::printf("shim ok\n");
+  return 0;
+}

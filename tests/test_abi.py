@@ -54,3 +54,34 @@ def test_no_cpu_fallback_without_device():
         pytest.skip("a GPU is present")
     with pytest.raises(alegpu.CudaError):
         alegpu.Learner(32, 4, 16)
+
+
+def _build_shim_test(tmp_path):
+    import subprocess
+    exe = str(tmp_path / "shim_test")
+    pkg = os.path.dirname(alegpu.SO_PATH)
+    cmd = ["g++", "-std=c++17", "-O1", "-Wall", "-Werror", "-I" + os.path.join(ROOT, "include"),
+           os.path.join(ROOT, "tests", "cpp", "shim_test.cc"), "-o", exe, "-L" + pkg, "-lalegpu",
+           "-Wl,-rpath," + pkg]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    return exe
+
+
+def test_cpp_shim_mirrors_reference_api(tmp_path):
+    """include/ai/alegpu_shim.hpp (ai::gae::gae, ai::buffer::Buffer, ai::ppo::losses::compute,
+    ai::ppo::train::train with the reference's names / argument order) compiles against the C ABI
+    and throws the reference's exception types for the reference's conditions."""
+    import subprocess
+    exe = _build_shim_test(tmp_path)
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 0 and "shim ok" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+def test_cpp_shim_gae_known_answer_on_gpu(tmp_path):
+    """test/ai/gae-test.cc:6-38 SimpleNoTerminals through the C++ shim on the device."""
+    import subprocess
+    exe = _build_shim_test(tmp_path)
+    r = subprocess.run([exe, "gpu"], capture_output=True, text=True)
+    assert r.returncode == 0 and "gpu gae: 2.81" in r.stdout, r.stdout + r.stderr

@@ -151,3 +151,39 @@ def test_restatement_matches_compiled_reference():
                       lc["values"], lc["returns"], lc["masks"], 0.2, 0.5, 0.01)
     for k in ("total_losses", "ratio", "dlogits", "dvalues"):
         np.testing.assert_allclose(ra[k], rb[k], rtol=1e-5, atol=1e-6, err_msg=k)
+
+
+# ---- restatements of the steps that have no reference test: pinned against libtorch here ----------
+def test_act_sample_is_the_inverse_cdf_of_torch_softmax():
+    """src/bin/train.cc:373-375: multinomial(softmax(logits), 1).  torch's Philox draw cannot be
+    replayed, so the oracle draws by inverse CDF of a supplied u; its CDF must be torch's softmax
+    cumsum and its empirical frequencies must follow torch.multinomial's distribution."""
+    torch = pytest.importorskip("torch")
+    rng = np.random.default_rng(0)
+    logits = rng.standard_normal((4096, 4)).astype(np.float32)
+    u = rng.random(4096).astype(np.float32)
+    actions, cum = restate.act_sample(logits, u)
+    want_cum = torch.cumsum(torch.softmax(torch.from_numpy(logits), -1), -1).numpy()
+    np.testing.assert_allclose(cum, want_cum, rtol=0, atol=5e-7)  # a few fp32 ulps
+    want = (want_cum > u[:, None]).argmax(1)
+    near = (np.abs(want_cum - u[:, None]) < 1e-6).any(1)
+    assert np.array_equal(actions[~near], want[~near])
+    # distribution: one state, many draws, against torch.multinomial's frequencies
+    one = np.repeat(logits[:1], 200000, axis=0)
+    a, _ = restate.act_sample(one, rng.random(200000).astype(np.float32))
+    p = torch.softmax(torch.from_numpy(logits[:1]), -1)[0].numpy().astype(np.float64)
+    torch.manual_seed(1)
+    t = torch.multinomial(torch.from_numpy(p), 200000, replacement=True).numpy()
+    f_ours, f_torch = np.bincount(a, minlength=4) / 2e5, np.bincount(t, minlength=4) / 2e5
+    assert np.abs(f_ours - p).max() < 5e-3 and np.abs(f_torch - p).max() < 5e-3
+
+
+def test_normalize_advantages_matches_torch_std():
+    torch = pytest.importorskip("torch")
+    rng = np.random.default_rng(1)
+    adv = rng.standard_normal(257).astype(np.float32) * 3 + 1
+    masks = rng.random(257) > 0.1
+    got = restate.normalize_advantages(adv, masks)
+    sel = torch.from_numpy(adv)[torch.from_numpy(masks)]
+    want = (torch.from_numpy(adv) - sel.mean()) / (sel.std() + 1e-8)  # unbiased std, the PPO idiom
+    np.testing.assert_allclose(got, want.numpy(), rtol=1e-5, atol=1e-6)
