@@ -6,6 +6,9 @@
 // 2-D copy instead of 8 strided copy_ kernels (buffer.cc:47-54); producers that can write in
 // place (alegpu_preprocess_step -> slot t+1) get the raw pointers through alegpu_rollout_view.
 // `get` = fused clamp + GAE + returns + masks (gae.cu) + log-softmax of the stored logits.
+#include <algorithm>
+#include <vector>
+
 #include "net.h"
 
 using namespace alegpu;
@@ -21,10 +24,17 @@ struct alegpu_rollout {
   uint8_t *terminals = nullptr, *truncations = nullptr, *starts = nullptr, *masks = nullptr;
   int *error_flag = nullptr;
   // hand-off state (alegpu_rollout_ingest)
-  static constexpr int kRing = 4;
+  // device ring of per-step frame slabs: as many slots as steps when that fits kRingBytes (then a
+  // whole rollout's copies can run ahead of the compute stream, e.g. under the previous train()),
+  // never fewer than kMinRing
+  static constexpr int kMinRing = 4;
+  static constexpr size_t kRingBytes = (size_t)6 << 30;
+  int ring_slots = 0;
   cudaStream_t copy_stream = nullptr;
   uint8_t *ring = nullptr;
-  cudaEvent_t copied[kRing] = {}, consumed[kRing] = {}, start = nullptr;
+  std::vector<cudaEvent_t> copied, consumed;
+  std::vector<char> used; // slot has been read by a kernel before (consumed[slot] is meaningful)
+  cudaEvent_t start = nullptr;
 };
 
 namespace {
@@ -100,7 +110,7 @@ extern "C" int alegpu_rollout_destroy(alegpu_rollout *r) {
     cudaStreamSynchronize(r->copy_stream);
     cudaStreamDestroy(r->copy_stream);
     cudaFree(r->ring);
-    for (int i = 0; i < alegpu_rollout::kRing; ++i) {
+    for (int i = 0; i < r->ring_slots; ++i) {
       cudaEventDestroy(r->copied[i]);
       cudaEventDestroy(r->consumed[i]);
     }
@@ -162,9 +172,14 @@ extern "C" int alegpu_rollout_ingest(alegpu_rollout *r, const uint8_t *frames_ho
   const int64_t E = r->E, T = r->T;
   const size_t slab = (size_t)E * 2 * 100800;
   if (!r->copy_stream) {
+    const int64_t fit = (int64_t)(alegpu_rollout::kRingBytes / slab);
+    r->ring_slots = (int)std::max<int64_t>(alegpu_rollout::kMinRing, std::min<int64_t>(T, fit));
+    ALEGPU_CUDA_CHECK(cudaMalloc(&r->ring, slab * (size_t)r->ring_slots));
     ALEGPU_CUDA_CHECK(cudaStreamCreateWithFlags(&r->copy_stream, cudaStreamNonBlocking));
-    ALEGPU_CUDA_CHECK(cudaMalloc(&r->ring, slab * alegpu_rollout::kRing));
-    for (int i = 0; i < alegpu_rollout::kRing; ++i) {
+    r->copied.assign((size_t)r->ring_slots, nullptr);
+    r->consumed.assign((size_t)r->ring_slots, nullptr);
+    r->used.assign((size_t)r->ring_slots, 0);
+    for (int i = 0; i < r->ring_slots; ++i) {
       ALEGPU_CUDA_CHECK(cudaEventCreateWithFlags(&r->copied[i], cudaEventDisableTiming));
       ALEGPU_CUDA_CHECK(cudaEventCreateWithFlags(&r->consumed[i], cudaEventDisableTiming));
     }
@@ -172,19 +187,43 @@ extern "C" int alegpu_rollout_ingest(alegpu_rollout *r, const uint8_t *frames_ho
   }
   uint8_t *carry_in = r->carry + (size_t)carry_index * E * 28224;
   uint8_t *carry_out = r->carry + (size_t)(1 - carry_index) * E * 28224;
+  const int slots = r->ring_slots;
+  // The copies depend only on their ring slot being free (the kernel that last read it has
+  // finished), NOT on what the compute stream is doing now: the frames of the next rollout stream
+  // in under the current train().
+  auto copy_slab = [&](int64_t t) -> int {
+    const int slot = (int)(t % slots);
+    if (r->used[slot])
+      ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(r->copy_stream, r->consumed[slot], 0));
+    ALEGPU_CUDA_CHECK(cudaMemcpyAsync(r->ring + slab * slot, frames_host + slab * t, slab,
+                                      cudaMemcpyHostToDevice, r->copy_stream));
+    ALEGPU_CUDA_CHECK(cudaEventRecord(r->copied[slot], r->copy_stream));
+    return ALEGPU_OK;
+  };
+  if (slots >= T) {
+    // the ring holds the whole rollout as [T,E,2,210,160,3]: one fused kernel over all steps
+    // (the T slabs are contiguous on both sides and share one reader, so they move as ONE copy)
+    if (r->used[0])
+      ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(r->copy_stream, r->consumed[0], 0));
+    ALEGPU_CUDA_CHECK(cudaMemcpyAsync(r->ring, frames_host, slab * (size_t)T, cudaMemcpyHostToDevice,
+                                      r->copy_stream));
+    ALEGPU_CUDA_CHECK(cudaEventRecord(r->copied[(size_t)(T - 1)], r->copy_stream));
+    ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(s, r->copied[(size_t)(T - 1)], 0));
+    if (int rc = alegpu_preprocess_rollout(r->ring, r->starts, carry_in, carry_out, r->obs, E, T,
+                                           stream))
+      return rc;
+    ALEGPU_CUDA_CHECK(cudaEventRecord(r->consumed[0], s)); // every slot was read by that kernel
+    r->used[0] = 1;
+    return ALEGPU_OK;
+  }
   // slot 0 <- the carried stack (Rollout::observations_ persists across rollouts)
   ALEGPU_CUDA_CHECK(cudaMemcpy2DAsync(r->obs, (size_t)T * 28224, carry_in, 28224, 28224,
                                       (size_t)E, cudaMemcpyDeviceToDevice, s));
-  ALEGPU_CUDA_CHECK(cudaEventRecord(r->start, s));
-  ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(r->copy_stream, r->start, 0));
   for (int64_t t = 0; t < T; ++t) {
-    const int slot = (int)(t % alegpu_rollout::kRing);
+    const int slot = (int)(t % slots);
     uint8_t *dev = r->ring + slab * slot;
-    if (t >= alegpu_rollout::kRing) // the kernel that last read this slot must be done
-      ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(r->copy_stream, r->consumed[slot], 0));
-    ALEGPU_CUDA_CHECK(cudaMemcpyAsync(dev, frames_host + slab * t, slab, cudaMemcpyHostToDevice,
-                                      r->copy_stream));
-    ALEGPU_CUDA_CHECK(cudaEventRecord(r->copied[slot], r->copy_stream));
+    if (int rc = copy_slab(t))
+      return rc;
     ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(s, r->copied[slot], 0));
     const bool last = t + 1 == T;
     // ring slab layout is [E,2,210,160,3]: frame a of env e at e*201600, frame b 100800 later,
@@ -194,6 +233,7 @@ extern "C" int alegpu_rollout_ingest(alegpu_rollout *r, const uint8_t *frames_ho
             last ? carry_out : r->obs + (t + 1) * 28224, last ? 28224 : T * 28224, E, stream))
       return rc;
     ALEGPU_CUDA_CHECK(cudaEventRecord(r->consumed[slot], s));
+    r->used[slot] = 1;
   }
   return ALEGPU_OK;
 }

@@ -315,18 +315,34 @@ def main():
     value = world * N / (ms_per_step * 1e-3)
 
     # ---- e2e: host buffers through the reference-facing API ---------------------------------------
-    host_scalars = {k: s[k] for k in pristine}
-    loss_host = np.zeros((epochs, nmb, mb), np.float32)
-    gn_host = np.zeros((epochs, nmb), np.float32)
+    # Every step copies its inputs from PINNED host memory (raw frames through the ring of
+    # alegpu_rollout_ingest, scalar streams, next_values) and reads its results (loss and pre-clip
+    # gradient norms of every minibatch) back into pinned host memory.  The host runs one step
+    # ahead of the device: step i is enqueued before the results of step i-1 are awaited, so the
+    # frame copies of step i (copy stream) overlap train() of step i-1; every step's results are
+    # read inside the timed region (the loop ends on a full synchronize).
+    def pinned_like(a):
+        p = C.c_void_p()
+        alegpu._check(lib.alegpu_host_alloc(C.byref(p), C.c_size_t(max(a.nbytes, 16))))
+        v = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(a.nbytes,))
+        v = v.view(a.dtype).reshape(a.shape)
+        v[...] = a
+        return v
+
+    host_scalars = {k: pinned_like(s[k]) for k in pristine}
+    nv_host = pinned_like(s["next_values"])
+    loss_host = [pinned_like(np.zeros((epochs, nmb, mb), np.float32)) for _ in range(2)]
+    gn_host = [pinned_like(np.zeros((epochs, nmb), np.float32)) for _ in range(2)]
+    done = [evt(), evt()]
+    pending = [False, False]
 
     def e2e_step(i):
         for k, a in host_scalars.items():
             d = getattr(buf, k)
             alegpu._check(lib.alegpu_memcpy_h2d(C.c_void_p(d.ptr), a.ctypes.data_as(C.c_void_p),
                                                 C.c_size_t(a.nbytes), C.c_void_p(stream)))
-        alegpu._check(lib.alegpu_memcpy_h2d(C.c_void_p(nv.ptr),
-                                            s["next_values"].ctypes.data_as(C.c_void_p),
-                                            C.c_size_t(s["next_values"].nbytes), C.c_void_p(stream)))
+        alegpu._check(lib.alegpu_memcpy_h2d(C.c_void_p(nv.ptr), nv_host.ctypes.data_as(C.c_void_p),
+                                            C.c_size_t(nv_host.nbytes), C.c_void_p(stream)))
         alegpu._check(lib.alegpu_rollout_ingest(buf.h, hptr, C.c_int(i % 2), C.c_void_p(stream)))
         b = alegpu._Batch()
         alegpu._check(lib.alegpu_rollout_get(buf.h, C.c_void_p(nv.ptr), C.c_float(HP["gamma"]),
@@ -335,13 +351,21 @@ def main():
         cm = met._c()
         alegpu._check(lib.alegpu_learner_train(L.h, C.byref(b), C.byref(cm), C.c_int64(epochs),
                                                C.c_int64(nmb), C.byref(hp), 1 if use_graph else 0))
-        alegpu._check(lib.alegpu_memcpy_d2h(loss_host.ctypes.data_as(C.c_void_p),
-                                            C.c_void_p(met.loss.ptr), C.c_size_t(loss_host.nbytes),
-                                            C.c_void_p(stream)))
-        alegpu._check(lib.alegpu_memcpy_d2h(gn_host.ctypes.data_as(C.c_void_p),
+        j = i % 2
+        if pending[j]:  # results of step i-2 were consumed below before this buffer is reused
+            pending[j] = False
+        alegpu._check(lib.alegpu_memcpy_d2h(loss_host[j].ctypes.data_as(C.c_void_p),
+                                            C.c_void_p(met.loss.ptr),
+                                            C.c_size_t(loss_host[j].nbytes), C.c_void_p(stream)))
+        alegpu._check(lib.alegpu_memcpy_d2h(gn_host[j].ctypes.data_as(C.c_void_p),
                                             C.c_void_p(met.clipped_gradients.ptr),
-                                            C.c_size_t(gn_host.nbytes), C.c_void_p(stream)))
-        alegpu.synchronize(stream)
+                                            C.c_size_t(gn_host[j].nbytes), C.c_void_p(stream)))
+        alegpu._check(lib.alegpu_event_record(done[j], C.c_void_p(stream)))
+        pending[j] = True
+        if pending[1 - j]:  # await and read the PREVIOUS step's results
+            alegpu._check(lib.alegpu_event_synchronize(done[1 - j]))
+            assert np.isfinite(loss_host[1 - j][0, 0, 0]) and np.isfinite(gn_host[1 - j]).all()
+            pending[1 - j] = False
 
     e2e_steps = max(3, min(args.steps, 10))
     for i in range(2):
@@ -349,8 +373,9 @@ def main():
     e2e_ms = timed_loop(e2e_step, e2e_steps) / e2e_steps
     e2e_value = world * N / (e2e_ms * 1e-3)
     h2d = T * slab + sum(a.nbytes for a in host_scalars.values()) + s["next_values"].nbytes
-    d2h = loss_host.nbytes + gn_host.nbytes
-    assert np.isfinite(loss_host).all() and np.isfinite(gn_host).all(), "non-finite metrics"
+    d2h = loss_host[0].nbytes + gn_host[0].nbytes
+    for j in range(2):
+        assert np.isfinite(loss_host[j]).all() and np.isfinite(gn_host[j]).all(), "non-finite metrics"
 
     # Multi-rank exit: every collective of this run has completed (timed_loop ends on a barrier).
     # Graceful NCCL teardown (ncclCommDestroy / destroy_process_group) of two communicators in one

@@ -60,9 +60,9 @@ int main(int argc, char **argv) {
   EXPECT(std::strstr(alegpu_version(), "sm_100a") != nullptr);
 
   if (argc > 1 && std::strcmp(argv[1], "gpu") == 0) {
-    // test/ai/gae-test.cc:6-38 SimpleNoTerminals: r = 1, v = 0, next = 0, gamma .99, lambda .95
+    // test/ai/gae-test.cc:6-38 SimpleNoTerminalsNoTruncations: r = 1, v = .5, next = .5
     const int E = 1, T = 3;
-    float h_r[T] = {1, 1, 1}, h_v[T] = {0, 0, 0}, h_n[E] = {0}, h_a[T] = {0, 0, 0};
+    float h_r[T] = {1, 1, 1}, h_v[T] = {0.5f, 0.5f, 0.5f}, h_n[E] = {0.5f}, h_a[T] = {0, 0, 0};
     uint8_t h_z[T] = {0, 0, 0};
     float *d_r, *d_v, *d_n, *d_a;
     uint8_t *d_z;
@@ -80,9 +80,15 @@ int main(int argc, char **argv) {
     ai::gae::gae(a, r, v, n, z, z, z, 0.99f, 0.95f);
     check(alegpu_memcpy_d2h(h_a, d_a, sizeof h_a, nullptr));
     check(alegpu_stream_synchronize(nullptr));
-    const float want[T] = {2.8109f, 1.9308f, 0.9950f}; // 1 + .9405*(1 + .9405*1), ...
+    float want[T], last = 0.0f, nvv = h_n[0]; // the expectation exactly as the reference test forms it
+    for (int i = T - 1; i >= 0; --i) {
+      const float delta = h_r[i] + 0.99f * nvv - h_v[i];
+      want[i] = delta + 0.99f * 0.95f * last;
+      last = want[i];
+      nvv = h_v[i];
+    }
     for (int t = 0; t < T; ++t)
-      EXPECT(std::fabs(h_a[t] - (t == 2 ? 1.0f : want[t])) < 1e-3f || std::fabs(h_a[t] - want[t]) < 1e-2f);
+      EXPECT(std::fabs(h_a[t] - want[t]) < 1e-5f);
     std::printf("gpu gae: %.4f %.4f %.4f\n", h_a[0], h_a[1], h_a[2]);
   }
   std::printf("shim ok\n");
