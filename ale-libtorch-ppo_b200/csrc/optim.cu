@@ -42,16 +42,31 @@ __global__ void __launch_bounds__(kThreads)
 }
 
 __global__ void __launch_bounds__(kThreads)
-    adam_clip_kernel(float *__restrict__ p, float *__restrict__ g, float *__restrict__ m,
+    adam_clip_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m,
                      float *__restrict__ v, __nv_bfloat16 *__restrict__ shadow, int64_t n4,
                      const float *__restrict__ partials, int nparts,
                      const OptState *__restrict__ st, float max_norm,
                      float *__restrict__ total_norm_out) {
   __shared__ float s_coef, s_step_size, s_bc2_sqrt;
+  float4 *p4 = reinterpret_cast<float4 *>(p);
+  const float4 *g4 = reinterpret_cast<const float4 *>(g);
+  float4 *m4 = reinterpret_cast<float4 *>(m);
+  float4 *v4 = reinterpret_cast<float4 *>(v);
+  const int64_t stride = (int64_t)gridDim.x * kThreads;
+  int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+  // the first element's four loads are in flight while warp 0 forms the clip coefficient
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 pp = zero4, gg = zero4, mm = zero4, vv = zero4;
+  if (i < n4) {
+    pp = p4[i];
+    gg = g4[i];
+    mm = m4[i];
+    vv = v4[i];
+  }
   if (threadIdx.x < 32) {
     double s = 0.0;
-    for (int i = threadIdx.x; i < nparts; i += 32)
-      s += (double)partials[i];
+    for (int k = threadIdx.x; k < nparts; k += 32)
+      s += (double)partials[k];
     s = warp_sum(s);
     if (threadIdx.x == 0) {
       const float total = (float)sqrt(s);
@@ -69,25 +84,25 @@ __global__ void __launch_bounds__(kThreads)
   const float coef = s_coef, step_size = s_step_size, bc2_sqrt = s_bc2_sqrt;
   const float b1 = 0.9f, b2 = 0.999f, omb1 = (float)(1.0 - 0.9), omb2 = (float)(1.0 - 0.999);
   const float eps = 1e-5f;
-  float4 *p4 = reinterpret_cast<float4 *>(p);
-  float4 *g4 = reinterpret_cast<float4 *>(g);
-  float4 *m4 = reinterpret_cast<float4 *>(m);
-  float4 *v4 = reinterpret_cast<float4 *>(v);
-  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n4;
-       i += (int64_t)gridDim.x * kThreads) {
-    float4 pp = p4[i], gg = g4[i], mm = m4[i], vv = v4[i];
+  while (i < n4) {
+    const int64_t nxt = i + stride;
+    float4 pn = zero4, gn = zero4, mn = zero4, vn = zero4;
+    if (nxt < n4) { // next element's loads before this one's math and stores
+      pn = p4[nxt];
+      gn = g4[nxt];
+      mn = m4[nxt];
+      vn = v4[nxt];
+    }
     float *pa = &pp.x, *ga = &gg.x, *ma = &mm.x, *va = &vv.x;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const float gc = ga[k] * coef; // train.cc:42-44
-      ga[k] = gc;
+      const float gc = ga[k] * coef; // train.cc:42-44 (the scaled gradient is consumed here only)
       ma[k] = ma[k] * b1 + gc * omb1;
       va[k] = va[k] * b2 + (gc * gc) * omb2;
       const float denom = sqrtf(va[k]) / bc2_sqrt + eps;
       pa[k] = pa[k] - step_size * (ma[k] / denom);
     }
     p4[i] = pp;
-    g4[i] = gg;
     m4[i] = mm;
     v4[i] = vv;
     if (shadow) {
@@ -97,6 +112,8 @@ __global__ void __launch_bounds__(kThreads)
       pk.y = *reinterpret_cast<uint32_t *>(&hi);
       reinterpret_cast<uint2 *>(shadow)[i] = pk;
     }
+    pp = pn; gg = gn; mm = mn; vv = vn;
+    i = nxt;
   }
 }
 
