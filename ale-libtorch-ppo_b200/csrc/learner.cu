@@ -189,15 +189,15 @@ int sync_opt_state(alegpu_learner *L) {
 
 bool use_tc(const alegpu_learner *L) { return L->cfg.math == ALEGPU_MATH_BF16; }
 
-int forward(alegpu_learner *L, const uint8_t *obs, int64_t n) {
+int forward(alegpu_learner *L, const uint8_t *obs, int64_t n, const void *obs16 = nullptr) {
   if (use_tc(L))
-    return net_tc_forward(L->Pv, L->tc, obs, n, L->acts, L->stream);
+    return net_tc_forward(L->Pv, L->tc, obs, n, L->acts, L->stream, obs16);
   return net_f32_forward(L->Pv, obs, n, L->acts, L->stream);
 }
 
-int backward(alegpu_learner *L, const uint8_t *obs, int64_t n) {
+int backward(alegpu_learner *L, const uint8_t *obs, int64_t n, const void *obs16 = nullptr) {
   if (use_tc(L)) // launches the heads' weight gradients itself, on its side branch
-    return net_tc_backward(L->Pv, L->Gv, L->tc, obs, n, L->acts, L->stream);
+    return net_tc_backward(L->Pv, L->Gv, L->tc, obs, n, L->acts, L->stream, obs16);
   if (int rc = heads_wgrad(L->Gv, L->acts, n, L->ws, L->ws_floats, L->stream))
     return rc;
   return net_f32_backward(L->Pv, L->Gv, obs, n, L->acts, L->ws, L->ws_floats, L->stream);
@@ -236,6 +236,7 @@ int clip_and_step(alegpu_learner *L, float max_norm, float *total_norm_out) {
     return rc;
   L->host_step += 1;
   return launch_adam_clip(L->params, L->grads, L->m, L->v, use_tc(L) ? L->tc.w_shadow : nullptr,
+                          use_tc(L) ? L->tc.c1w_perm : nullptr,
                           L->Ppad, L->norm_partials, L->opt, max_norm, total_norm_out, L->stream);
 }
 
@@ -260,6 +261,12 @@ int enqueue_train(alegpu_learner *L, const alegpu_batch &b, const alegpu_metrics
                   const alegpu_train_options &opt) {
   const int64_t mb = b.size / nmb, A = L->cfg.action_size;
   const bool shuffled = opt.indices != nullptr;
+  // tensor-core path: conv1 reads a bf16 NHWC copy of the observations; with contiguous slices it
+  // is made ONCE here for the whole batch (reused by every epoch), else per gathered minibatch
+  const void *obs16_all = nullptr;
+  if (use_tc(L) && !shuffled)
+    if (int rc = net_tc_prepare_obs(L->tc, b.observations, b.size, &obs16_all, L->stream))
+      return rc;
   // contiguous slices: the per-minibatch unmasked counts are known up front; shuffled: per step
   if (!shuffled)
     if (int rc = launch_mask_count(b.masks, mb, nmb, L->counts, L->stream))
@@ -322,7 +329,9 @@ int enqueue_train(alegpu_learner *L, const alegpu_batch &b, const alegpu_metrics
 #endif
         la.adv_stats = st;
       }
-      if (int rc = forward(L, obs, mb))
+      const void *obs16 =
+          obs16_all ? (const void *)((const uint16_t *)obs16_all + (size_t)s * 28224) : nullptr;
+      if (int rc = forward(L, obs, mb, obs16))
         return rc;
       la.clip = hp.clip_param;
       la.vcoef = hp.value_loss_coef;
@@ -339,7 +348,7 @@ int enqueue_train(alegpu_learner *L, const alegpu_batch &b, const alegpu_metrics
       int nparts = 0;
       if (int rc = heads_loss_backward(L->Pv, L->acts, mb, la, L->loss_partials, &nparts, L->stream))
         return rc;
-      if (int rc = backward(L, obs, mb))
+      if (int rc = backward(L, obs, mb, obs16))
         return rc;
       if (int rc = allreduce_grads(L))
         return rc;
@@ -898,6 +907,9 @@ extern "C" int alegpu_learner_train_ex(alegpu_learner *L, const alegpu_batch *ba
       return fail(ALEGPU_OUT_OF_RANGE, "train: a minibatch index was outside [0, batch size)");
     }
   }
+  if (use_tc(L) && !opt.indices)
+    if (int rc = net_tc_reserve_obs(L->tc, batch->size))
+      return rc;
   alegpu_metrics mt{};
   if (metrics)
     mt = *metrics;

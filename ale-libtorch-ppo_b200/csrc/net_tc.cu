@@ -110,6 +110,28 @@ struct Col1 {
     return make_uint2(__ldg(p), __ldg(p + 1));
   }
 };
+// conv1 over the bf16 NHWC copy of the observations ([n,84,84,4], made once per train() by
+// obs_to_nhwc_bf16_kernel): row m = (n,oy,ox) of 20x20, k' = ky*32 + kx*4 + c, so the 8 kx of one
+// ky are 32 contiguous elements and every 16-byte chunk (2 pixels x 4 channels) can be copied with
+// cp.async.  The conv1 weights are read from a shadow permuted to the same k' order.
+struct Col1N {
+  ALEGPU_RAW_BF16
+  static constexpr bool kAsyncSrc = true;
+  static constexpr int kPrefetch = 2;
+  const bf16 *x; // obs16 [n,84,84,4]
+  using PosPtr = const bf16 *;
+  __device__ __forceinline__ const void *anchor() const { return x; }
+  __device__ __forceinline__ const bf16 *pos_ptr(int m) const {
+    const int n = m / 400, pix = m - n * 400, oy = pix / 20, ox = pix - oy * 20;
+    return x + ((size_t)(n * 84 + 4 * oy) * 84 + 4 * ox) * 4;
+  }
+  __device__ __forceinline__ int k_off(int k) const { return (k >> 5) * 336 + (k & 31); }
+  __device__ __forceinline__ uint4 at(int m, int k) const { return ldg16(pos_ptr(m) + k_off(k)); }
+};
+// k' = ky*32 + kx*4 + c  ->  the reference's OIHW reduction index k = c*64 + ky*8 + kx
+__host__ __device__ __forceinline__ int conv1_k_of_kprime(int kp) {
+  return (kp & 3) * 64 + (kp >> 5) * 8 + ((kp >> 2) & 7);
+}
 // conv2: row m = (n,oy,ox) of 9x9, k = (ky*4+kx)*32 + ci
 struct Col2 {
   ALEGPU_RAW_BF16
@@ -479,7 +501,7 @@ struct EpiWgradDirect { // gw[i*K + j] = acc (j < K), gb[i] = acc (j == K)
 // combined in fixed order, so the result is deterministic.  block = (32, 8), grid = (K+1, C/32)
 __global__ void __launch_bounds__(256)
     reduce_wgrad_t_kernel(const float *__restrict__ ws, int splits, int K, int C, float scale,
-                          float *__restrict__ gw, float *__restrict__ gb) {
+                          float *__restrict__ gw, float *__restrict__ gb, bool conv1_perm) {
   __shared__ float part[8][32];
   const int k = blockIdx.x, co = blockIdx.y * 32 + threadIdx.x, ty = threadIdx.y;
   const size_t per = (size_t)(K + 1) * C;
@@ -494,8 +516,8 @@ __global__ void __launch_bounds__(256)
 #pragma unroll
     for (int g = 1; g < 8; ++g)
       t += part[g][threadIdx.x];
-    if (k < K)
-      gw[(size_t)co * K + k] = t * scale;
+    if (k < K) // conv1 runs in the k' order of Col1N; the gradient goes back to OIHW
+      gw[(size_t)co * K + (conv1_perm ? conv1_k_of_kprime(k) : k)] = t * scale;
     else
       gb[co] = t;
   }
@@ -546,7 +568,7 @@ void plan_splits(int64_t R, int64_t tiles, size_t per_split_floats, size_t ws_fl
 // conv weight gradient: ws[z][k][co] partials of  sum_m col(m,k) * dY[m][co], then fixed-order sum
 template <class Col, int K, int C>
 int conv_wgrad(const Col &col, const bf16 *dy, int64_t Mtot, float scale, float *gw, float *gb,
-               float *ws, size_t ws_floats, cudaStream_t s) {
+               float *ws, size_t ws_floats, cudaStream_t s, bool conv1_perm = false) {
   const int64_t mtiles = ceil_div(K + 1, tc::BM);
   const size_t per = (size_t)(K + 1) * C;
   ALEGPU_REQUIRE(ws_floats >= per, ALEGPU_RUNTIME_ERROR, "wgrad: workspace too small");
@@ -557,7 +579,7 @@ int conv_wgrad(const Col &col, const bf16 *dy, int64_t Mtot, float scale, float 
     return rc;
   static_assert(C % 32 == 0, "channel count must be a multiple of 32");
   reduce_wgrad_t_kernel<<<dim3(K + 1, C / 32), dim3(32, 8), 0, s>>>(
-      ws, splits, K, C, scale, gw, gb);
+      ws, splits, K, C, scale, gw, gb, conv1_perm);
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
   return ALEGPU_OK;
@@ -567,6 +589,49 @@ __global__ void bf16_to_f32_kernel(const bf16 *__restrict__ src, float *__restri
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (int64_t)gridDim.x * blockDim.x)
     dst[i] = __bfloat162float(src[i]);
+}
+
+// u8 NCHW [n,4,84,84] -> bf16 NHWC [n,84,84,4] (u8 is exact in bf16).  One thread = 4 pixels of one
+// row: four coalesced 4-byte loads (one per channel plane), one 32-byte store.  HBM-bound:
+// 28 224 B read + 56 448 B written per observation, once per train() (not per epoch / minibatch).
+__global__ void __launch_bounds__(256)
+    obs_to_nhwc_bf16_kernel(const uint8_t *__restrict__ obs, bf16 *__restrict__ out, int64_t total) {
+  // total = n * 84 * 21 work items (n, y, x4)
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row = i / 21; // n*84 + y
+    const int x4 = (int)(i - row * 21);
+    const int64_t n = row / 84;
+    const int y = (int)(row - n * 84);
+    const uint8_t *src = obs + n * 28224 + (size_t)y * 84 + x4 * 4;
+    uint32_t w[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+      w[c] = __ldg(reinterpret_cast<const uint32_t *>(src + c * 7056));
+    uint32_t o[8]; // pixel j: channels 0..3 -> two packed bf16 pairs
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t sel = 0x0040u + (uint32_t)j * 0x0011u; // byte j of the 1st, byte j of the 2nd
+      const uint32_t px = (__byte_perm(w[0], w[1], sel) & 0xFFFFu) |               // c0, c1
+                          (__byte_perm(w[2], w[3], sel) << 16);                    // c2, c3
+      // px bytes = (c0, c1, c2, c3) of pixel j
+      uint32_t lo, hi;
+      u8x4_to_bf16(px, lo, hi);
+      o[2 * j] = lo;
+      o[2 * j + 1] = hi;
+    }
+    uint4 *dst = reinterpret_cast<uint4 *>(out + ((size_t)row * 84 + x4 * 4) * 4);
+    dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+    dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+  }
+}
+// c1w bf16 [32][256] OIHW order -> [32][256] in Col1N's k' order
+__global__ void permute_c1w_kernel(const bf16 *__restrict__ w, bf16 *__restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < 32 * 256) {
+    const int co = i >> 8, kp = i & 255;
+    out[i] = w[co * 256 + conv1_k_of_kprime(kp)];
+  }
 }
 
 struct Shadow { // bf16 views of the flat parameter buffer (same offsets as NetParams)
@@ -599,6 +664,8 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
     return ALEGPU_OK;
   };
   if (int rc = alloc(&T.w_shadow, sizeof(bf16) * (size_t)Ppad)) return rc;
+  if (int rc = alloc(&T.c1w_perm, sizeof(bf16) * 32 * 256)) return rc;
+  if (int rc = alloc(&T.obs16_mb, sizeof(bf16) * (size_t)cap * 28224)) return rc;
   if (int rc = alloc(&T.act1, sizeof(bf16) * (size_t)cap * 12800)) return rc;
   if (int rc = alloc(&T.act2, sizeof(bf16) * (size_t)cap * 5184)) return rc;
   if (int rc = alloc(&T.act3, sizeof(bf16) * (size_t)cap * 3136)) return rc;
@@ -621,11 +688,15 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
     ALEGPU_CUDA_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
   const char *env = getenv("ALEGPU_TC_SERIAL");
   T.serial = env && env[0] == '1';
+  env = getenv("ALEGPU_CONV1_U8");
+  T.conv1_u8 = env && env[0] == '1';
+  env = getenv("ALEGPU_CONV1_WGRAD_NHWC");
+  T.conv1_wgrad_nhwc = env && env[0] == '1';
   return ALEGPU_OK;
 }
 
 void net_tc_destroy(TcState &T) {
-  for (void *p : {T.w_shadow, T.act1, T.act2, T.act3, T.dact1, T.dact2, T.dact3, T.fc16, T.dfc16,
+  for (void *p : {T.c1w_perm, T.obs16_mb, T.obs16_all, T.w_shadow, T.act1, T.act2, T.act3, T.dact1, T.dact2, T.dact3, T.fc16, T.dfc16,
                   T.wt, (void *)T.stage, (void *)T.ws_heads, (void *)T.ws_fc, (void *)T.ws_c3,
                   (void *)T.ws_c2, (void *)T.ws_c1})
     if (p)
@@ -639,18 +710,74 @@ void net_tc_destroy(TcState &T) {
 }
 
 int net_tc_refresh_weights(TcState &T, const float *params, int64_t Ppad, cudaStream_t s) {
-  return launch_f32_to_bf16(params, T.w_shadow, Ppad, s);
+  if (int rc = launch_f32_to_bf16(params, T.w_shadow, Ppad, s))
+    return rc;
+  permute_c1w_kernel<<<32, 256, 0, s>>>((const bf16 *)T.w_shadow, (bf16 *)T.c1w_perm); // c1w is first
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}
+
+namespace {
+int convert_obs(const uint8_t *obs, int64_t n, void *out, cudaStream_t s) {
+  const int64_t total = n * 84 * 21;
+  if (total == 0)
+    return ALEGPU_OK;
+  const int blocks = (int)std::min<int64_t>(ceil_div(total, 256), (int64_t)kNumSMs * 16);
+  obs_to_nhwc_bf16_kernel<<<blocks, 256, 0, s>>>(obs, (bf16 *)out, total);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}
+constexpr int64_t kObs16MaxRows = (int64_t)1 << 17; // 131 072 rows = 7.4 GB of bf16 observations
+} // namespace
+
+// allocation only (never inside a stream capture): room for n rows of bf16 observations
+int net_tc_reserve_obs(TcState &T, int64_t n) {
+  if (T.conv1_u8 || n > kObs16MaxRows || T.obs16_all_rows >= n)
+    return ALEGPU_OK;
+  if (T.obs16_all)
+    ALEGPU_CUDA_CHECK(cudaFree(T.obs16_all));
+  T.obs16_all = nullptr;
+  T.obs16_all_rows = 0;
+  ALEGPU_CUDA_CHECK(cudaMalloc(&T.obs16_all, sizeof(bf16) * (size_t)n * 28224));
+  T.obs16_all_rows = n;
+  return ALEGPU_OK;
+}
+
+int net_tc_prepare_obs(TcState &T, const uint8_t *obs, int64_t n, const void **obs16,
+                       cudaStream_t s) {
+  *obs16 = nullptr;
+  if (T.conv1_u8 || T.obs16_all_rows < n)
+    return ALEGPU_OK; // not reserved (too big to keep): the forward converts per minibatch
+  if (int rc = convert_obs(obs, n, T.obs16_all, s))
+    return rc;
+  *obs16 = T.obs16_all;
+  return ALEGPU_OK;
 }
 
 int net_tc_forward(const NetParams &P, TcState &T, const uint8_t *obs, int64_t n, NetActs &A,
-                   cudaStream_t s) {
+                   cudaStream_t s, const void *obs16) {
   const int H = (int)P.hidden;
   const Shadow W = shadow_view(T, P);
   bf16 *act1 = (bf16 *)T.act1, *act2 = (bf16 *)T.act2, *act3 = (bf16 *)T.act3;
-  if (int rc = tc::launch_gemm_tc<32, 4>(ColK<Col1>{Col1{obs}}, RowsK{W.c1w, 256},
-                                         EpiBiasReluBf16{act1, P.c1b, 32, 1.0f / 255.0f}, n * 400,
-                                         32, 256, 1, 0, s))
-    return rc;
+  if (T.conv1_u8) { // A/B switch: conv1 straight from the u8 observations (register producers)
+    if (int rc = tc::launch_gemm_tc<32, 4>(ColK<Col1>{Col1{obs}}, RowsK{W.c1w, 256},
+                                           EpiBiasReluBf16{act1, P.c1b, 32, 1.0f / 255.0f},
+                                           n * 400, 32, 256, 1, 0, s))
+      return rc;
+  } else {
+    if (!obs16) {
+      if (int rc = convert_obs(obs, n, T.obs16_mb, s))
+        return rc;
+      obs16 = T.obs16_mb;
+    }
+    if (int rc = tc::launch_gemm_tc<32, 4>(ColK<Col1N>{Col1N{(const bf16 *)obs16}},
+                                           RowsK{(const bf16 *)T.c1w_perm, 256},
+                                           EpiBiasReluBf16{act1, P.c1b, 32, 1.0f / 255.0f},
+                                           n * 400, 32, 256, 1, 0, s))
+      return rc;
+  }
   if (int rc = tc::launch_gemm_tc<64, 4>(ColK<Col2>{Col2{act1}}, RowsK{W.c2w, 512},
                                          EpiBiasReluBf16{act2, P.c2b, 64, 1.0f}, n * 81, 64, 512,
                                          1, 0, s))
@@ -687,7 +814,7 @@ int net_tc_forward(const NetParams &P, TcState &T, const uint8_t *obs, int64_t n
 // gradient.  Two branches: the data-gradient chain fc -> conv3 -> conv2 (+ conv1's weight gradient)
 // on `s`, and the other weight gradients on T.side as soon as their inputs exist.
 int net_tc_backward(const NetParams &P, const NetParams &G, TcState &T, const uint8_t *obs,
-                    int64_t n, NetActs &A, cudaStream_t s) {
+                    int64_t n, NetActs &A, cudaStream_t s, const void *obs16) {
   const int H = (int)P.hidden;
   const Shadow W = shadow_view(T, P);
   bf16 *act1 = (bf16 *)T.act1, *act2 = (bf16 *)T.act2, *act3 = (bf16 *)T.act3;
@@ -760,9 +887,20 @@ int net_tc_backward(const NetParams &P, const NetParams &G, TcState &T, const ui
                                          n * 100, 32, 256, 4, 0, s))
     return rc;
   // conv1 (input needs no gradient); the 1/255 of the input scale lands on the weight gradient
-  if (int rc = conv_wgrad<Col1, 256, 32>(Col1{obs}, dact1, n * 400, 1.0f / 255.0f, G.c1w, G.c1b,
-                                         T.ws_c1, T.ws_c1_n, s))
-    return rc;
+  // conv1's weight gradient keeps the u8 register producers: measured at the v1 minibatch (1280
+  // rows) 132 us against 185 us for the cp.async view of obs16, whose im2col-expanded bf16 traffic
+  // (4x the unique bytes, twice the u8 volume) all comes from L2 while the u8 windows hit in L1;
+  // the forward, with 4 k-blocks per tile, is the other way round (87 -> 52 us).
+  if (T.conv1_u8 || !T.conv1_wgrad_nhwc) {
+    if (int rc = conv_wgrad<Col1, 256, 32>(Col1{obs}, dact1, n * 400, 1.0f / 255.0f, G.c1w, G.c1b,
+                                           T.ws_c1, T.ws_c1_n, s))
+      return rc;
+  } else { // the forward of these rows left their bf16 copy in obs16_mb unless the caller has one
+    const bf16 *x = (const bf16 *)(obs16 ? obs16 : T.obs16_mb);
+    if (int rc = conv_wgrad<Col1N, 256, 32>(Col1N{x}, dact1, n * 400, 1.0f / 255.0f, G.c1w, G.c1b,
+                                            T.ws_c1, T.ws_c1_n, s, /*conv1_perm=*/true))
+      return rc;
+  }
   if (!T.serial)
     ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(s, T.ev_join, 0));
   return ALEGPU_OK;

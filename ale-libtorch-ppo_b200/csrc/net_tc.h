@@ -7,6 +7,11 @@ namespace alegpu {
 struct TcState {
   int64_t hidden = 0, actions = 0, cap = 0, Ppad = 0;
   void *w_shadow = nullptr;  // bf16 copy of the flat parameter buffer (written by Adam)
+  void *c1w_perm = nullptr;  // bf16 conv1 weights [32][256] in the k' = (ky,kx,c) order of obs16
+  // bf16 NHWC copy of the observations conv1 reads: one minibatch (cap rows) and, lazily, a whole
+  // train() batch so the conversion runs once per train() instead of once per minibatch step
+  void *obs16_mb = nullptr, *obs16_all = nullptr;
+  int64_t obs16_all_rows = 0;
   void *act1 = nullptr, *act2 = nullptr, *act3 = nullptr;    // bf16 NHWC activations
   void *dact1 = nullptr, *dact2 = nullptr, *dact3 = nullptr; // bf16 NHWC activation grads
   void *fc16 = nullptr, *dfc16 = nullptr;                    // bf16 copies of fc in/out grads
@@ -21,17 +26,25 @@ struct TcState {
   float *ws_heads = nullptr, *ws_fc = nullptr, *ws_c3 = nullptr, *ws_c2 = nullptr, *ws_c1 = nullptr;
   size_t ws_heads_n = 0, ws_fc_n = 0, ws_c3_n = 0, ws_c2_n = 0, ws_c1_n = 0;
   bool serial = false;       // ALEGPU_TC_SERIAL=1: keep everything on one stream (profiling)
+  bool conv1_u8 = false;     // ALEGPU_CONV1_U8=1: conv1 forward reads the u8 observations (A/B)
+  bool conv1_wgrad_nhwc = false; // ALEGPU_CONV1_WGRAD_NHWC=1: conv1 wgrad reads obs16 (A/B)
 };
 
 int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_t Ppad,
                 cudaStream_t s);
 void net_tc_destroy(TcState &T);
 int net_tc_refresh_weights(TcState &T, const float *params, int64_t Ppad, cudaStream_t s);
+// obs16 = the rows' bf16 NHWC copy when the caller already made one (net_tc_prepare_obs); nullptr:
+// the forward converts `obs` into T.obs16_mb itself and the backward of the same rows reuses it
 int net_tc_forward(const NetParams &P, TcState &T, const uint8_t *obs, int64_t n, NetActs &A,
-                   cudaStream_t s);
+                   cudaStream_t s, const void *obs16 = nullptr);
+// reserve: (re)allocates T.obs16_all for n rows (skipped above 131 072 rows; never call it inside a
+// stream capture).  prepare: converts rows [n,4,84,84] u8 into it; *obs16 = nullptr if not reserved
+int net_tc_reserve_obs(TcState &T, int64_t n);
+int net_tc_prepare_obs(TcState &T, const uint8_t *obs, int64_t n, const void **obs16, cudaStream_t s);
 // includes the heads' weight gradients (heads_wgrad) — the caller must not launch them again
 int net_tc_backward(const NetParams &P, const NetParams &G, TcState &T, const uint8_t *obs,
-                    int64_t n, NetActs &A, cudaStream_t s);
+                    int64_t n, NetActs &A, cudaStream_t s, const void *obs16 = nullptr);
 int net_tc_fetch_activation(TcState &T, int which, int64_t n, float *host, cudaStream_t s);
 
 } // namespace alegpu

@@ -43,7 +43,8 @@ __global__ void __launch_bounds__(kThreads)
 
 __global__ void __launch_bounds__(kThreads)
     adam_clip_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m,
-                     float *__restrict__ v, __nv_bfloat16 *__restrict__ shadow, int64_t n4,
+                     float *__restrict__ v, __nv_bfloat16 *__restrict__ shadow,
+                     __nv_bfloat16 *__restrict__ c1w_perm, int64_t n4,
                      const float *__restrict__ partials, int nparts,
                      const OptState *__restrict__ st, float max_norm,
                      float *__restrict__ total_norm_out) {
@@ -111,6 +112,17 @@ __global__ void __launch_bounds__(kThreads)
       pk.x = *reinterpret_cast<uint32_t *>(&lo);
       pk.y = *reinterpret_cast<uint32_t *>(&hi);
       reinterpret_cast<uint2 *>(shadow)[i] = pk;
+      // conv1's weights (the first 32*256 parameters, OIHW: k = c*64 + ky*8 + kx) are also kept in
+      // the (ky,kx,c) order in which the tensor-core conv1 walks the NHWC observations
+      if (c1w_perm && i < 32 * 256 / 4) {
+        const int idx = (int)i * 4, co = idx >> 8, k = idx & 255;
+        const int c = k >> 6, ky = (k >> 3) & 7, kx = k & 7;
+        __nv_bfloat16 *o = c1w_perm + co * 256 + ky * 32 + kx * 4 + c;
+        o[0] = __float2bfloat16_rn(pp.x);
+        o[4] = __float2bfloat16_rn(pp.y);
+        o[8] = __float2bfloat16_rn(pp.z);
+        o[12] = __float2bfloat16_rn(pp.w);
+      }
     }
     pp = pn; gg = gn; mm = mn; vv = vn;
     i = nxt;
@@ -135,11 +147,13 @@ int launch_grad_sumsq(const float *grads, int64_t n_padded, float *partials, Opt
 }
 
 int launch_adam_clip(float *params, float *grads, float *m, float *v, void *bf16_shadow,
+                     void *c1w_perm,
                      int64_t n_padded, const float *partials, const OptState *st,
                      float max_norm, float *total_norm_out, cudaStream_t s) {
   const int blocks = (int)std::min<int64_t>(ceil_div(n_padded / 4, kThreads), kNumSMs * 8);
   adam_clip_kernel<<<blocks, kThreads, 0, s>>>(params, grads, m, v,
                                                static_cast<__nv_bfloat16 *>(bf16_shadow),
+                                               static_cast<__nv_bfloat16 *>(c1w_perm),
                                                n_padded / 4, partials, kNormBlocks, st, max_norm,
                                                total_norm_out);
   ALEGPU_COUNT_LAUNCH();

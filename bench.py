@@ -41,7 +41,9 @@ WORKLOADS = {  # configs/*.yaml shapes; E is per GPU
     "debug": dict(E=8, T=32, H=32, epochs=2, nmb=4),
     "v0": dict(E=8, T=128, H=512, epochs=4, nmb=4),
     "v1": dict(E=4096, T=5, H=512, epochs=1, nmb=16),
-    "sweep": dict(E=4096, T=128, H=512, epochs=4, nmb=32),
+    # BASELINE.json config 4: 4096 envs x 128 steps env-sharded over 8 GPUs = 512 envs per GPU
+    # (weak-scaling form: the per-GPU slice is fixed, N GPUs hold N*512 envs); minibatch 2048/GPU
+    "sweep": dict(E=512, T=128, H=512, epochs=4, nmb=32),
 }
 HP = dict(clip=0.1, vcoef=0.5, ecoef=0.01, max_norm=0.5, lr=2.5e-4, gamma=0.99, lam=0.95)
 PREPROCESS_BYTES_PER_STEP = 250_992  # 2*100800 read + 28224 write + 21168 carried
