@@ -543,3 +543,56 @@ def selftest_tc_gemm(A, B, M, N, R, a_mn=False, b_mn=False, bn=64, splits=1, use
               C.c_int(int(a_mn)), C.c_int(int(b_mn)), C.c_int(bn), C.c_int(splits), None))
     synchronize()
     return dC.numpy()
+
+
+# ---- ai::rollout::Rollout::rollout() — src/ai/rollout.cc:198-278 ------------------------------------
+class _RolloutLog(C.Structure):
+    _fields_ = [("steps", C.c_int64), ("episodes", C.c_int64), ("finished_episodes", C.c_int64),
+                ("finished_games", C.c_int64), ("mean_episode_return", C.c_float),
+                ("mean_episode_length", C.c_float), ("mean_game_return", C.c_float),
+                ("mean_game_length", C.c_float)]
+
+
+ENV_STEP_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.POINTER(C.c_uint8),
+                          C.POINTER(C.c_uint8), C.POINTER(C.c_float), C.POINTER(C.c_uint8),
+                          C.POINTER(C.c_uint8), C.POINTER(C.c_uint8))
+
+
+class Collector:
+    """Rollout collection (alegpu_collector_*): CPU emulator threads behind a step callback (None =
+    the built-in Breakout-shaped frame source), pinned frame ring, per-step hand-off."""
+
+    def __init__(self, total_environments, horizon, action_size=4, num_workers=1, step_fn=None,
+                 seed=0, device=0):
+        self._fn = ENV_STEP_FN(step_fn) if step_fn is not None else None
+        h = C.c_void_p()
+        _check(lib().alegpu_collector_create(
+            C.c_int64(total_environments), C.c_int64(horizon), C.c_int64(action_size),
+            C.c_int(num_workers), self._fn if self._fn is not None else C.cast(None, ENV_STEP_FN),
+            None, C.c_uint64(seed), C.c_int(device), C.byref(h)))
+        self.h = h
+        self.E, self.T, self.A = total_environments, horizon, action_size
+
+    def __del__(self):
+        if getattr(self, "h", None) and _lib is not None:
+            _lib.alegpu_collector_destroy(self.h)
+            self.h = None
+
+    def rollout(self, buffer, learner, gamma, lambda_):
+        """Returns (Batch of [N] views, log dict); synchronises the learner's stream."""
+        b, log = _Batch(), _RolloutLog()
+        _check(lib().alegpu_collector_rollout(self.h, buffer.h, learner.h, C.c_float(gamma),
+                                              C.c_float(lambda_), C.byref(b), C.byref(log)))
+        synchronize(learner.stream)
+        N = self.E * self.T
+        batch = Batch(buffer.observations.view(0, (N, 4, 84, 84)), buffer.actions.view(0, (N,)),
+                      buffer.log_probabilities.view(0, (N, self.A)),
+                      buffer.advantages.view(0, (N,)), buffer.returns.view(0, (N,)),
+                      buffer.masks.view(0, (N,)))
+        return batch, {k: getattr(log, k) for k, _ in _RolloutLog._fields_}
+
+    def frames(self):
+        """The pinned host frame ring of the last rollout as a numpy view [T,E,2,210,160,3]."""
+        lib().alegpu_collector_frames.restype = C.POINTER(C.c_uint8)
+        p = lib().alegpu_collector_frames(self.h)
+        return np.ctypeslib.as_array(p, shape=(self.T, self.E, 2, 210, 160, 3))

@@ -349,6 +349,41 @@ int alegpu_learner_train_ex(alegpu_learner *learner, const alegpu_batch *batch,
 /* number of kernels the last alegpu_learner_train call launched (or replayed) */
 int64_t alegpu_learner_last_launch_count(const alegpu_learner *learner);
 
+/* ---- rollout collection: ai::rollout::Rollout::rollout() — src/ai/rollout.cc:198-278 -------------
+ * The emulator stays on CPU threads behind a step callback (where ALE's step and the last two raw
+ * frames of the MaxAndSkip window plug in, src/ai/environment/max_and_skip.cc:21-45,
+ * src/ai/rollout.cc:289-328); the collector owns the worker threads, the pinned frame ring and the
+ * per-step hand-off (one cudaMemcpyAsync of the step's [E,2,210,160,3] slab on a copy stream, one
+ * fused preprocess kernel into slot t+1, rewards/flags as one small copy, the E actions back in one
+ * pinned D2H instead of E .item() syncs).
+ * step(user, env, action, reset, frame_a, frame_b, &reward, &terminated, &truncated, &game_over):
+ * reset != 0 -> environment->reset() (rollout.cc:299-305: reward 0, flags false, frames = the
+ * reset observation twice); else step with `action` and write the window's last two RGB frames
+ * [210,160,3].  Called concurrently for different envs.  NULL = the built-in Breakout-shaped
+ * frame source (ALE and its ROMs are not part of this library). */
+typedef void (*alegpu_env_step_fn)(void *user, int64_t env, int64_t action, int reset,
+                                   uint8_t *frame_a, uint8_t *frame_b, float *reward,
+                                   uint8_t *terminated, uint8_t *truncated, uint8_t *game_over);
+typedef struct alegpu_collector alegpu_collector;
+/* ai::rollout::Log — src/ai/rollout.h (steps, episodes, the finished episodes of this rollout) */
+typedef struct {
+  int64_t steps, episodes, finished_episodes, finished_games;
+  float mean_episode_return, mean_episode_length, mean_game_return, mean_game_length;
+} alegpu_rollout_log;
+int alegpu_collector_create(int64_t E, int64_t T, int64_t A, int num_workers,
+                            alegpu_env_step_fn step, void *user, uint64_t seed, int device,
+                            alegpu_collector **out);
+int alegpu_collector_destroy(alegpu_collector *collector);
+/* T steps of {act, step all envs, buffer column t, next observation stack, episode bookkeeping},
+ * one more policy call for the bootstrap values, then Buffer::get: on return the rollout storage is
+ * full and *flat holds the [N] views alegpu_learner_train consumes.  std::out_of_range
+ * (ALEGPU_OUT_OF_RANGE) for an action index outside [0, A) (rollout.cc:314-316). */
+int alegpu_collector_rollout(alegpu_collector *collector, alegpu_rollout *rollout,
+                             alegpu_learner *learner, float gamma, float lambda,
+                             alegpu_batch *flat, alegpu_rollout_log *log);
+/* the pinned host frame ring [T,E,2,210,160,3] of the last rollout (parity tests replay it) */
+const uint8_t *alegpu_collector_frames(const alegpu_collector *collector);
+
 /* Self-test of the tcgen05/TMEM implicit-GEMM engine behind ALEGPU_MATH_BF16 (no reference
  * counterpart: cuBLAS plays this role under libtorch).  C[M][N] fp32 = A . B^T with fp32 inputs
  * rounded to bf16 on load.  a_mn == 0: A is [M][R] row-major; a_mn == 1: A is stored [R][M];

@@ -445,3 +445,63 @@ def test_metrics_summary_and_masked_select(shape):
     for k in ("total_losses", "advantages"):  # bit-exact, order preserved
         assert np.array_equal(met.masked(k), host[k][m])
 
+
+
+# ---- rollout collection loop (Rollout::rollout, src/ai/rollout.cc:198-278) -----------------------
+def _collect(E, T, H, workers, seed):
+    params = cases.net_params(H)
+    L = alegpu.Learner(H, 4, max(E, 8), alegpu.MATH_FP32, cases.LR)
+    L.set_params(params)
+    buf = alegpu.Buffer(E, T, 4)
+    col = alegpu.Collector(E, T, 4, num_workers=workers, seed=seed)
+    out = []
+    for _ in range(2):  # two rollouts: the second starts from the carried stacks / episode state
+        batch, log = col.rollout(buf, L, cases.GAMMA, cases.LAMBDA)
+        out.append({"frames": col.frames().copy(), "log": log,
+                    **{k: getattr(buf, k).numpy().copy() for k in
+                       ("observations", "actions", "rewards", "values", "logits", "terminals",
+                        "truncations", "episode_starts", "advantages", "returns", "masks")}})
+    return params, L, out
+
+
+def test_collector_rollout_replays_through_the_oracle():
+    E, T, H = 6, 40, 32
+    params, L, outs = _collect(E, T, H, workers=3, seed=5)
+    stack = np.zeros((E, 4, 84, 84), np.uint8)
+    prev_end = None
+    for r, o in enumerate(outs):
+        st, te, tr = o["episode_starts"], o["terminals"], o["truncations"]
+        # flag invariants of rollout.cc:239-265 / gae.cc:49-53
+        assert not np.any((st & te) | (st & tr) | (te & tr))
+        assert np.array_equal(st[:, 1:] != 0, (te[:, :-1] | tr[:, :-1]) != 0)
+        if r == 0:
+            assert np.all(st[:, 0] == 1)
+        else:
+            assert np.array_equal(st[:, 0] != 0, prev_end)
+        prev_end = (te[:, -1] | tr[:, -1]) != 0
+        # observations: bit-exact replay of max -> area resize -> gray -> stack on the recorded frames
+        for t in range(T):
+            assert np.array_equal(o["observations"][:, t], stack), (r, t)
+            gray = restate.preprocess(o["frames"][t, :, 0], o["frames"][t, :, 1])[1]
+            stack = restate.stack_update(stack, gray, st[:, t])
+        # the policy outputs stored in column t are the network's outputs on slot t
+        lg, vl = restate.net_forward(params, H, o["observations"].reshape(-1, 4, 84, 84))
+        np.testing.assert_allclose(o["logits"].reshape(-1, 4), lg, rtol=1e-4, atol=1e-5)
+        np.testing.assert_allclose(o["values"].ravel(), vl, rtol=1e-4, atol=1e-5)
+        assert o["actions"].min() >= 0 and o["actions"].max() < 4
+        # Buffer::get on the collected scalars (rewards were clamped in place, buffer.cc:67)
+        nv = restate.net_forward(params, H, stack)[1]
+        assert np.all(np.abs(o["rewards"]) <= 1.0)
+        want = restate.buffer_get(o["rewards"], o["values"], nv, te, tr, st, cases.GAMMA, cases.LAMBDA)
+        np.testing.assert_allclose(o["advantages"], want["advantages"], rtol=1e-4, atol=1e-5)
+        np.testing.assert_array_equal(o["masks"] != 0, want["masks"] != 0)
+    assert outs[1]["log"]["steps"] > outs[0]["log"]["steps"] > 0
+
+
+def test_collector_is_deterministic_across_worker_counts():
+    a = _collect(5, 12, 32, workers=1, seed=9)[2]
+    b = _collect(5, 12, 32, workers=4, seed=9)[2]
+    for x, y in zip(a, b):
+        assert np.array_equal(x["frames"], y["frames"])
+        for k in ("actions", "rewards", "terminals", "truncations", "episode_starts", "observations"):
+            assert np.array_equal(x[k], y[k]), k
