@@ -232,12 +232,12 @@ int allreduce_grads(alegpu_learner *L) {
 }
 
 int clip_and_step(alegpu_learner *L, float max_norm, float *total_norm_out) {
-  if (int rc = launch_grad_sumsq(L->grads, L->Ppad, L->norm_partials, L->opt, L->stream))
+  if (int rc = launch_grad_sumsq(L->grads, L->Ppad, L->norm_partials, L->opt, max_norm,
+                                 total_norm_out, L->stream))
     return rc;
   L->host_step += 1;
   return launch_adam_clip(L->params, L->grads, L->m, L->v, use_tc(L) ? L->tc.w_shadow : nullptr,
-                          use_tc(L) ? L->tc.c1w_perm : nullptr,
-                          L->Ppad, L->norm_partials, L->opt, max_norm, total_norm_out, L->stream);
+                          use_tc(L) ? L->tc.c1w_perm : nullptr, L->Ppad, L->opt, L->stream);
 }
 
 // the body of train(): everything is stream-ordered, nothing synchronises

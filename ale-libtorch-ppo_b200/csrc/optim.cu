@@ -5,8 +5,10 @@
 // src/bin/train.cc:360-362 (betas 0.9/0.999, no weight decay, no amsgrad) with two launches:
 //   grad_sumsq : deterministic per-block partial sums of g^2 (sqrt(sum_i ||g_i||^2) over the
 //                per-tensor norms == the L2 norm of the flat gradient)
-//   adam_clip  : every block re-reduces the partials in index order, forms
-//                coef = min(1, max_norm/(total+1e-6)) (train.cc:39-41), and applies
+//                per-tensor norms == the L2 norm of the flat gradient); the LAST block to finish
+//                sums the partials in index order and leaves coef = min(1, max_norm/(total+1e-6))
+//                (train.cc:39-41), lr/(1-b1^t) and sqrt(1-b2^t) in the device-side OptState
+//   adam_clip  : applies
 //                g*=coef; m=b1 m+(1-b1)g; v=b2 v+(1-b2)g^2;
 //                p -= (lr/(1-b1^t)) m / (sqrt(v)/sqrt(1-b2^t) + eps)      (torch's form)
 // with 16-byte vector loads/stores: 28 B per parameter per step (+2 B for the bf16 shadow the
@@ -24,8 +26,9 @@ constexpr int kThreads = 256;
 
 __global__ void __launch_bounds__(kThreads)
     grad_sumsq_kernel(const float *__restrict__ g, int64_t n4, float *__restrict__ partials,
-                      OptState *__restrict__ st) {
+                      OptState *__restrict__ st, float max_norm, float *__restrict__ total_norm_out) {
   __shared__ float red[kThreads / 32];
+  __shared__ bool s_last;
   float acc = 0.0f;
   const float4 *g4 = reinterpret_cast<const float4 *>(g);
   for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n4;
@@ -36,8 +39,32 @@ __global__ void __launch_bounds__(kThreads)
   acc = block_sum<float, kThreads>(acc, red);
   if (threadIdx.x == 0) {
     partials[blockIdx.x] = acc;
-    if (blockIdx.x == 0)
-      st->step += 1; // Adam's step counter counts minibatch updates (train.h:129)
+    __threadfence();
+    s_last = atomicAdd(&st->done_count, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!s_last || threadIdx.x >= 32)
+    return;
+  // the last block: every partial is visible; sum them in index order (bit-reproducible), then
+  // everything the Adam kernel needs as three floats, so it starts straight on its loads
+  __threadfence();
+  double s = 0.0;
+  for (int i = threadIdx.x; i < (int)gridDim.x; i += 32)
+    s += (double)__ldcg(partials + i);
+  s = warp_sum(s);
+  if (threadIdx.x == 0) {
+    const float total = (float)sqrt(s);
+    const float coef = (float)((double)max_norm / ((double)total + 1e-6)); // train.cc:39
+    st->coef = fminf(coef, 1.0f);                                          // train.cc:40-41
+    const long long step = st->step + 1; // Adam's counter counts minibatch updates (train.h:129)
+    st->step = step;
+    const double t = (double)step;
+    const double bc1 = 1.0 - pow(0.9, t), bc2 = 1.0 - pow(0.999, t);
+    st->step_size = (float)(st->lr / bc1);
+    st->bc2_sqrt = (float)sqrt(bc2);
+    st->done_count = 0u;
+    if (total_norm_out)
+      *total_norm_out = total; // the PRE-clip norm (train.h:104)
   }
 }
 
@@ -45,17 +72,13 @@ __global__ void __launch_bounds__(kThreads)
     adam_clip_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m,
                      float *__restrict__ v, __nv_bfloat16 *__restrict__ shadow,
                      __nv_bfloat16 *__restrict__ c1w_perm, int64_t n4,
-                     const float *__restrict__ partials, int nparts,
-                     const OptState *__restrict__ st, float max_norm,
-                     float *__restrict__ total_norm_out) {
-  __shared__ float s_coef, s_step_size, s_bc2_sqrt;
+                     const OptState *__restrict__ st) {
   float4 *p4 = reinterpret_cast<float4 *>(p);
   const float4 *g4 = reinterpret_cast<const float4 *>(g);
   float4 *m4 = reinterpret_cast<float4 *>(m);
   float4 *v4 = reinterpret_cast<float4 *>(v);
   const int64_t stride = (int64_t)gridDim.x * kThreads;
   int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
-  // the first element's four loads are in flight while warp 0 forms the clip coefficient
   const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
   float4 pp = zero4, gg = zero4, mm = zero4, vv = zero4;
   if (i < n4) {
@@ -64,25 +87,7 @@ __global__ void __launch_bounds__(kThreads)
     mm = m4[i];
     vv = v4[i];
   }
-  if (threadIdx.x < 32) {
-    double s = 0.0;
-    for (int k = threadIdx.x; k < nparts; k += 32)
-      s += (double)partials[k];
-    s = warp_sum(s);
-    if (threadIdx.x == 0) {
-      const float total = (float)sqrt(s);
-      float coef = (float)((double)max_norm / ((double)total + 1e-6)); // train.cc:39
-      s_coef = fminf(coef, 1.0f);                                      // train.cc:40-41
-      const double t = (double)st->step;
-      const double bc1 = 1.0 - pow(0.9, t), bc2 = 1.0 - pow(0.999, t);
-      s_step_size = (float)(st->lr / bc1);
-      s_bc2_sqrt = (float)sqrt(bc2);
-      if (blockIdx.x == 0 && total_norm_out)
-        *total_norm_out = total; // the PRE-clip norm (train.h:104)
-    }
-  }
-  __syncthreads();
-  const float coef = s_coef, step_size = s_step_size, bc2_sqrt = s_bc2_sqrt;
+  const float coef = st->coef, step_size = st->step_size, bc2_sqrt = st->bc2_sqrt;
   const float b1 = 0.9f, b2 = 0.999f, omb1 = (float)(1.0 - 0.9), omb2 = (float)(1.0 - 0.999);
   const float eps = 1e-5f;
   while (i < n4) {
@@ -139,23 +144,21 @@ __global__ void f32_to_bf16_kernel(const float *__restrict__ src, __nv_bfloat16 
 } // namespace
 
 int launch_grad_sumsq(const float *grads, int64_t n_padded, float *partials, OptState *st,
-                      cudaStream_t s) {
-  grad_sumsq_kernel<<<kNormBlocks, kThreads, 0, s>>>(grads, n_padded / 4, partials, st);
+                      float max_norm, float *total_norm_out, cudaStream_t s) {
+  grad_sumsq_kernel<<<kNormBlocks, kThreads, 0, s>>>(grads, n_padded / 4, partials, st, max_norm,
+                                                     total_norm_out);
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
   return ALEGPU_OK;
 }
 
 int launch_adam_clip(float *params, float *grads, float *m, float *v, void *bf16_shadow,
-                     void *c1w_perm,
-                     int64_t n_padded, const float *partials, const OptState *st,
-                     float max_norm, float *total_norm_out, cudaStream_t s) {
+                     void *c1w_perm, int64_t n_padded, const OptState *st, cudaStream_t s) {
   const int blocks = (int)std::min<int64_t>(ceil_div(n_padded / 4, kThreads), kNumSMs * 8);
   adam_clip_kernel<<<blocks, kThreads, 0, s>>>(params, grads, m, v,
                                                static_cast<__nv_bfloat16 *>(bf16_shadow),
-                                               static_cast<__nv_bfloat16 *>(c1w_perm),
-                                               n_padded / 4, partials, kNormBlocks, st, max_norm,
-                                               total_norm_out);
+                                               static_cast<__nv_bfloat16 *>(c1w_perm), n_padded / 4,
+                                               st);
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
   return ALEGPU_OK;

@@ -8,16 +8,22 @@ namespace alegpu {
 struct OptState {
   double lr;      // src/bin/train.cc:424-428 writes it once per rollout
   long long step; // torch Adam's per-parameter step (identical for all parameters)
+  // written by the last block of grad_sumsq for the Adam kernel of the same step
+  unsigned int done_count; // blocks of the running grad_sumsq that have stored their partial
+  float coef;              // min(1, max_norm / (total + 1e-6))            train.cc:39-41
+  float step_size;         // lr / (1 - beta1^t)
+  float bc2_sqrt;          // sqrt(1 - beta2^t)
 };
 
 constexpr int kNormBlocks = 296; // 2 CTAs per SM, fixed => bit-reproducible partial order
 
+// partial sums of g^2; the last block to finish sums them in fixed order, advances the step counter
+// and leaves the clip coefficient / bias corrections in *st; total_norm_out <- the PRE-clip norm
 int launch_grad_sumsq(const float *grads, int64_t n_padded, float *partials, OptState *st,
-                      cudaStream_t s);
+                      float max_norm, float *total_norm_out, cudaStream_t s);
 int launch_adam_clip(float *params, float *grads, float *m, float *v, void *bf16_shadow,
                      void *c1w_perm, // optional bf16 [32][256] conv1 weights in (ky,kx,c) order
-                     int64_t n_padded, const float *partials, const OptState *st,
-                     float max_norm, float *total_norm_out, cudaStream_t s);
+                     int64_t n_padded, const OptState *st, cudaStream_t s);
 int launch_f32_to_bf16(const float *src, void *dst, int64_t n, cudaStream_t s);
 
 } // namespace alegpu
