@@ -441,6 +441,25 @@ class Learner:
                                              v.ctypes.data_as(C.c_void_p), C.byref(st)))
         return m, v, int(st.value)
 
+    def set_adam(self, exp_avg, exp_avg_sq, step):
+        m = np.ascontiguousarray(exp_avg, np.float32)
+        v = np.ascontiguousarray(exp_avg_sq, np.float32)
+        assert m.size == self.P and v.size == self.P
+        _check(lib().alegpu_learner_set_adam(self.h, m.ctypes.data_as(C.c_void_p),
+                                             v.ctypes.data_as(C.c_void_p), C.c_int64(step)))
+
+    def save(self, path):
+        """Checkpoint: parameters (reference order / OIHW), Adam moments, step -> one .npz file."""
+        m, v, step = self.get_adam()
+        np.savez(path, params=self.get_params(), exp_avg=m, exp_avg_sq=v, step=np.int64(step),
+                 hidden_size=self.hidden_size, action_size=self.action_size)
+
+    def load(self, path):
+        z = np.load(path)
+        assert int(z["hidden_size"]) == self.hidden_size and int(z["action_size"]) == self.action_size
+        self.set_params(z["params"])
+        self.set_adam(z["exp_avg"], z["exp_avg_sq"], int(z["step"]))
+
     def set_lr(self, lr):
         _check(lib().alegpu_learner_set_lr(self.h, C.c_double(lr)))
 

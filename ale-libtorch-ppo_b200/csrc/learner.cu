@@ -707,6 +707,20 @@ extern "C" int alegpu_learner_get_adam(alegpu_learner *L, float *exp_avg_host,
   return ALEGPU_OK;
 }
 
+// checkpoint restore: Adam moments (reference order/layout) and the optimiser step counter
+extern "C" int alegpu_learner_set_adam(alegpu_learner *L, const float *exp_avg_host,
+                                       const float *exp_avg_sq_host, int64_t step) {
+  ALEGPU_REQUIRE(L && exp_avg_host && exp_avg_sq_host && step >= 0, ALEGPU_INVALID_ARGUMENT,
+                 "set_adam: bad argument");
+  ALEGPU_CUDA_CHECK(cudaSetDevice(L->cfg.device));
+  if (int rc = upload_flat(L, L->m, exp_avg_host))
+    return rc;
+  if (int rc = upload_flat(L, L->v, exp_avg_sq_host))
+    return rc;
+  L->host_step = step;
+  return sync_opt_state(L);
+}
+
 extern "C" int alegpu_learner_set_lr(alegpu_learner *L, double lr) {
   ALEGPU_REQUIRE(L, ALEGPU_INVALID_ARGUMENT, "set_lr: null learner");
   ALEGPU_CUDA_CHECK(cudaSetDevice(L->cfg.device));

@@ -278,6 +278,11 @@ int alegpu_learner_get_params(alegpu_learner *learner, float *params_host);
 /* Adam moments in the same order/layout, and the optimiser step counter. */
 int alegpu_learner_get_adam(alegpu_learner *learner, float *exp_avg_host, float *exp_avg_sq_host,
                             int64_t *step);
+/* Checkpoint / resume (the reference has none): together with set_params this restores
+ * a learner exactly — parameters, both Adam moments and the step counter that drives the bias
+ * correction — so training continues bit-identically. */
+int alegpu_learner_set_adam(alegpu_learner *learner, const float *exp_avg_host,
+                            const float *exp_avg_sq_host, int64_t step);
 /* the per-rollout lr anneal of src/bin/train.cc:424-428 (lr lives in a device scalar so a
  * captured graph stays correct) */
 int alegpu_learner_set_lr(alegpu_learner *learner, double lr);

@@ -505,3 +505,27 @@ def test_collector_is_deterministic_across_worker_counts():
         assert np.array_equal(x["frames"], y["frames"])
         for k in ("actions", "rewards", "terminals", "truncations", "episode_starts", "observations"):
             assert np.array_equal(x[k], y[k]), k
+
+
+# ---- N4: checkpoint / resume ------------------------------------------------------------------------
+@pytest.mark.parametrize("math", [alegpu.MATH_FP32, alegpu.MATH_BF16])
+def test_checkpoint_resume_is_bit_identical(tmp_path, math):
+    H, N, nmb = 32, 64, 2
+    tc = cases.train_case(N, seed=8)
+    batch = alegpu.Batch(tc["obs"], tc["actions"], tc["log_probs"], tc["advantages"], tc["returns"],
+                         tc["masks"])
+    hp = alegpu.Hyperparameters(cases.CLIP, cases.VCOEF, cases.ECOEF, cases.MAX_NORM)
+    a = alegpu.Learner(H, 4, N // nmb, math, cases.LR)
+    a.set_params(cases.net_params(H))
+    a.train(batch, None, 2, nmb, hp)
+    path = str(tmp_path / "ckpt.npz")
+    a.save(path)
+    a.train(batch, None, 1, nmb, hp)
+    b = alegpu.Learner(H, 4, N // nmb, math, cases.LR)
+    b.load(path)
+    assert b.get_adam()[2] == 2 * nmb
+    b.train(batch, None, 1, nmb, hp)
+    assert np.array_equal(a.get_params(), b.get_params())
+    ma, va, sa = a.get_adam()
+    mb_, vb, sb = b.get_adam()
+    assert sa == sb == 3 * nmb and np.array_equal(ma, mb_) and np.array_equal(va, vb)
