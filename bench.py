@@ -250,8 +250,8 @@ def main():
         alegpu._check(lib.alegpu_event_create(C.byref(e)))
         return e
 
-    ev = [evt() for _ in range(4)]
-    pre_ms = []
+    ev = [evt() for _ in range(6)]
+    pre_ms, train_ms = [], []
 
     def device_step(i, timed):
         restore_scalars_d2d()
@@ -267,13 +267,18 @@ def main():
                                              C.c_float(HP["lam"]), C.byref(b), 1,
                                              C.c_void_p(stream)))
         cm = met._c()
+        if timed:
+            alegpu._check(lib.alegpu_event_record(ev[4], C.c_void_p(stream)))
         alegpu._check(lib.alegpu_learner_train(L.h, C.byref(b), C.byref(cm), C.c_int64(epochs),
                                                C.c_int64(nmb), C.byref(hp), 1 if use_graph else 0))
         if timed:
+            alegpu._check(lib.alegpu_event_record(ev[5], C.c_void_p(stream)))
             alegpu.synchronize(stream)
             ms = C.c_float(0)
             alegpu._check(lib.alegpu_event_elapsed_ms(ev[2], ev[3], C.byref(ms)))
             pre_ms.append(ms.value)
+            alegpu._check(lib.alegpu_event_elapsed_ms(ev[4], ev[5], C.byref(ms)))
+            train_ms.append(ms.value)
 
     def barrier():
         alegpu.synchronize(stream)
@@ -399,6 +404,19 @@ def main():
         roof = {"kernel": "preprocess_rollout_pipe_kernel", "bound": "hbm", "achieved": ach, "peak": hbm,
                 "unit": "GB/s", "frac": ach / hbm, "traffic": traffic, "peak_source": which,
                 "ms_per_launch": pre, "algorithmic_bytes_per_launch": N * PREPROCESS_BYTES_PER_STEP}
+    # the tensor-core side of the step, for the same honesty: train() = epochs x N samples x
+    # 49.52 MFLOP (18.69 fwd + 30.83 bwd at H=512; 40.47 at H=32) against the measured
+    # dense bf16 peak.  At these minibatch sizes the chain of small GEMMs is latency / L2-bound, far
+    # from the tensor roof; the number is reported so that nobody has to guess it.
+    roof_tc = None
+    if train_ms:
+        tr = float(np.median(train_ms))
+        flop = epochs * N * (49.52e6 if H == 512 else 40.47e6 if H == 32 else 0.0)
+        if flop:
+            ach = flop / (tr * 1e-3) / 1e12
+            roof_tc = {"kernel": "train(): 11 gemm_tc_kernel launches per minibatch step", "bound": "tensor",
+                       "achieved": ach, "peak": tflops, "unit": "TFLOP/s", "frac": ach / tflops,
+                       "ms_per_train": tr, "peak_source": which}
     line = {"metric": METRIC, "value": value, "unit": "agent-steps/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -409,7 +427,8 @@ def main():
                        "l2": "inputs larger than L2 (raw frames %.0f MB per step)" % (T * slab / 1e6)},
             "e2e": {"value": e2e_value, "unit": "agent-steps/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms},
-            "gpu_launches": int(launches), "clocks": sampler.summary(), "roofline": roof}
+            "gpu_launches": int(launches), "clocks": sampler.summary(), "roofline": roof,
+            "roofline_tensor": roof_tc}
     if not args.no_cpu_baseline and world == 1:  # reported on rank 0 at N=1 only
         threads = os.cpu_count() or 1
         frac = 1.0 if N <= 4096 else 4096.0 / N

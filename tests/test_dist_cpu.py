@@ -73,3 +73,41 @@ def test_sharded_gradient_equals_single_process(tmp_path):
     err = np.linalg.norm((g0 - want).astype(np.float64)) / np.linalg.norm(want.astype(np.float64))
     assert err <= 1e-5, err
     assert abs(float(np.load(tmp_path / "loss_0.npy")) - lo["loss"]) <= 1e-5 * abs(lo["loss"]) + 1e-6
+
+
+def _adv_worker(rank, world, port, out_dir):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    rng = np.random.default_rng(77)
+    adv = (rng.standard_normal(64) * 2 + 0.5).astype(np.float32)
+    masks = rng.random(64) > 0.15
+    lo, hi = rank * 32, (rank + 1) * 32  # each rank holds half of the global minibatch
+    a, m = adv[lo:hi].astype(np.float64), masks[lo:hi]
+    # what adv_stats_kernel leaves per rank: (count, sum, sum of squares) in double; one
+    # all-reduce(sum) of 3 doubles gives the GLOBAL statistics (learner.cu, ncclDouble)
+    st = torch.tensor([m.sum(), a[m].sum(), (a[m] ** 2).sum()], dtype=torch.float64)
+    dist.all_reduce(st)
+    c, mean = st[0].item(), st[1].item() / st[0].item()
+    var = (st[2].item() - c * mean * mean) / (c - 1.0)
+    out = ((a - mean) / (np.sqrt(max(var, 0.0)) + 1e-8)).astype(np.float32)
+    np.save(os.path.join(out_dir, f"adv_{rank}.npy"), out)
+    dist.destroy_process_group()
+
+
+def test_global_advantage_statistics_world2(tmp_path):
+    """normalize_advantages with world_size 2: local (count, sum, sumsq) all-reduced == the
+    single-process normalisation of the whole minibatch (oracle/restate.normalize_advantages)."""
+    import torch.multiprocessing as mp
+    sys.path[:0] = [ROOT, os.path.join(ROOT, "tests")]
+    from oracle import restate
+    world, port = 2, _free_port()
+    mp.spawn(_adv_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    rng = np.random.default_rng(77)
+    adv = (rng.standard_normal(64) * 2 + 0.5).astype(np.float32)
+    masks = rng.random(64) > 0.15
+    want = restate.normalize_advantages(adv, masks)
+    got = np.concatenate([np.load(tmp_path / f"adv_{r}.npy") for r in range(world)])
+    np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-6)
