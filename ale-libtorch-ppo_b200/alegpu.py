@@ -196,6 +196,47 @@ def preprocess_rollout(frames, episode_starts, carry_in, carry_out, obs, E, T, s
                                            C.c_void_p(stream)))
 
 
+# ---- live path: per-frame stb resize (vision.cc:86-95) -> 2-frame max -> stack ------------------
+class vision:
+    """ai::vision — src/ai/vision.h:15-17 (the std::vector<unsigned char> overload)."""
+
+    @staticmethod
+    def resize_grayscale_image(image, width, height, new_width, new_height, return_f32=False):
+        """image: [height*width] or [n,height,width] u8 (host or DeviceArray) -> same rank, resized.
+        Restated stbir_resize_uint8_linear — parity unpinned, see include/alegpu.h."""
+        host = not isinstance(image, DeviceArray)
+        a = np.ascontiguousarray(image, dtype=np.uint8) if host else image
+        size = int(np.prod(a.shape))
+        if width <= 0 or height <= 0 or size % (width * height) != 0:
+            raise ValueError("image.size() must be a multiple of width*height")  # vision.cc:89
+        n = size // (width * height)
+        flat = len(a.shape) == 1
+        x = _dev(a, np.uint8)
+        out = DeviceArray((n, new_height, new_width) if new_height > 0 and new_width > 0 else (0,),
+                          np.uint8)
+        f32 = DeviceArray((n, new_height, new_width), np.float32) if return_f32 else None
+        _check(lib().alegpu_resize_grayscale(_p(x), C.c_int64(n), C.c_int(width), C.c_int(height),
+                                             C.c_int(new_width), C.c_int(new_height), _p(out),
+                                             _p(f32), None))
+        res = out.numpy() if host else out
+        if host and flat:
+            res = res.reshape(-1)
+        return (res, f32.numpy()) if return_f32 else res
+
+
+def preprocess_gray_step(frames_a, frames_b, starts, src_stack, dst_stack, frame_env_stride=210 * 160,
+                         starts_stride=1, src_env_stride=STACK_BYTES, dst_env_stride=STACK_BYTES,
+                         E=None, stream=None):
+    """resize(a), resize(b) -> max -> stack update (rollout.cc:146-161, 184-196), one kernel."""
+    E = frames_a.shape[0] if E is None else E
+    _check(lib().alegpu_preprocess_gray_step(_p(frames_a), _p(frames_b),
+                                             C.c_int64(frame_env_stride), _p(starts),
+                                             C.c_int64(starts_stride), _p(src_stack),
+                                             C.c_int64(src_env_stride), _p(dst_stack),
+                                             C.c_int64(dst_env_stride), C.c_int64(E),
+                                             C.c_void_p(stream)))
+
+
 # ---- ai::ppo::losses — src/ai/ppo/losses.h:6-37 ----------------------------------------------
 class losses:
     @staticmethod

@@ -71,6 +71,23 @@ inline void *&current_stream() {
 
 } // namespace alegpu_shim
 
+// ---- src/ai/vision.h:15-17 — the live path's per-frame grayscale resize (vision.cc:86-95) ------------
+namespace vision {
+// images [n,height,width] u8 -> out [n,new_height,new_width] u8 (device views); n = 1 with a
+// [height*width] view is the reference's single-image std::vector form.
+inline void resize_grayscale_image(const alegpu_shim::U8 &image, int width, int height,
+                                   int new_width, int new_height, alegpu_shim::U8 &out) {
+  using namespace alegpu_shim;
+  if (width <= 0 || height <= 0 || image.numel() % ((int64_t)width * height) != 0)
+    throw std::invalid_argument("image.size() must be a multiple of width*height"); // vision.cc:89
+  const int64_t n = image.numel() / ((int64_t)width * height);
+  if (new_width > 0 && new_height > 0 && out.numel() != n * new_width * new_height)
+    throw std::invalid_argument("out must hold n*new_width*new_height bytes");
+  check(alegpu_resize_grayscale(image.data, n, width, height, new_width, new_height, out.data,
+                                nullptr, current_stream()));
+}
+} // namespace vision
+
 // ---- src/ai/gae.h:4-7 -----------------------------------------------------------------------------
 namespace gae {
 inline void gae(alegpu_shim::F32 &advantages, const alegpu_shim::F32 &rewards,

@@ -110,6 +110,33 @@ int alegpu_preprocess_rollout(const uint8_t *frames, const uint8_t *episode_star
                               const uint8_t *carry_in, uint8_t *carry_out, uint8_t *obs,
                               int64_t E, int64_t T, void *stream);
 
+/* ai::vision::resize_grayscale_image(const std::vector<unsigned char>&, width, height, new_width,
+ * new_height) — src/ai/vision.h:15-17, src/ai/vision.cc:86-95 — the LIVE path's per-frame resize
+ * (ResizeEnvironment::resize, src/ai/environment/resize.cc:34-41), batched over n images:
+ * images [n,height,width] u8 -> out [n,new_height,new_width] u8, device pointers.
+ * Arithmetic: stbir_resize_uint8_linear(..., STBIR_1CHANNEL) with stb's defaults (Mitchell when an
+ * axis shrinks, Catmull-Rom when it grows, clamp edges, linear light, round to nearest), restated
+ * from the published algorithm — stb_image_resize2 (stb@0.0.0-20241109-5c20573, MODULE.bazel:38)
+ * is not under /root/reference and the reference has no test of this overload: PARITY UNPINNED.
+ * out_f32 (optional, [n,new_height,new_width]) receives the value before rounding.
+ * new_width/new_height <= 0 -> ALEGPU_INVALID_ARGUMENT (std::invalid_argument, resize.cc:15-16). */
+int alegpu_resize_grayscale(const uint8_t *images, int64_t n, int width, int height,
+                            int new_width, int new_height, uint8_t *out, float *out_f32,
+                            void *stream);
+
+/* One env step of the LIVE wrapper stack (src/ai/rollout.cc:146-161) for E environments whose
+ * emulator delivers grayscale screens: frames_a/frames_b = the last two 210x160 u8 screens of the
+ * skip window at frames_x + e*frame_env_stride; each is resized to 84x84 as above
+ * (ResizeEnvironment), the two results are max'ed (MaxAndSkipEnvironment, max_and_skip.cc:33-42;
+ * pass frames_a == frames_b when the window ended after one frame, :40-42) and the frame stack is
+ * updated exactly as in alegpu_preprocess_step (Rollout::update_observations, rollout.cc:184-196).
+ * One fused kernel; stacks 8-byte aligned, src != dst. */
+int alegpu_preprocess_gray_step(const uint8_t *frames_a, const uint8_t *frames_b,
+                                int64_t frame_env_stride, const uint8_t *starts,
+                                int64_t starts_stride, const uint8_t *src_stack,
+                                int64_t src_env_stride, uint8_t *dst_stack,
+                                int64_t dst_env_stride, int64_t E, void *stream);
+
 /* ai::ppo::losses::normalize_logits — src/ai/ppo/losses.cc:45-47. [n,A] -> [n,A]. */
 int alegpu_normalize_logits(const float *logits, int64_t n, int64_t A, float *out,
                             void *stream);

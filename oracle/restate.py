@@ -220,3 +220,71 @@ def gather_minibatches(indices, *arrays):
     idx = np.asarray(indices, np.int64)
     return tuple(np.ascontiguousarray(np.asarray(x)[idx]) for x in arrays)
 
+
+
+# ---- live path: stb_image_resize2's stbir_resize_uint8_linear, restated (PARITY UNPINNED) ------------
+# src/ai/vision.cc:86-95 calls the third-party header (stb@0.0.0-20241109-5c20573, MODULE.bazel:38),
+# which is not under /root/reference; the reference holds no test of this overload.  The rules below
+# are the published algorithm with stb's defaults: per axis Mitchell-Netravali (B = C = 1/3) when the
+# axis shrinks — evaluated in output space, support 2 output pixels — Catmull-Rom when it grows,
+# clamp edges (outside taps fold onto the edge pixel), weights of each output pixel normalised to 1,
+# linear light, u8 <-> float unscaled, result = (u8)clamp(x + .5, 0, 255).
+def _mitchell(x):
+    x = np.abs(x).astype(np.float32)
+    one, two = np.float32(1), np.float32(2)
+    near = (np.float32(16) + x * x * (np.float32(21) * x - np.float32(36))) / np.float32(18)
+    far = (np.float32(32) + x * (np.float32(-60) + x * (np.float32(36) - np.float32(7) * x))) / np.float32(18)
+    return np.where(x < one, near, np.where(x < two, far, np.float32(0))).astype(np.float32)
+
+
+def _catmull_rom(x):
+    x = np.abs(x).astype(np.float32)
+    one, two = np.float32(1), np.float32(2)
+    near = one - x * x * (np.float32(2.5) - np.float32(1.5) * x)
+    far = two - x * (np.float32(4) + x * (np.float32(0.5) * x - np.float32(2.5)))
+    return np.where(x < one, near, np.where(x < two, far, np.float32(0))).astype(np.float32)
+
+
+def stb_axis_matrix(n_in, n_out):
+    """Dense [n_out, n_in] fp32 weight matrix of one axis, built in SCATTER form for shrinking axes
+    (each input pixel spreads onto the output pixels within 2 of its centre — the way stb forms
+    its downsampling coefficients), gather form for growing ones."""
+    scale = np.float32(n_out) / np.float32(n_in)
+    W = np.zeros((n_out, n_in), np.float32)
+    if scale < 1:
+        margin = int(np.ceil(2.0 / float(scale))) + 2
+        for i in range(-margin, n_in + margin):
+            centre = (np.float32(i) + np.float32(0.5)) * scale        # in output space
+            lo = int(np.floor(float(centre) - 2.0 - 0.5)) - 1
+            hi = int(np.ceil(float(centre) + 2.0 - 0.5)) + 1
+            o = np.arange(max(lo, 0), min(hi, n_out - 1) + 1)
+            if o.size == 0:
+                continue
+            x = (o.astype(np.float32) + np.float32(0.5)) - centre
+            W[o, min(max(i, 0), n_in - 1)] += _mitchell(x) * scale     # clamp: fold onto the edge
+    else:
+        for o in range(n_out):
+            centre = (np.float32(o) + np.float32(0.5)) / scale        # in input space
+            for i in range(int(np.floor(float(centre))) - 3, int(np.floor(float(centre))) + 4):
+                w = _catmull_rom(np.float32(centre - (np.float32(i) + np.float32(0.5))))
+                W[o, min(max(i, 0), n_in - 1)] += w
+    W /= W.sum(axis=1, dtype=np.float32, keepdims=True)
+    return W.astype(np.float32)
+
+
+def resize_grayscale_stb(images, new_width, new_height):
+    """images [n,h,w] u8 -> (u8 [n,nh,nw], fp32 value before rounding)."""
+    a = np.asarray(images, np.uint8)
+    n, h, w = a.shape
+    Wv, Wh = stb_axis_matrix(h, new_height), stb_axis_matrix(w, new_width)
+    # float64 accumulation of the fp32 weights: the reference value the fp32 kernel is held to
+    f = np.einsum("oh,nhw,pw->nop", Wv.astype(np.float64), a.astype(np.float64), Wh.astype(np.float64))
+    q = np.clip(f + 0.5, 0.0, 255.0).astype(np.int64).astype(np.uint8)
+    return q, f.astype(np.float32)
+
+
+def preprocess_gray(frames_a, frames_b):
+    """live order (rollout.cc:146-161): resize each screen, then the 2-frame max."""
+    qa, _ = resize_grayscale_stb(frames_a, 84, 84)
+    qb, _ = resize_grayscale_stb(frames_b, 84, 84)
+    return np.maximum(qa, qb)

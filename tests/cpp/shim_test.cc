@@ -90,6 +90,27 @@ int main(int argc, char **argv) {
     for (int t = 0; t < T; ++t)
       EXPECT(std::fabs(h_a[t] - want[t]) < 1e-5f);
     std::printf("gpu gae: %.4f %.4f %.4f\n", h_a[0], h_a[1], h_a[2]);
+    // ai::vision::resize_grayscale_image (vision.cc:86-95): constant in -> constant out, bad size throws
+    {
+      std::vector<uint8_t> h_img(210 * 160, 93), h_out(84 * 84, 0);
+      uint8_t *d_img, *d_out;
+      check(alegpu_malloc((void **)&d_img, h_img.size()));
+      check(alegpu_malloc((void **)&d_out, h_out.size()));
+      check(alegpu_memcpy_h2d(d_img, h_img.data(), h_img.size(), nullptr));
+      U8 img(d_img, {210 * 160}), out(d_out, {84 * 84});
+      ai::vision::resize_grayscale_image(img, 160, 210, 84, 84, out);
+      check(alegpu_memcpy_d2h(h_out.data(), d_out, h_out.size(), nullptr));
+      check(alegpu_stream_synchronize(nullptr));
+      bool all = true;
+      for (uint8_t px : h_out)
+        all = all && px == 93;
+      EXPECT(all);
+      EXPECT(throws<std::invalid_argument>(
+          [&] { ai::vision::resize_grayscale_image(img, 160, 210, 0, 84, out); })); // resize.cc:15-16
+      EXPECT(throws<std::invalid_argument>(
+          [&] { ai::vision::resize_grayscale_image(img, 161, 210, 84, 84, out); }));
+      std::printf("gpu vision: resize ok\n");
+    }
   }
   std::printf("shim ok\n");
   return 0;

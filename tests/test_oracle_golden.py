@@ -187,3 +187,26 @@ def test_normalize_advantages_matches_torch_std():
     sel = torch.from_numpy(adv)[torch.from_numpy(masks)]
     want = (torch.from_numpy(adv) - sel.mean()) / (sel.std() + 1e-8)  # unbiased std, the PPO idiom
     np.testing.assert_allclose(got, want.numpy(), rtol=1e-5, atol=1e-6)
+
+
+# ---- live-path resize (stb restated; PARITY UNPINNED — no reference vector exists) ---------------
+def test_stb_resize_restatement_properties():
+    # hand-derived known answer of the stated rules: Mitchell at scale 1/2 on [0,0,255,255]:
+    # o=0 weighs in[3] (and its clamp-folded neighbour) by M(1.25)+M(1.75) and in[2] by M(.75), over 2
+    M = lambda x: (16 + x * x * (21 * x - 36)) / 18 if x < 1 else (32 + x * (-60 + x * (36 - 7 * x))) / 18
+    want0 = 255 * (M(.75) + M(1.25) + M(1.75)) / (2 * (M(.25) + M(.75) + M(1.25) + M(1.75)))
+    q, f = restate.resize_grayscale_stb(np.array([[[0, 0, 255, 255]]], np.uint8), 2, 1)
+    assert abs(float(f[0, 0, 0]) - want0) < 1e-4 and q[0, 0].tolist() == [28, 227]
+    for n_in, n_out in ((210, 84), (160, 84), (84, 84), (10, 33), (7, 3)):
+        W = restate.stb_axis_matrix(n_in, n_out)
+        np.testing.assert_allclose(W.sum(axis=1), 1.0, atol=1e-6)       # normalised
+        np.testing.assert_allclose(W, W[::-1, ::-1], atol=1e-5)          # mirror symmetric (fp32 weights)
+        taps = (W != 0).sum(axis=1).max()
+        assert taps <= (int(np.ceil(4 * max(n_in / n_out, 1.0))) + 1)    # support 2 each side
+    assert np.array_equal(restate.stb_axis_matrix(84, 84), np.eye(84, dtype=np.float32))
+    for val in (0, 1, 200, 255):                                         # test/ai/vision-test.cc:5-30 analogue
+        img = np.full((1, 210, 160), val, np.uint8)
+        assert np.all(restate.resize_grayscale_stb(img, 84, 84)[0] == val)
+    rng = np.random.default_rng(0)
+    a, b = rng.integers(0, 256, (2, 2, 210, 160), dtype=np.uint8)
+    assert np.array_equal(restate.preprocess_gray(a, b), restate.preprocess_gray(b, a))
