@@ -111,26 +111,31 @@ struct Col1 {
   }
 };
 // conv1 over the bf16 NHWC copy of the observations ([n,84,84,4], made once per train() by
-// obs_to_nhwc_bf16_kernel): row m = (n,oy,ox) of 20x20, k' = ky*32 + kx*4 + c, so the 8 kx of one
-// ky are 32 contiguous elements and every 16-byte chunk (2 pixels x 4 channels) can be copied with
-// cp.async.  The conv1 weights are read from a shadow permuted to the same k' order.
+// obs_to_s2d_bf16_kernel): row m = (n,oy,ox) of 20x20; on the space-to-depth layout the 8x8 stride-4
+// window is 2x2 taps of 64 contiguous channels, so every 16-byte chunk can be copied with cp.async.  The conv1 weights are read from a shadow permuted to the same k' order.
 struct Col1N {
   ALEGPU_RAW_BF16
   static constexpr bool kAsyncSrc = true;
   static constexpr int kPrefetch = 2;
-  const bf16 *x; // obs16 [n,84,84,4]
+  const bf16 *x; // obs16, space-to-depth [n,21,21,64]: channel = (y&3)*16 + (x&3)*4 + c
   using PosPtr = const bf16 *;
   __device__ __forceinline__ const void *anchor() const { return x; }
   __device__ __forceinline__ const bf16 *pos_ptr(int m) const {
     const int n = m / 400, pix = m - n * 400, oy = pix / 20, ox = pix - oy * 20;
-    return x + ((size_t)(n * 84 + 4 * oy) * 84 + 4 * ox) * 4;
+    return x + ((size_t)(n * 21 + oy) * 21 + ox) * 64;
   }
-  __device__ __forceinline__ int k_off(int k) const { return (k >> 5) * 336 + (k & 31); }
+  // k' = tap*64 + ch, tap = a*2 + b: the 2x2 stride-1 convolution over 64 channels that the 8x8
+  // stride-4 convolution becomes on this layout; one tap = 128 contiguous bytes
+  __device__ __forceinline__ int k_off(int k) const {
+    return ((k >> 7) * 21 + ((k >> 6) & 1)) * 64 + (k & 63);
+  }
   __device__ __forceinline__ uint4 at(int m, int k) const { return ldg16(pos_ptr(m) + k_off(k)); }
 };
-// k' = ky*32 + kx*4 + c  ->  the reference's OIHW reduction index k = c*64 + ky*8 + kx
+// k' = (a*2+b)*64 + r*16 + s*4 + c  ->  the reference's OIHW reduction index k = c*64 + ky*8 + kx
+// with ky = 4a + r, kx = 4b + s
 __host__ __device__ __forceinline__ int conv1_k_of_kprime(int kp) {
-  return (kp & 3) * 64 + (kp >> 5) * 8 + ((kp >> 2) & 7);
+  const int c = kp & 3, sx = (kp >> 2) & 3, ry = (kp >> 4) & 3, b = (kp >> 6) & 1, a = kp >> 7;
+  return c * 64 + (4 * a + ry) * 8 + 4 * b + sx;
 }
 // conv2: row m = (n,oy,ox) of 9x9, k = (ky*4+kx)*32 + ci
 struct Col2 {
@@ -263,6 +268,41 @@ struct ColsMN {
   __device__ __forceinline__ const void *anchor() const { return p; }
   __device__ __forceinline__ const void *at(RowCtx rc, ColCtx cc) const {
     return rc >= 0 ? (const void *)(cc + rc) : (const void *)&g_ones_chunk;
+  }
+};
+// conv1 wgrad on the space-to-depth layout, A operand (MN-major): row m = tap*32 + oc (tap = a*2+b),
+// reduction index r = s2d block (n, Y, X) of 21x21.  Element = dact1[n, Y-a, X-b, oc] or 0 outside
+// 20x20: the FOUR TAPS ARE FOUR SHIFTED VIEWS OF THE (small) OUTPUT GRADIENT, so the observation
+// operand (ColsMN over obs16, 128 contiguous bytes per r) is read exactly once, un-expanded:
+//   dW[(a,b,oc)][ch] = sum_{n,Y,X} dact1[n, Y-a, X-b, oc] * S[n, Y, X, ch]
+struct DYShift {
+  ALEGPU_RAW_BF16
+  static constexpr bool kMN = true;
+  static constexpr bool kAsync = true;
+  const bf16 *dy; // dact1 [n,20,20,32]
+  struct RowCtx {
+    int off, a, b; // off = oc0 - (a*20 + b)*32
+  };
+  struct ColCtx {
+    const bf16 *base; // dy element of (n, oy = Y, ox = X), channel 0 (may lie outside: only an offset)
+    int Y, X;
+  };
+  __device__ __forceinline__ RowCtx row(int m0) const {
+    const int tap = m0 >> 5, a = tap >> 1, b = tap & 1;
+    return RowCtx{(m0 & 31) - (a * 20 + b) * 32, a, b};
+  }
+  __device__ __forceinline__ ColCtx col(int r, int) const {
+    const int n = r / 441, pix = r - n * 441, Y = pix / 21, X = pix - Y * 21;
+    return ColCtx{dy + ((ptrdiff_t)(n * 20 + Y) * 20 + X) * 32, Y, X};
+  }
+  __device__ __forceinline__ const void *anchor() const { return dy; }
+  __device__ __forceinline__ const void *at(const RowCtx &rc, const ColCtx &cc) const {
+    const int oy = cc.Y - rc.a, ox = cc.X - rc.b;
+    return ((unsigned)oy < 20u && (unsigned)ox < 20u) ? (const void *)(cc.base + rc.off) : nullptr;
+  }
+  __device__ __forceinline__ uint4 load(int m0, int r, int z) const {
+    const void *p = at(row(m0), col(r, z));
+    return p ? ldg16(p) : zero16();
   }
 };
 struct ColsMNF32 {
@@ -553,6 +593,76 @@ __global__ void reduce_wgrad_kernel(const float *__restrict__ ws, int splits, in
   }
 }
 
+// conv1 wgrad (space-to-depth form): gw[oc*256 + k] = scale * sum_z ws[z][(tap,oc)][ch] with
+// k = conv1_k_of_kprime(tap*64 + ch); gb[oc] = sum over the column-sum partials bp[g][oc].
+// block (32, 8): 32 outputs, the 8 thread rows sum interleaved z subsets that are then combined in
+// fixed order (deterministic).  grid = 256 blocks of weights + 1 block of biases.
+__global__ void __launch_bounds__(256)
+    reduce_c1_s2d_kernel(const float *__restrict__ ws, int splits, float scale,
+                         const float *__restrict__ bp, int bias_parts, float *__restrict__ gw,
+                         float *__restrict__ gb) {
+  __shared__ float part[8][32];
+  const int ty = threadIdx.y, tx = threadIdx.x;
+  const bool bias = blockIdx.x == 256;
+  const int idx = blockIdx.x * 32 + tx;
+  const float *p = bias ? bp + tx : ws + idx;
+  const size_t stride = bias ? 32 : 128 * 64;
+  const int count = bias ? bias_parts : splits;
+  float s0 = 0.0f, s1 = 0.0f;
+  int z = ty;
+  for (; z + 8 < count; z += 16) { // two independent chains per thread
+    s0 += p[(size_t)z * stride];
+    s1 += p[(size_t)(z + 8) * stride];
+  }
+  if (z < count)
+    s0 += p[(size_t)z * stride];
+  part[ty][tx] = s0 + s1;
+  __syncthreads();
+  if (ty == 0) {
+    float t = part[0][tx];
+#pragma unroll
+    for (int g = 1; g < 8; ++g)
+      t += part[g][tx];
+    if (bias) {
+      gb[tx] = t;
+    } else {
+      const int m = idx >> 6, ch = idx & 63, tap = m >> 5, oc = m & 31;
+      gw[oc * 256 + conv1_k_of_kprime(tap * 64 + ch)] = t * scale;
+    }
+  }
+}
+// column sums of dact1 [rows][32] bf16 (the conv1 bias gradient): block g sums its contiguous row
+// range -> bp[g][32].  A thread owns 8 channels (one 16-byte load) of every 64th row; the 64 row
+// lanes are combined in fixed order.
+constexpr int kBiasParts = 296;
+__global__ void __launch_bounds__(256)
+    c1_bias_partial_kernel(const bf16 *__restrict__ dy, int64_t rows, float *__restrict__ bp) {
+  __shared__ float part[64][33];
+  const int64_t per = (rows + gridDim.x - 1) / gridDim.x;
+  const int64_t r0 = (int64_t)blockIdx.x * per, r1 = r0 + per < rows ? r0 + per : rows;
+  const int ch8 = threadIdx.x & 3, rl = threadIdx.x >> 2;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int64_t r = r0 + rl; r < r1; r += 64) {
+    const uint4 v = ldg16(dy + r * 32 + ch8 * 8);
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { // bf16 -> fp32: the bits are the upper half
+      acc[2 * j] += __uint_as_float(w[j] << 16);
+      acc[2 * j + 1] += __uint_as_float(w[j] & 0xFFFF0000u);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    part[rl][ch8 * 8 + j] = acc[j];
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float t = 0.0f;
+    for (int g = 0; g < 64; ++g)
+      t += part[g][threadIdx.x];
+    bp[blockIdx.x * 32 + threadIdx.x] = t;
+  }
+}
+
 // how to split a reduction of length R over CTAs when the output has `tiles` tiles
 void plan_splits(int64_t R, int64_t tiles, size_t per_split_floats, size_t ws_floats, int *splits,
                  int *r_per_split) {
@@ -585,17 +695,44 @@ int conv_wgrad(const Col &col, const bf16 *dy, int64_t Mtot, float scale, float 
   return ALEGPU_OK;
 }
 
+// conv1 weight gradient from the space-to-depth observations (see DYShift): one 128 x 64 output
+// tile, split over the reduction (n*441 blocks); partials + bias partials summed in fixed order.
+// The bias column sums run on stream `w` (the wgrad side stream) next to the GEMM; `join` (may be
+// null when w == s) is recorded after them and awaited before the final reduction.
+int conv1_wgrad_s2d(const bf16 *s2d, const bf16 *dy, int64_t n, float scale, float *gw, float *gb,
+                    float *ws, size_t ws_floats, cudaStream_t s, cudaStream_t w, cudaEvent_t join) {
+  constexpr size_t per = 128 * 64;
+  const size_t bias_floats = (size_t)kBiasParts * 32;
+  ALEGPU_REQUIRE(ws_floats >= per + bias_floats, ALEGPU_RUNTIME_ERROR, "conv1 wgrad: workspace too small");
+  float *bp = ws + (ws_floats - bias_floats);
+  int splits, rps;
+  plan_splits(n * 441, 2, per, ws_floats - bias_floats, &splits, &rps); // one tile: up to 148 splits
+  c1_bias_partial_kernel<<<kBiasParts, 256, 0, w>>>(dy, n * 400, bp);
+  ALEGPU_COUNT_LAUNCH();
+  if (join)
+    ALEGPU_CUDA_CHECK(cudaEventRecord(join, w));
+  if (int rc = tc::launch_gemm_tc<64, 4>(DYShift{dy}, ColsMN{s2d, 64}, EpiPartial{ws, 128, 64}, 128,
+                                         64, n * 441, splits, rps, s))
+    return rc;
+  if (join)
+    ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(s, join, 0));
+  reduce_c1_s2d_kernel<<<257, dim3(32, 8), 0, s>>>(ws, splits, scale, bp, kBiasParts, gw, gb);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}
+
 __global__ void bf16_to_f32_kernel(const bf16 *__restrict__ src, float *__restrict__ dst, int64_t n) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (int64_t)gridDim.x * blockDim.x)
     dst[i] = __bfloat162float(src[i]);
 }
 
-// u8 NCHW [n,4,84,84] -> bf16 NHWC [n,84,84,4] (u8 is exact in bf16).  One thread = 4 pixels of one
+// u8 NCHW [n,4,84,84] -> bf16 space-to-depth NHWC [n,21,21,64] (u8 is exact in bf16).  One thread = 4 pixels of one
 // row: four coalesced 4-byte loads (one per channel plane), one 32-byte store.  HBM-bound:
 // 28 224 B read + 56 448 B written per observation, once per train() (not per epoch / minibatch).
 __global__ void __launch_bounds__(256)
-    obs_to_nhwc_bf16_kernel(const uint8_t *__restrict__ obs, bf16 *__restrict__ out, int64_t total) {
+    obs_to_s2d_bf16_kernel(const uint8_t *__restrict__ obs, bf16 *__restrict__ out, int64_t total) {
   // total = n * 84 * 21 work items (n, y, x4)
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (int64_t)gridDim.x * blockDim.x) {
@@ -620,7 +757,8 @@ __global__ void __launch_bounds__(256)
       o[2 * j] = lo;
       o[2 * j + 1] = hi;
     }
-    uint4 *dst = reinterpret_cast<uint4 *>(out + ((size_t)row * 84 + x4 * 4) * 4);
+    // space-to-depth: block (Y, X) = (y/4, x4), channel = (y&3)*16 + s*4 + c, s = pixel j of the four
+    uint4 *dst = reinterpret_cast<uint4 *>(out + (((size_t)n * 21 + (y >> 2)) * 21 + x4) * 64 + (y & 3) * 16);
     dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
     dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
   }
@@ -684,14 +822,14 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
   if (int rc = alloc((void **)&T.ws_c2, sizeof(float) * T.ws_c2_n)) return rc;
   if (int rc = alloc((void **)&T.ws_c1, sizeof(float) * T.ws_c1_n)) return rc;
   ALEGPU_CUDA_CHECK(cudaStreamCreateWithFlags(&T.side, cudaStreamNonBlocking));
-  for (cudaEvent_t *e : {&T.ev_fork, &T.ev_d3, &T.ev_d2, &T.ev_join, &T.ev_fcw})
+  for (cudaEvent_t *e : {&T.ev_fork, &T.ev_d3, &T.ev_d2, &T.ev_d1, &T.ev_join, &T.ev_fcw})
     ALEGPU_CUDA_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
   const char *env = getenv("ALEGPU_TC_SERIAL");
   T.serial = env && env[0] == '1';
   env = getenv("ALEGPU_CONV1_U8");
   T.conv1_u8 = env && env[0] == '1';
-  env = getenv("ALEGPU_CONV1_WGRAD_NHWC");
-  T.conv1_wgrad_nhwc = env && env[0] == '1';
+  env = getenv("ALEGPU_CONV1_WGRAD_U8");
+  T.conv1_wgrad_u8 = env && env[0] == '1';
   return ALEGPU_OK;
 }
 
@@ -701,7 +839,7 @@ void net_tc_destroy(TcState &T) {
                   (void *)T.ws_c2, (void *)T.ws_c1})
     if (p)
       cudaFree(p);
-  for (cudaEvent_t e : {T.ev_fork, T.ev_d3, T.ev_d2, T.ev_join, T.ev_fcw})
+  for (cudaEvent_t e : {T.ev_fork, T.ev_d3, T.ev_d2, T.ev_d1, T.ev_join, T.ev_fcw})
     if (e)
       cudaEventDestroy(e);
   if (T.side)
@@ -724,7 +862,7 @@ int convert_obs(const uint8_t *obs, int64_t n, void *out, cudaStream_t s) {
   if (total == 0)
     return ALEGPU_OK;
   const int blocks = (int)std::min<int64_t>(ceil_div(total, 256), (int64_t)kNumSMs * 16);
-  obs_to_nhwc_bf16_kernel<<<blocks, 256, 0, s>>>(obs, (bf16 *)out, total);
+  obs_to_s2d_bf16_kernel<<<blocks, 256, 0, s>>>(obs, (bf16 *)out, total);
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
   return ALEGPU_OK;
@@ -886,19 +1024,26 @@ int net_tc_backward(const NetParams &P, const NetParams &G, TcState &T, const ui
   if (int rc = tc::launch_gemm_tc<64, 4>(DCol2{dact2}, W2T{W.c2w}, EpiReluMaskConv2{dact1, act1},
                                          n * 100, 32, 256, 4, 0, s))
     return rc;
-  // conv1 (input needs no gradient); the 1/255 of the input scale lands on the weight gradient
-  // conv1's weight gradient keeps the u8 register producers: measured at the v1 minibatch (1280
-  // rows) 132 us against 185 us for the cp.async view of obs16, whose im2col-expanded bf16 traffic
-  // (4x the unique bytes, twice the u8 volume) all comes from L2 while the u8 windows hit in L1;
-  // the forward, with 4 k-blocks per tile, is the other way round (87 -> 52 us).
-  if (T.conv1_u8 || !T.conv1_wgrad_nhwc) {
+  // conv1 (input needs no gradient); the 1/255 of the input scale lands on the weight gradient.
+  // On the space-to-depth copy the observation operand is read once, un-expanded, and the four
+  // taps become shifted views of dact1 (DYShift); ALEGPU_CONV1_WGRAD_U8=1 keeps the im2col form
+  // over the u8 observations (register producers) for A/B.
+  const bf16 *x16 = (const bf16 *)(obs16 ? obs16 : T.obs16_mb);
+  if (T.conv1_u8 || T.conv1_wgrad_u8 || !x16) {
     if (int rc = conv_wgrad<Col1, 256, 32>(Col1{obs}, dact1, n * 400, 1.0f / 255.0f, G.c1w, G.c1b,
                                            T.ws_c1, T.ws_c1_n, s))
       return rc;
   } else { // the forward of these rows left their bf16 copy in obs16_mb unless the caller has one
-    const bf16 *x = (const bf16 *)(obs16 ? obs16 : T.obs16_mb);
-    if (int rc = conv_wgrad<Col1N, 256, 32>(Col1N{x}, dact1, n * 400, 1.0f / 255.0f, G.c1w, G.c1b,
-                                            T.ws_c1, T.ws_c1_n, s, /*conv1_perm=*/true))
+    // the bias column sums run next to the GEMM on the side stream once dact1 exists — when they are
+    // long enough to pay for the fork/join edges (measured: 7.72 -> 7.51 ms per v1 iteration at 1280
+    // rows, but 2.51 -> 2.59 ms at v0's 256 rows, where they stay in front of the GEMM)
+    const bool fork = !T.serial && n > 512;
+    if (fork) {
+      ALEGPU_CUDA_CHECK(cudaEventRecord(T.ev_d1, s));
+      ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(w, T.ev_d1, 0));
+    }
+    if (int rc = conv1_wgrad_s2d(x16, dact1, n, 1.0f / 255.0f, G.c1w, G.c1b, T.ws_c1, T.ws_c1_n, s,
+                                 fork ? w : s, fork ? T.ev_join : nullptr))
       return rc;
   }
   if (!T.serial)

@@ -7,7 +7,7 @@ namespace alegpu {
 struct TcState {
   int64_t hidden = 0, actions = 0, cap = 0, Ppad = 0;
   void *w_shadow = nullptr;  // bf16 copy of the flat parameter buffer (written by Adam)
-  void *c1w_perm = nullptr;  // bf16 conv1 weights [32][256] in the k' = (ky,kx,c) order of obs16
+  void *c1w_perm = nullptr;  // bf16 conv1 weights [32][256] in the k' = (tap, y&3, x&3, c) order of the space-to-depth obs16
   // bf16 NHWC copy of the observations conv1 reads: one minibatch (cap rows) and, lazily, a whole
   // train() batch so the conversion runs once per train() instead of once per minibatch step
   void *obs16_mb = nullptr, *obs16_all = nullptr;
@@ -21,13 +21,13 @@ struct TcState {
   // with events, so it also becomes a parallel branch of a captured CUDA graph); every wgrad
   // has its own split-partials workspace because they may be in flight together
   cudaStream_t side = nullptr;
-  cudaEvent_t ev_fork = nullptr, ev_d3 = nullptr, ev_d2 = nullptr, ev_join = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_d3 = nullptr, ev_d2 = nullptr, ev_d1 = nullptr, ev_join = nullptr;
   cudaEvent_t ev_fcw = nullptr; // recorded on the side branch once the FC + heads gradients exist
   float *ws_heads = nullptr, *ws_fc = nullptr, *ws_c3 = nullptr, *ws_c2 = nullptr, *ws_c1 = nullptr;
   size_t ws_heads_n = 0, ws_fc_n = 0, ws_c3_n = 0, ws_c2_n = 0, ws_c1_n = 0;
   bool serial = false;       // ALEGPU_TC_SERIAL=1: keep everything on one stream (profiling)
   bool conv1_u8 = false;     // ALEGPU_CONV1_U8=1: conv1 forward reads the u8 observations (A/B)
-  bool conv1_wgrad_nhwc = false; // ALEGPU_CONV1_WGRAD_NHWC=1: conv1 wgrad reads obs16 (A/B)
+  bool conv1_wgrad_u8 = false; // ALEGPU_CONV1_WGRAD_U8=1: conv1 wgrad in im2col form over the u8 observations (A/B)
 };
 
 int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_t Ppad,

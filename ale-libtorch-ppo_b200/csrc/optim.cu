@@ -118,11 +118,12 @@ __global__ void __launch_bounds__(kThreads)
       pk.y = *reinterpret_cast<uint32_t *>(&hi);
       reinterpret_cast<uint2 *>(shadow)[i] = pk;
       // conv1's weights (the first 32*256 parameters, OIHW: k = c*64 + ky*8 + kx) are also kept in
-      // the (ky,kx,c) order in which the tensor-core conv1 walks the NHWC observations
+      // the (tap, y&3, x&3, c) order in which the tensor-core conv1 walks the space-to-depth observations
       if (c1w_perm && i < 32 * 256 / 4) {
         const int idx = (int)i * 4, co = idx >> 8, k = idx & 255;
         const int c = k >> 6, ky = (k >> 3) & 7, kx = k & 7;
-        __nv_bfloat16 *o = c1w_perm + co * 256 + ky * 32 + kx * 4 + c;
+        __nv_bfloat16 *o = c1w_perm + co * 256 + ((ky >> 2) * 2 + (kx >> 2)) * 64 + (ky & 3) * 16 +
+                           (kx & 3) * 4 + c; // net_tc.cu: conv1_k_of_kprime
         o[0] = __float2bfloat16_rn(pp.x);
         o[4] = __float2bfloat16_rn(pp.y);
         o[8] = __float2bfloat16_rn(pp.z);
