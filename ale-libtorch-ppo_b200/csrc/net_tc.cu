@@ -26,6 +26,8 @@
 #include <cstdlib>
 #include <vector>
 
+#include <cuda.h>
+
 #include "net_tc.h"
 #include "optim.h"
 #include "tc_gemm.cuh"
@@ -174,6 +176,36 @@ struct Col3 {
   }
   __device__ __forceinline__ uint4 at(int m, int k) const { return ldg16(pos_ptr(m) + k_off(k)); }
 };
+
+// K-major A operand fetched by TMA im2col loads: NHWC bf16 tensor with 64 channels (one tap = one
+// 128-byte swizzle row), rows = output pixels (n, oy, ox) of OH x OW, reduction k = tap*64 + c with
+// tap = ky*KW + kx.  LOW = lower corner of the pixel box (= -padding); kFlip = the transposed
+// (data-gradient) walk, where tap (ky,kx) reads pixel (oy-ky, ox-kx).  One instruction per
+// (128-row tile, k-block) replaces 1024 16-byte cp.async copies and their address arithmetic;
+// pixels outside the tensor (padding, rows past the last image) arrive as zeros.
+template <int OH, int OW, int KW, int LOW, bool kFlip> struct ColTma {
+  ALEGPU_RAW_BF16
+  static constexpr bool kMN = false;
+  static constexpr bool kAsync = true;
+  static constexpr bool kTma = true;
+  const void *map; // CUtensorMap in global memory
+  int n_base;      // image index of row 0 inside the mapped buffer
+  struct TileCtx {
+    int w, h, n;
+  };
+  __device__ __forceinline__ TileCtx tile(int m0) const {
+    const int n = m0 / (OH * OW), pix = m0 - n * (OH * OW), oy = pix / OW, ox = pix - oy * OW;
+    return TileCtx{ox + LOW, oy + LOW, n + n_base};
+  }
+  __device__ __forceinline__ void tma(const TileCtx &t, uint32_t dst, int r0, int, uint64_t *bar) const {
+    const int tap = r0 >> 6, ky = tap / KW, kx = tap - ky * KW;
+    const int ow = kFlip ? -LOW - kx : kx, oh = kFlip ? -LOW - ky : ky;
+    tc::tma_im2col_4d(dst, map, 0, t.w, t.h, t.n, (uint16_t)ow, (uint16_t)oh, bar);
+  }
+};
+using Col3Tma = ColTma<7, 7, 3, 0, false>;   // conv3 forward over act2 [n,9,9,64]
+using DCol3Tma = ColTma<9, 9, 3, -2, true>;  // conv3 data gradient over dact3 [n,7,7,64]
+using Col1Tma = ColTma<20, 20, 2, 0, false>; // conv1 forward over the space-to-depth obs16 [n,21,21,64]
 
 // K-major A operand of a forward conv: (row m, reduction k..k+7)
 template <class Col> struct ColK {
@@ -785,6 +817,43 @@ Shadow shadow_view(const TcState &T, const NetParams &P) {
   return s;
 }
 
+// ---- TMA im2col tensor maps ---------------------------------------------------------------------------
+enum TmaSlot { kMapAct2 = 0, kMapDact3, kMapDact2, kMapObsMb, kMapObsAll, kMapCount };
+using EncodeIm2colFn = CUresult (*)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
+                                    const cuuint64_t *, const cuuint64_t *, const int *, const int *,
+                                    cuuint32_t, cuuint32_t, const cuuint32_t *, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeIm2colFn encode_im2col_fn() {
+  static EncodeIm2colFn fn = [] {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return (EncodeIm2colFn)p;
+  }();
+  return fn;
+}
+// map slot <- NHWC bf16 tensor [N,H,W,64] at `base`, pixel box [lower, dim + upper) in both axes,
+// 128 pixels x 64 channels per load, 128-byte swizzle, zeros outside
+int set_im2col_map(TcState &T, int slot, void *base, int H, int W, int64_t N, int lower, int upper) {
+  EncodeIm2colFn fn = encode_im2col_fn();
+  ALEGPU_REQUIRE(fn != nullptr, ALEGPU_RUNTIME_ERROR, "cuTensorMapEncodeIm2col is not available");
+  alignas(64) CUtensorMap m;
+  const cuuint64_t dims[4] = {64, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  const cuuint64_t strides[3] = {128, (cuuint64_t)W * 128, (cuuint64_t)H * W * 128};
+  const int lo[2] = {lower, lower}, hi[2] = {upper, upper};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  const CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, base, dims, strides, lo, hi, 64, 128,
+                        estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  ALEGPU_REQUIRE(r == CUDA_SUCCESS, ALEGPU_RUNTIME_ERROR,
+                 "cuTensorMapEncodeIm2col failed: " + std::to_string((int)r));
+  ALEGPU_CUDA_CHECK(cudaMemcpy((CUtensorMap *)T.tmaps + slot, &m, sizeof(m), cudaMemcpyHostToDevice));
+  return ALEGPU_OK;
+}
+const void *tmap(const TcState &T, int slot) { return (const CUtensorMap *)T.tmaps + slot; }
+
 } // namespace
 
 // ---- public (net_tc.h) ----------------------------------------------------------------------------
@@ -830,12 +899,20 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
   T.conv1_u8 = env && env[0] == '1';
   env = getenv("ALEGPU_CONV1_WGRAD_U8");
   T.conv1_wgrad_u8 = env && env[0] == '1';
+  env = getenv("ALEGPU_NO_TMA");
+  T.use_tma = !(env && env[0] == '1');
+  if (T.use_tma) {
+    ALEGPU_CUDA_CHECK(cudaMalloc(&T.tmaps, sizeof(CUtensorMap) * kMapCount));
+    if (int rc = set_im2col_map(T, kMapAct2, T.act2, 9, 9, cap, 0, -2)) return rc;   // 3x3, no padding
+    if (int rc = set_im2col_map(T, kMapDact3, T.dact3, 7, 7, cap, -2, 0)) return rc; // 3x3, padding 2
+    if (int rc = set_im2col_map(T, kMapObsMb, T.obs16_mb, 21, 21, cap, 0, -1)) return rc; // 2x2 taps
+  }
   return ALEGPU_OK;
 }
 
 void net_tc_destroy(TcState &T) {
   for (void *p : {T.c1w_perm, T.obs16_mb, T.obs16_all, T.w_shadow, T.act1, T.act2, T.act3, T.dact1, T.dact2, T.dact3, T.fc16, T.dfc16,
-                  T.wt, (void *)T.stage, (void *)T.ws_heads, (void *)T.ws_fc, (void *)T.ws_c3,
+                  T.wt, T.tmaps, (void *)T.stage, (void *)T.ws_heads, (void *)T.ws_fc, (void *)T.ws_c3,
                   (void *)T.ws_c2, (void *)T.ws_c1})
     if (p)
       cudaFree(p);
@@ -920,9 +997,14 @@ int net_tc_forward(const NetParams &P, TcState &T, const uint8_t *obs, int64_t n
                                          EpiBiasReluBf16{act2, P.c2b, 64, 1.0f}, n * 81, 64, 512,
                                          1, 0, s))
     return rc;
-  if (int rc = tc::launch_gemm_tc<64, 4>(ColK<Col3>{Col3{act2}}, RowsK{W.c3w, 576},
-                                         EpiBiasReluBf16{act3, P.c3b, 64, 1.0f}, n * 49, 64, 576,
-                                         1, 0, s))
+  if (T.use_tma) {
+    if (int rc = tc::launch_gemm_tc<64, 4>(Col3Tma{tmap(T, kMapAct2), 0}, RowsK{W.c3w, 576},
+                                           EpiBiasReluBf16{act3, P.c3b, 64, 1.0f}, n * 49, 64, 576,
+                                           1, 0, s))
+      return rc;
+  } else if (int rc = tc::launch_gemm_tc<64, 4>(ColK<Col3>{Col3{act2}}, RowsK{W.c3w, 576},
+                                                EpiBiasReluBf16{act3, P.c3b, 64, 1.0f}, n * 49, 64,
+                                                576, 1, 0, s))
     return rc;
   // FC: with few output tiles (small minibatch) the 3136-long reduction is split over CTAs and
   // summed in fixed order; otherwise one pass with the bias fused in the epilogue

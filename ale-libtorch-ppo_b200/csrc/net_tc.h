@@ -25,6 +25,9 @@ struct TcState {
   cudaEvent_t ev_fcw = nullptr; // recorded on the side branch once the FC + heads gradients exist
   float *ws_heads = nullptr, *ws_fc = nullptr, *ws_c3 = nullptr, *ws_c2 = nullptr, *ws_c1 = nullptr;
   size_t ws_heads_n = 0, ws_fc_n = 0, ws_c3_n = 0, ws_c2_n = 0, ws_c1_n = 0;
+  // TMA im2col tensor maps (device array of CUtensorMap, see net_tc.cu: TmaSlot); nullptr = not in use
+  void *tmaps = nullptr;
+  bool use_tma = true;       // ALEGPU_NO_TMA=1: gather conv operands with cp.async instead (A/B)
   bool serial = false;       // ALEGPU_TC_SERIAL=1: keep everything on one stream (profiling)
   bool conv1_u8 = false;     // ALEGPU_CONV1_U8=1: conv1 forward reads the u8 observations (A/B)
   bool conv1_wgrad_u8 = false; // ALEGPU_CONV1_WGRAD_U8=1: conv1 wgrad in im2col form over the u8 observations (A/B)

@@ -45,6 +45,20 @@ __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+// TMA im2col load of one [pixels x channels] box (4-d NHWC tensor map): base pixel (w, h, n), filter
+// offsets (off_w, off_h); lands as 128-byte swizzled rows, completion counted on `bar` in bytes
+__device__ __forceinline__ void tma_im2col_4d(uint32_t dst, const void *map, int c, int w, int h,
+                                              int n, uint16_t off_w, uint16_t off_h, uint64_t *bar) {
+  asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
+               " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(dst),
+               "l"(map), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
+               : "memory");
+}
 constexpr uint32_t kSuspendHintNs = 20000u;
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
   const uint32_t a = smem_u32(bar);
@@ -254,10 +268,34 @@ template <class Op> struct PrefetchDepth<Op, decltype((void)Op::kPrefetch)> {
 // K-major tiles: a thread always serves reduction chunk kc = ptid & 7 of rows il = ptid/8 + 32*it,
 // so its kPer row contexts are fixed and ONE column context per k-block serves all of them.
 // MN-major tiles: a thread always serves row chunk c = ptid % (ROWS/8); only r changes.
-template <int ROWS, class Op, bool kAsyncOp = IsAsync<Op>::value> struct AsyncCtx {
+// Op::kTma: a K-major operand fetched by ONE elected thread with a TMA im2col load per k-block
+// (Op::tile(row0) -> TileCtx, Op::tma(ctx, dst, r0, z, bar)); the bytes complete on the stage's
+// full barrier next to the producer warps' arrivals.
+template <class Op, class = void> struct IsTma {
+  static constexpr bool value = false;
+};
+template <class Op> struct IsTma<Op, decltype((void)Op::kTma)> {
+  static constexpr bool value = Op::kTma;
+};
+template <int ROWS, class Op, bool kAsyncOp = IsAsync<Op>::value, bool kTmaOp = IsTma<Op>::value>
+struct AsyncCtx {
   __device__ __forceinline__ void init(const Op &, int, int, int) {}
 };
-template <int ROWS, class Op> struct AsyncCtx<ROWS, Op, true> {
+template <int ROWS, class Op> struct AsyncCtx<ROWS, Op, true, true> {
+  typename Op::TileCtx tc;
+  __device__ __forceinline__ void init(const Op &op, int row0, int, int ptid) {
+    if (ptid == 0)
+      tc = op.tile(row0);
+  }
+  __device__ __forceinline__ void issue(const Op &op, uint32_t tile, int r0, int, int z, int ptid,
+                                        uint64_t *bar) const {
+    if (ptid == 0) {
+      mbar_expect_tx(bar, (uint32_t)(ROWS * 128));
+      op.tma(tc, tile, r0, z, bar);
+    }
+  }
+};
+template <int ROWS, class Op> struct AsyncCtx<ROWS, Op, true, false> {
   static constexpr int kChunks = ROWS * 8;
   static constexpr int kProducers = kProducerWarps * 32;
   static_assert(kChunks % kProducers == 0, "tile rows must be a multiple of 32");
@@ -289,7 +327,7 @@ template <int ROWS, class Op> struct AsyncCtx<ROWS, Op, true> {
     }
   }
   __device__ __forceinline__ void issue(const Op &op, uint32_t tile, int r0, int r_end, int z,
-                                        int ptid) const {
+                                        int ptid, uint64_t *) const {
     if constexpr (!Op::kMN) {
       const int r = r0 + (ptid & 7) * 8;
       const bool rv = r < r_end;
@@ -322,15 +360,15 @@ template <int ROWS, class Op, bool kAsyncOp = IsAsync<Op>::value> struct TileSta
     t.load(op, row0, rows_total, r0, r_end, z, ptid);
   }
   __device__ __forceinline__ void put(const Op &, const AsyncCtx<ROWS, Op> &, uint32_t tile, int,
-                                      int, int, int ptid) const {
+                                      int, int, int ptid, uint64_t *) const {
     t.store(tile, ptid);
   }
 };
 template <int ROWS, class Op> struct TileStage<ROWS, Op, true> {
   __device__ __forceinline__ void load(const Op &, int, int, int, int, int, int) {}
   __device__ __forceinline__ void put(const Op &op, const AsyncCtx<ROWS, Op> &ctx, uint32_t tile,
-                                      int r0, int r_end, int z, int ptid) const {
-    ctx.issue(op, tile, r0, r_end, z, ptid);
+                                      int r0, int r_end, int z, int ptid, uint64_t *bar) const {
+    ctx.issue(op, tile, r0, r_end, z, ptid, bar);
   }
 };
 
@@ -442,8 +480,8 @@ __global__ void __launch_bounds__(kThreads, BN <= 128 ? 2 : 1)
             const uint32_t ph = (uint32_t)(g / STAGES) & 1u;
             mbar_wait(&empty_bar[s], ph ^ 1u);
             const uint32_t st = tiles_s + (uint32_t)(s * kStage);
-            ra[u].put(aop, ca, st, r_begin + kb * BK, r_end, z, ptid);
-            rb[u].put(bop, cb, st + kATile, r_begin + kb * BK, r_end, z, ptid);
+            ra[u].put(aop, ca, st, r_begin + kb * BK, r_end, z, ptid, &full_bar[s]);
+            rb[u].put(bop, cb, st + kATile, r_begin + kb * BK, r_end, z, ptid, &full_bar[s]);
             cp_async_commit();
             if (kb >= kLag) {
               cp_async_wait<kLag>();
