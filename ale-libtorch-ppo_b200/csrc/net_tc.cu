@@ -206,6 +206,9 @@ template <int OH, int OW, int KW, int LOW, bool kFlip> struct ColTma {
 using Col3Tma = ColTma<7, 7, 3, 0, false>;   // conv3 forward over act2 [n,9,9,64]
 using DCol3Tma = ColTma<9, 9, 3, -2, true>;  // conv3 data gradient over dact3 [n,7,7,64]
 using Col1Tma = ColTma<20, 20, 2, 0, false>; // conv1 forward over the space-to-depth obs16 [n,21,21,64]
+// conv2 data gradient: every parity class of the stride-2 transposed convolution reads the same
+// 2x2-tap, padding-1 walk over dact2 [n,9,9,64] (rows = (n,qy,qx) of 10x10); only the weights differ
+using DCol2Tma = ColTma<10, 10, 2, -1, true>;
 
 // K-major A operand of a forward conv: (row m, reduction k..k+7)
 template <class Col> struct ColK {
@@ -458,6 +461,30 @@ struct W2T {
   __device__ __forceinline__ const void *anchor() const { return w; }
   __device__ __forceinline__ const void *at(RowCtx rc, ColCtx cc) const { return cc + rc; }
 };
+// conv2 dgrad B for all four parity classes at once: row j = cls*32 + ci (cls = py*2+px),
+// r = (t,co): c2w[co][(ky*4+kx)*32 + ci], ky = py+2ty, kx = px+2tx.  One pass over the (shared) A
+// operand then produces the whole 2x2 output block of every (qy,qx).
+struct W2TAll {
+  ALEGPU_RAW_BF16
+  static constexpr bool kMN = true;
+  static constexpr bool kAsync = true;
+  const bf16 *w;
+  struct RowCtx {
+    int off; // (py*4 + px)*32 + ci0
+  };
+  using ColCtx = const bf16 *; // w + co*512 + (2ty*4 + 2tx)*32
+  __device__ __forceinline__ RowCtx row(int j0) const {
+    const int cls = j0 >> 5;
+    return RowCtx{((cls >> 1) * 4 + (cls & 1)) * 32 + (j0 & 31)};
+  }
+  __device__ __forceinline__ ColCtx col(int r, int) const {
+    const int t = r >> 6, ty = t >> 1, tx = t & 1, co = r & 63;
+    return w + (size_t)co * 512 + (ty * 8 + tx * 2) * 32;
+  }
+  __device__ __forceinline__ const void *anchor() const { return w; }
+  __device__ __forceinline__ const void *at(const RowCtx &rc, ColCtx cc) const { return cc + rc.off; }
+  __device__ __forceinline__ uint4 load(int j0, int r, int z) const { return ldg16(at(row(j0), col(r, z))); }
+};
 
 // ---- epilogues (16 consecutive columns of one row per call) --------------------------------------
 __device__ __forceinline__ void store_bf16x16(bf16 *dst, const float (&v)[16]) {
@@ -522,6 +549,21 @@ struct EpiReluMaskConv2 { // scatter parity class z back into NHWC [n,20,20,32]
   __device__ void operator()(int i, int j0, float (&v)[16], int z) const {
     const int n = i / 100, pix = i - n * 100, qy = pix / 10, qx = pix - qy * 10;
     const size_t o = ((size_t)(n * 20 + 2 * qy + (z >> 1)) * 20 + 2 * qx + (z & 1)) * 32 + j0;
+    float yy[16];
+    load_bf16x16(y + o, yy);
+#pragma unroll
+    for (int t = 0; t < 16; ++t)
+      v[t] = yy[t] > 0.0f ? v[t] : 0.0f;
+    store_bf16x16(out + o, v);
+  }
+};
+struct EpiReluMaskConv2All { // columns j = cls*32 + ci: all four parity classes of one (n,qy,qx) row
+  bf16 *out;
+  const bf16 *y;
+  __device__ void operator()(int i, int j0, float (&v)[16], int) const {
+    const int n = i / 100, pix = i - n * 100, qy = pix / 10, qx = pix - qy * 10, cls = j0 >> 5;
+    const size_t o =
+        ((size_t)(n * 20 + 2 * qy + (cls >> 1)) * 20 + 2 * qx + (cls & 1)) * 32 + (j0 & 31);
     float yy[16];
     load_bf16x16(y + o, yy);
 #pragma unroll
@@ -905,6 +947,7 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
     ALEGPU_CUDA_CHECK(cudaMalloc(&T.tmaps, sizeof(CUtensorMap) * kMapCount));
     if (int rc = set_im2col_map(T, kMapAct2, T.act2, 9, 9, cap, 0, -2)) return rc;   // 3x3, no padding
     if (int rc = set_im2col_map(T, kMapDact3, T.dact3, 7, 7, cap, -2, 0)) return rc; // 3x3, padding 2
+    if (int rc = set_im2col_map(T, kMapDact2, T.dact2, 9, 9, cap, -1, 0)) return rc; // 2x2, padding 1
     if (int rc = set_im2col_map(T, kMapObsMb, T.obs16_mb, 21, 21, cap, 0, -1)) return rc; // 2x2 taps
   }
   return ALEGPU_OK;
@@ -957,6 +1000,8 @@ int net_tc_reserve_obs(TcState &T, int64_t n) {
   T.obs16_all_rows = 0;
   ALEGPU_CUDA_CHECK(cudaMalloc(&T.obs16_all, sizeof(bf16) * (size_t)n * 28224));
   T.obs16_all_rows = n;
+  if (T.use_tma)
+    return set_im2col_map(T, kMapObsAll, T.obs16_all, 21, 21, n, 0, -1);
   return ALEGPU_OK;
 }
 
@@ -987,7 +1032,15 @@ int net_tc_forward(const NetParams &P, TcState &T, const uint8_t *obs, int64_t n
         return rc;
       obs16 = T.obs16_mb;
     }
-    if (int rc = tc::launch_gemm_tc<32, 4>(ColK<Col1N>{Col1N{(const bf16 *)obs16}},
+    const bf16 *x16 = (const bf16 *)obs16, *all = (const bf16 *)T.obs16_all;
+    const bool in_all = all && x16 >= all && x16 < all + (size_t)T.obs16_all_rows * 28224;
+    if (T.use_tma && (x16 == (const bf16 *)T.obs16_mb || in_all)) {
+      const Col1Tma a{tmap(T, in_all ? kMapObsAll : kMapObsMb), in_all ? (int)((x16 - all) / 28224) : 0};
+      if (int rc = tc::launch_gemm_tc<32, 4>(a, RowsK{(const bf16 *)T.c1w_perm, 256},
+                                             EpiBiasReluBf16{act1, P.c1b, 32, 1.0f / 255.0f},
+                                             n * 400, 32, 256, 1, 0, s))
+        return rc;
+    } else if (int rc = tc::launch_gemm_tc<32, 4>(ColK<Col1N>{Col1N{(const bf16 *)obs16}},
                                            RowsK{(const bf16 *)T.c1w_perm, 256},
                                            EpiBiasReluBf16{act1, P.c1b, 32, 1.0f / 255.0f},
                                            n * 400, 32, 256, 1, 0, s))
@@ -1089,8 +1142,13 @@ int net_tc_backward(const NetParams &P, const NetParams &G, TcState &T, const ui
                                          T.ws_c3_n, w))
     return rc;
   // ---- main: conv3 dgrad
-  if (int rc = tc::launch_gemm_tc<64, 4>(DCol3{dact3}, W3T{W.c3w}, EpiReluMaskBf16{dact2, act2, 64},
-                                         n * 81, 64, 576, 1, 0, s))
+  if (T.use_tma) {
+    if (int rc = tc::launch_gemm_tc<64, 4>(DCol3Tma{tmap(T, kMapDact3), 0}, W3T{W.c3w},
+                                           EpiReluMaskBf16{dact2, act2, 64}, n * 81, 64, 576, 1, 0, s))
+      return rc;
+  } else if (int rc = tc::launch_gemm_tc<64, 4>(DCol3{dact3}, W3T{W.c3w},
+                                                EpiReluMaskBf16{dact2, act2, 64}, n * 81, 64, 576, 1,
+                                                0, s))
     return rc;
   if (!T.serial) {
     ALEGPU_CUDA_CHECK(cudaEventRecord(T.ev_d2, s));
@@ -1102,9 +1160,16 @@ int net_tc_backward(const NetParams &P, const NetParams &G, TcState &T, const ui
     return rc;
   if (!T.serial)
     ALEGPU_CUDA_CHECK(cudaEventRecord(T.ev_join, w));
-  // ---- main: conv2 dgrad (4 parity classes of the stride-2 transposed convolution in one launch)
-  if (int rc = tc::launch_gemm_tc<64, 4>(DCol2{dact2}, W2T{W.c2w}, EpiReluMaskConv2{dact1, act1},
-                                         n * 100, 32, 256, 4, 0, s))
+  // ---- main: conv2 dgrad (the 4 parity classes of the stride-2 transposed convolution as 128 output
+  // columns of ONE GEMM over the TMA-fetched 2x2-tap walk of dact2; cp.async fallback: 4 z-slices)
+  if (T.use_tma) {
+    if (int rc = tc::launch_gemm_tc<128, 3>(DCol2Tma{tmap(T, kMapDact2), 0}, W2TAll{W.c2w},
+                                            EpiReluMaskConv2All{dact1, act1}, n * 100, 128, 256, 1, 0,
+                                            s))
+      return rc;
+  } else if (int rc = tc::launch_gemm_tc<64, 4>(DCol2{dact2}, W2T{W.c2w},
+                                                EpiReluMaskConv2{dact1, act1}, n * 100, 32, 256, 4,
+                                                0, s))
     return rc;
   // conv1 (input needs no gradient); the 1/255 of the input scale lands on the weight gradient.
   // On the space-to-depth copy the observation operand is read once, un-expanded, and the four
