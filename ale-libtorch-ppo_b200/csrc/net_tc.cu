@@ -179,11 +179,11 @@ struct Col3 {
 
 // K-major A operand fetched by TMA im2col loads: NHWC bf16 tensor with 64 channels (one tap = one
 // 128-byte swizzle row), rows = output pixels (n, oy, ox) of OH x OW, reduction k = tap*64 + c with
-// tap = ky*KW + kx.  LOW = lower corner of the pixel box (= -padding); kFlip = the transposed
+// tap = ky*KW + kx.  LOW = lower corner of the pixel box (= -padding); SH = stride in h; kFlip = the transposed
 // (data-gradient) walk, where tap (ky,kx) reads pixel (oy-ky, ox-kx).  One instruction per
 // (128-row tile, k-block) replaces 1024 16-byte cp.async copies and their address arithmetic;
 // pixels outside the tensor (padding, rows past the last image) arrive as zeros.
-template <int OH, int OW, int KW, int LOW, bool kFlip> struct ColTma {
+template <int OH, int OW, int KW, int LOW, bool kFlip, int SH = 1> struct ColTma {
   ALEGPU_RAW_BF16
   static constexpr bool kMN = false;
   static constexpr bool kAsync = true;
@@ -195,7 +195,7 @@ template <int OH, int OW, int KW, int LOW, bool kFlip> struct ColTma {
   };
   __device__ __forceinline__ TileCtx tile(int m0) const {
     const int n = m0 / (OH * OW), pix = m0 - n * (OH * OW), oy = pix / OW, ox = pix - oy * OW;
-    return TileCtx{ox + LOW, oy + LOW, n + n_base};
+    return TileCtx{ox + LOW, oy * SH + LOW, n + n_base}; // SH = traversal stride in h
   }
   __device__ __forceinline__ void tma(const TileCtx &t, uint32_t dst, int r0, int, uint64_t *bar) const {
     const int tap = r0 >> 6, ky = tap / KW, kx = tap - ky * KW;
@@ -205,6 +205,10 @@ template <int OH, int OW, int KW, int LOW, bool kFlip> struct ColTma {
 };
 using Col3Tma = ColTma<7, 7, 3, 0, false>;   // conv3 forward over act2 [n,9,9,64]
 using DCol3Tma = ColTma<9, 9, 3, -2, true>;  // conv3 data gradient over dact3 [n,7,7,64]
+// conv2 forward over act1 [n,20,20,32] viewed as pixel PAIRS [n,20,10,64]: with stride 2 the taps
+// kx = (0,1) and (2,3) are the pairs ox and ox+1, so it is a 4 (ky, stride 2) x 2 (pairs, stride 1)
+// convolution over 64 channels and k = (ky*2 + pair)*64 + (kx&1)*32 + ci is the weights' own order
+using Col2Tma = ColTma<9, 9, 2, 0, false, 2>;
 using Col1Tma = ColTma<20, 20, 2, 0, false>; // conv1 forward over the space-to-depth obs16 [n,21,21,64]
 // conv2 data gradient: every parity class of the stride-2 transposed convolution reads the same
 // 2x2-tap, padding-1 walk over dact2 [n,9,9,64] (rows = (n,qy,qx) of 10x10); only the weights differ
@@ -860,7 +864,7 @@ Shadow shadow_view(const TcState &T, const NetParams &P) {
 }
 
 // ---- TMA im2col tensor maps ---------------------------------------------------------------------------
-enum TmaSlot { kMapAct2 = 0, kMapDact3, kMapDact2, kMapObsMb, kMapObsAll, kMapCount };
+enum TmaSlot { kMapAct1 = 0, kMapAct2, kMapDact3, kMapDact2, kMapObsMb, kMapObsAll, kMapCount };
 using EncodeIm2colFn = CUresult (*)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
                                     const cuuint64_t *, const cuuint64_t *, const int *, const int *,
                                     cuuint32_t, cuuint32_t, const cuuint32_t *, CUtensorMapInterleave,
@@ -878,14 +882,17 @@ EncodeIm2colFn encode_im2col_fn() {
 }
 // map slot <- NHWC bf16 tensor [N,H,W,64] at `base`, pixel box [lower, dim + upper) in both axes,
 // 128 pixels x 64 channels per load, 128-byte swizzle, zeros outside
-int set_im2col_map(TcState &T, int slot, void *base, int H, int W, int64_t N, int lower, int upper) {
+int set_im2col_map(TcState &T, int slot, void *base, int H, int W, int64_t N, int lower, int upper,
+                   int upper_h = 1 << 30, int stride_h = 1) {
+  if (upper_h == (1 << 30))
+    upper_h = upper;
   EncodeIm2colFn fn = encode_im2col_fn();
   ALEGPU_REQUIRE(fn != nullptr, ALEGPU_RUNTIME_ERROR, "cuTensorMapEncodeIm2col is not available");
   alignas(64) CUtensorMap m;
   const cuuint64_t dims[4] = {64, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
   const cuuint64_t strides[3] = {128, (cuuint64_t)W * 128, (cuuint64_t)H * W * 128};
-  const int lo[2] = {lower, lower}, hi[2] = {upper, upper};
-  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  const int lo[2] = {lower, lower}, hi[2] = {upper, upper_h};
+  const cuuint32_t estr[4] = {1, 1, (cuuint32_t)stride_h, 1};
   const CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, base, dims, strides, lo, hi, 64, 128,
                         estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                         CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -945,6 +952,7 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
   T.use_tma = !(env && env[0] == '1');
   if (T.use_tma) {
     ALEGPU_CUDA_CHECK(cudaMalloc(&T.tmaps, sizeof(CUtensorMap) * kMapCount));
+    if (int rc = set_im2col_map(T, kMapAct1, T.act1, 20, 10, cap, 0, -1, -3, 2)) return rc; // pairs
     if (int rc = set_im2col_map(T, kMapAct2, T.act2, 9, 9, cap, 0, -2)) return rc;   // 3x3, no padding
     if (int rc = set_im2col_map(T, kMapDact3, T.dact3, 7, 7, cap, -2, 0)) return rc; // 3x3, padding 2
     if (int rc = set_im2col_map(T, kMapDact2, T.dact2, 9, 9, cap, -1, 0)) return rc; // 2x2, padding 1
@@ -1046,9 +1054,14 @@ int net_tc_forward(const NetParams &P, TcState &T, const uint8_t *obs, int64_t n
                                            n * 400, 32, 256, 1, 0, s))
       return rc;
   }
-  if (int rc = tc::launch_gemm_tc<64, 4>(ColK<Col2>{Col2{act1}}, RowsK{W.c2w, 512},
-                                         EpiBiasReluBf16{act2, P.c2b, 64, 1.0f}, n * 81, 64, 512,
-                                         1, 0, s))
+  if (T.use_tma) {
+    if (int rc = tc::launch_gemm_tc<64, 4>(Col2Tma{tmap(T, kMapAct1), 0}, RowsK{W.c2w, 512},
+                                           EpiBiasReluBf16{act2, P.c2b, 64, 1.0f}, n * 81, 64, 512,
+                                           1, 0, s))
+      return rc;
+  } else if (int rc = tc::launch_gemm_tc<64, 4>(ColK<Col2>{Col2{act1}}, RowsK{W.c2w, 512},
+                                                EpiBiasReluBf16{act2, P.c2b, 64, 1.0f}, n * 81, 64,
+                                                512, 1, 0, s))
     return rc;
   if (T.use_tma) {
     if (int rc = tc::launch_gemm_tc<64, 4>(Col3Tma{tmap(T, kMapAct2), 0}, RowsK{W.c3w, 576},
