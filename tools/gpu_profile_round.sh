@@ -2,7 +2,7 @@
 # Round evidence for profiles/: launch list of the default bench command + ncu --set full of the
 # dominant memory-bound kernel (preprocess) and of the tensor-core GEMMs of one minibatch step.
 # $1 = tag prefix (default r01d)
-TAG=${1:-r01d}
+TAG=${1:-r01e}
 mkdir -p gpurun_out
 CMD="python bench.py --steps 2 --warmup 1 --no-cpu-baseline"
 $CMD > gpurun_out/plain_default.log 2>&1 &&
@@ -24,9 +24,12 @@ CMD0="python bench.py --workload v0 --steps 1 --warmup 1 --no-cpu-baseline --no-
 ncu --set full --clock-control none --import-source on -k regex:gemm_tc -s 176 -c 11 -f \
     -o gpurun_out/${TAG}_gemm_v0 $CMD0 > gpurun_out/ncu_gemm_v0.log 2>&1
 echo "gemm v0 rc=$?"
-ncu --set full --clock-control none -k regex:"adam_clip|gae_scan|heads_kernel|obs_to_nhwc|grad_sumsq" -s 0 -c 8 -f \
+ncu --set full --clock-control none -k regex:"adam_clip|gae_scan|heads_kernel|obs_to_s2d|grad_sumsq" -s 0 -c 8 -f \
     -o gpurun_out/${TAG}_membound_v1 $CMD1 > gpurun_out/ncu_mem_v1.log 2>&1
 echo "membound v1 rc=$?"
+ncu --set full --clock-control none --import-source on -k regex:"resize_gray_kernel|preprocess_gray_step" -s 20 -c 2 -f \
+    -o gpurun_out/${TAG}_livepath python tools/time_live.py > gpurun_out/ncu_live.log 2>&1
+echo "live path rc=$?"
 tail -2 gpurun_out/ncu_default.log | cut -c1-200
 # keep the evidence small: text summaries of every report, then drop the reports (gpurun_out <= 64 MiB)
 for r in gpurun_out/${TAG}_*.ncu-rep; do
