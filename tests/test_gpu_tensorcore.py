@@ -128,3 +128,43 @@ def test_train_bf16_vs_oracle_and_determinism():
     assert cosine(du, dw) >= 0.98, cosine(du, dw)
     assert rel_l2(outs[0], p) <= 1e-3
     assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[1], outs[2])  # bit-reproducible
+
+
+def test_tma_im2col_operands_equal_the_gather_operands(monkeypatch):
+    """The TMA im2col producers (conv1/2/3 forward, conv3/conv2 data gradients; conv2's four parity
+    classes as one GEMM) against the cp.async gather producers they replace (ALEGPU_NO_TMA=1): the same
+    bf16 products summed in the same k order, so the results must agree to the bit.  37 rows: every
+    layer's last 128-row tile is ragged and tiles straddle image borders (padding / OOB zero fill)."""
+    H, n = 64, 37
+    params = cases.net_params(H, seed=5)
+    tc = cases.train_case(n, seed=19)
+    outs = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("ALEGPU_NO_TMA", flag)
+        L = alegpu.Learner(H, 4, n, alegpu.MATH_BF16, cases.LR)
+        L.set_params(params)
+        grads, loss, logits, values = L.grads(_batch(tc), hp())
+        outs[flag] = (grads, logits, values) + tuple(L.activations(n))
+    for a, b in zip(outs["0"][1:], outs["1"][1:]):          # logits, values, act1..3, fc
+        assert np.array_equal(a, b)
+    assert np.array_equal(outs["0"][0], outs["1"][0])      # and the whole gradient
+
+
+def test_conv1_wgrad_shifted_views_match_the_im2col_form(monkeypatch):
+    """conv1's weight gradient from the space-to-depth observations (four shifted views of dact1 as
+    the A operand, observations read once) against the im2col form over the u8 observations
+    (ALEGPU_CONV1_WGRAD_U8=1): same bf16 products, different fp32 summation order."""
+    H, n = 64, 37
+    params = cases.net_params(H, seed=6)
+    tc = cases.train_case(n, seed=23)
+    offs = cases.param_offsets(H)
+    g = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("ALEGPU_CONV1_WGRAD_U8", flag)
+        L = alegpu.Learner(H, 4, n, alegpu.MATH_BF16, cases.LR)
+        L.set_params(params)
+        g[flag] = L.grads(_batch(tc), hp())[0]
+    for i in (0, 1):                                        # conv1 weight, conv1 bias
+        a, b = g["0"][offs[i]:offs[i + 1]], g["1"][offs[i]:offs[i + 1]]
+        assert rel_l2(a, b) <= 1e-5, (i, rel_l2(a, b))
+    assert np.array_equal(g["0"][offs[2]:], g["1"][offs[2]:])  # every other tensor: identical path
