@@ -864,7 +864,10 @@ Shadow shadow_view(const TcState &T, const NetParams &P) {
 }
 
 // ---- TMA im2col tensor maps ---------------------------------------------------------------------------
-enum TmaSlot { kMapAct1 = 0, kMapAct2, kMapDact3, kMapDact2, kMapObsMb, kMapObsAll, kMapCount };
+// kMapObsAll.. : one slot per (re)allocation of obs16_all, used round-robin, so a descriptor that an
+// earlier kernel may still have cached is never rewritten in place
+enum TmaSlot { kMapAct1 = 0, kMapAct2, kMapDact3, kMapDact2, kMapObsMb, kMapObsAll, kMapObsAllSlots = 16,
+               kMapCount = kMapObsAll + kMapObsAllSlots };
 using EncodeIm2colFn = CUresult (*)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
                                     const cuuint64_t *, const cuuint64_t *, const int *, const int *,
                                     cuuint32_t, cuuint32_t, const cuuint32_t *, CUtensorMapInterleave,
@@ -1008,8 +1011,10 @@ int net_tc_reserve_obs(TcState &T, int64_t n) {
   T.obs16_all_rows = 0;
   ALEGPU_CUDA_CHECK(cudaMalloc(&T.obs16_all, sizeof(bf16) * (size_t)n * 28224));
   T.obs16_all_rows = n;
-  if (T.use_tma)
-    return set_im2col_map(T, kMapObsAll, T.obs16_all, 21, 21, n, 0, -1);
+  if (T.use_tma) {
+    T.obs_all_map = (T.obs_all_map + 1) % kMapObsAllSlots;
+    return set_im2col_map(T, kMapObsAll + T.obs_all_map, T.obs16_all, 21, 21, n, 0, -1);
+  }
   return ALEGPU_OK;
 }
 
@@ -1043,7 +1048,8 @@ int net_tc_forward(const NetParams &P, TcState &T, const uint8_t *obs, int64_t n
     const bf16 *x16 = (const bf16 *)obs16, *all = (const bf16 *)T.obs16_all;
     const bool in_all = all && x16 >= all && x16 < all + (size_t)T.obs16_all_rows * 28224;
     if (T.use_tma && (x16 == (const bf16 *)T.obs16_mb || in_all)) {
-      const Col1Tma a{tmap(T, in_all ? kMapObsAll : kMapObsMb), in_all ? (int)((x16 - all) / 28224) : 0};
+      const Col1Tma a{tmap(T, in_all ? kMapObsAll + T.obs_all_map : kMapObsMb),
+                      in_all ? (int)((x16 - all) / 28224) : 0};
       if (int rc = tc::launch_gemm_tc<32, 4>(a, RowsK{(const bf16 *)T.c1w_perm, 256},
                                              EpiBiasReluBf16{act1, P.c1b, 32, 1.0f / 255.0f},
                                              n * 400, 32, 256, 1, 0, s))

@@ -27,6 +27,7 @@ struct TcState {
   size_t ws_heads_n = 0, ws_fc_n = 0, ws_c3_n = 0, ws_c2_n = 0, ws_c1_n = 0;
   // TMA im2col tensor maps (device array of CUtensorMap, see net_tc.cu: TmaSlot); nullptr = not in use
   void *tmaps = nullptr;
+  int obs_all_map = 0;       // which of the round-robin obs16_all descriptor slots is current
   bool use_tma = true;       // ALEGPU_NO_TMA=1: gather conv operands with cp.async instead (A/B)
   bool serial = false;       // ALEGPU_TC_SERIAL=1: keep everything on one stream (profiling)
   bool conv1_u8 = false;     // ALEGPU_CONV1_U8=1: conv1 forward reads the u8 observations (A/B)

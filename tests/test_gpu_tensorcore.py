@@ -168,3 +168,23 @@ def test_conv1_wgrad_shifted_views_match_the_im2col_form(monkeypatch):
         a, b = g["0"][offs[i]:offs[i + 1]], g["1"][offs[i]:offs[i + 1]]
         assert rel_l2(a, b) <= 1e-5, (i, rel_l2(a, b))
     assert np.array_equal(g["0"][offs[2]:], g["1"][offs[2]:])  # every other tensor: identical path
+
+
+def test_tma_descriptor_follows_a_regrown_observation_copy(monkeypatch):
+    """train() on 64 rows, then on 128 rows with the same Learner: the whole-batch bf16 copy of the
+    observations is reallocated and its TMA descriptor re-encoded (a fresh descriptor slot).  The
+    cp.async gather path (no descriptors) run through the same sequence is the reference: identical bits."""
+    H, mb = 64, 32
+    params = cases.net_params(H, seed=8)
+    small, big = cases.train_case(64, seed=41), cases.train_case(128, seed=43)
+    outs = []
+    for flag in ("1", "0"):
+        monkeypatch.setenv("ALEGPU_NO_TMA", flag)
+        L = alegpu.Learner(H, 4, mb, alegpu.MATH_BF16, cases.LR)
+        L.set_params(params)
+        L.train(_batch(small), alegpu.Metrics(1, 2, mb), 1, 2, hp(), cuda_graph=True)
+        L.train(_batch(big), alegpu.Metrics(2, 4, mb), 2, 4, hp(), cuda_graph=True)
+        L.train(_batch(small), alegpu.Metrics(1, 2, mb), 1, 2, hp(), cuda_graph=True)
+        outs.append(L.get_params())
+    assert np.array_equal(outs[0], outs[1])
+    assert not np.array_equal(outs[0], params)
