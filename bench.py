@@ -59,25 +59,55 @@ def peaks():
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    """SM clock / throttle reasons sampled DURING the timed region: NVML every 2 ms (a v0 timed
+    region is ~50 ms, shorter than one nvidia-smi call), nvidia-smi when NVML cannot be opened."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    # nvmlClocksEventReason bits, in the order of Q's reason columns
+    BITS = (0x8, 0x40, 0x20, 0x4)
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.samples, self.stop_flag = index, [], False
+        self.index, self.samples, self.stop_flag, self.source = index, [], False, "nvidia-smi"
+        self.nvml_error = None
+
+    def _nvml_loop(self):
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+        mx = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+        while not self.stop_flag:
+            sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+            r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+            self.samples.append([str(sm), str(mx)] +
+                                ["Active" if r & b else "Not Active" for b in self.BITS])
+            time.sleep(0.002)
+
+    def _smi_once(self):
+        out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                              "--format=csv,noheader,nounits"], capture_output=True,
+                             text=True, timeout=5).stdout.strip()
+        if out:
+            self.samples.append([x.strip() for x in out.split(",")])
 
     def run(self):
-        while not self.stop_flag:
+        try:
+            self.source = "nvml"
+            self._nvml_loop()
+            if self.samples:
+                return
+        except Exception as e:  # reported in the bench line so the cause is visible next run
+            self.nvml_error = repr(e)[:120]
+        self.source = "nvidia-smi"
+        self.samples = []
+        while True:  # at least one sample even if the region already ended
             try:
-                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                      "--format=csv,noheader,nounits"], capture_output=True,
-                                     text=True, timeout=5).stdout.strip()
-                if out:
-                    self.samples.append([x.strip() for x in out.split(",")])
+                self._smi_once()
             except Exception:
                 pass
+            if self.stop_flag:
+                break
             time.sleep(0.2)
 
     def summary(self):
@@ -88,7 +118,8 @@ class ClockSampler(threading.Thread):
         reasons = [n for i, n in enumerate(names)
                    if any(s[2 + i].lower().startswith("active") for s in self.samples)]
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.samples[0][1]),
-                "reasons": reasons, "samples": len(self.samples)}
+                "reasons": reasons, "samples": len(self.samples), "source": self.source,
+                **({"nvml_error": self.nvml_error} if self.nvml_error else {})}
 
 
 def synth_inputs(w, seed):
