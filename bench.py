@@ -186,7 +186,10 @@ def run_reference(args, w):
             "steps": n_steps, "warmup": 1, "ms_per_step": 1e3 * E * w["T"] / v,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "impl": "reference",
-            "config": {"workload": args.workload, **{k: w[k] for k in ("E", "T", "H", "epochs", "nmb")},
+            # same keys as our arm's config; sample_envs = the bounded sample one step runs
+            "config": {"workload": args.workload, "envs_per_gpu": w["E"], "horizon": w["T"],
+                       "hidden_size": w["H"], "num_epochs": w["epochs"], "num_mini_batches": w["nmb"],
+                       "mini_batch_per_gpu": w["E"] * w["T"] // w["nmb"], "math": "fp32 (libtorch CPU)",
                        "sample_envs": E},
             "cpu_baseline": {"value": v, "unit": "agent-steps/s", "cores": threads,
                              "kind": "reference", "sample": desc},

@@ -85,3 +85,48 @@ def test_cpp_shim_gae_known_answer_on_gpu(tmp_path):
     exe = _build_shim_test(tmp_path)
     r = subprocess.run([exe, "gpu"], capture_output=True, text=True)
     assert r.returncode == 0 and "gpu gae: 2.81" in r.stdout, r.stdout + r.stderr
+
+
+def test_bench_reference_arm_line_contract():
+    """`bench.py --impl reference` (the reference's own CPU code, oracle/_ref) prints one JSON line
+    with the keys the driver reads; it never loads the CUDA library."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference",
+                          "--workload", "debug", "--steps", "1", "--warmup", "1"],
+                         capture_output=True, text=True, timeout=300, cwd=root)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [ln for ln in out.stdout.splitlines() if ln.startswith("{")]
+    assert len(lines) == 1
+    line = json.loads(lines[0])
+    assert line["impl"] == "reference"
+    if "unavailable" in line:
+        pytest.skip("oracle/_ref not built here: " + line["unavailable"])
+    for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step",
+                "higher_is_better", "scaling", "vs_baseline", "dtype", "data", "config",
+                "cpu_baseline", "e2e"):
+        assert key in line, key
+    assert line["unit"] == "agent-steps/s" and line["higher_is_better"] is True
+    assert line["config"]["workload"] == "debug" and line["config"]["envs_per_gpu"] == 8
+    assert line["cpu_baseline"]["kind"] == "reference" and line["cpu_baseline"]["cores"] >= 1
+    assert line["e2e"] == {"value": line["value"], "unit": line["unit"], "h2d_bytes_per_step": 0,
+                           "d2h_bytes_per_step": 0}
+    assert line["gpu_launches"] == 0 and line["value"] > 0
+
+
+def test_bench_clock_summary_flags_throttle_reasons():
+    """The clocks object of the bench line: median SM clock under load, reasons seen in ANY sample;
+    a run without a single sample says so instead of reporting a clean run."""
+    import sys
+    sys.path.insert(0, ROOT)
+    import bench
+    c = bench.ClockSampler(0)
+    assert c.summary()["reasons"] == ["unsampled"]
+    idle = ["Not Active"] * 4
+    c.samples = [["1965", "1965"] + idle, ["1800", "1965", "Not Active", "Active", "Not Active", "Active"],
+                 ["1950", "1965"] + idle]
+    s = c.summary()
+    assert s["sm_mhz"] == 1950.0 and s["sm_max_mhz"] == 1965.0 and s["samples"] == 3
+    assert s["reasons"] == ["hw_thermal_slowdown", "sw_power_cap"]
