@@ -33,6 +33,17 @@ def test_sass_is_sm100a_only():
     assert archs == {"sm_100a"}, archs
 
 
+def test_sass_uses_tcgen05_tmem_and_tma():
+    """The GEMM engine is tcgen05 (UTCHMMA, accumulators read back from TMEM with LDTM), its conv
+    operands come through TMA im2col (UTMALDG.*IM2COL) and the preprocess pipe through bulk copies
+    (UBLKCP); no legacy warp-level HMMA tensor-core path is shipped."""
+    import subprocess
+    sass = subprocess.run(["cuobjdump", "-sass", alegpu.SO_PATH], capture_output=True, text=True).stdout
+    for mnemonic in ("UTCHMMA", "LDTM", "UTCBAR", "UTMALDG.4D.IM2COL", "UBLKCP", "SYNCS.PHASECHK"):
+        assert mnemonic in sass, mnemonic
+    assert not re.search(r"\bHMMA\.", sass), "legacy mma.sync path in the shipped library"
+
+
 def test_host_side_validation_matches_reference_exceptions():
     lib = alegpu.lib()
     # Buffer::get on a non-full buffer -> std::runtime_error (buffer.cc:64-65); checked before any CUDA call
