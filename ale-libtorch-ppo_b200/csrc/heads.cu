@@ -6,6 +6,7 @@
 // the per-sample metrics straight to their final [epoch,k,:] offsets (Metrics::set,
 // src/ai/ppo/train.h:93-108) and back-propagates through the heads into dfc — so logits,
 // values, dlogits and dvalues never round-trip through HBM between separate kernels.
+#include <cstdlib>
 #include <cuda_bf16.h>
 
 #include "loss.cuh"
@@ -318,7 +319,14 @@ int heads_wgrad(const NetParams &G, const NetActs &A, int64_t n, float *ws, size
                 cudaStream_t s) {
   const int H = (int)G.hidden, Ac = (int)G.actions, A1 = Ac + 1;
   const size_t per = (size_t)A1 * (H + 1);
-  int splits = (int)std::max<int64_t>(1, std::min<int64_t>(n / 64, 2 * kNumSMs));
+  // rows per split: 64 by default (4 splits x 5 column blocks = 20 CTAs at v0's 256-row minibatch, 14 us in
+  // profiles/r01e_launches_v0_default.txt); ALEGPU_HEADS_WGRAD_ROWS is the A/B switch for finer splits
+  static const int64_t rows = [] {
+    const char *e = getenv("ALEGPU_HEADS_WGRAD_ROWS");
+    const int64_t v = e ? atoll(e) : 64;
+    return v >= 1 ? v : 64;
+  }();
+  int splits = (int)std::max<int64_t>(1, std::min<int64_t>(n / rows, 2 * kNumSMs));
   splits = (int)std::min<size_t>(splits, ws_floats / per);
   ALEGPU_REQUIRE(splits >= 1, ALEGPU_RUNTIME_ERROR, "heads_wgrad: workspace too small");
   const int rps = (int)ceil_div(n, splits);
