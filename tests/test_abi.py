@@ -141,3 +141,17 @@ def test_bench_clock_summary_flags_throttle_reasons():
     s = c.summary()
     assert s["sm_mhz"] == 1950.0 and s["sm_max_mhz"] == 1965.0 and s["samples"] == 3
     assert s["reasons"] == ["hw_thermal_slowdown", "sw_power_cap"]
+
+
+def test_bench_product_arm_fails_loudly_without_device():
+    """No CPU fallback: without a CUDA device `bench.py` (our arm) exits non-zero and prints no
+    bench line — it never routes through the oracle."""
+    if alegpu.device_count() > 0:
+        pytest.skip("a GPU is present")
+    import subprocess
+    import sys
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1", "--warmup", "1",
+                          "--no-cpu-baseline"], capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert out.returncode != 0
+    assert not [ln for ln in out.stdout.splitlines() if ln.startswith("{")]
+    assert "CudaError" in out.stderr
