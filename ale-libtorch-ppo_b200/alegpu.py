@@ -21,7 +21,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_HERE, "libalegpu.so")
 _lib = None
 
-MATH_FP32, MATH_BF16 = 0, 1
+MATH_FP32, MATH_BF16, MATH_TF32 = 0, 1, 2
 FRAME_BYTES = 210 * 160 * 3
 STACK_BYTES = 4 * 84 * 84
 
@@ -586,7 +586,8 @@ class Learner:
         return int(lib().alegpu_learner_last_launch_count(self.h))
 
 
-def selftest_tc_gemm(A, B, M, N, R, a_mn=False, b_mn=False, bn=64, splits=1, use_async=False):
+def selftest_tc_gemm(A, B, M, N, R, a_mn=False, b_mn=False, bn=64, splits=1, use_async=False,
+                     tf32=False):
     """C[M,N] = A . B^T through the tcgen05/TMEM engine (alegpu_selftest_tc_gemm).  A is
     [M,R] (a_mn False) or [R,M] (a_mn True) fp32; likewise B.  Returns [z,M,N] partial
     products (z == 1 unless splits > 1)."""
@@ -599,6 +600,8 @@ def selftest_tc_gemm(A, B, M, N, R, a_mn=False, b_mn=False, bn=64, splits=1, use
     dA, dB = DeviceArray.from_numpy(A), DeviceArray.from_numpy(B)
     dC = DeviceArray.zeros((z, M, N), np.float32)
     fn = lib().alegpu_selftest_tc_gemm_async if use_async else lib().alegpu_selftest_tc_gemm
+    if tf32:  # kind::tf32: fp32 inputs read as they are (upper 19 bits) by the cp.async producers
+        fn = lib().alegpu_selftest_tc_gemm_tf32
     _check(fn(_p(dA), _p(dB), _p(dC), C.c_int64(M), C.c_int64(N), C.c_int64(R),
               C.c_int(int(a_mn)), C.c_int(int(b_mn)), C.c_int(bn), C.c_int(splits), None))
     synchronize()

@@ -24,7 +24,7 @@ __global__ void __launch_bounds__(kThreads)
                  const float *__restrict__ vw, const float *__restrict__ vb,
                  const float *__restrict__ fc, int64_t n, int H, int A,
                  float *__restrict__ logits, float *__restrict__ values,
-                 float *__restrict__ dfc, __nv_bfloat16 *__restrict__ dfc16,
+                 float *__restrict__ dfc, __nv_bfloat16 *__restrict__ dfc16, bool round_tf32,
                  float *__restrict__ dout, LossArgs L, float *__restrict__ partials) {
   extern __shared__ float sw[]; // [(A+1)][H] head weights, row A = value head
   __shared__ float red[kWarps];
@@ -107,6 +107,11 @@ __global__ void __launch_bounds__(kThreads)
         for (int a = 0; a < kMaxA; ++a)
           if (a < A)
             g = fmaf(dz[a], sw[a * H + j], g);
+        if (round_tf32) { // the tf32 tensor-core backward multiplies the upper 19 bits: round, not truncate
+          uint32_t r;
+          asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(g));
+          g = __uint_as_float(r);
+        }
         dfc[i * H + j] = g;
         if (dfc16)
           dfc16[i * H + j] = __float2bfloat16_rn(g);
@@ -207,8 +212,8 @@ int heads_grid(int64_t n) {
 
 template <bool kLoss>
 int launch_heads(const NetParams &P, const float *fc, int64_t n, float *logits, float *values,
-                 float *dfc, void *dfc16, float *dout, const LossArgs &L, float *partials,
-                 int grid, cudaStream_t s) {
+                 float *dfc, void *dfc16, bool round_tf32, float *dout, const LossArgs &L,
+                 float *partials, int grid, cudaStream_t s) {
   const int H = (int)P.hidden, A = (int)P.actions;
   const size_t smem = (size_t)(A + 1) * H * sizeof(float);
   ALEGPU_REQUIRE(smem <= 200 * 1024, ALEGPU_INVALID_ARGUMENT, "heads: (A+1)*H too large");
@@ -217,13 +222,13 @@ int launch_heads(const NetParams &P, const float *fc, int64_t n, float *logits, 
     if (smem > 48 * 1024)
       ALEGPU_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k<<<grid, kThreads, smem, s>>>(P.piw, P.pib, P.vw, P.vb, fc, n, H, A, logits, values, dfc,
-                                   (__nv_bfloat16 *)dfc16, dout, L, partials);
+                                   (__nv_bfloat16 *)dfc16, round_tf32, dout, L, partials);
   } else {
     auto k = heads_kernel<18, kLoss>;
     if (smem > 48 * 1024)
       ALEGPU_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k<<<grid, kThreads, smem, s>>>(P.piw, P.pib, P.vw, P.vb, fc, n, H, A, logits, values, dfc,
-                                   (__nv_bfloat16 *)dfc16, dout, L, partials);
+                                   (__nv_bfloat16 *)dfc16, round_tf32, dout, L, partials);
   }
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
@@ -303,7 +308,7 @@ int heads_forward(const NetParams &P, const float *fc, int64_t n, float *logits,
   if (n == 0)
     return ALEGPU_OK;
   LossArgs L{};
-  return launch_heads<false>(P, fc, n, logits, values, nullptr, nullptr, nullptr, L, nullptr,
+  return launch_heads<false>(P, fc, n, logits, values, nullptr, nullptr, false, nullptr, L, nullptr,
                              heads_grid(n), s);
 }
 
@@ -311,8 +316,8 @@ int heads_loss_backward(const NetParams &P, NetActs &A, int64_t n, const LossArg
                         float *loss_partials, int *nparts, cudaStream_t s) {
   const int grid = heads_grid(n);
   *nparts = grid;
-  return launch_heads<true>(P, A.fc, n, A.logits, A.values, A.dfc, A.dfc16, A.dout, L, loss_partials,
-                            grid, s);
+  return launch_heads<true>(P, A.fc, n, A.logits, A.values, A.dfc, A.dfc16, A.dfc_round_tf32, A.dout,
+                            L, loss_partials, grid, s);
 }
 
 int heads_wgrad(const NetParams &G, const NetActs &A, int64_t n, float *ws, size_t ws_floats,

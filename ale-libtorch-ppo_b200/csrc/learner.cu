@@ -187,7 +187,9 @@ int sync_opt_state(alegpu_learner *L) {
   return ALEGPU_OK;
 }
 
-bool use_tc(const alegpu_learner *L) { return L->cfg.math == ALEGPU_MATH_BF16; }
+bool use_tc(const alegpu_learner *L) {
+  return L->cfg.math == ALEGPU_MATH_BF16 || L->cfg.math == ALEGPU_MATH_TF32;
+}
 
 int forward(alegpu_learner *L, const uint8_t *obs, int64_t n, const void *obs16 = nullptr) {
   if (use_tc(L))
@@ -237,7 +239,8 @@ int clip_and_step(alegpu_learner *L, float max_norm, float *total_norm_out) {
     return rc;
   L->host_step += 1;
   return launch_adam_clip(L->params, L->grads, L->m, L->v, use_tc(L) ? L->tc.w_shadow : nullptr,
-                          use_tc(L) ? L->tc.c1w_perm : nullptr, L->Ppad, L->opt, L->stream);
+                          use_tc(L) ? L->tc.c1w_perm : nullptr, use_tc(L) ? L->tc.elem_bytes : 0,
+                          L->Ppad, L->opt, L->stream);
 }
 
 // the body of train(): everything is stream-ordered, nothing synchronises
@@ -330,7 +333,8 @@ int enqueue_train(alegpu_learner *L, const alegpu_batch &b, const alegpu_metrics
         la.adv_stats = st;
       }
       const void *obs16 =
-          obs16_all ? (const void *)((const uint16_t *)obs16_all + (size_t)s * 28224) : nullptr;
+          obs16_all ? (const void *)((const uint8_t *)obs16_all + (size_t)s * 28224 * L->tc.elem_bytes)
+                    : nullptr;
       if (int rc = forward(L, obs, mb, obs16))
         return rc;
       la.clip = hp.clip_param;
@@ -542,9 +546,10 @@ extern "C" int alegpu_learner_create(const alegpu_learner_config *config, alegpu
                  "learner_create: action_size must be in [1,18]");
   ALEGPU_REQUIRE(config->max_minibatch >= 1, ALEGPU_INVALID_ARGUMENT,
                  "learner_create: max_minibatch must be >= 1");
-  ALEGPU_REQUIRE(config->math == ALEGPU_MATH_FP32 || config->math == ALEGPU_MATH_BF16,
+  ALEGPU_REQUIRE(config->math == ALEGPU_MATH_FP32 || config->math == ALEGPU_MATH_BF16 ||
+                     config->math == ALEGPU_MATH_TF32,
                  ALEGPU_INVALID_ARGUMENT, "learner_create: unknown math mode");
-  if (config->math == ALEGPU_MATH_BF16)
+  if (config->math != ALEGPU_MATH_FP32)
     ALEGPU_REQUIRE(config->hidden_size % 16 == 0, ALEGPU_INVALID_ARGUMENT,
                    "learner_create: the tensor-core path needs hidden_size % 16 == 0");
   ALEGPU_CUDA_CHECK(cudaSetDevice(config->device));
@@ -568,7 +573,7 @@ extern "C" int alegpu_learner_create(const alegpu_learner_config *config, alegpu
   L->Gv = net_params_view(L->grads, H, A);
   NetActs &a = L->acts;
   a.cap = cap;
-  const bool tc = config->math == ALEGPU_MATH_BF16;
+  const bool tc = config->math != ALEGPU_MATH_FP32;
   auto fmalloc = [&](float **p, size_t n) -> int {
     ALEGPU_CUDA_CHECK(cudaMalloc(p, sizeof(float) * (n ? n : 1)));
     return ALEGPU_OK;
@@ -600,9 +605,11 @@ extern "C" int alegpu_learner_create(const alegpu_learner_config *config, alegpu
   if (int rc = fmalloc(&L->scalars, 16)) return rc;
   ALEGPU_CUDA_CHECK(cudaMalloc(&L->opt, sizeof(OptState)));
   if (tc)
-    if (int rc = net_tc_init(L->tc, H, A, cap, L->Ppad, L->stream))
+    if (int rc = net_tc_init(L->tc, H, A, cap, L->Ppad, config->math == ALEGPU_MATH_TF32 ? 4 : 2,
+                             L->stream))
       return rc;
-  a.dfc16 = L->tc.dfc16; // the heads kernel also emits dfc in bf16 for the tensor-core backward
+  a.dfc16 = L->tc.dfc16; // bf16 mode: the heads kernel also emits dfc in bf16 for the tensor-core backward
+  a.dfc_round_tf32 = config->math == ALEGPU_MATH_TF32; // tf32 mode: it rounds dfc itself to tf32
 #ifdef ALEGPU_WITH_NCCL
   if (L->cfg.world_size > 1) {
     ALEGPU_REQUIRE(config->nccl_unique_id, ALEGPU_INVALID_ARGUMENT,

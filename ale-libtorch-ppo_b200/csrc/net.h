@@ -45,6 +45,7 @@ struct NetActs {
   float *logits = nullptr, *values = nullptr; // [cap,A], [cap]
   float *dout = nullptr;                      // [cap, A+1] = (dlogits, dvalue)
   void *dfc16 = nullptr;                      // optional bf16 copy of dfc (tensor-core path)
+  bool dfc_round_tf32 = false;                // tf32 path: dfc is stored rounded to tf32 (cvt.rna)
   float *fc_ws = nullptr;                     // split-K partials of the FC forward (tensor-core path)
   size_t fc_ws_floats = 0;
 };

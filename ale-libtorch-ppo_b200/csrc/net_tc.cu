@@ -45,6 +45,13 @@ __device__ __forceinline__ uint4 zero16() { return make_uint4(0u, 0u, 0u, 0u); }
 // the chunk (1, 0, 0, 0, 0, 0, 0, 0) in bf16: source of the "ones" row/column that turns a weight
 // gradient GEMM into weight + bias gradient, for the cp.async producers
 __device__ const uint4 g_ones_chunk = {0x00003F80u, 0u, 0u, 0u};
+__device__ const uint4 g_ones_chunk_f32 = {0x3F800000u, 0u, 0u, 0u}; // (1, 0, 0, 0) in fp32 / tf32
+template <int kElemBytes> __device__ __forceinline__ const void *ones_chunk_ptr() {
+  if constexpr (kElemBytes == 4)
+    return &g_ones_chunk_f32;
+  else
+    return &g_ones_chunk;
+}
 __device__ __forceinline__ uint4 ones_first16() { return make_uint4(0x00003F80u, 0u, 0u, 0u); }
 // four u8 -> four bf16 (exact): bf16(v) = high half of float(v)
 // (byte k dropped into the mantissa of 2^23, minus 2^23: PRMT + FADD instead of the slow I2F pipe)
@@ -115,14 +122,15 @@ struct Col1 {
 // conv1 over the bf16 NHWC copy of the observations ([n,84,84,4], made once per train() by
 // obs_to_s2d_bf16_kernel): row m = (n,oy,ox) of 20x20; on the space-to-depth layout the 8x8 stride-4
 // window is 2x2 taps of 64 contiguous channels, so every 16-byte chunk can be copied with cp.async.  The conv1 weights are read from a shadow permuted to the same k' order.
-struct Col1N {
+template <class T> struct Col1N {
+  static constexpr int kElemBytes = (int)sizeof(T);
   ALEGPU_RAW_BF16
   static constexpr bool kAsyncSrc = true;
   static constexpr int kPrefetch = 2;
-  const bf16 *x; // obs16, space-to-depth [n,21,21,64]: channel = (y&3)*16 + (x&3)*4 + c
-  using PosPtr = const bf16 *;
+  const T *x; // obs16, space-to-depth [n,21,21,64]: channel = (y&3)*16 + (x&3)*4 + c
+  using PosPtr = const T *;
   __device__ __forceinline__ const void *anchor() const { return x; }
-  __device__ __forceinline__ const bf16 *pos_ptr(int m) const {
+  __device__ __forceinline__ const T *pos_ptr(int m) const {
     const int n = m / 400, pix = m - n * 400, oy = pix / 20, ox = pix - oy * 20;
     return x + ((size_t)(n * 21 + oy) * 21 + ox) * 64;
   }
@@ -140,15 +148,16 @@ __host__ __device__ __forceinline__ int conv1_k_of_kprime(int kp) {
   return c * 64 + (4 * a + ry) * 8 + 4 * b + sx;
 }
 // conv2: row m = (n,oy,ox) of 9x9, k = (ky*4+kx)*32 + ci
-struct Col2 {
+template <class T> struct Col2 {
+  static constexpr int kElemBytes = (int)sizeof(T);
   ALEGPU_RAW_BF16
   static constexpr bool kAsyncSrc = true;
   static constexpr int kPrefetch = 2;
-  const bf16 *x; // act1 [n,20,20,32]
+  const T *x; // act1 [n,20,20,32]
   // address of element (m, k) = pos_ptr(m) + k_off(k): the position part and the tap part
-  using PosPtr = const bf16 *;
+  using PosPtr = const T *;
   __device__ __forceinline__ const void *anchor() const { return x; }
-  __device__ __forceinline__ const bf16 *pos_ptr(int m) const {
+  __device__ __forceinline__ const T *pos_ptr(int m) const {
     const int n = m / 81, pix = m - n * 81, oy = pix / 9, ox = pix - oy * 9;
     return x + ((size_t)(n * 20 + 2 * oy) * 20 + 2 * ox) * 32;
   }
@@ -159,14 +168,15 @@ struct Col2 {
   __device__ __forceinline__ uint4 at(int m, int k) const { return ldg16(pos_ptr(m) + k_off(k)); }
 };
 // conv3: row m = (n,oy,ox) of 7x7, k = (ky*3+kx)*64 + ci
-struct Col3 {
+template <class T> struct Col3 {
+  static constexpr int kElemBytes = (int)sizeof(T);
   ALEGPU_RAW_BF16
   static constexpr bool kAsyncSrc = true;
   static constexpr int kPrefetch = 2;
-  const bf16 *x; // act2 [n,9,9,64]
-  using PosPtr = const bf16 *;
+  const T *x; // act2 [n,9,9,64]
+  using PosPtr = const T *;
   __device__ __forceinline__ const void *anchor() const { return x; }
-  __device__ __forceinline__ const bf16 *pos_ptr(int m) const {
+  __device__ __forceinline__ const T *pos_ptr(int m) const {
     const int n = m / 49, pix = m - n * 49, oy = pix / 7, ox = pix - oy * 7;
     return x + ((size_t)(n * 9 + oy) * 9 + ox) * 64;
   }
@@ -183,8 +193,10 @@ struct Col3 {
 // (data-gradient) walk, where tap (ky,kx) reads pixel (oy-ky, ox-kx).  One instruction per
 // (128-row tile, k-block) replaces 1024 16-byte cp.async copies and their address arithmetic;
 // pixels outside the tensor (padding, rows past the last image) arrive as zeros.
-template <int OH, int OW, int KW, int LOW, bool kFlip, int SH = 1> struct ColTma {
+template <class T, int OH, int OW, int KW, int LOW, bool kFlip, int SH = 1> struct ColTma {
   ALEGPU_RAW_BF16
+  static constexpr int kElemBytes = (int)sizeof(T);
+  static constexpr int kBK = 128 / kElemBytes; // channels per k-block (64 bf16 / 32 fp32 of the 64 per pixel)
   static constexpr bool kMN = false;
   static constexpr bool kAsync = true;
   static constexpr bool kTma = true;
@@ -200,23 +212,30 @@ template <int OH, int OW, int KW, int LOW, bool kFlip, int SH = 1> struct ColTma
   __device__ __forceinline__ void tma(const TileCtx &t, uint32_t dst, int r0, int, uint64_t *bar) const {
     const int tap = r0 >> 6, ky = tap / KW, kx = tap - ky * KW;
     const int ow = kFlip ? -LOW - kx : kx, oh = kFlip ? -LOW - ky : ky;
-    tc::tma_im2col_4d(dst, map, 0, t.w, t.h, t.n, (uint16_t)ow, (uint16_t)oh, bar);
+    tc::tma_im2col_4d(dst, map, r0 & 63 & ~(kBK - 1), t.w, t.h, t.n, (uint16_t)ow, (uint16_t)oh, bar);
   }
 };
-using Col3Tma = ColTma<7, 7, 3, 0, false>;   // conv3 forward over act2 [n,9,9,64]
-using DCol3Tma = ColTma<9, 9, 3, -2, true>;  // conv3 data gradient over dact3 [n,7,7,64]
+template <class T> using Col3Tma = ColTma<T, 7, 7, 3, 0, false>;   // conv3 forward over act2 [n,9,9,64]
+template <class T> using DCol3Tma = ColTma<T, 9, 9, 3, -2, true>;  // conv3 data gradient over dact3 [n,7,7,64]
 // conv2 forward over act1 [n,20,20,32] viewed as pixel PAIRS [n,20,10,64]: with stride 2 the taps
 // kx = (0,1) and (2,3) are the pairs ox and ox+1, so it is a 4 (ky, stride 2) x 2 (pairs, stride 1)
 // convolution over 64 channels and k = (ky*2 + pair)*64 + (kx&1)*32 + ci is the weights' own order
-using Col2Tma = ColTma<9, 9, 2, 0, false, 2>;
-using Col1Tma = ColTma<20, 20, 2, 0, false>; // conv1 forward over the space-to-depth obs16 [n,21,21,64]
+template <class T> using Col2Tma = ColTma<T, 9, 9, 2, 0, false, 2>;
+template <class T> using Col1Tma = ColTma<T, 20, 20, 2, 0, false>; // conv1 forward over the space-to-depth obs16 [n,21,21,64]
 // conv2 data gradient: every parity class of the stride-2 transposed convolution reads the same
 // 2x2-tap, padding-1 walk over dact2 [n,9,9,64] (rows = (n,qy,qx) of 10x10); only the weights differ
-using DCol2Tma = ColTma<10, 10, 2, -1, true>;
+template <class T> using DCol2Tma = ColTma<T, 10, 10, 2, -1, true>;
 
 // K-major A operand of a forward conv: (row m, reduction k..k+7)
+template <class Col, class = void> struct ColElemBytes {
+  static constexpr int value = 2;
+};
+template <class Col> struct ColElemBytes<Col, decltype((void)Col::kElemBytes)> {
+  static constexpr int value = Col::kElemBytes;
+};
 template <class Col> struct ColK {
   static constexpr bool kMN = false;
+  static constexpr int kElemBytes = ColElemBytes<Col>::value;
   using Raw = typename Col::Raw;
   static __device__ __forceinline__ Raw zero() { return Col::zero(); }
   static __device__ __forceinline__ uint4 cvt(const Raw &v) { return Col::cvt(v); }
@@ -236,6 +255,7 @@ template <class Col> struct ColK {
 // this operand: raw u8 0xFFFFFFFF|.. pixels or a bf16 NaN pair) and decoded in cvt().
 template <class Col, int K> struct ColMN {
   static constexpr bool kMN = true;
+  static constexpr int kElemBytes = ColElemBytes<Col>::value;
   struct Raw {
     typename Col::Raw v;
     bool ones;
@@ -259,20 +279,21 @@ template <class Col, int K> struct ColMN {
   __device__ __forceinline__ ColCtx col(int m, int) const { return src.pos_ptr(m); }
   __device__ __forceinline__ const void *anchor() const { return src.anchor(); }
   __device__ __forceinline__ const void *at(RowCtx rc, ColCtx cc) const {
-    return rc >= 0 ? (const void *)(cc + rc) : (const void *)&g_ones_chunk;
+    return rc >= 0 ? (const void *)(cc + rc) : ones_chunk_ptr<kElemBytes>();
   }
 };
 // plain bf16 matrix [rows][ld]: K-major view (row, r..r+7)
-struct RowsK {
+template <class T> struct RowsK {
+  static constexpr int kElemBytes = (int)sizeof(T);
   ALEGPU_RAW_BF16
   static constexpr bool kMN = false;
   static constexpr bool kAsync = true;
-  const bf16 *p;
+  const T *p;
   int ld;
   __device__ __forceinline__ uint4 load(int i, int r, int) const {
     return ldg16(p + (size_t)i * ld + r);
   }
-  using RowCtx = const bf16 *;
+  using RowCtx = const T *;
   using ColCtx = int;
   __device__ __forceinline__ RowCtx row(int i) const { return p + (size_t)i * ld; }
   __device__ __forceinline__ ColCtx col(int r, int) const { return r; }
@@ -291,22 +312,23 @@ struct RowsKF32 {
 };
 // transposed view of a bf16 matrix stored [r][ld]: element (i, r) = p[r*ld + i]; MN-major;
 // rows i >= ld (only i == ld is ever requested) give the ones row/column used for bias grads
-struct ColsMN {
+template <class T> struct ColsMN {
+  static constexpr int kElemBytes = (int)sizeof(T);
   ALEGPU_RAW_BF16
   static constexpr bool kMN = true;
-  const bf16 *p;
+  const T *p;
   int ld;
   static constexpr bool kAsync = true;
   __device__ __forceinline__ uint4 load(int i0, int r, int) const {
     return i0 < ld ? ldg16(p + (size_t)r * ld + i0) : ones_first16();
   }
   using RowCtx = int; // i0, or -1 for the ones row
-  using ColCtx = const bf16 *;
+  using ColCtx = const T *;
   __device__ __forceinline__ RowCtx row(int i0) const { return i0 < ld ? i0 : -1; }
   __device__ __forceinline__ ColCtx col(int r, int) const { return p + (size_t)r * ld; }
   __device__ __forceinline__ const void *anchor() const { return p; }
   __device__ __forceinline__ const void *at(RowCtx rc, ColCtx cc) const {
-    return rc >= 0 ? (const void *)(cc + rc) : (const void *)&g_ones_chunk;
+    return rc >= 0 ? (const void *)(cc + rc) : ones_chunk_ptr<kElemBytes>();
   }
 };
 // conv1 wgrad on the space-to-depth layout, A operand (MN-major): row m = tap*32 + oc (tap = a*2+b),
@@ -314,16 +336,17 @@ struct ColsMN {
 // 20x20: the FOUR TAPS ARE FOUR SHIFTED VIEWS OF THE (small) OUTPUT GRADIENT, so the observation
 // operand (ColsMN over obs16, 128 contiguous bytes per r) is read exactly once, un-expanded:
 //   dW[(a,b,oc)][ch] = sum_{n,Y,X} dact1[n, Y-a, X-b, oc] * S[n, Y, X, ch]
-struct DYShift {
+template <class T> struct DYShift {
+  static constexpr int kElemBytes = (int)sizeof(T);
   ALEGPU_RAW_BF16
   static constexpr bool kMN = true;
   static constexpr bool kAsync = true;
-  const bf16 *dy; // dact1 [n,20,20,32]
+  const T *dy; // dact1 [n,20,20,32]
   struct RowCtx {
     int off, a, b; // off = oc0 - (a*20 + b)*32
   };
   struct ColCtx {
-    const bf16 *base; // dy element of (n, oy = Y, ox = X), channel 0 (may lie outside: only an offset)
+    const T *base; // dy element of (n, oy = Y, ox = X), channel 0 (may lie outside: only an offset)
     int Y, X;
   };
   __device__ __forceinline__ RowCtx row(int m0) const {
@@ -354,10 +377,11 @@ struct ColsMNF32 {
   }
 };
 // conv3 dgrad A: rows = act2 pixels (n,iy,ix) of 9x9, r = (ky*3+kx)*64 + co
-struct DCol3 {
+template <class T> struct DCol3 {
+  static constexpr int kElemBytes = (int)sizeof(T);
   ALEGPU_RAW_BF16
   static constexpr bool kMN = false;
-  const bf16 *dy; // dact3 [n,7,7,64]
+  const T *dy; // dact3 [n,7,7,64]
   __device__ __forceinline__ uint4 load(int i, int r, int) const {
     const int n = i / 81, pix = i - n * 81, iy = pix / 9, ix = pix - iy * 9;
     const int t = r >> 6, ky = t / 3, kx = t - ky * 3, co = r & 63;
@@ -368,7 +392,7 @@ struct DCol3 {
   }
   static constexpr bool kAsync = true;
   struct RowCtx {
-    const bf16 *base; // dy element of (n, oy = iy, ox = ix), channel 0 (may lie outside: only offset)
+    const T *base; // dy element of (n, oy = iy, ox = ix), channel 0 (may lie outside: only offset)
     int iy, ix;
   };
   struct ColCtx {
@@ -389,17 +413,18 @@ struct DCol3 {
   }
 };
 // conv3 dgrad B: (ci0..ci0+7, r = (t,co)) = c3w[co][t*64 + ci]
-struct W3T {
+template <class T> struct W3T {
+  static constexpr int kElemBytes = (int)sizeof(T);
   ALEGPU_RAW_BF16
   static constexpr bool kMN = true;
-  const bf16 *w;
+  const T *w;
   __device__ __forceinline__ uint4 load(int ci0, int r, int) const {
     const int t = r >> 6, co = r & 63;
     return ldg16(w + (size_t)co * 576 + t * 64 + ci0);
   }
   static constexpr bool kAsync = true;
   using RowCtx = int;
-  using ColCtx = const bf16 *;
+  using ColCtx = const T *;
   __device__ __forceinline__ RowCtx row(int ci0) const { return ci0; }
   __device__ __forceinline__ ColCtx col(int r, int) const {
     const int t = r >> 6, co = r & 63;
@@ -409,10 +434,11 @@ struct W3T {
   __device__ __forceinline__ const void *at(RowCtx rc, ColCtx cc) const { return cc + rc; }
 };
 // conv2 dgrad A, parity class z = py*2+px: rows (n,qy,qx) of 10x10, r = (ty*2+tx)*64 + co
-struct DCol2 {
+template <class T> struct DCol2 {
+  static constexpr int kElemBytes = (int)sizeof(T);
   ALEGPU_RAW_BF16
   static constexpr bool kMN = false;
-  const bf16 *dy; // dact2 [n,9,9,64]
+  const T *dy; // dact2 [n,9,9,64]
   __device__ __forceinline__ uint4 load(int i, int r, int) const {
     const int n = i / 100, pix = i - n * 100, qy = pix / 10, qx = pix - qy * 10;
     const int t = r >> 6, ty = t >> 1, tx = t & 1, co = r & 63;
@@ -423,7 +449,7 @@ struct DCol2 {
   }
   static constexpr bool kAsync = true;
   struct RowCtx {
-    const bf16 *base; // dy element of (n, oy = qy, ox = qx), channel 0 (only an offset base)
+    const T *base; // dy element of (n, oy = qy, ox = qx), channel 0 (only an offset base)
     int qy, qx;
   };
   struct ColCtx {
@@ -444,10 +470,11 @@ struct DCol2 {
   }
 };
 // conv2 dgrad B: (ci0.., r=(t,co), z) = c2w[co][(ky*4+kx)*32 + ci], ky = py+2ty, kx = px+2tx
-struct W2T {
+template <class T> struct W2T {
+  static constexpr int kElemBytes = (int)sizeof(T);
   ALEGPU_RAW_BF16
   static constexpr bool kMN = true;
-  const bf16 *w;
+  const T *w;
   __device__ __forceinline__ uint4 load(int ci0, int r, int z) const {
     const int t = r >> 6, ty = t >> 1, tx = t & 1, co = r & 63;
     const int ky = (z >> 1) + 2 * ty, kx = (z & 1) + 2 * tx;
@@ -455,7 +482,7 @@ struct W2T {
   }
   static constexpr bool kAsync = true;
   using RowCtx = int;
-  using ColCtx = const bf16 *;
+  using ColCtx = const T *;
   __device__ __forceinline__ RowCtx row(int ci0) const { return ci0; }
   __device__ __forceinline__ ColCtx col(int r, int z) const {
     const int t = r >> 6, ty = t >> 1, tx = t & 1, co = r & 63;
@@ -468,15 +495,16 @@ struct W2T {
 // conv2 dgrad B for all four parity classes at once: row j = cls*32 + ci (cls = py*2+px),
 // r = (t,co): c2w[co][(ky*4+kx)*32 + ci], ky = py+2ty, kx = px+2tx.  One pass over the (shared) A
 // operand then produces the whole 2x2 output block of every (qy,qx).
-struct W2TAll {
+template <class T> struct W2TAll {
+  static constexpr int kElemBytes = (int)sizeof(T);
   ALEGPU_RAW_BF16
   static constexpr bool kMN = true;
   static constexpr bool kAsync = true;
-  const bf16 *w;
+  const T *w;
   struct RowCtx {
     int off; // (py*4 + px)*32 + ci0
   };
-  using ColCtx = const bf16 *; // w + co*512 + (2ty*4 + 2tx)*32
+  using ColCtx = const T *; // w + co*512 + (2ty*4 + 2tx)*32
   __device__ __forceinline__ RowCtx row(int j0) const {
     const int cls = j0 >> 5;
     return RowCtx{((cls >> 1) * 4 + (cls & 1)) * 32 + (j0 & 31)};
@@ -508,8 +536,30 @@ __device__ __forceinline__ void load_bf16x16(const bf16 *src, float (&y)[16]) {
     y[2 * t + 1] = __uint_as_float(w[t] & 0xFFFF0000u);
   }
 }
-struct EpiBiasReluBf16 { // out[i][j] = relu(acc*scale + bias[j]) -> bf16, ld % 16 == 0
-  bf16 *out;
+// fp32 -> the value the tensor core will actually multiply: round-to-nearest tf32 (the MMA reads the
+// upper 19 bits of an fp32 operand, so rounding where the data is produced replaces its truncation)
+__device__ __forceinline__ float round_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+__device__ __forceinline__ void store_x16(bf16 *dst, const float (&v)[16]) { store_bf16x16(dst, v); }
+__device__ __forceinline__ void store_x16(float *dst, const float (&v)[16]) {
+#pragma unroll
+  for (int t = 0; t < 4; ++t)
+    reinterpret_cast<float4 *>(dst)[t] = make_float4(round_tf32(v[4 * t]), round_tf32(v[4 * t + 1]),
+                                                     round_tf32(v[4 * t + 2]), round_tf32(v[4 * t + 3]));
+}
+__device__ __forceinline__ void load_x16(const bf16 *src, float (&y)[16]) { load_bf16x16(src, y); }
+__device__ __forceinline__ void load_x16(const float *src, float (&y)[16]) {
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    const float4 q = reinterpret_cast<const float4 *>(src)[t];
+    y[4 * t] = q.x; y[4 * t + 1] = q.y; y[4 * t + 2] = q.z; y[4 * t + 3] = q.w;
+  }
+}
+template <class T> struct EpiBiasRelu { // out[i][j] = relu(acc*scale + bias[j]) -> T, ld % 16 == 0
+  T *out;
   const float *bias;
   int ld;
   float scale;
@@ -517,7 +567,7 @@ struct EpiBiasReluBf16 { // out[i][j] = relu(acc*scale + bias[j]) -> bf16, ld % 
 #pragma unroll
     for (int t = 0; t < 16; ++t)
       v[t] = fmaxf(fmaf(v[t], scale, __ldg(bias + j0 + t)), 0.0f);
-    store_bf16x16(out + (size_t)i * ld + j0, v);
+    store_x16(out + (size_t)i * ld + j0, v);
   }
 };
 struct EpiBiasF32 { // out[i][j] = acc + bias[j] -> fp32 (the FC layer has no activation)
@@ -533,47 +583,47 @@ struct EpiBiasF32 { // out[i][j] = acc + bias[j] -> fp32 (the FC layer has no ac
                          v[4 * t + 3] + __ldg(bias + j0 + 4 * t + 3));
   }
 };
-struct EpiReluMaskBf16 { // out[i][j] = y[i][j] > 0 ? acc : 0 -> bf16
-  bf16 *out;
-  const bf16 *y;
+template <class T> struct EpiReluMask { // out[i][j] = y[i][j] > 0 ? acc : 0 -> T
+  T *out;
+  const T *y;
   int ld;
   __device__ void operator()(int i, int j0, float (&v)[16], int) const {
     const size_t o = (size_t)i * ld + j0;
     float yy[16];
-    load_bf16x16(y + o, yy);
+    load_x16(y + o, yy);
 #pragma unroll
     for (int t = 0; t < 16; ++t)
       v[t] = yy[t] > 0.0f ? v[t] : 0.0f;
-    store_bf16x16(out + o, v);
+    store_x16(out + o, v);
   }
 };
-struct EpiReluMaskConv2 { // scatter parity class z back into NHWC [n,20,20,32]
-  bf16 *out;
-  const bf16 *y;
+template <class T> struct EpiReluMaskConv2 { // scatter parity class z back into NHWC [n,20,20,32]
+  T *out;
+  const T *y;
   __device__ void operator()(int i, int j0, float (&v)[16], int z) const {
     const int n = i / 100, pix = i - n * 100, qy = pix / 10, qx = pix - qy * 10;
     const size_t o = ((size_t)(n * 20 + 2 * qy + (z >> 1)) * 20 + 2 * qx + (z & 1)) * 32 + j0;
     float yy[16];
-    load_bf16x16(y + o, yy);
+    load_x16(y + o, yy);
 #pragma unroll
     for (int t = 0; t < 16; ++t)
       v[t] = yy[t] > 0.0f ? v[t] : 0.0f;
-    store_bf16x16(out + o, v);
+    store_x16(out + o, v);
   }
 };
-struct EpiReluMaskConv2All { // columns j = cls*32 + ci: all four parity classes of one (n,qy,qx) row
-  bf16 *out;
-  const bf16 *y;
+template <class T> struct EpiReluMaskConv2All { // columns j = cls*32 + ci: all four parity classes of one (n,qy,qx) row
+  T *out;
+  const T *y;
   __device__ void operator()(int i, int j0, float (&v)[16], int) const {
     const int n = i / 100, pix = i - n * 100, qy = pix / 10, qx = pix - qy * 10, cls = j0 >> 5;
     const size_t o =
         ((size_t)(n * 20 + 2 * qy + (cls >> 1)) * 20 + 2 * qx + (cls & 1)) * 32 + (j0 & 31);
     float yy[16];
-    load_bf16x16(y + o, yy);
+    load_x16(y + o, yy);
 #pragma unroll
     for (int t = 0; t < 16; ++t)
       v[t] = yy[t] > 0.0f ? v[t] : 0.0f;
-    store_bf16x16(out + o, v);
+    store_x16(out + o, v);
   }
 };
 struct EpiPartial { // ws[z][i][j] fp32, row length ldn (any), columns >= ldn skipped
@@ -709,33 +759,44 @@ __global__ void __launch_bounds__(256)
     }
   }
 }
-// column sums of dact1 [rows][32] bf16 (the conv1 bias gradient): block g sums its contiguous row
-// range -> bp[g][32].  A thread owns 8 channels (one 16-byte load) of every 64th row; the 64 row
-// lanes are combined in fixed order.
+// column sums of dact1 [rows][32] (the conv1 bias gradient): block g sums its contiguous row
+// range -> bp[g][32].  A thread owns one 16-byte chunk (8 bf16 / 4 fp32 channels) of every kLanes-th
+// row; the row lanes are combined in fixed order.
 constexpr int kBiasParts = 296;
+template <class T>
 __global__ void __launch_bounds__(256)
-    c1_bias_partial_kernel(const bf16 *__restrict__ dy, int64_t rows, float *__restrict__ bp) {
-  __shared__ float part[64][33];
+    c1_bias_partial_kernel(const T *__restrict__ dy, int64_t rows, float *__restrict__ bp) {
+  constexpr int kEPC = 16 / (int)sizeof(T), kCPR = 32 / kEPC, kLanes = 256 / kCPR;
+  __shared__ float part[kLanes][33];
   const int64_t per = (rows + gridDim.x - 1) / gridDim.x;
   const int64_t r0 = (int64_t)blockIdx.x * per, r1 = r0 + per < rows ? r0 + per : rows;
-  const int ch8 = threadIdx.x & 3, rl = threadIdx.x >> 2;
-  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  for (int64_t r = r0 + rl; r < r1; r += 64) {
-    const uint4 v = ldg16(dy + r * 32 + ch8 * 8);
-    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+  const int chk = threadIdx.x % kCPR, rl = threadIdx.x / kCPR;
+  float acc[kEPC];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) { // bf16 -> fp32: the bits are the upper half
-      acc[2 * j] += __uint_as_float(w[j] << 16);
-      acc[2 * j + 1] += __uint_as_float(w[j] & 0xFFFF0000u);
+  for (int j = 0; j < kEPC; ++j)
+    acc[j] = 0.f;
+  for (int64_t r = r0 + rl; r < r1; r += kLanes) {
+    const uint4 v = ldg16(dy + r * 32 + chk * kEPC);
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    if constexpr (sizeof(T) == 2) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { // bf16 -> fp32: the bits are the upper half
+        acc[2 * j] += __uint_as_float(w[j] << 16);
+        acc[2 * j + 1] += __uint_as_float(w[j] & 0xFFFF0000u);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        acc[j] += __uint_as_float(w[j]);
     }
   }
 #pragma unroll
-  for (int j = 0; j < 8; ++j)
-    part[rl][ch8 * 8 + j] = acc[j];
+  for (int j = 0; j < kEPC; ++j)
+    part[rl][chk * kEPC + j] = acc[j];
   __syncthreads();
   if (threadIdx.x < 32) {
     float t = 0.0f;
-    for (int g = 0; g < 64; ++g)
+    for (int g = 0; g < kLanes; ++g)
       t += part[g][threadIdx.x];
     bp[blockIdx.x * 32 + threadIdx.x] = t;
   }
@@ -754,15 +815,15 @@ void plan_splits(int64_t R, int64_t tiles, size_t per_split_floats, size_t ws_fl
 }
 
 // conv weight gradient: ws[z][k][co] partials of  sum_m col(m,k) * dY[m][co], then fixed-order sum
-template <class Col, int K, int C>
-int conv_wgrad(const Col &col, const bf16 *dy, int64_t Mtot, float scale, float *gw, float *gb,
+template <class T, class Col, int K, int C>
+int conv_wgrad(const Col &col, const T *dy, int64_t Mtot, float scale, float *gw, float *gb,
                float *ws, size_t ws_floats, cudaStream_t s, bool conv1_perm = false) {
   const int64_t mtiles = ceil_div(K + 1, tc::BM);
   const size_t per = (size_t)(K + 1) * C;
   ALEGPU_REQUIRE(ws_floats >= per, ALEGPU_RUNTIME_ERROR, "wgrad: workspace too small");
   int splits, rps;
   plan_splits(Mtot, mtiles, per, ws_floats, &splits, &rps);
-  if (int rc = tc::launch_gemm_tc<64, 4>(ColMN<Col, K>{col}, ColsMN{dy, C},
+  if (int rc = tc::launch_gemm_tc<64, 4>(ColMN<Col, K>{col}, ColsMN<T>{dy, C},
                                          EpiPartial{ws, K + 1, C}, K + 1, C, Mtot, splits, rps, s))
     return rc;
   static_assert(C % 32 == 0, "channel count must be a multiple of 32");
@@ -777,7 +838,8 @@ int conv_wgrad(const Col &col, const bf16 *dy, int64_t Mtot, float scale, float 
 // tile, split over the reduction (n*441 blocks); partials + bias partials summed in fixed order.
 // The bias column sums run on stream `w` (the wgrad side stream) next to the GEMM; `join` (may be
 // null when w == s) is recorded after them and awaited before the final reduction.
-int conv1_wgrad_s2d(const bf16 *s2d, const bf16 *dy, int64_t n, float scale, float *gw, float *gb,
+template <class T>
+int conv1_wgrad_s2d(const T *s2d, const T *dy, int64_t n, float scale, float *gw, float *gb,
                     float *ws, size_t ws_floats, cudaStream_t s, cudaStream_t w, cudaEvent_t join) {
   constexpr size_t per = 128 * 64;
   const size_t bias_floats = (size_t)kBiasParts * 32;
@@ -787,11 +849,11 @@ int conv1_wgrad_s2d(const bf16 *s2d, const bf16 *dy, int64_t n, float scale, flo
   // one output tile: up to 148 splits (one CTA per SM).  Measured per iteration, v0 / v1: 296 splits
   // 2.41 / 6.84 ms, 148 splits 2.32 / 6.82 ms, 74 splits 2.36 / 6.90 ms, 37 splits 2.58 / 8.07 ms
   plan_splits(n * 441, 2, per, ws_floats - bias_floats, &splits, &rps);
-  c1_bias_partial_kernel<<<kBiasParts, 256, 0, w>>>(dy, n * 400, bp);
+  c1_bias_partial_kernel<T><<<kBiasParts, 256, 0, w>>>(dy, n * 400, bp);
   ALEGPU_COUNT_LAUNCH();
   if (join)
     ALEGPU_CUDA_CHECK(cudaEventRecord(join, w));
-  if (int rc = tc::launch_gemm_tc<64, 4>(DYShift{dy}, ColsMN{s2d, 64}, EpiPartial{ws, 128, 64}, 128,
+  if (int rc = tc::launch_gemm_tc<64, 4>(DYShift<T>{dy}, ColsMN<T>{s2d, 64}, EpiPartial{ws, 128, 64}, 128,
                                          64, n * 441, splits, rps, s))
     return rc;
   if (join)
@@ -808,11 +870,13 @@ __global__ void bf16_to_f32_kernel(const bf16 *__restrict__ src, float *__restri
     dst[i] = __bfloat162float(src[i]);
 }
 
-// u8 NCHW [n,4,84,84] -> bf16 space-to-depth NHWC [n,21,21,64] (u8 is exact in bf16).  One thread = 4 pixels of one
-// row: four coalesced 4-byte loads (one per channel plane), one 32-byte store.  HBM-bound:
-// 28 224 B read + 56 448 B written per observation, once per train() (not per epoch / minibatch).
+// u8 NCHW [n,4,84,84] -> space-to-depth NHWC [n,21,21,64] in the operand type T (bf16, or fp32 for
+// the tf32 path; u8 is exact in both).  One thread = 4 pixels of one row: four coalesced 4-byte loads
+// (one per channel plane), one 32-byte (bf16) / 64-byte (fp32) store.  HBM-bound: 28 224 B read +
+// 56 448 / 112 896 B written per observation, once per train() (not per epoch / minibatch).
+template <class T>
 __global__ void __launch_bounds__(256)
-    obs_to_s2d_bf16_kernel(const uint8_t *__restrict__ obs, bf16 *__restrict__ out, int64_t total) {
+    obs_to_s2d_kernel(const uint8_t *__restrict__ obs, T *__restrict__ out, int64_t total) {
   // total = n * 84 * 21 work items (n, y, x4)
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (int64_t)gridDim.x * blockDim.x) {
@@ -825,39 +889,54 @@ __global__ void __launch_bounds__(256)
 #pragma unroll
     for (int c = 0; c < 4; ++c)
       w[c] = __ldg(reinterpret_cast<const uint32_t *>(src + c * 7056));
-    uint32_t o[8]; // pixel j: channels 0..3 -> two packed bf16 pairs
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const uint32_t sel = 0x0040u + (uint32_t)j * 0x0011u; // byte j of the 1st, byte j of the 2nd
-      const uint32_t px = (__byte_perm(w[0], w[1], sel) & 0xFFFFu) |               // c0, c1
-                          (__byte_perm(w[2], w[3], sel) << 16);                    // c2, c3
-      // px bytes = (c0, c1, c2, c3) of pixel j
-      uint32_t lo, hi;
-      u8x4_to_bf16(px, lo, hi);
-      o[2 * j] = lo;
-      o[2 * j + 1] = hi;
-    }
     // space-to-depth: block (Y, X) = (y/4, x4), channel = (y&3)*16 + s*4 + c, s = pixel j of the four
-    uint4 *dst = reinterpret_cast<uint4 *>(out + (((size_t)n * 21 + (y >> 2)) * 21 + x4) * 64 + (y & 3) * 16);
-    dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
-    dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+    T *dstp = out + (((size_t)n * 21 + (y >> 2)) * 21 + x4) * 64 + (y & 3) * 16;
+    if constexpr (sizeof(T) == 2) {
+      uint32_t o[8]; // pixel j: channels 0..3 -> two packed bf16 pairs
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const uint32_t sel = 0x0040u + (uint32_t)j * 0x0011u; // byte j of the 1st, byte j of the 2nd
+        const uint32_t px = (__byte_perm(w[0], w[1], sel) & 0xFFFFu) |               // c0, c1
+                            (__byte_perm(w[2], w[3], sel) << 16);                    // c2, c3
+        // px bytes = (c0, c1, c2, c3) of pixel j
+        uint32_t lo, hi;
+        u8x4_to_bf16(px, lo, hi);
+        o[2 * j] = lo;
+        o[2 * j + 1] = hi;
+      }
+      uint4 *dst = reinterpret_cast<uint4 *>(dstp);
+      dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+      dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+    } else {
+      float4 *dst = reinterpret_cast<float4 *>(dstp);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) // pixel j: channels 0..3 as fp32 (exact)
+        dst[j] = make_float4((float)((w[0] >> (8 * j)) & 0xFFu), (float)((w[1] >> (8 * j)) & 0xFFu),
+                             (float)((w[2] >> (8 * j)) & 0xFFu), (float)((w[3] >> (8 * j)) & 0xFFu));
+    }
   }
 }
-// c1w bf16 [32][256] OIHW order -> [32][256] in Col1N's k' order
-__global__ void permute_c1w_kernel(const bf16 *__restrict__ w, bf16 *__restrict__ out) {
+// c1w [32][256] OIHW order -> [32][256] in Col1N's k' order
+template <class T> __global__ void permute_c1w_kernel(const T *__restrict__ w, T *__restrict__ out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < 32 * 256) {
     const int co = i >> 8, kp = i & 255;
     out[i] = w[co * 256 + conv1_k_of_kprime(kp)];
   }
 }
+// fp32 -> tf32-rounded fp32 (the weight shadow of the tf32 path)
+__global__ void f32_round_tf32_kernel(const float *__restrict__ src, float *__restrict__ dst, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    dst[i] = round_tf32(src[i]);
+}
 
-struct Shadow { // bf16 views of the flat parameter buffer (same offsets as NetParams)
-  const bf16 *c1w, *c2w, *c3w, *fcw;
+template <class T> struct Shadow { // operand-type views of the flat parameter buffer (same offsets as NetParams)
+  const T *c1w, *c2w, *c3w, *fcw;
 };
-Shadow shadow_view(const TcState &T, const NetParams &P) {
-  const bf16 *base = static_cast<const bf16 *>(T.w_shadow);
-  Shadow s;
+template <class T> Shadow<T> shadow_view(const TcState &S, const NetParams &P) {
+  const T *base = static_cast<const T *>(S.w_shadow);
+  Shadow<T> s;
   s.c1w = base + (P.c1w - P.c1w);
   s.c2w = base + (P.c2w - P.c1w);
   s.c3w = base + (P.c3w - P.c1w);
@@ -885,8 +964,9 @@ EncodeIm2colFn encode_im2col_fn() {
   }();
   return fn;
 }
-// map slot <- NHWC bf16 tensor [N,H,W,64] at `base`, pixel box [lower, dim + upper) in both axes,
-// 128 pixels x 64 channels per load, 128-byte swizzle, zeros outside
+// map slot <- NHWC tensor [N,H,W,64] of eb-byte elements at `base`, pixel box [lower, dim + upper) in
+// both axes, 128 pixels x one 128-byte row of channels (64 bf16 / 32 fp32) per load, 128-byte swizzle,
+// zeros outside
 int set_im2col_map(TcState &T, int slot, void *base, int H, int W, int64_t N, int lower, int upper,
                    int upper_h = 1 << 30, int stride_h = 1) {
   if (upper_h == (1 << 30))
@@ -894,12 +974,14 @@ int set_im2col_map(TcState &T, int slot, void *base, int H, int W, int64_t N, in
   EncodeIm2colFn fn = encode_im2col_fn();
   ALEGPU_REQUIRE(fn != nullptr, ALEGPU_RUNTIME_ERROR, "cuTensorMapEncodeIm2col is not available");
   alignas(64) CUtensorMap m;
+  const cuuint64_t eb = (cuuint64_t)T.elem_bytes, px = 64 * eb;
   const cuuint64_t dims[4] = {64, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
-  const cuuint64_t strides[3] = {128, (cuuint64_t)W * 128, (cuuint64_t)H * W * 128};
+  const cuuint64_t strides[3] = {px, (cuuint64_t)W * px, (cuuint64_t)H * W * px};
   const int lo[2] = {lower, lower}, hi[2] = {upper, upper_h};
   const cuuint32_t estr[4] = {1, 1, (cuuint32_t)stride_h, 1};
-  const CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, base, dims, strides, lo, hi, 64, 128,
-                        estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+  const CUresult r = fn(&m, eb == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16,
+                        4, base, dims, strides, lo, hi, (cuuint32_t)(128 / eb), 128, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                         CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   ALEGPU_REQUIRE(r == CUDA_SUCCESS, ALEGPU_RUNTIME_ERROR,
                  "cuTensorMapEncodeIm2col failed: " + std::to_string((int)r));
@@ -912,28 +994,33 @@ const void *tmap(const TcState &T, int slot) { return (const CUtensorMap *)T.tma
 
 // ---- public (net_tc.h) ----------------------------------------------------------------------------
 int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_t Ppad,
-                cudaStream_t) {
+                int elem_bytes, cudaStream_t) {
   ALEGPU_REQUIRE(hidden % 16 == 0, ALEGPU_INVALID_ARGUMENT,
                  "the tensor-core path needs hidden_size % 16 == 0");
+  ALEGPU_REQUIRE(elem_bytes == 2 || elem_bytes == 4, ALEGPU_INVALID_ARGUMENT,
+                 "tensor-core operands are bf16 (2 bytes) or tf32 (4 bytes)");
   T.hidden = hidden;
   T.actions = actions;
   T.cap = cap;
   T.Ppad = Ppad;
+  T.elem_bytes = elem_bytes;
+  const size_t eb = (size_t)elem_bytes;
   auto alloc = [](void **p, size_t bytes) -> int {
     ALEGPU_CUDA_CHECK(cudaMalloc(p, bytes ? bytes : 16));
     ALEGPU_CUDA_CHECK(cudaMemset(*p, 0, bytes ? bytes : 16));
     return ALEGPU_OK;
   };
-  if (int rc = alloc(&T.w_shadow, sizeof(bf16) * (size_t)Ppad)) return rc;
-  if (int rc = alloc(&T.c1w_perm, sizeof(bf16) * 32 * 256)) return rc;
-  if (int rc = alloc(&T.obs16_mb, sizeof(bf16) * (size_t)cap * 28224)) return rc;
-  if (int rc = alloc(&T.act1, sizeof(bf16) * (size_t)cap * 12800)) return rc;
-  if (int rc = alloc(&T.act2, sizeof(bf16) * (size_t)cap * 5184)) return rc;
-  if (int rc = alloc(&T.act3, sizeof(bf16) * (size_t)cap * 3136)) return rc;
-  if (int rc = alloc(&T.dact1, sizeof(bf16) * (size_t)cap * 12800)) return rc;
-  if (int rc = alloc(&T.dact2, sizeof(bf16) * (size_t)cap * 5184)) return rc;
-  if (int rc = alloc(&T.dact3, sizeof(bf16) * (size_t)cap * 3136)) return rc;
-  if (int rc = alloc(&T.dfc16, sizeof(bf16) * (size_t)cap * hidden)) return rc;
+  if (int rc = alloc(&T.w_shadow, eb * (size_t)Ppad)) return rc;
+  if (int rc = alloc(&T.c1w_perm, eb * 32 * 256)) return rc;
+  if (int rc = alloc(&T.obs16_mb, eb * (size_t)cap * 28224)) return rc;
+  if (int rc = alloc(&T.act1, eb * (size_t)cap * 12800)) return rc;
+  if (int rc = alloc(&T.act2, eb * (size_t)cap * 5184)) return rc;
+  if (int rc = alloc(&T.act3, eb * (size_t)cap * 3136)) return rc;
+  if (int rc = alloc(&T.dact1, eb * (size_t)cap * 12800)) return rc;
+  if (int rc = alloc(&T.dact2, eb * (size_t)cap * 5184)) return rc;
+  if (int rc = alloc(&T.dact3, eb * (size_t)cap * 3136)) return rc;
+  if (elem_bytes == 2) // tf32: the tensor core reads the (tf32-rounded) fp32 dfc itself
+    if (int rc = alloc(&T.dfc16, eb * (size_t)cap * hidden)) return rc;
   T.ws_heads_n = (size_t)(actions + 1) * (hidden + 1) * 2 * kNumSMs;
   T.ws_fc_n = (size_t)hidden * 3137 * 2;
   T.ws_c3_n = (size_t)577 * 64 * 64;
@@ -949,10 +1036,10 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
     ALEGPU_CUDA_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
   const char *env = getenv("ALEGPU_TC_SERIAL");
   T.serial = env && env[0] == '1';
-  env = getenv("ALEGPU_CONV1_U8");
-  T.conv1_u8 = env && env[0] == '1';
+  env = getenv("ALEGPU_CONV1_U8"); // the u8 register producers convert to bf16: bf16 mode only
+  T.conv1_u8 = env && env[0] == '1' && elem_bytes == 2;
   env = getenv("ALEGPU_CONV1_WGRAD_U8");
-  T.conv1_wgrad_u8 = env && env[0] == '1';
+  T.conv1_wgrad_u8 = env && env[0] == '1' && elem_bytes == 2;
   env = getenv("ALEGPU_NO_TMA");
   T.use_tma = !(env && env[0] == '1');
   if (T.use_tma) {
@@ -981,29 +1068,38 @@ void net_tc_destroy(TcState &T) {
 }
 
 int net_tc_refresh_weights(TcState &T, const float *params, int64_t Ppad, cudaStream_t s) {
-  if (int rc = launch_f32_to_bf16(params, T.w_shadow, Ppad, s))
-    return rc;
-  permute_c1w_kernel<<<32, 256, 0, s>>>((const bf16 *)T.w_shadow, (bf16 *)T.c1w_perm); // c1w is first
+  if (T.elem_bytes == 4) {
+    f32_round_tf32_kernel<<<kNumSMs * 2, 256, 0, s>>>(params, (float *)T.w_shadow, Ppad);
+    ALEGPU_COUNT_LAUNCH();
+    permute_c1w_kernel<float><<<32, 256, 0, s>>>((const float *)T.w_shadow, (float *)T.c1w_perm);
+  } else {
+    if (int rc = launch_f32_to_bf16(params, T.w_shadow, Ppad, s))
+      return rc;
+    permute_c1w_kernel<bf16><<<32, 256, 0, s>>>((const bf16 *)T.w_shadow, (bf16 *)T.c1w_perm); // c1w is first
+  }
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
   return ALEGPU_OK;
 }
 
 namespace {
-int convert_obs(const uint8_t *obs, int64_t n, void *out, cudaStream_t s) {
+int convert_obs(const TcState &T, const uint8_t *obs, int64_t n, void *out, cudaStream_t s) {
   const int64_t total = n * 84 * 21;
   if (total == 0)
     return ALEGPU_OK;
   const int blocks = (int)std::min<int64_t>(ceil_div(total, 256), (int64_t)kNumSMs * 16);
-  obs_to_s2d_bf16_kernel<<<blocks, 256, 0, s>>>(obs, (bf16 *)out, total);
+  if (T.elem_bytes == 4)
+    obs_to_s2d_kernel<float><<<blocks, 256, 0, s>>>(obs, (float *)out, total);
+  else
+    obs_to_s2d_kernel<bf16><<<blocks, 256, 0, s>>>(obs, (bf16 *)out, total);
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
   return ALEGPU_OK;
 }
-constexpr int64_t kObs16MaxRows = (int64_t)1 << 17; // 131 072 rows = 7.4 GB of bf16 observations
+constexpr int64_t kObs16MaxRows = (int64_t)1 << 17; // 131 072 rows = 7.4 GB of bf16 (14.8 GB of fp32) observations
 } // namespace
 
-// allocation only (never inside a stream capture): room for n rows of bf16 observations
+// allocation only (never inside a stream capture): room for n rows of operand-type observations
 int net_tc_reserve_obs(TcState &T, int64_t n) {
   if (T.conv1_u8 || n > kObs16MaxRows || T.obs16_all_rows >= n)
     return ALEGPU_OK;
@@ -1011,7 +1107,7 @@ int net_tc_reserve_obs(TcState &T, int64_t n) {
     ALEGPU_CUDA_CHECK(cudaFree(T.obs16_all));
   T.obs16_all = nullptr;
   T.obs16_all_rows = 0;
-  ALEGPU_CUDA_CHECK(cudaMalloc(&T.obs16_all, sizeof(bf16) * (size_t)n * 28224));
+  ALEGPU_CUDA_CHECK(cudaMalloc(&T.obs16_all, (size_t)T.elem_bytes * (size_t)n * 28224));
   T.obs16_all_rows = n;
   if (T.use_tma) {
     T.obs_all_map = (T.obs_all_map + 1) % kMapObsAllSlots;
@@ -1025,59 +1121,65 @@ int net_tc_prepare_obs(TcState &T, const uint8_t *obs, int64_t n, const void **o
   *obs16 = nullptr;
   if (T.conv1_u8 || T.obs16_all_rows < n)
     return ALEGPU_OK; // not reserved (too big to keep): the forward converts per minibatch
-  if (int rc = convert_obs(obs, n, T.obs16_all, s))
+  if (int rc = convert_obs(T, obs, n, T.obs16_all, s))
     return rc;
   *obs16 = T.obs16_all;
   return ALEGPU_OK;
 }
 
-int net_tc_forward(const NetParams &P, TcState &T, const uint8_t *obs, int64_t n, NetActs &A,
-                   cudaStream_t s, const void *obs16) {
+namespace {
+template <class T>
+int forward_impl(const NetParams &P, TcState &S, const uint8_t *obs, int64_t n, NetActs &A,
+                 cudaStream_t s, const void *obs16) {
   const int H = (int)P.hidden;
-  const Shadow W = shadow_view(T, P);
-  bf16 *act1 = (bf16 *)T.act1, *act2 = (bf16 *)T.act2, *act3 = (bf16 *)T.act3;
-  if (T.conv1_u8) { // A/B switch: conv1 straight from the u8 observations (register producers)
-    if (int rc = tc::launch_gemm_tc<32, 4>(ColK<Col1>{Col1{obs}}, RowsK{W.c1w, 256},
-                                           EpiBiasReluBf16{act1, P.c1b, 32, 1.0f / 255.0f},
-                                           n * 400, 32, 256, 1, 0, s))
-      return rc;
-  } else {
-    if (!obs16) {
-      if (int rc = convert_obs(obs, n, T.obs16_mb, s))
-        return rc;
-      obs16 = T.obs16_mb;
-    }
-    const bf16 *x16 = (const bf16 *)obs16, *all = (const bf16 *)T.obs16_all;
-    const bool in_all = all && x16 >= all && x16 < all + (size_t)T.obs16_all_rows * 28224;
-    if (T.use_tma && (x16 == (const bf16 *)T.obs16_mb || in_all)) {
-      const Col1Tma a{tmap(T, in_all ? kMapObsAll + T.obs_all_map : kMapObsMb),
-                      in_all ? (int)((x16 - all) / 28224) : 0};
-      if (int rc = tc::launch_gemm_tc<32, 4>(a, RowsK{(const bf16 *)T.c1w_perm, 256},
-                                             EpiBiasReluBf16{act1, P.c1b, 32, 1.0f / 255.0f},
+  const Shadow<T> W = shadow_view<T>(S, P);
+  T *act1 = (T *)S.act1, *act2 = (T *)S.act2, *act3 = (T *)S.act3;
+  if constexpr (sizeof(T) == 2) {
+    if (S.conv1_u8) { // A/B switch: conv1 straight from the u8 observations (register producers)
+      if (int rc = tc::launch_gemm_tc<32, 4>(ColK<Col1>{Col1{obs}}, RowsK<T>{W.c1w, 256},
+                                             EpiBiasRelu<T>{act1, P.c1b, 32, 1.0f / 255.0f},
                                              n * 400, 32, 256, 1, 0, s))
         return rc;
-    } else if (int rc = tc::launch_gemm_tc<32, 4>(ColK<Col1N>{Col1N{(const bf16 *)obs16}},
-                                           RowsK{(const bf16 *)T.c1w_perm, 256},
-                                           EpiBiasReluBf16{act1, P.c1b, 32, 1.0f / 255.0f},
-                                           n * 400, 32, 256, 1, 0, s))
+      obs16 = nullptr;
+    }
+  }
+  if (!S.conv1_u8) {
+    if (!obs16) {
+      if (int rc = convert_obs(S, obs, n, S.obs16_mb, s))
+        return rc;
+      obs16 = S.obs16_mb;
+    }
+    const T *x16 = (const T *)obs16, *all = (const T *)S.obs16_all;
+    const bool in_all = all && x16 >= all && x16 < all + (size_t)S.obs16_all_rows * 28224;
+    if (S.use_tma && (x16 == (const T *)S.obs16_mb || in_all)) {
+      const Col1Tma<T> a{tmap(S, in_all ? kMapObsAll + S.obs_all_map : kMapObsMb),
+                         in_all ? (int)((x16 - all) / 28224) : 0};
+      if (int rc = tc::launch_gemm_tc<32, 4>(a, RowsK<T>{(const T *)S.c1w_perm, 256},
+                                             EpiBiasRelu<T>{act1, P.c1b, 32, 1.0f / 255.0f},
+                                             n * 400, 32, 256, 1, 0, s))
+        return rc;
+    } else if (int rc = tc::launch_gemm_tc<32, 4>(ColK<Col1N<T>>{Col1N<T>{x16}},
+                                                  RowsK<T>{(const T *)S.c1w_perm, 256},
+                                                  EpiBiasRelu<T>{act1, P.c1b, 32, 1.0f / 255.0f},
+                                                  n * 400, 32, 256, 1, 0, s))
       return rc;
   }
-  if (T.use_tma) {
-    if (int rc = tc::launch_gemm_tc<64, 4>(Col2Tma{tmap(T, kMapAct1), 0}, RowsK{W.c2w, 512},
-                                           EpiBiasReluBf16{act2, P.c2b, 64, 1.0f}, n * 81, 64, 512,
+  if (S.use_tma) {
+    if (int rc = tc::launch_gemm_tc<64, 4>(Col2Tma<T>{tmap(S, kMapAct1), 0}, RowsK<T>{W.c2w, 512},
+                                           EpiBiasRelu<T>{act2, P.c2b, 64, 1.0f}, n * 81, 64, 512,
                                            1, 0, s))
       return rc;
-  } else if (int rc = tc::launch_gemm_tc<64, 4>(ColK<Col2>{Col2{act1}}, RowsK{W.c2w, 512},
-                                                EpiBiasReluBf16{act2, P.c2b, 64, 1.0f}, n * 81, 64,
+  } else if (int rc = tc::launch_gemm_tc<64, 4>(ColK<Col2<T>>{Col2<T>{act1}}, RowsK<T>{W.c2w, 512},
+                                                EpiBiasRelu<T>{act2, P.c2b, 64, 1.0f}, n * 81, 64,
                                                 512, 1, 0, s))
     return rc;
-  if (T.use_tma) {
-    if (int rc = tc::launch_gemm_tc<64, 4>(Col3Tma{tmap(T, kMapAct2), 0}, RowsK{W.c3w, 576},
-                                           EpiBiasReluBf16{act3, P.c3b, 64, 1.0f}, n * 49, 64, 576,
+  if (S.use_tma) {
+    if (int rc = tc::launch_gemm_tc<64, 4>(Col3Tma<T>{tmap(S, kMapAct2), 0}, RowsK<T>{W.c3w, 576},
+                                           EpiBiasRelu<T>{act3, P.c3b, 64, 1.0f}, n * 49, 64, 576,
                                            1, 0, s))
       return rc;
-  } else if (int rc = tc::launch_gemm_tc<64, 4>(ColK<Col3>{Col3{act2}}, RowsK{W.c3w, 576},
-                                                EpiBiasReluBf16{act3, P.c3b, 64, 1.0f}, n * 49, 64,
+  } else if (int rc = tc::launch_gemm_tc<64, 4>(ColK<Col3<T>>{Col3<T>{act2}}, RowsK<T>{W.c3w, 576},
+                                                EpiBiasRelu<T>{act3, P.c3b, 64, 1.0f}, n * 49, 64,
                                                 576, 1, 0, s))
     return rc;
   // FC: with few output tiles (small minibatch) the 3136-long reduction is split over CTAs and
@@ -1089,7 +1191,7 @@ int net_tc_forward(const NetParams &P, TcState &T, const uint8_t *obs, int64_t n
     splits = std::max(splits, 1);
     const int rps = (int)(ceil_div(ceil_div(3136, splits), tc::BK) * tc::BK);
     splits = (int)ceil_div(3136, rps);
-    if (int rc = tc::launch_gemm_tc<64, 4>(RowsK{act3, 3136}, RowsK{W.fcw, 3136},
+    if (int rc = tc::launch_gemm_tc<64, 4>(RowsK<T>{act3, 3136}, RowsK<T>{W.fcw, 3136},
                                            EpiPartial{A.fc_ws, (int)n, H}, n, H, 3136, splits, rps, s))
       return rc;
     const int64_t total4 = n * H / 4;
@@ -1100,132 +1202,159 @@ int net_tc_forward(const NetParams &P, TcState &T, const uint8_t *obs, int64_t n
     ALEGPU_LAUNCH_CHECK();
     return ALEGPU_OK;
   }
-  return tc::launch_gemm_tc<128, 3>(RowsK{act3, 3136}, RowsK{W.fcw, 3136},
+  return tc::launch_gemm_tc<128, 3>(RowsK<T>{act3, 3136}, RowsK<T>{W.fcw, 3136},
                                     EpiBiasF32{A.fc, P.fcb, H}, n, H, 3136, 1, 0, s);
 }
 
 // A.dfc [n,H] fp32 is d loss / d fc-output and A.dout the head gradients (heads.cu).  Fills every
 // gradient.  Two branches: the data-gradient chain fc -> conv3 -> conv2 (+ conv1's weight gradient)
-// on `s`, and the other weight gradients on T.side as soon as their inputs exist.
-int net_tc_backward(const NetParams &P, const NetParams &G, TcState &T, const uint8_t *obs,
-                    int64_t n, NetActs &A, cudaStream_t s, const void *obs16) {
+// on `s`, and the other weight gradients on S.side as soon as their inputs exist.
+template <class T>
+int backward_impl(const NetParams &P, const NetParams &G, TcState &S, const uint8_t *obs,
+                  int64_t n, NetActs &A, cudaStream_t s, const void *obs16) {
   const int H = (int)P.hidden;
-  const Shadow W = shadow_view(T, P);
-  bf16 *act1 = (bf16 *)T.act1, *act2 = (bf16 *)T.act2, *act3 = (bf16 *)T.act3;
-  bf16 *dact1 = (bf16 *)T.dact1, *dact2 = (bf16 *)T.dact2, *dact3 = (bf16 *)T.dact3;
-  const bf16 *dfc16 = (const bf16 *)T.dfc16; // bf16 copy of A.dfc written by the heads kernel
-  cudaStream_t w = T.serial ? s : T.side;
-  if (!T.serial) {
-    ALEGPU_CUDA_CHECK(cudaEventRecord(T.ev_fork, s));
-    ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(w, T.ev_fork, 0));
+  const Shadow<T> W = shadow_view<T>(S, P);
+  T *act1 = (T *)S.act1, *act2 = (T *)S.act2, *act3 = (T *)S.act3;
+  T *dact1 = (T *)S.dact1, *dact2 = (T *)S.dact2, *dact3 = (T *)S.dact3;
+  // bf16: the copy of A.dfc written by the heads kernel; tf32: A.dfc itself (tf32-rounded there)
+  const T *dfcT = sizeof(T) == 2 ? (const T *)S.dfc16 : (const T *)A.dfc;
+  cudaStream_t w = S.serial ? s : S.side;
+  if (!S.serial) {
+    ALEGPU_CUDA_CHECK(cudaEventRecord(S.ev_fork, s));
+    ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(w, S.ev_fork, 0));
   }
   // ---- side: heads + FC weight gradients (need only dout / dfc / act3)
-  if (int rc = heads_wgrad(G, A, n, T.ws_heads, T.ws_heads_n, w))
+  if (int rc = heads_wgrad(G, A, n, S.ws_heads, S.ws_heads_n, w))
     return rc;
   {
     const int64_t tiles = ceil_div(H, tc::BM) * ceil_div(3137, 128);
     const size_t per = (size_t)H * 3137;
     int splits, rps;
-    plan_splits(n, tiles, per, T.ws_fc_n, &splits, &rps);
+    plan_splits(n, tiles, per, S.ws_fc_n, &splits, &rps);
     if (n <= 1024)
       splits = 1, rps = 0; // 100 output tiles already fill the chip; skip the partial round trip
     if (splits == 1) { // [H][3136 | bias] = dfc^T . [act3 | 1]
-      if (int rc = tc::launch_gemm_tc<128, 3>(ColsMN{dfc16, H}, ColsMN{act3, 3136},
+      if (int rc = tc::launch_gemm_tc<128, 3>(ColsMN<T>{dfcT, H}, ColsMN<T>{act3, 3136},
                                               EpiWgradDirect{G.fcw, G.fcb, 3136}, H, 3137, n, 1, 0, w))
         return rc;
     } else {
-      if (int rc = tc::launch_gemm_tc<128, 3>(ColsMN{dfc16, H}, ColsMN{act3, 3136},
-                                              EpiPartial{T.ws_fc, H, 3137}, H, 3137, n, splits, rps, w))
+      if (int rc = tc::launch_gemm_tc<128, 3>(ColsMN<T>{dfcT, H}, ColsMN<T>{act3, 3136},
+                                              EpiPartial{S.ws_fc, H, 3137}, H, 3137, n, splits, rps, w))
         return rc;
       const int blocks = (int)std::min<int64_t>(ceil_div((int64_t)per, 256), 4 * kNumSMs);
-      reduce_wgrad_kernel<<<blocks, 256, 0, w>>>(T.ws_fc, splits, H, 3136, G.fcw, G.fcb);
+      reduce_wgrad_kernel<<<blocks, 256, 0, w>>>(S.ws_fc, splits, H, 3136, G.fcw, G.fcb);
       ALEGPU_COUNT_LAUNCH();
       ALEGPU_LAUNCH_CHECK();
     }
   }
-  if (!T.serial) // the FC + heads gradients (95 % of the bytes) can already be exchanged
-    ALEGPU_CUDA_CHECK(cudaEventRecord(T.ev_fcw, w));
+  if (!S.serial) // the FC + heads gradients (95 % of the bytes) can already be exchanged
+    ALEGPU_CUDA_CHECK(cudaEventRecord(S.ev_fcw, w));
   // ---- main: FC dgrad: dact3 = (dfc . fcw) * relu'(act3)
   if (ceil_div(n, tc::BM) * 25 < kNumSMs) { // small minibatch: narrower tiles, twice the CTAs
-    if (int rc = tc::launch_gemm_tc<64, 4>(RowsK{dfc16, H}, ColsMN{W.fcw, 3136},
-                                           EpiReluMaskBf16{dact3, act3, 3136}, n, 3136, H, 1, 0, s))
+    if (int rc = tc::launch_gemm_tc<64, 4>(RowsK<T>{dfcT, H}, ColsMN<T>{W.fcw, 3136},
+                                           EpiReluMask<T>{dact3, act3, 3136}, n, 3136, H, 1, 0, s))
       return rc;
-  } else if (int rc = tc::launch_gemm_tc<128, 3>(RowsK{dfc16, H}, ColsMN{W.fcw, 3136},
-                                                 EpiReluMaskBf16{dact3, act3, 3136}, n, 3136, H, 1,
+  } else if (int rc = tc::launch_gemm_tc<128, 3>(RowsK<T>{dfcT, H}, ColsMN<T>{W.fcw, 3136},
+                                                 EpiReluMask<T>{dact3, act3, 3136}, n, 3136, H, 1,
                                                  0, s))
     return rc;
-  if (!T.serial) {
-    ALEGPU_CUDA_CHECK(cudaEventRecord(T.ev_d3, s));
-    ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(w, T.ev_d3, 0));
+  if (!S.serial) {
+    ALEGPU_CUDA_CHECK(cudaEventRecord(S.ev_d3, s));
+    ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(w, S.ev_d3, 0));
   }
   // ---- side: conv3 wgrad (needs dact3)
-  if (int rc = conv_wgrad<Col3, 576, 64>(Col3{act2}, dact3, n * 49, 1.0f, G.c3w, G.c3b, T.ws_c3,
-                                         T.ws_c3_n, w))
+  if (int rc = conv_wgrad<T, Col3<T>, 576, 64>(Col3<T>{act2}, dact3, n * 49, 1.0f, G.c3w, G.c3b,
+                                               S.ws_c3, S.ws_c3_n, w))
     return rc;
   // ---- main: conv3 dgrad
-  if (T.use_tma) {
-    if (int rc = tc::launch_gemm_tc<64, 4>(DCol3Tma{tmap(T, kMapDact3), 0}, W3T{W.c3w},
-                                           EpiReluMaskBf16{dact2, act2, 64}, n * 81, 64, 576, 1, 0, s))
+  if (S.use_tma) {
+    if (int rc = tc::launch_gemm_tc<64, 4>(DCol3Tma<T>{tmap(S, kMapDact3), 0}, W3T<T>{W.c3w},
+                                           EpiReluMask<T>{dact2, act2, 64}, n * 81, 64, 576, 1, 0, s))
       return rc;
-  } else if (int rc = tc::launch_gemm_tc<64, 4>(DCol3{dact3}, W3T{W.c3w},
-                                                EpiReluMaskBf16{dact2, act2, 64}, n * 81, 64, 576, 1,
+  } else if (int rc = tc::launch_gemm_tc<64, 4>(DCol3<T>{dact3}, W3T<T>{W.c3w},
+                                                EpiReluMask<T>{dact2, act2, 64}, n * 81, 64, 576, 1,
                                                 0, s))
     return rc;
-  if (!T.serial) {
-    ALEGPU_CUDA_CHECK(cudaEventRecord(T.ev_d2, s));
-    ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(w, T.ev_d2, 0));
+  if (!S.serial) {
+    ALEGPU_CUDA_CHECK(cudaEventRecord(S.ev_d2, s));
+    ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(w, S.ev_d2, 0));
   }
   // ---- side: conv2 wgrad (needs dact2)
-  if (int rc = conv_wgrad<Col2, 512, 64>(Col2{act1}, dact2, n * 81, 1.0f, G.c2w, G.c2b, T.ws_c2,
-                                         T.ws_c2_n, w))
+  if (int rc = conv_wgrad<T, Col2<T>, 512, 64>(Col2<T>{act1}, dact2, n * 81, 1.0f, G.c2w, G.c2b,
+                                               S.ws_c2, S.ws_c2_n, w))
     return rc;
-  if (!T.serial)
-    ALEGPU_CUDA_CHECK(cudaEventRecord(T.ev_join, w));
+  if (!S.serial)
+    ALEGPU_CUDA_CHECK(cudaEventRecord(S.ev_join, w));
   // ---- main: conv2 dgrad (the 4 parity classes of the stride-2 transposed convolution as 128 output
   // columns of ONE GEMM over the TMA-fetched 2x2-tap walk of dact2; cp.async fallback: 4 z-slices)
-  if (T.use_tma) {
-    if (int rc = tc::launch_gemm_tc<128, 3>(DCol2Tma{tmap(T, kMapDact2), 0}, W2TAll{W.c2w},
-                                            EpiReluMaskConv2All{dact1, act1}, n * 100, 128, 256, 1, 0,
+  if (S.use_tma) {
+    if (int rc = tc::launch_gemm_tc<128, 3>(DCol2Tma<T>{tmap(S, kMapDact2), 0}, W2TAll<T>{W.c2w},
+                                            EpiReluMaskConv2All<T>{dact1, act1}, n * 100, 128, 256, 1, 0,
                                             s))
       return rc;
-  } else if (int rc = tc::launch_gemm_tc<64, 4>(DCol2{dact2}, W2T{W.c2w},
-                                                EpiReluMaskConv2{dact1, act1}, n * 100, 32, 256, 4,
+  } else if (int rc = tc::launch_gemm_tc<64, 4>(DCol2<T>{dact2}, W2T<T>{W.c2w},
+                                                EpiReluMaskConv2<T>{dact1, act1}, n * 100, 32, 256, 4,
                                                 0, s))
     return rc;
   // conv1 (input needs no gradient); the 1/255 of the input scale lands on the weight gradient.
   // On the space-to-depth copy the observation operand is read once, un-expanded, and the four
   // taps become shifted views of dact1 (DYShift); ALEGPU_CONV1_WGRAD_U8=1 keeps the im2col form
-  // over the u8 observations (register producers) for A/B.
-  const bf16 *x16 = (const bf16 *)(obs16 ? obs16 : T.obs16_mb);
-  if (T.conv1_u8 || T.conv1_wgrad_u8 || !x16) {
-    if (int rc = conv_wgrad<Col1, 256, 32>(Col1{obs}, dact1, n * 400, 1.0f / 255.0f, G.c1w, G.c1b,
-                                           T.ws_c1, T.ws_c1_n, s))
-      return rc;
-  } else { // the forward of these rows left their bf16 copy in obs16_mb unless the caller has one
+  // over the u8 observations (register producers, bf16 mode only) for A/B.
+  const T *x16 = (const T *)(obs16 ? obs16 : S.obs16_mb);
+  bool done = false;
+  if constexpr (sizeof(T) == 2) {
+    if (S.conv1_u8 || S.conv1_wgrad_u8 || !x16) {
+      if (int rc = conv_wgrad<T, Col1, 256, 32>(Col1{obs}, dact1, n * 400, 1.0f / 255.0f, G.c1w,
+                                                G.c1b, S.ws_c1, S.ws_c1_n, s))
+        return rc;
+      done = true;
+    }
+  }
+  if (!done) { // the forward of these rows left their operand copy in obs16_mb unless the caller has one
     // the bias column sums run next to the GEMM on the side stream once dact1 exists — when they are
     // long enough to pay for the fork/join edges (measured: 7.72 -> 7.51 ms per v1 iteration at 1280
     // rows, but 2.51 -> 2.59 ms at v0's 256 rows, where they stay in front of the GEMM)
-    const bool fork = !T.serial && n > 512;
+    const bool fork = !S.serial && n > 512;
     if (fork) {
-      ALEGPU_CUDA_CHECK(cudaEventRecord(T.ev_d1, s));
-      ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(w, T.ev_d1, 0));
+      ALEGPU_CUDA_CHECK(cudaEventRecord(S.ev_d1, s));
+      ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(w, S.ev_d1, 0));
     }
-    if (int rc = conv1_wgrad_s2d(x16, dact1, n, 1.0f / 255.0f, G.c1w, G.c1b, T.ws_c1, T.ws_c1_n, s,
-                                 fork ? w : s, fork ? T.ev_join : nullptr))
+    if (int rc = conv1_wgrad_s2d<T>(x16, dact1, n, 1.0f / 255.0f, G.c1w, G.c1b, S.ws_c1, S.ws_c1_n,
+                                    s, fork ? w : s, fork ? S.ev_join : nullptr))
       return rc;
   }
-  if (!T.serial)
-    ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(s, T.ev_join, 0));
+  if (!S.serial)
+    ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(s, S.ev_join, 0));
   return ALEGPU_OK;
+}
+} // namespace
+
+int net_tc_forward(const NetParams &P, TcState &S, const uint8_t *obs, int64_t n, NetActs &A,
+                   cudaStream_t s, const void *obs16) {
+  if (S.elem_bytes == 4)
+    return forward_impl<float>(P, S, obs, n, A, s, obs16);
+  return forward_impl<bf16>(P, S, obs, n, A, s, obs16);
+}
+
+int net_tc_backward(const NetParams &P, const NetParams &G, TcState &S, const uint8_t *obs,
+                    int64_t n, NetActs &A, cudaStream_t s, const void *obs16) {
+  if (S.elem_bytes == 4)
+    return backward_impl<float>(P, G, S, obs, n, A, s, obs16);
+  return backward_impl<bf16>(P, G, S, obs, n, A, s, obs16);
 }
 
 int net_tc_fetch_activation(TcState &T, int which, int64_t n, float *host, cudaStream_t s) {
   const int64_t per = which == 1 ? 12800 : which == 2 ? 5184 : 3136;
-  const bf16 *src = (const bf16 *)(which == 1 ? T.act1 : which == 2 ? T.act2 : T.act3);
+  const void *src = which == 1 ? T.act1 : which == 2 ? T.act2 : T.act3;
   const int64_t total = n * per;
+  if (T.elem_bytes == 4) {
+    ALEGPU_CUDA_CHECK(cudaMemcpyAsync(host, src, sizeof(float) * total, cudaMemcpyDeviceToHost, s));
+    ALEGPU_CUDA_CHECK(cudaStreamSynchronize(s));
+    return ALEGPU_OK;
+  }
   if (!T.stage)
     ALEGPU_CUDA_CHECK(cudaMalloc(&T.stage, sizeof(float) * (size_t)T.cap * 12800));
-  bf16_to_f32_kernel<<<kNumSMs * 2, 256, 0, s>>>(src, T.stage, total);
+  bf16_to_f32_kernel<<<kNumSMs * 2, 256, 0, s>>>((const bf16 *)src, T.stage, total);
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
   ALEGPU_CUDA_CHECK(cudaMemcpyAsync(host, T.stage, sizeof(float) * total, cudaMemcpyDeviceToHost, s));
@@ -1297,12 +1426,32 @@ static int selftest_impl(const float *A, const float *B, float *C, int64_t M, in
   if (!rc)
     rc = launch_f32_to_bf16(B, b16, N * R, s);
   if (!rc) // ColsMN's ones row (i0 >= ld) is never requested here: rows < M == ld
-    rc = selftest_dispatch(RowsK{a16, (int)R}, ColsMN{a16, (int)M}, RowsK{b16, (int)R},
-                           ColsMN{b16, (int)N}, C, M, N, R, a_mn, b_mn, bn, z, rps, s);
+    rc = selftest_dispatch(RowsK<bf16>{a16, (int)R}, ColsMN<bf16>{a16, (int)M}, RowsK<bf16>{b16, (int)R},
+                           ColsMN<bf16>{b16, (int)N}, C, M, N, R, a_mn, b_mn, bn, z, rps, s);
   cudaStreamSynchronize(s);
   cudaFree(a16);
   cudaFree(b16);
   return rc;
+}
+
+// kind::tf32: the fp32 inputs are read as they are by the cp.async producers (the tensor core uses the
+// upper 19 bits of every element); contiguous dimensions must be multiples of 4
+extern "C" int alegpu_selftest_tc_gemm_tf32(const float *A, const float *B, float *C, int64_t M,
+                                            int64_t N, int64_t R, int a_mn, int b_mn, int bn,
+                                            int splits, void *stream) {
+  using namespace alegpu;
+  ALEGPU_REQUIRE(A && B && C && M > 0 && N > 0 && R > 0, ALEGPU_INVALID_ARGUMENT,
+                 "selftest_tc_gemm_tf32: bad argument");
+  ALEGPU_REQUIRE(splits >= 1, ALEGPU_INVALID_ARGUMENT, "selftest_tc_gemm_tf32: splits >= 1");
+  ALEGPU_REQUIRE((a_mn ? M : R) % 4 == 0 && (b_mn ? N : R) % 4 == 0, ALEGPU_INVALID_ARGUMENT,
+                 "selftest_tc_gemm_tf32: the contiguous dimension of each operand must be a multiple of 4");
+  cudaStream_t s = as_stream(stream);
+  int rps = 0;
+  if (splits > 1)
+    rps = (int)(ceil_div(ceil_div(R, splits), tc::BK) * tc::BK);
+  const int z = splits > 1 ? (int)ceil_div(R, rps) : 1;
+  return selftest_dispatch(RowsK<float>{A, (int)R}, ColsMN<float>{A, (int)M}, RowsK<float>{B, (int)R},
+                           ColsMN<float>{B, (int)N}, C, M, N, R, a_mn, b_mn, bn, z, rps, s);
 }
 
 extern "C" int alegpu_selftest_tc_gemm(const float *A, const float *B, float *C, int64_t M, int64_t N,

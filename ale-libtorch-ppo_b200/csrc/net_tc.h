@@ -6,7 +6,8 @@ namespace alegpu {
 
 struct TcState {
   int64_t hidden = 0, actions = 0, cap = 0, Ppad = 0;
-  void *w_shadow = nullptr;  // bf16 copy of the flat parameter buffer (written by Adam)
+  int elem_bytes = 2;        // operand type of every buffer below: 2 = bf16 (kind::f16), 4 = fp32 rounded to tf32 (kind::tf32)
+  void *w_shadow = nullptr;  // operand-type copy of the flat parameter buffer (written by Adam)
   void *c1w_perm = nullptr;  // bf16 conv1 weights [32][256] in the k' = (tap, y&3, x&3, c) order of the space-to-depth obs16
   // bf16 NHWC copy of the observations conv1 reads: one minibatch (cap rows) and, lazily, a whole
   // train() batch so the conversion runs once per train() instead of once per minibatch step
@@ -35,7 +36,7 @@ struct TcState {
 };
 
 int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_t Ppad,
-                cudaStream_t s);
+                int elem_bytes, cudaStream_t s);
 void net_tc_destroy(TcState &T);
 int net_tc_refresh_weights(TcState &T, const float *params, int64_t Ppad, cudaStream_t s);
 // obs16 = the rows' bf16 NHWC copy when the caller already made one (net_tc_prepare_obs); nullptr:

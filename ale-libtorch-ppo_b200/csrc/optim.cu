@@ -68,11 +68,17 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
+__device__ __forceinline__ float round_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+// ST = element type of the operand shadow the tensor-core path reads: bf16, or float (tf32-rounded)
+template <class ST>
 __global__ void __launch_bounds__(kThreads)
     adam_clip_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m,
-                     float *__restrict__ v, __nv_bfloat16 *__restrict__ shadow,
-                     __nv_bfloat16 *__restrict__ c1w_perm, int64_t n4,
-                     const OptState *__restrict__ st) {
+                     float *__restrict__ v, ST *__restrict__ shadow, ST *__restrict__ c1w_perm,
+                     int64_t n4, const OptState *__restrict__ st) {
   float4 *p4 = reinterpret_cast<float4 *>(p);
   const float4 *g4 = reinterpret_cast<const float4 *>(g);
   float4 *m4 = reinterpret_cast<float4 *>(m);
@@ -112,22 +118,34 @@ __global__ void __launch_bounds__(kThreads)
     m4[i] = mm;
     v4[i] = vv;
     if (shadow) {
-      __nv_bfloat162 lo = __floats2bfloat162_rn(pp.x, pp.y), hi = __floats2bfloat162_rn(pp.z, pp.w);
-      uint2 pk;
-      pk.x = *reinterpret_cast<uint32_t *>(&lo);
-      pk.y = *reinterpret_cast<uint32_t *>(&hi);
-      reinterpret_cast<uint2 *>(shadow)[i] = pk;
+      if constexpr (sizeof(ST) == 2) {
+        __nv_bfloat162 lo = __floats2bfloat162_rn(pp.x, pp.y), hi = __floats2bfloat162_rn(pp.z, pp.w);
+        uint2 pk;
+        pk.x = *reinterpret_cast<uint32_t *>(&lo);
+        pk.y = *reinterpret_cast<uint32_t *>(&hi);
+        reinterpret_cast<uint2 *>(shadow)[i] = pk;
+      } else {
+        reinterpret_cast<float4 *>(shadow)[i] =
+            make_float4(round_tf32(pp.x), round_tf32(pp.y), round_tf32(pp.z), round_tf32(pp.w));
+      }
       // conv1's weights (the first 32*256 parameters, OIHW: k = c*64 + ky*8 + kx) are also kept in
       // the (tap, y&3, x&3, c) order in which the tensor-core conv1 walks the space-to-depth observations
       if (c1w_perm && i < 32 * 256 / 4) {
         const int idx = (int)i * 4, co = idx >> 8, k = idx & 255;
         const int c = k >> 6, ky = (k >> 3) & 7, kx = k & 7;
-        __nv_bfloat16 *o = c1w_perm + co * 256 + ((ky >> 2) * 2 + (kx >> 2)) * 64 + (ky & 3) * 16 +
-                           (kx & 3) * 4 + c; // net_tc.cu: conv1_k_of_kprime
-        o[0] = __float2bfloat16_rn(pp.x);
-        o[4] = __float2bfloat16_rn(pp.y);
-        o[8] = __float2bfloat16_rn(pp.z);
-        o[12] = __float2bfloat16_rn(pp.w);
+        ST *o = c1w_perm + co * 256 + ((ky >> 2) * 2 + (kx >> 2)) * 64 + (ky & 3) * 16 +
+                (kx & 3) * 4 + c; // net_tc.cu: conv1_k_of_kprime
+        if constexpr (sizeof(ST) == 2) {
+          o[0] = __float2bfloat16_rn(pp.x);
+          o[4] = __float2bfloat16_rn(pp.y);
+          o[8] = __float2bfloat16_rn(pp.z);
+          o[12] = __float2bfloat16_rn(pp.w);
+        } else {
+          o[0] = round_tf32(pp.x);
+          o[4] = round_tf32(pp.y);
+          o[8] = round_tf32(pp.z);
+          o[12] = round_tf32(pp.w);
+        }
       }
     }
     pp = pn; gg = gn; mm = mn; vv = vn;
@@ -153,13 +171,17 @@ int launch_grad_sumsq(const float *grads, int64_t n_padded, float *partials, Opt
   return ALEGPU_OK;
 }
 
-int launch_adam_clip(float *params, float *grads, float *m, float *v, void *bf16_shadow,
-                     void *c1w_perm, int64_t n_padded, const OptState *st, cudaStream_t s) {
+int launch_adam_clip(float *params, float *grads, float *m, float *v, void *shadow,
+                     void *c1w_perm, int shadow_elem_bytes, int64_t n_padded, const OptState *st,
+                     cudaStream_t s) {
   const int blocks = (int)std::min<int64_t>(ceil_div(n_padded / 4, kThreads), kNumSMs * 8);
-  adam_clip_kernel<<<blocks, kThreads, 0, s>>>(params, grads, m, v,
-                                               static_cast<__nv_bfloat16 *>(bf16_shadow),
-                                               static_cast<__nv_bfloat16 *>(c1w_perm), n_padded / 4,
-                                               st);
+  if (shadow && shadow_elem_bytes == 4)
+    adam_clip_kernel<float><<<blocks, kThreads, 0, s>>>(params, grads, m, v, static_cast<float *>(shadow),
+                                                        static_cast<float *>(c1w_perm), n_padded / 4, st);
+  else
+    adam_clip_kernel<__nv_bfloat16><<<blocks, kThreads, 0, s>>>(
+        params, grads, m, v, static_cast<__nv_bfloat16 *>(shadow),
+        static_cast<__nv_bfloat16 *>(c1w_perm), n_padded / 4, st);
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
   return ALEGPU_OK;

@@ -21,9 +21,11 @@ constexpr int kNormBlocks = 296; // 2 CTAs per SM, fixed => bit-reproducible par
 // and leaves the clip coefficient / bias corrections in *st; total_norm_out <- the PRE-clip norm
 int launch_grad_sumsq(const float *grads, int64_t n_padded, float *partials, OptState *st,
                       float max_norm, float *total_norm_out, cudaStream_t s);
-int launch_adam_clip(float *params, float *grads, float *m, float *v, void *bf16_shadow,
-                     void *c1w_perm, // optional bf16 [32][256] conv1 weights in the space-to-depth k' order
-                     int64_t n_padded, const OptState *st, cudaStream_t s);
+// shadow (optional): operand-type copy of the parameters for the tensor-core path, bf16
+// (shadow_elem_bytes 2) or tf32-rounded fp32 (4); c1w_perm: [32][256] conv1 weights of the same type
+// in the space-to-depth k' order
+int launch_adam_clip(float *params, float *grads, float *m, float *v, void *shadow, void *c1w_perm,
+                     int shadow_elem_bytes, int64_t n_padded, const OptState *st, cudaStream_t s);
 int launch_f32_to_bf16(const float *src, void *dst, int64_t n, cudaStream_t s);
 
 } // namespace alegpu

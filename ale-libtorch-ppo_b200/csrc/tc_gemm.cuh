@@ -1,6 +1,7 @@
 // tc_gemm.cuh — the tcgen05/TMEM implicit-GEMM engine of the tensor-core Nature-CNN path.
 //
-//   C[i][j] = sum_r A(i,r) * B(j,r)        bf16 operands, fp32 accumulation in tensor memory
+//   C[i][j] = sum_r A(i,r) * B(j,r)        bf16 (kind::f16) or fp32-as-tf32 (kind::tf32) operands,
+//                                          fp32 accumulation in tensor memory
 //
 // One CTA computes one 128 x BN tile.  Operands are never materialised in global memory: eight
 // producer warps gather 16-byte chunks (8 bf16) through loader functors (im2col, transposed-conv
@@ -12,7 +13,13 @@
 // eight warps then read the accumulator with tcgen05.ld (32 lanes x 16 columns per instruction)
 // and run the fused epilogue functor (bias/ReLU, ReLU-mask, scatter, split partials).
 //
-// Shared-memory tile layouts (one k-block = 64 reduction elements):
+// Element size: an operand view declares kElemBytes = 4 for fp32 data consumed as TF32 (the tensor
+// core reads the upper 19 bits; producers round with cvt.rna.tf32 where they create the data); the
+// default is 2 (bf16).  A k-block is always 128 bytes of reduction per row: 64 bf16 or 32 tf32
+// elements = 4 UMMAs (K = 16 / K = 8), a 16-byte chunk is 8 bf16 / 4 tf32 elements, and the
+// byte layouts below are the same for both (MN-major atoms are 64 / 32 rows x 8 reduction indices).
+//
+// Shared-memory tile layouts (one k-block = 64 bf16 / 32 tf32 reduction elements):
 //   K-major operand  (reduction index contiguous in the 16-byte chunk):
 //       row i owns 128 contiguous bytes; chunk kc sits at i*128 + ((kc ^ (i&7)) << 4);
 //       8-row groups are 1024 B apart (SBO); one UMMA (K=16) advances the start address by 32 B.
@@ -34,6 +41,14 @@ constexpr int BM = 128;          // UMMA M (cta_group::1)
 constexpr int BK = 64;           // reduction elements per pipeline stage (4 UMMAs of K=16)
 constexpr int kProducerWarps = 8;
 constexpr int kThreads = (kProducerWarps + 1) * 32;
+// bytes per operand element: 2 (bf16, kind::f16) unless the view says kElemBytes = 4 (tf32)
+template <class Op, class = void> struct ElemBytes {
+  static constexpr int value = 2;
+};
+template <class Op> struct ElemBytes<Op, decltype((void)Op::kElemBytes)> {
+  static constexpr int value = Op::kElemBytes;
+};
+__host__ __device__ constexpr int bk_of(int elem_bytes) { return 128 / elem_bytes; }
 
 // ---- PTX wrappers -------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
@@ -108,6 +123,16 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
                "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
                : "memory");
 }
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                          uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{\n\t"
+               ".reg .pred p;\n\t"
+               "setp.ne.b32 p, %4, 0;\n\t"
+               "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+               "}" ::"r"(tmem_d),
+               "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+               : "memory");
+}
 // arrive on an mbarrier once every tcgen05.mma issued so far by this thread has completed
 __device__ __forceinline__ void umma_commit(uint64_t *bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
@@ -141,9 +166,11 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t 
   d |= (uint64_t)2 << 61;
   return d;
 }
-// UMMA instruction descriptor, kind::f16: D=f32, A=B=bf16, M=128, N=BN, per-operand major bits
-__host__ __device__ constexpr uint32_t make_idesc(int n, bool a_mn, bool b_mn) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn ? 1u : 0u) << 15) |
+// UMMA instruction descriptor, kind::f16 / kind::tf32: D=f32, A=B=bf16 (format 1) or tf32 (format 2),
+// M=128, N=BN, per-operand major bits
+__host__ __device__ constexpr uint32_t make_idesc(int n, bool a_mn, bool b_mn, int elem_bytes = 2) {
+  const uint32_t fmt = elem_bytes == 4 ? 2u : 1u;
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | ((a_mn ? 1u : 0u) << 15) |
          ((b_mn ? 1u : 0u) << 16) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 }
 
@@ -176,6 +203,7 @@ template <class Op> struct PosFastest<Op, decltype((void)Op::kPosFastest)> {
   static constexpr bool value = Op::kPosFastest;
 };
 template <int ROWS, class Op> struct TileRegs {
+  static_assert(ElemBytes<Op>::value == 2, "the register path converts to bf16; tf32 operands are async");
   static constexpr int kChunks = ROWS * 8;
   static constexpr int kProducers = kProducerWarps * 32;
   static constexpr int kPer = (kChunks + kProducers - 1) / kProducers;
@@ -300,7 +328,10 @@ template <int ROWS, class Op> struct AsyncCtx<ROWS, Op, true, false> {
   static constexpr int kProducers = kProducerWarps * 32;
   static_assert(kChunks % kProducers == 0, "tile rows must be a multiple of 32");
   static constexpr int kPer = kChunks / kProducers;
-  static constexpr int kRowChunks = ROWS / 8;
+  static constexpr int kEB = ElemBytes<Op>::value;
+  static constexpr int kEPC = 16 / kEB;               // elements per 16-byte chunk
+  static constexpr int kRowChunks = ROWS / kEPC;      // MN-major: chunks along the row index
+  static constexpr uint32_t kAtomLBO = (uint32_t)(bk_of(kEB) / 8) * 1024u; // bytes between MN atoms
   static_assert(Op::kMN ? kProducers % kRowChunks == 0 : true, "row chunks must divide 256");
   static constexpr int kCtx = Op::kMN ? 1 : kPer;
   typename Op::RowCtx rc[kCtx];
@@ -320,16 +351,16 @@ template <int ROWS, class Op> struct AsyncCtx<ROWS, Op, true, false> {
       }
     } else {
       const int c = ptid % kRowChunks;
-      const int i = row0 + c * 8;
+      const int i = row0 + c * kEPC;
       rc[0] = op.row(i < rows_total ? i : row0);
       valid = i < rows_total ? 1u : 0u;
-      off0 = (uint32_t)((c >> 3) * 8192);
+      off0 = (uint32_t)(c >> 3) * kAtomLBO;
     }
   }
   __device__ __forceinline__ void issue(const Op &op, uint32_t tile, int r0, int r_end, int z,
                                         int ptid, uint64_t *) const {
     if constexpr (!Op::kMN) {
-      const int r = r0 + (ptid & 7) * 8;
+      const int r = r0 + (ptid & 7) * kEPC;
       const bool rv = r < r_end;
       const typename Op::ColCtx cc = op.col(rv ? r : r0, z);
 #pragma unroll
@@ -395,7 +426,10 @@ __global__ void __launch_bounds__(kThreads, BN <= 128 ? 2 : 1)
   static_assert(!BOp::kMN || BN >= 64, "an MN-major B tile needs at least one 64-row atom");
   constexpr int kATile = tile_bytes(BM), kBTile = tile_bytes(BN < 64 ? 64 : BN);
   constexpr int kStage = kATile + kBTile;
-  constexpr uint32_t kIdesc = make_idesc(BN, AOp::kMN, BOp::kMN);
+  constexpr int kEB = ElemBytes<AOp>::value; // 2: bf16 / kind::f16, 4: tf32 / kind::tf32
+  static_assert(kEB == ElemBytes<BOp>::value, "both operands must have the same element type");
+  constexpr int BK = bk_of(kEB);             // reduction elements per k-block (128 bytes per row)
+  constexpr uint32_t kIdesc = make_idesc(BN, AOp::kMN, BOp::kMN, kEB);
   constexpr uint32_t kCols = tmem_cols(BN); // per accumulator buffer; two are allocated
 
   extern __shared__ uint8_t smem_raw[];
@@ -564,13 +598,20 @@ __global__ void __launch_bounds__(kThreads, BN <= 128 ? 2 : 1)
         mbar_wait(&full_bar[s], ph);
         tc_fence_after();
         const uint32_t a_addr = smem_u32(tiles + s * kStage), b_addr = a_addr + kATile;
-        const uint64_t adesc = make_smem_desc(a_addr, AOp::kMN ? 8192u : 16u, 1024u);
-        const uint64_t bdesc = make_smem_desc(b_addr, BOp::kMN ? 8192u : 16u, 1024u);
+        // MN-major: LBO = bytes between the 64-row (bf16) / 32-row (tf32) atoms = one k-block of
+        // 8-index groups; one UMMA (K = 16 bf16 / 8 tf32) spans 2 / 1 of those 1024-byte groups
+        constexpr uint32_t kLboMN = (uint32_t)(BK / 8) * 1024u;
+        constexpr int kUmmaK = 32 / kEB, kAdvMN = (kUmmaK / 8) * 1024 / 16;
+        const uint64_t adesc = make_smem_desc(a_addr, AOp::kMN ? kLboMN : 16u, 1024u);
+        const uint64_t bdesc = make_smem_desc(b_addr, BOp::kMN ? kLboMN : 16u, 1024u);
 #pragma unroll
-        for (int kk = 0; kk < BK / 16; ++kk) {
-          const uint64_t ad = adesc + (uint64_t)(kk * (AOp::kMN ? 128 : 2));
-          const uint64_t bd = bdesc + (uint64_t)(kk * (BOp::kMN ? 128 : 2));
-          umma_bf16(tmem_d, ad, bd, kIdesc, (uint32_t)((kb | kk) != 0));
+        for (int kk = 0; kk < BK / kUmmaK; ++kk) {
+          const uint64_t ad = adesc + (uint64_t)(kk * (AOp::kMN ? kAdvMN : 2));
+          const uint64_t bd = bdesc + (uint64_t)(kk * (BOp::kMN ? kAdvMN : 2));
+          if constexpr (kEB == 4)
+            umma_tf32(tmem_d, ad, bd, kIdesc, (uint32_t)((kb | kk) != 0));
+          else
+            umma_bf16(tmem_d, ad, bd, kIdesc, (uint32_t)((kb | kk) != 0));
         }
         umma_commit(&empty_bar[s]); // slot reusable once these UMMAs have read it
       }

@@ -177,7 +177,10 @@ typedef struct alegpu_rollout alegpu_rollout;
 
 typedef enum {
   ALEGPU_MATH_FP32 = 0, /* CUDA-core fp32 implicit GEMM: the fp32-faithful parity mode      */
-  ALEGPU_MATH_BF16 = 1  /* tcgen05/TMEM tensor-core implicit GEMM, bf16 operands, fp32 accum */
+  ALEGPU_MATH_BF16 = 1, /* tcgen05/TMEM tensor-core implicit GEMM, bf16 operands, fp32 accum */
+  ALEGPU_MATH_TF32 = 2  /* the same engine with tcgen05.mma kind::tf32: fp32 activations / weights /
+                           gradients rounded to tf32 where they are produced, fp32 accumulation —
+                           the precision cuDNN gives the reference's convolutions on a GPU          */
 } alegpu_math;
 
 typedef struct {
@@ -429,6 +432,12 @@ int alegpu_selftest_tc_gemm(const float *A, const float *B, float *C, int64_t M,
  * operand of the network takes; the fp32 entry point above exercises the register producers. */
 int alegpu_selftest_tc_gemm_async(const float *A, const float *B, float *C, int64_t M, int64_t N,
                                   int64_t R, int a_mn, int b_mn, int bn, int splits, void *stream);
+
+/* the same product on the kind::tf32 path behind ALEGPU_MATH_TF32: fp32 inputs copied as they are by
+ * the cp.async producers, the tensor core multiplies their upper 19 bits (tf32), fp32 accumulation.
+ * Contiguous dimensions must be multiples of 4. */
+int alegpu_selftest_tc_gemm_tf32(const float *A, const float *B, float *C, int64_t M, int64_t N,
+                                 int64_t R, int a_mn, int b_mn, int bn, int splits, void *stream);
 
 #ifdef __cplusplus
 }

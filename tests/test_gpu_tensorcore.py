@@ -65,6 +65,41 @@ def test_tc_gemm_engine_splits(use_async):
     assert np.abs(got.sum(0) - want).max() <= 2e-3
 
 
+def tf32_trunc(x):
+    """what kind::tf32 multiplies: the upper 19 bits of an fp32 operand"""
+    return (np.ascontiguousarray(x, np.float32).view(np.uint32) & np.uint32(0xFFFFE000)).view(np.float32)
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (True, False), (False, True), (True, True)])
+@pytest.mark.parametrize("M,N,R,bn", [(128, 64, 32, 64), (304, 64, 576, 64), (256, 136, 200, 128),
+                                      (520, 256, 1000, 256), (64, 32, 256, 32), (128, 64, 96, 64)])
+def test_tc_gemm_engine_tf32(a_mn, b_mn, M, N, R, bn):
+    """tcgen05.mma kind::tf32 through the same engine: K-major and MN-major fp32 operand tiles
+    (32 tf32 per 128-byte k-block row, UMMA K = 8), against float64 products of the truncated inputs."""
+    if b_mn and bn < 64:
+        pytest.skip("an MN-major B tile needs bn >= 64")
+    rng = np.random.default_rng(M * 7 + N * 3 + R + 1)
+    A = rng.standard_normal((M, R)).astype(np.float32)
+    B = rng.standard_normal((N, R)).astype(np.float32)
+    want = tf32_trunc(A).astype(np.float64) @ tf32_trunc(B).astype(np.float64).T
+    got = alegpu.selftest_tc_gemm(A.T if a_mn else A, B.T if b_mn else B, M, N, R, a_mn, b_mn, bn,
+                                  tf32=True)
+    assert got.shape == (1, M, N)
+    err = np.abs(got[0] - want).max()
+    assert err <= 1e-4 * np.sqrt(R) * 4, (err, a_mn, b_mn)
+
+
+def test_tc_gemm_engine_tf32_splits():
+    M, N, R = 264, 64, 1000
+    rng = np.random.default_rng(6)
+    A = rng.standard_normal((M, R)).astype(np.float32)
+    B = rng.standard_normal((N, R)).astype(np.float32)
+    want = tf32_trunc(A).astype(np.float64) @ tf32_trunc(B).astype(np.float64).T
+    got = alegpu.selftest_tc_gemm(A.T, B.T, M, N, R, True, True, 64, splits=5, tf32=True)
+    assert got.shape[0] == 4  # rps = 256 -> 4 parts
+    assert np.abs(got.sum(0) - want).max() <= 2e-3
+
+
 def _batch(tc, n=None):
     sl = slice(0, n)
     return alegpu.Batch(tc["obs"][sl], tc["actions"][sl], tc["log_probs"][sl], tc["advantages"][sl],
@@ -103,6 +138,78 @@ def test_network_bf16_vs_oracle(H, n, pseed, dseed, gtol, gcos):
     print("bf16 grad report (tensor, rel-L2, cosine):", [(i, round(r, 5), round(c, 6)) for i, r, c in report])
     for i, r, c in report:
         assert r <= gtol and c >= gcos, report
+
+
+# tf32 mode: SURVEY.md §8c's bounds for the tensor-core parity default — outputs rel-L2 <= 2e-3,
+# per-tensor gradient rel-L2 <= 1e-2 and cosine >= 0.9999 (fp32 operands rounded to tf32 where they
+# are produced, fp32 accumulation)
+@pytest.mark.parametrize("H,n,pseed,dseed", [(32, 16, 3, 109), (512, 256, 13, 31), (512, 37, 14, 33)])
+def test_network_tf32_vs_oracle(H, n, pseed, dseed):
+    params = cases.net_params(H, seed=pseed)
+    tc = cases.train_case(n, seed=dseed)
+    L = alegpu.Learner(H, 4, n, alegpu.MATH_TF32, cases.LR)
+    L.set_params(params)
+    grads, loss, logits, values = L.grads(_batch(tc), hp())
+    lg, v, acts = restate.net_forward(params, H, tc["obs"], keep_acts=True)
+    k = min(n, 4)
+    c1, c2, c3, fc = L.activations(k)
+    o1, o2, o3 = 28224, 28224 + 12800, 28224 + 12800 + 5184
+    for name, a, b in (("act1", c1, acts[:k, o1:o2]), ("act2", c2, acts[:k, o2:o3]),
+                       ("act3", c3, acts[:k, o3:o3 + 3136]), ("fc", fc, acts[:k, o3 + 3136:]),
+                       ("logits", logits, lg), ("values", values, v)):
+        assert rel_l2(a, b) <= 2e-3, (name, rel_l2(a, b))
+    lo = restate.loss(lg, tc["log_probs"], tc["actions"], tc["advantages"], v, tc["returns"],
+                      tc["masks"], cases.CLIP, cases.VCOEF, cases.ECOEF)
+    assert abs(loss - lo["loss"]) <= 2e-3 * abs(lo["loss"]) + 1e-4
+    want = restate.net_backward(params, H, acts, lo["dlogits"], lo["dvalues"])
+    offs = cases.param_offsets(H)
+    report = []
+    for i in range(12):
+        a, b = grads[offs[i]:offs[i + 1]], want[offs[i]:offs[i + 1]]
+        report.append((i, rel_l2(a, b), cosine(a, b)))
+    print("tf32 grad report (tensor, rel-L2, cosine):", [(i, round(r, 6), round(c, 7)) for i, r, c in report])
+    for i, r, c in report:
+        assert r <= 1e-2 and c >= 0.9999, report
+
+
+def test_train_tf32_vs_oracle_and_determinism():
+    H, n = 64, 64
+    params = cases.net_params(H, seed=21)
+    tc = cases.train_case(n, seed=77)
+    z = np.zeros_like(params)
+    p, _, _, _, m = restate.train(params, z, z, 0, H, tc["obs"], tc["actions"], tc["log_probs"],
+                                  tc["advantages"], tc["returns"], tc["masks"], 2, 2, cases.CLIP,
+                                  cases.VCOEF, cases.ECOEF, cases.MAX_NORM, cases.LR)
+    outs = []
+    for graph in (False, True, True):
+        L = alegpu.Learner(H, 4, n // 2, alegpu.MATH_TF32, cases.LR)
+        L.set_params(params)
+        met = alegpu.Metrics(2, 2, n // 2)
+        L.train(_batch(tc), met, 2, 2, hp(), cuda_graph=graph)
+        outs.append(L.get_params())
+        np.testing.assert_allclose(met.numpy()["loss"], m["loss"], rtol=1e-2, atol=1e-4)
+        assert L.get_adam()[2] == 4
+    assert cosine(outs[0] - params, p - params) >= 0.999, cosine(outs[0] - params, p - params)
+    assert rel_l2(outs[0], p) <= 1e-3  # whole train(), tf32
+    assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[1], outs[2])  # bit-reproducible
+
+
+def test_tf32_tma_operands_equal_the_gather_operands(monkeypatch):
+    """tf32 mode, TMA im2col producers (32-channel fp32 boxes, two k-blocks per tap) against the
+    cp.async gathers: same products, same k order -> identical bits.  Ragged 37-row tiles."""
+    H, n = 64, 37
+    params = cases.net_params(H, seed=5)
+    tc = cases.train_case(n, seed=19)
+    outs = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("ALEGPU_NO_TMA", flag)
+        L = alegpu.Learner(H, 4, n, alegpu.MATH_TF32, cases.LR)
+        L.set_params(params)
+        grads, loss, logits, values = L.grads(_batch(tc), hp())
+        outs[flag] = (grads, logits, values) + tuple(L.activations(n))
+    for a, b in zip(outs["0"][1:], outs["1"][1:]):
+        assert np.array_equal(a, b)
+    assert np.array_equal(outs["0"][0], outs["1"][0])
 
 
 def test_train_bf16_vs_oracle_and_determinism():
