@@ -271,6 +271,56 @@ class losses:
         return res
 
 
+# ---- configs/*.yaml: Config / load_config — src/bin/train.cc:33-60, 108-136 ---------------------
+class Config(C.Structure):
+    """The reference's flat YAML schema (alegpu_config); load with Config.load(path)."""
+    _fields_ = [("total_environments", C.c_int64), ("hidden_size", C.c_int64), ("horizon", C.c_int64),
+                ("max_steps", C.c_int64), ("frame_stack", C.c_int64), ("learning_rate", C.c_double),
+                ("clip_param", C.c_float), ("value_loss_coef", C.c_float), ("entropy_coef", C.c_float),
+                ("num_epochs", C.c_int64), ("mini_batch_size", C.c_int64),
+                ("num_mini_batches", C.c_int64), ("gae_discount", C.c_float),
+                ("gae_lambda", C.c_float), ("max_gradient_norm", C.c_float),
+                ("num_rollouts", C.c_int64), ("num_workers", C.c_int64),
+                ("worker_batch_size", C.c_int64), ("frame_skip", C.c_int64), ("max_return", C.c_float),
+                ("record_observation", C.c_int), ("record_video", C.c_int), ("cuda_graph", C.c_int),
+                ("deterministic", C.c_int), ("action_size", C.c_int64),
+                ("normalize_advantages", C.c_int), ("clip_value_loss", C.c_int), ("shuffle", C.c_int),
+                ("num_gpus", C.c_int64)]
+
+    @classmethod
+    def defaults(cls):
+        c = cls()
+        _check(lib().alegpu_config_defaults(C.byref(c)))
+        return c
+
+    @classmethod
+    def load(cls, path, validate=True):
+        c = cls()
+        _check(lib().alegpu_config_load(str(path).encode(), C.byref(c)))
+        if validate:
+            c.validate()
+        return c
+
+    @classmethod
+    def parse(cls, text, validate=True):
+        c = cls()
+        _check(lib().alegpu_config_parse(text.encode(), C.byref(c)))
+        if validate:
+            c.validate()
+        return c
+
+    def validate(self):
+        _check(lib().alegpu_config_validate(C.byref(self)))
+
+    def hyperparameters(self):
+        """prepare_hyperparameters — src/bin/train.cc:285-291."""
+        return Hyperparameters(self.clip_param, self.value_loss_coef, self.entropy_coef,
+                               self.max_gradient_norm)
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
 # ---- structs ----------------------------------------------------------------------------------
 class _LearnerConfig(C.Structure):
     _fields_ = [("hidden_size", C.c_int64), ("action_size", C.c_int64),
@@ -288,7 +338,8 @@ class Hyperparameters(C.Structure):
 class _Batch(C.Structure):
     _fields_ = [("observations", C.c_void_p), ("actions", C.c_void_p),
                 ("log_probabilities", C.c_void_p), ("advantages", C.c_void_p),
-                ("returns", C.c_void_p), ("masks", C.c_void_p), ("size", C.c_int64)]
+                ("returns", C.c_void_p), ("masks", C.c_void_p), ("size", C.c_int64),
+                ("values", C.c_void_p)]
 
 
 class _Metrics(C.Structure):
@@ -307,7 +358,9 @@ class _RolloutView(C.Structure):
 class Batch:
     """ai::ppo::train::Batch — src/ai/ppo/train.h:34-57 (device arrays, N rows)."""
 
-    def __init__(self, observations, actions, log_probabilities, advantages, returns, masks):
+    def __init__(self, observations, actions, log_probabilities, advantages, returns, masks,
+                 values=None):
+        self.values = _dev(values, np.float32) if values is not None else None  # old values (clip_value_loss)
         self.observations = _dev(observations, np.uint8)
         self.actions = _dev(actions, np.int64)
         self.log_probabilities = _dev(log_probabilities, np.float32)
@@ -323,11 +376,13 @@ class Batch:
                      self.actions.view(start, (n,)),
                      self.log_probabilities.view(start * A, (n, A)),
                      self.advantages.view(start, (n,)), self.returns.view(start, (n,)),
-                     self.masks.view(start, (n,)))
+                     self.masks.view(start, (n,)),
+                     self.values.view(start, (n,)) if self.values is not None else None)
 
     def _c(self):
         return _Batch(self.observations.ptr, self.actions.ptr, self.log_probabilities.ptr,
-                      self.advantages.ptr, self.returns.ptr, self.masks.ptr, self.size)
+                      self.advantages.ptr, self.returns.ptr, self.masks.ptr, self.size,
+                      self.values.ptr if self.values is not None else None)
 
 
 class Metrics:
@@ -428,11 +483,13 @@ class Buffer:
         N = self.E * self.T
         return Batch(self.observations.view(0, (N, 4, 84, 84)), self.actions.view(0, (N,)),
                      self.log_probabilities.view(0, (N, self.A)), self.advantages.view(0, (N,)),
-                     self.returns.view(0, (N,)), self.masks.view(0, (N,)))
+                     self.returns.view(0, (N,)), self.masks.view(0, (N,)),
+                     self.values.view(0, (N,)))
 
 
 class _TrainOptions(C.Structure):
-    _fields_ = [("indices", C.c_void_p), ("normalize_advantages", C.c_int)]
+    _fields_ = [("indices", C.c_void_p), ("normalize_advantages", C.c_int),
+                ("clip_value_loss", C.c_int)]
 
 
 class Learner:
@@ -567,14 +624,15 @@ class Learner:
         return float(tn.value)
 
     def train(self, batch, metrics, num_epochs, num_mini_batches, hp, cuda_graph=False,
-              sync=True, indices=None, normalize_advantages=False):
+              sync=True, indices=None, normalize_advantages=False, clip_value_loss=False):
         """ai::ppo::train::train — src/ai/ppo/train.h:133-157.  indices ([epochs*N] int64 row
-        order) and normalize_advantages are the opt-in extras of alegpu_train_options."""
+        order), normalize_advantages and clip_value_loss (needs batch.values) are the opt-in extras
+        of alegpu_train_options."""
         cb = batch._c()
         cm = metrics._c() if metrics is not None else None
         self._idx = _dev(indices, np.int64) if indices is not None else None
         opt = _TrainOptions(self._idx.ptr if self._idx is not None else None,
-                            1 if normalize_advantages else 0)
+                            1 if normalize_advantages else 0, 1 if clip_value_loss else 0)
         _check(lib().alegpu_learner_train_ex(self.h, C.byref(cb),
                                              C.byref(cm) if cm is not None else None,
                                              C.c_int64(num_epochs), C.c_int64(num_mini_batches),

@@ -76,6 +76,8 @@ __global__ void __launch_bounds__(kThreads)
         if (a < A)
           ol[a] = L.old_log_probs[i * A + a];
       const bool m = L.masks[i] != 0;
+      if (lane == 0 && L.error_flag && (L.actions[i] < 0 || L.actions[i] >= A))
+        atomicExch(L.error_flag, 1); // the reference's gather(-1, actions) would throw (losses.cc:12)
       const float adv_raw = L.advantages[i];
       float adv = adv_raw;
       const float ret = L.returns[i];
@@ -85,7 +87,9 @@ __global__ void __launch_bounds__(kThreads)
         adv = (float)(((double)adv - mean) / (sqrt(fmax(var, 0.0)) + 1e-8));
       }
       const PpoSample s = ppo_sample<kMaxA>(z, ol, A, (int)L.actions[i], adv, v, ret, L.clip,
-                                            L.vcoef, L.ecoef, m ? inv : 0.0f, dz, &dv);
+                                            L.vcoef, L.ecoef, m ? inv : 0.0f, dz, &dv,
+                                            L.old_values != nullptr,
+                                            L.old_values ? L.old_values[i] : 0.0f);
       if (lane == 0) {
         if (L.m_clipped) L.m_clipped[i] = s.surr;
         if (L.m_value) L.m_value[i] = s.value_loss;
@@ -122,11 +126,29 @@ __global__ void __launch_bounds__(kThreads)
     if (lane == 0)
       red[warp] = contrib;
     __syncthreads();
+    __shared__ bool s_last;
     if (threadIdx.x == 0) {
       float t = 0.0f;
       for (int w = 0; w < kWarps; ++w)
         t += red[w];
       partials[blockIdx.x] = t;
+      s_last = false;
+      if (L.loss_sum) {
+        __threadfence();
+        s_last = atomicAdd(L.done_counter, 1u) == gridDim.x - 1;
+      }
+    }
+    __syncthreads();
+    if (s_last && threadIdx.x < 32) { // every partial is visible: fixed-order sum (bit-reproducible)
+      __threadfence();
+      float t = 0.0f;
+      for (int i = threadIdx.x; i < (int)gridDim.x; i += 32)
+        t += __ldcg(partials + i);
+      t = warp_sum(t);
+      if (threadIdx.x == 0) {
+        *L.loss_sum = t;
+        *L.done_counter = 0u;
+      }
     }
   }
 }
@@ -184,20 +206,10 @@ __global__ void heads_reduce_kernel(const float *__restrict__ ws, int splits, in
   }
 }
 
-__global__ void finalize_metrics_kernel(const float *__restrict__ partials, int nparts,
+__global__ void finalize_metrics_kernel(const float *__restrict__ loss_sum,
                                         const float *__restrict__ count, float *__restrict__ m_loss,
                                         int64_t mb, float *__restrict__ loss_out) {
-  __shared__ float s_loss;
-  if (threadIdx.x < 32) {
-    float s = 0.0f;
-    for (int i = threadIdx.x; i < nparts; i += 32)
-      s += partials[i];
-    s = warp_sum(s);
-    if (threadIdx.x == 0)
-      s_loss = s / count[0]; // losses.cc:19
-  }
-  __syncthreads();
-  const float loss = s_loss;
+  const float loss = loss_sum[0] / count[0]; // losses.cc:19
   if (blockIdx.x == 0 && threadIdx.x == 0 && loss_out)
     loss_out[0] = loss;
   if (m_loss) // Metrics.loss[epoch,k,:] is the scalar broadcast over mb (train.h:98)
@@ -350,11 +362,10 @@ int heads_wgrad(const NetParams &G, const NetActs &A, int64_t n, float *ws, size
   return ALEGPU_OK;
 }
 
-int finalize_metrics(const float *loss_partials, int nparts, const float *count, float *m_loss,
-                     int64_t mb, float *loss_out, cudaStream_t s) {
+int finalize_metrics(const float *loss_sum, const float *count, float *m_loss, int64_t mb,
+                     float *loss_out, cudaStream_t s) {
   const int blocks = m_loss ? (int)std::min<int64_t>(ceil_div(mb, 256), 64) : 1;
-  finalize_metrics_kernel<<<blocks, 256, 0, s>>>(loss_partials, nparts, count, m_loss, mb,
-                                                 loss_out);
+  finalize_metrics_kernel<<<blocks, 256, 0, s>>>(loss_sum, count, m_loss, mb, loss_out);
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
   return ALEGPU_OK;

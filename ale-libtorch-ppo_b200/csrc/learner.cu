@@ -109,6 +109,10 @@ struct alegpu_learner {
   StagedBatch staged;
   double *adv_stats = nullptr;
   int *gather_error = nullptr;
+  unsigned int *loss_done = nullptr; // counter of the heads kernel's last-block loss reduction
+  // device-side input errors (action index outside [0,A): the reference's gather would throw) land in
+  // a MAPPED pinned int the host can read without synchronising; checked at the next learner call
+  int *err_host = nullptr, *err_dev = nullptr;
   OptState *opt = nullptr;
   int64_t host_step = 0;
   double lr = 0.0;
@@ -191,6 +195,15 @@ bool use_tc(const alegpu_learner *L) {
   return L->cfg.math == ALEGPU_MATH_BF16 || L->cfg.math == ALEGPU_MATH_TF32;
 }
 
+// an input error a kernel of an EARLIER call reported through the mapped flag (no synchronisation)
+int learner_input_error(alegpu_learner *L) {
+  if (L->err_host && *(volatile int *)L->err_host) {
+    *(volatile int *)L->err_host = 0;
+    return fail(ALEGPU_OUT_OF_RANGE, "train: an action index was outside [0, action_size)");
+  }
+  return ALEGPU_OK;
+}
+
 int forward(alegpu_learner *L, const uint8_t *obs, int64_t n, const void *obs16 = nullptr) {
   if (use_tc(L))
     return net_tc_forward(L->Pv, L->tc, obs, n, L->acts, L->stream, obs16);
@@ -234,7 +247,8 @@ int allreduce_grads(alegpu_learner *L) {
 }
 
 int clip_and_step(alegpu_learner *L, float max_norm, float *total_norm_out) {
-  if (int rc = launch_grad_sumsq(L->grads, L->Ppad, L->norm_partials, L->opt, max_norm,
+  // the padding behind the P parameters carries the loss sum (see enqueue_train): not part of the norm
+  if (int rc = launch_grad_sumsq(L->grads, L->Ppad, L->P, L->norm_partials, L->opt, max_norm,
                                  total_norm_out, L->stream))
     return rc;
   L->host_step += 1;
@@ -253,6 +267,7 @@ int ensure_staging(alegpu_learner *L) {
   ALEGPU_CUDA_CHECK(cudaMalloc(&L->staged.logp, cap * A * sizeof(float)));
   ALEGPU_CUDA_CHECK(cudaMalloc(&L->staged.adv, cap * sizeof(float)));
   ALEGPU_CUDA_CHECK(cudaMalloc(&L->staged.ret, cap * sizeof(float)));
+  ALEGPU_CUDA_CHECK(cudaMalloc(&L->staged.values, cap * sizeof(float)));
   ALEGPU_CUDA_CHECK(cudaMalloc(&L->staged.masks, cap));
   ALEGPU_CUDA_CHECK(cudaMalloc(&L->gather_error, sizeof(int)));
   ALEGPU_CUDA_CHECK(cudaMemset(L->gather_error, 0, sizeof(int)));
@@ -293,12 +308,14 @@ int enqueue_train(alegpu_learner *L, const alegpu_batch &b, const alegpu_metrics
       la.advantages = b.advantages + s;
       la.returns = b.returns + s;
       la.masks = b.masks + s;
+      la.old_values = opt.clip_value_loss ? b.values + s : nullptr;
       float *count = L->counts + k;
       if (shuffled) { // minibatch k of epoch ep = rows indices[ep*N + k*mb ...], gathered once
         if (int rc = launch_gather_rows(opt.indices + ep * b.size + s, mb, b.size, (int)A,
                                         b.observations, b.actions, b.log_probabilities,
-                                        b.advantages, b.returns, b.masks, L->staged,
-                                        L->gather_error, L->stream))
+                                        b.advantages, b.returns,
+                                        opt.clip_value_loss ? b.values : nullptr, b.masks,
+                                        L->staged, L->gather_error, L->stream))
           return rc;
         obs = L->staged.obs;
         la.actions = L->staged.actions;
@@ -306,6 +323,8 @@ int enqueue_train(alegpu_learner *L, const alegpu_batch &b, const alegpu_metrics
         la.advantages = L->staged.adv;
         la.returns = L->staged.ret;
         la.masks = L->staged.masks;
+        if (opt.clip_value_loss)
+          la.old_values = L->staged.values;
         count = L->counts + (ep * nmb + k) % L->counts_cap;
         if (int rc = launch_mask_count(la.masks, mb, 1, count, L->stream))
           return rc;
@@ -349,6 +368,12 @@ int enqueue_train(alegpu_learner *L, const alegpu_batch &b, const alegpu_metrics
       la.m_adv = mt.advantages ? mt.advantages + o : nullptr;
       la.m_ret = mt.returns ? mt.returns + o : nullptr;
       la.m_masks = mt.masks ? mt.masks + o : nullptr;
+      // the un-normalised loss sum of this rank's rows goes into the first padding slot of the flat
+      // gradient: with world_size > 1 it is summed over ranks by the gradient exchange itself, so
+      // Metrics.loss is the GLOBAL minibatch loss (losses.cc:19) on every rank
+      la.loss_sum = L->grads + L->P;
+      la.done_counter = L->loss_done;
+      la.error_flag = L->err_dev;
       int nparts = 0;
       if (int rc = heads_loss_backward(L->Pv, L->acts, mb, la, L->loss_partials, &nparts, L->stream))
         return rc;
@@ -361,8 +386,7 @@ int enqueue_train(alegpu_learner *L, const alegpu_batch &b, const alegpu_metrics
                                                       : L->scalars))
         return rc;
       if (mt.loss)
-        if (int rc = finalize_metrics(L->loss_partials, nparts, count, mt.loss + o, mb,
-                                      nullptr, L->stream))
+        if (int rc = finalize_metrics(L->grads + L->P, count, mt.loss + o, mb, nullptr, L->stream))
           return rc;
     }
   return ALEGPU_OK;
@@ -559,7 +583,7 @@ extern "C" int alegpu_learner_create(const alegpu_learner_config *config, alegpu
     L->cfg.world_size = 1;
   const int64_t H = config->hidden_size, A = config->action_size, cap = config->max_minibatch;
   L->P = net_param_count(H, A);
-  L->Ppad = ceil_div(L->P, 8) * 8;
+  L->Ppad = ceil_div(L->P + 1, 8) * 8; // >= 1 padding slot: grads[P] carries the loss sum
   L->cap = cap;
   L->lr = config->learning_rate;
   ALEGPU_CUDA_CHECK(cudaStreamCreateWithFlags(&L->stream, cudaStreamNonBlocking));
@@ -604,6 +628,11 @@ extern "C" int alegpu_learner_create(const alegpu_learner_config *config, alegpu
   ALEGPU_CUDA_CHECK(cudaMalloc(&L->adv_stats, sizeof(double) * 3 * (size_t)L->counts_cap));
   if (int rc = fmalloc(&L->scalars, 16)) return rc;
   ALEGPU_CUDA_CHECK(cudaMalloc(&L->opt, sizeof(OptState)));
+  ALEGPU_CUDA_CHECK(cudaMalloc(&L->loss_done, sizeof(unsigned int)));
+  ALEGPU_CUDA_CHECK(cudaMemset(L->loss_done, 0, sizeof(unsigned int)));
+  ALEGPU_CUDA_CHECK(cudaHostAlloc(&L->err_host, sizeof(int), cudaHostAllocMapped));
+  *L->err_host = 0;
+  ALEGPU_CUDA_CHECK(cudaHostGetDevicePointer(&L->err_dev, L->err_host, 0));
   if (tc)
     if (int rc = net_tc_init(L->tc, H, A, cap, L->Ppad, config->math == ALEGPU_MATH_TF32 ? 4 : 2,
                              L->stream))
@@ -663,9 +692,14 @@ extern "C" int alegpu_learner_destroy(alegpu_learner *L) {
       cudaFree(p);
   if (L->opt)
     cudaFree(L->opt);
+  if (L->loss_done)
+    cudaFree(L->loss_done);
+  if (L->err_host)
+    cudaFreeHost(L->err_host);
   net_tc_destroy(L->tc);
   for (void *p : {(void *)L->staged.obs, (void *)L->staged.actions, (void *)L->staged.logp,
-                  (void *)L->staged.adv, (void *)L->staged.ret, (void *)L->staged.masks,
+                  (void *)L->staged.adv, (void *)L->staged.ret, (void *)L->staged.values,
+                  (void *)L->staged.masks,
                   (void *)L->adv_stats, (void *)L->gather_error})
     if (p)
       cudaFree(p);
@@ -845,13 +879,15 @@ extern "C" int alegpu_learner_grads(alegpu_learner *L, const alegpu_batch *mbatc
   la.vcoef = hp->value_loss_coef;
   la.ecoef = hp->entropy_coef;
   la.count = L->counts;
+  la.loss_sum = L->scalars + 2;
+  la.done_counter = L->loss_done;
+  la.error_flag = L->err_dev;
   int nparts = 0;
   if (int rc = heads_loss_backward(L->Pv, L->acts, n, la, L->loss_partials, &nparts, L->stream))
     return rc;
   if (int rc = backward(L, mbatch->observations, n))
     return rc;
-  if (int rc = finalize_metrics(L->loss_partials, nparts, L->counts, nullptr, 0, L->scalars + 1,
-                                L->stream))
+  if (int rc = finalize_metrics(L->scalars + 2, L->counts, nullptr, 0, L->scalars + 1, L->stream))
     return rc;
   if (logits)
     ALEGPU_CUDA_CHECK(cudaMemcpyAsync(logits, L->acts.logits, sizeof(float) * n * A,
@@ -916,10 +952,19 @@ extern "C" int alegpu_learner_train_ex(alegpu_learner *L, const alegpu_batch *ba
   alegpu_train_options opt{};
   if (options)
     opt = *options;
+  ALEGPU_REQUIRE(!opt.clip_value_loss || batch->values, ALEGPU_INVALID_ARGUMENT,
+                 "train: clip_value_loss needs batch.values (the values stored at collection time)");
+  if (int rc = learner_input_error(L))
+    return rc;
   if (opt.indices) {
     if (int rc = ensure_staging(L))
       return rc;
-    int bad = 0; // a previous shuffled train() found an index outside [0, N)
+    // every index is validated BEFORE anything trains on it (an index_select in the reference
+    // would throw before the first optimiser step): one pass over the index vector + one 4-byte read
+    if (int rc = launch_check_indices(opt.indices, num_epochs * batch->size, batch->size,
+                                      L->gather_error, L->stream))
+      return rc;
+    int bad = 0;
     ALEGPU_CUDA_CHECK(cudaMemcpyAsync(&bad, L->gather_error, sizeof(int), cudaMemcpyDeviceToHost,
                                       L->stream));
     ALEGPU_CUDA_CHECK(cudaStreamSynchronize(L->stream));
@@ -951,6 +996,7 @@ extern "C" int alegpu_learner_train_ex(alegpu_learner *L, const alegpu_batch *ba
   key_push(key, hp->clip_param); key_push(key, hp->value_loss_coef);
   key_push(key, hp->entropy_coef); key_push(key, hp->max_gradient_norm);
   key_push(key, opt.indices); key_push(key, opt.normalize_advantages);
+  key_push(key, opt.clip_value_loss); key_push(key, batch->values);
   if (!L->graph_exec || key != L->graph_key) {
     if (L->graph_exec) {
       cudaGraphExecDestroy(L->graph_exec);
@@ -962,8 +1008,11 @@ extern "C" int alegpu_learner_train_ex(alegpu_learner *L, const alegpu_batch *ba
     cudaGraph_t graph = nullptr;
     cudaError_t ce = cudaStreamEndCapture(L->stream, &graph);
     L->host_step = step_before; // capture enqueued nothing; the replay below advances it
-    if (rc)
+    if (rc) {
+      if (graph)
+        cudaGraphDestroy(graph);
       return rc;
+    }
     if (ce != cudaSuccess)
       return fail(ALEGPU_CUDA_ERROR, std::string("cudaStreamEndCapture: ") + cudaGetErrorString(ce));
     ce = cudaGraphInstantiate(&L->graph_exec, graph, 0);

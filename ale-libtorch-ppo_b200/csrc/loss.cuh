@@ -10,6 +10,13 @@
 // Backward rule for min/clamp (torch semantics): clamp passes gradient on the CLOSED range
 // and min splits ties 1/2+1/2, so d surr/d rho = A when 1-e <= rho <= 1+e or the unclipped
 // branch is the strict minimum, else 0.
+//
+// Opt-in clipped value loss (north_star / SURVEY D3; absent from the reference, losses.cc:15 is the
+// plain form): with v_old the value stored at collection time (ai::buffer::Batch.values, buffer.h:11)
+//   v_clip = v_old + clamp(v - v_old, -e, e);  vl = 0.5 max((v-R)^2, (v_clip-R)^2)
+// (the CleanRL form the reference's README compares against, same e as the policy clip).  Backward
+// with torch semantics: max routes to the larger branch (ties split 1/2 + 1/2), clamp passes the
+// gradient on the closed range.
 #pragma once
 #include "common.cuh"
 
@@ -25,7 +32,8 @@ template <int kMaxA>
 __device__ __forceinline__ PpoSample ppo_sample(const float *z, const float *old_lp, int A,
                                                 int action, float adv, float v, float ret,
                                                 float clip, float vcoef, float ecoef,
-                                                float scale, float *dz, float *dv) {
+                                                float scale, float *dz, float *dv,
+                                                bool clip_v = false, float old_v = 0.0f) {
   float mx = z[0];
   for (int j = 1; j < A; ++j)
     mx = fmaxf(mx, z[j]);
@@ -58,7 +66,17 @@ __device__ __forceinline__ PpoSample ppo_sample(const float *z, const float *old
   const float un = rho * adv, cl = crho * adv;
   o.surr = fminf(un, cl);
   const float d = v - ret;
-  o.value_loss = 0.5f * (d * d);
+  float dvl = d; // d value_loss / d v
+  if (!clip_v) {
+    o.value_loss = 0.5f * (d * d);
+  } else {
+    const float dv_old = v - old_v;
+    const float vc = old_v + fminf(fmaxf(dv_old, -clip), clip);
+    const float dc = vc - ret, lu = d * d, lc = dc * dc;
+    const float gc = (dv_old >= -clip && dv_old <= clip) ? dc : 0.0f; // through the clamp
+    o.value_loss = 0.5f * fmaxf(lu, lc);
+    dvl = lu > lc ? d : (lu < lc ? gc : 0.5f * d + 0.5f * gc);
+  }
   o.entropy = ent;
   o.total = -o.surr + vcoef * o.value_loss - ecoef * ent;
   o.ratio = rho;
@@ -81,7 +99,7 @@ __device__ __forceinline__ PpoSample ppo_sample(const float *z, const float *old
         dz[j] = (g[j] - p[j] * gsum) * scale; // log-softmax backward
   }
   if (dv)
-    *dv = vcoef * d * scale;
+    *dv = vcoef * dvl * scale;
   return o;
 }
 

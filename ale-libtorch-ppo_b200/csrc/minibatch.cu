@@ -3,6 +3,8 @@
 // advantage normalisation.  The reference slices contiguously and never normalises
 // (src/ai/ppo/train.h:146-151 — its randperm is generated but not consumed), so both are OFF
 // unless alegpu_train_options asks for them (include/alegpu.h).
+#include <algorithm>
+
 #include "minibatch.h"
 
 namespace alegpu {
@@ -15,16 +17,26 @@ __global__ void __launch_bounds__(256)
     gather_rows_kernel(const int64_t *__restrict__ idx, int64_t n_rows_src, int A,
                        const uint8_t *__restrict__ obs, const int64_t *__restrict__ actions,
                        const float *__restrict__ logp, const float *__restrict__ adv,
-                       const float *__restrict__ ret, const uint8_t *__restrict__ masks,
-                       uint8_t *__restrict__ o_obs, int64_t *__restrict__ o_actions,
+                       const float *__restrict__ ret, const float *__restrict__ values,
+                       const uint8_t *__restrict__ masks, uint8_t *__restrict__ o_obs, int64_t *__restrict__ o_actions,
                        float *__restrict__ o_logp, float *__restrict__ o_adv,
-                       float *__restrict__ o_ret, uint8_t *__restrict__ o_masks,
-                       int *__restrict__ error_flag) {
+                       float *__restrict__ o_ret, float *__restrict__ o_values,
+                       uint8_t *__restrict__ o_masks, int *__restrict__ error_flag) {
   const int64_t i = blockIdx.x;
-  const int64_t src = idx[i];
-  if (src < 0 || src >= n_rows_src) { // std::out_of_range in a torch index_select; reported once
-    if (threadIdx.x == 0)
-      atomicExch(error_flag, 1);
+  int64_t src = idx[i];
+  if (src < 0 || src >= n_rows_src) { // std::out_of_range in a torch index_select; reported by the
+    if (threadIdx.x == 0)             // SAME train() call (checked before it returns); the staged row
+      atomicExch(error_flag, 1);      // is zero-filled and masked out, never stale
+    uint4 *d = reinterpret_cast<uint4 *>(o_obs + i * 28224);
+    for (int c = threadIdx.x; c < 1764; c += 256)
+      d[c] = make_uint4(0u, 0u, 0u, 0u);
+    if (threadIdx.x < A)
+      o_logp[i * A + threadIdx.x] = 0.0f;
+    if (threadIdx.x == 32) o_actions[i] = 0;
+    if (threadIdx.x == 33) o_adv[i] = 0.0f;
+    if (threadIdx.x == 34) o_ret[i] = 0.0f;
+    if (threadIdx.x == 35) o_masks[i] = 0;
+    if (threadIdx.x == 36 && o_values) o_values[i] = 0.0f;
     return;
   }
   const uint4 *s = reinterpret_cast<const uint4 *>(obs + src * 28224);
@@ -42,6 +54,17 @@ __global__ void __launch_bounds__(256)
   if (threadIdx.x == 33) o_adv[i] = adv[src];
   if (threadIdx.x == 34) o_ret[i] = ret[src];
   if (threadIdx.x == 35) o_masks[i] = masks[src];
+  if (threadIdx.x == 36 && values) o_values[i] = values[src];
+}
+
+__global__ void check_indices_kernel(const int64_t *__restrict__ idx, int64_t n, int64_t n_rows_src,
+                                     int *__restrict__ error_flag) {
+  bool bad = false;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    bad |= idx[i] < 0 || idx[i] >= n_rows_src;
+  if (bad)
+    atomicExch(error_flag, 1);
 }
 
 // (count, sum, sum of squares) of the unmasked advantages of one minibatch, in double, one CTA,
@@ -91,14 +114,25 @@ __global__ void __launch_bounds__(1024)
 
 int launch_gather_rows(const int64_t *idx, int64_t n, int64_t n_rows_src, int A,
                        const uint8_t *obs, const int64_t *actions, const float *logp,
-                       const float *adv, const float *ret, const uint8_t *masks,
-                       const StagedBatch &out, int *error_flag, cudaStream_t s) {
+                       const float *adv, const float *ret, const float *values,
+                       const uint8_t *masks, const StagedBatch &out, int *error_flag, cudaStream_t s) {
   if (n == 0)
     return ALEGPU_OK;
   ALEGPU_REQUIRE(A <= 32, ALEGPU_INVALID_ARGUMENT, "gather: action_size > 32");
   gather_rows_kernel<<<(unsigned)n, 256, 0, s>>>(idx, n_rows_src, A, obs, actions, logp, adv, ret,
-                                                 masks, out.obs, out.actions, out.logp, out.adv,
-                                                 out.ret, out.masks, error_flag);
+                                                 values, masks, out.obs, out.actions, out.logp,
+                                                 out.adv, out.ret, out.values, out.masks, error_flag);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}
+
+int launch_check_indices(const int64_t *idx, int64_t n, int64_t n_rows_src, int *error_flag,
+                         cudaStream_t s) {
+  if (n == 0)
+    return ALEGPU_OK;
+  check_indices_kernel<<<(unsigned)std::min<int64_t>(ceil_div(n, 256), 2 * kNumSMs), 256, 0, s>>>(
+      idx, n, n_rows_src, error_flag);
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
   return ALEGPU_OK;

@@ -10,14 +10,18 @@ struct StagedBatch {
   int64_t *actions = nullptr; // [cap]
   float *logp = nullptr;      // [cap,A]
   float *adv = nullptr, *ret = nullptr;
+  float *values = nullptr;    // [cap] old values (clipped value loss only)
   uint8_t *masks = nullptr;
 };
 
 // out row i = source row idx[i] (i < n); an index outside [0, n_rows_src) sets *error_flag
 int launch_gather_rows(const int64_t *idx, int64_t n, int64_t n_rows_src, int A,
                        const uint8_t *obs, const int64_t *actions, const float *logp,
-                       const float *adv, const float *ret, const uint8_t *masks,
-                       const StagedBatch &out, int *error_flag, cudaStream_t s);
+                       const float *adv, const float *ret, const float *values /* may be null */,
+                       const uint8_t *masks, const StagedBatch &out, int *error_flag, cudaStream_t s);
+// *error_flag = 1 if any idx[i] (i < n) lies outside [0, n_rows_src)
+int launch_check_indices(const int64_t *idx, int64_t n, int64_t n_rows_src, int *error_flag,
+                         cudaStream_t s);
 // stats[0..2] = (count, sum, sum of squares) of adv over rows with masks != 0, in double
 int launch_adv_stats(const float *adv, const uint8_t *masks, int64_t n, double *stats,
                      cudaStream_t s);

@@ -65,6 +65,13 @@ struct LossArgs {
   // optional advantage normalisation: (count, sum, sum of squares) of the minibatch's unmasked
   // advantages in double; adv' = (adv - mean) / (std + 1e-8), unbiased std.  nullptr = off.
   const double *adv_stats;
+  // optional clipped value loss (loss.cuh): the values stored at collection time; nullptr = off
+  const float *old_values;
+  // the LAST block of the heads kernel sums the per-block loss partials in index order into
+  // *loss_sum (un-normalised: divide by *count); done_counter is a zeroed device counter it resets
+  float *loss_sum;
+  unsigned int *done_counter;
+  int *error_flag; // optional: set to 1 when an action index lies outside [0, A)
   // per-sample metric outputs at their final offsets (any may be null) — Metrics::set, train.h:93-108
   float *m_clipped, *m_value, *m_entropy, *m_total, *m_ratio, *m_adv, *m_ret;
   uint8_t *m_masks;
@@ -85,9 +92,9 @@ int heads_loss_backward(const NetParams &P, NetActs &A, int64_t n, const LossArg
 // gradients of piw/pib/vw/vb from A.dout and A.fc (split over rows, fixed-order reduce)
 int heads_wgrad(const NetParams &G, const NetActs &A, int64_t n, float *ws, size_t ws_floats,
                 cudaStream_t s);
-// Metrics::set tail: loss (broadcast over mb) = sum(partials)/count; loss_out[0] if non-null
-int finalize_metrics(const float *loss_partials, int nparts, const float *count, float *m_loss,
-                     int64_t mb, float *loss_out, cudaStream_t s);
+// Metrics::set tail: loss (broadcast over mb) = *loss_sum / *count; loss_out[0] if non-null
+int finalize_metrics(const float *loss_sum, const float *count, float *m_loss, int64_t mb,
+                     float *loss_out, cudaStream_t s);
 
 // loss.cu
 int launch_mask_count(const uint8_t *masks, int64_t n, int64_t groups, float *count,

@@ -25,7 +25,8 @@ namespace {
 constexpr int kThreads = 256;
 
 __global__ void __launch_bounds__(kThreads)
-    grad_sumsq_kernel(const float *__restrict__ g, int64_t n4, float *__restrict__ partials,
+    grad_sumsq_kernel(const float *__restrict__ g, int64_t n4, int64_t n_valid,
+                      float *__restrict__ partials,
                       OptState *__restrict__ st, float max_norm, float *__restrict__ total_norm_out) {
   __shared__ float red[kThreads / 32];
   __shared__ bool s_last;
@@ -33,7 +34,13 @@ __global__ void __launch_bounds__(kThreads)
   const float4 *g4 = reinterpret_cast<const float4 *>(g);
   for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n4;
        i += (int64_t)gridDim.x * kThreads) {
-    const float4 x = g4[i];
+    float4 x = g4[i];
+    if (4 * i + 3 >= n_valid) { // the padding behind the last parameter is not part of the norm
+      x.y = 4 * i + 1 < n_valid ? x.y : 0.0f;
+      x.z = 4 * i + 2 < n_valid ? x.z : 0.0f;
+      x.w = 0.0f;
+      x.x = 4 * i < n_valid ? x.x : 0.0f;
+    }
     acc += x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
   }
   acc = block_sum<float, kThreads>(acc, red);
@@ -162,10 +169,10 @@ __global__ void f32_to_bf16_kernel(const float *__restrict__ src, __nv_bfloat16 
 
 } // namespace
 
-int launch_grad_sumsq(const float *grads, int64_t n_padded, float *partials, OptState *st,
-                      float max_norm, float *total_norm_out, cudaStream_t s) {
-  grad_sumsq_kernel<<<kNormBlocks, kThreads, 0, s>>>(grads, n_padded / 4, partials, st, max_norm,
-                                                     total_norm_out);
+int launch_grad_sumsq(const float *grads, int64_t n_padded, int64_t n_valid, float *partials,
+                      OptState *st, float max_norm, float *total_norm_out, cudaStream_t s) {
+  grad_sumsq_kernel<<<kNormBlocks, kThreads, 0, s>>>(grads, n_padded / 4, n_valid, partials, st,
+                                                     max_norm, total_norm_out);
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
   return ALEGPU_OK;

@@ -19,8 +19,9 @@ constexpr int kNormBlocks = 296; // 2 CTAs per SM, fixed => bit-reproducible par
 
 // partial sums of g^2; the last block to finish sums them in fixed order, advances the step counter
 // and leaves the clip coefficient / bias corrections in *st; total_norm_out <- the PRE-clip norm
-int launch_grad_sumsq(const float *grads, int64_t n_padded, float *partials, OptState *st,
-                      float max_norm, float *total_norm_out, cudaStream_t s);
+// (over the first n_valid of the n_padded floats)
+int launch_grad_sumsq(const float *grads, int64_t n_padded, int64_t n_valid, float *partials,
+                      OptState *st, float max_norm, float *total_norm_out, cudaStream_t s);
 // shadow (optional): operand-type copy of the parameters for the tensor-core path, bf16
 // (shadow_elem_bytes 2) or tf32-rounded fp32 (4); c1w_perm: [32][256] conv1 weights of the same type
 // in the space-to-depth k' order

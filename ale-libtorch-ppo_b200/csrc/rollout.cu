@@ -7,6 +7,7 @@
 // place (alegpu_preprocess_step -> slot t+1) get the raw pointers through alegpu_rollout_view.
 // `get` = fused clamp + GAE + returns + masks (gae.cu) + log-softmax of the stored logits.
 #include <algorithm>
+#include <cstdlib>
 #include <vector>
 
 #include "net.h"
@@ -174,6 +175,9 @@ extern "C" int alegpu_rollout_ingest(alegpu_rollout *r, const uint8_t *frames_ho
   if (!r->copy_stream) {
     const int64_t fit = (int64_t)(alegpu_rollout::kRingBytes / slab);
     r->ring_slots = (int)std::max<int64_t>(alegpu_rollout::kMinRing, std::min<int64_t>(T, fit));
+    if (const char *e = getenv("ALEGPU_RING_SLOTS")) // test knob: force the per-step ring branch
+      if (atoi(e) >= 2)
+        r->ring_slots = atoi(e);
     ALEGPU_CUDA_CHECK(cudaMalloc(&r->ring, slab * (size_t)r->ring_slots));
     ALEGPU_CUDA_CHECK(cudaStreamCreateWithFlags(&r->copy_stream, cudaStreamNonBlocking));
     r->copied.assign((size_t)r->ring_slots, nullptr);
@@ -267,6 +271,7 @@ extern "C" int alegpu_rollout_get(alegpu_rollout *r, const float *next_values, f
     flat->returns = r->returns;
     flat->masks = r->masks;
     flat->size = r->E * r->T;
+    flat->values = r->values; // ai::buffer::Batch.values (buffer.h:11), for the opt-in clipped value loss
   }
   if (!(flags & 1)) {
     int h = 0;

@@ -17,7 +17,11 @@
 // core reads the upper 19 bits; producers round with cvt.rna.tf32 where they create the data); the
 // default is 2 (bf16).  A k-block is always 128 bytes of reduction per row: 64 bf16 or 32 tf32
 // elements = 4 UMMAs (K = 16 / K = 8), a 16-byte chunk is 8 bf16 / 4 tf32 elements, and the
-// byte layouts below are the same for both (MN-major atoms are 64 / 32 rows x 8 reduction indices).
+// K-major byte layout below is the same for both.  MN-major tf32 operands have ONE legal layout,
+// SWIZZLE_128B_BASE32B (descriptor layout type 1): atoms of 32 rows x 4 reduction indices (512 B), the
+// 128-byte row of reduction index kr swizzled in 32-byte units: 16-byte chunk c sits at
+// kr*128 + (((c>>1) ^ kr) << 5) + ((c&1) << 4); reduction groups of 4 are 512 B apart (SBO), 32-row
+// blocks 4096 B (LBO); one UMMA (K = 8) spans two groups = 1024 B.
 //
 // Shared-memory tile layouts (one k-block = 64 bf16 / 32 tf32 reduction elements):
 //   K-major operand  (reduction index contiguous in the 16-byte chunk):
@@ -156,15 +160,27 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
 // ---- descriptors ----------------------------------------------------------------------------------
 // UMMA shared-memory descriptor (SWIZZLE_128B): start>>4 [0,14) | LBO>>4 [16,30) | SBO>>4 [32,46)
 // | version=1 [46,48) | layout_type=2 [61,64)
+// layout_type: 2 = SWIZZLE_128B, 1 = SWIZZLE_128B_BASE32B (the MN-major tf32 layout)
 __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes,
-                                                   uint32_t sbo_bytes) {
+                                                   uint32_t sbo_bytes, uint32_t layout_type = 2u) {
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr >> 4) & 0x3FFFu);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
   d |= (uint64_t)1 << 46;
-  d |= (uint64_t)2 << 61;
+  d |= (uint64_t)layout_type << 61;
   return d;
+}
+// byte offset inside an MN-major tile of the 16-byte chunk c (8 bf16 / 4 tf32 rows) of reduction index k
+template <int kEB> __device__ __forceinline__ uint32_t mn_chunk_offset(int c, int k) {
+  if constexpr (kEB == 2) { // 64-row x 8-k atoms (1024 B), 16-byte swizzle; 64-row blocks 8192 B apart
+    const int kr = k & 7;
+    return (uint32_t)((c >> 3) * 8192 + (k >> 3) * 1024 + kr * 128 + (((c & 7) ^ kr) << 4));
+  } else { // 32-row x 4-k atoms (512 B), 32-byte swizzle; 32-row blocks 4096 B apart
+    const int kr = k & 3, cc = c & 7;
+    return (uint32_t)((c >> 3) * 4096 + (k >> 2) * 512 + kr * 128 + (((cc >> 1) ^ kr) << 5) +
+                      ((cc & 1) << 4));
+  }
 }
 // UMMA instruction descriptor, kind::f16 / kind::tf32: D=f32, A=B=bf16 (format 1) or tf32 (format 2),
 // M=128, N=BN, per-operand major bits
@@ -331,7 +347,6 @@ template <int ROWS, class Op> struct AsyncCtx<ROWS, Op, true, false> {
   static constexpr int kEB = ElemBytes<Op>::value;
   static constexpr int kEPC = 16 / kEB;               // elements per 16-byte chunk
   static constexpr int kRowChunks = ROWS / kEPC;      // MN-major: chunks along the row index
-  static constexpr uint32_t kAtomLBO = (uint32_t)(bk_of(kEB) / 8) * 1024u; // bytes between MN atoms
   static_assert(Op::kMN ? kProducers % kRowChunks == 0 : true, "row chunks must divide 256");
   static constexpr int kCtx = Op::kMN ? 1 : kPer;
   typename Op::RowCtx rc[kCtx];
@@ -354,7 +369,7 @@ template <int ROWS, class Op> struct AsyncCtx<ROWS, Op, true, false> {
       const int i = row0 + c * kEPC;
       rc[0] = op.row(i < rows_total ? i : row0);
       valid = i < rows_total ? 1u : 0u;
-      off0 = (uint32_t)(c >> 3) * kAtomLBO;
+      off0 = 0u;
     }
   }
   __device__ __forceinline__ void issue(const Op &op, uint32_t tile, int r0, int r_end, int z,
@@ -372,9 +387,9 @@ template <int ROWS, class Op> struct AsyncCtx<ROWS, Op, true, false> {
       const int c = ptid % kRowChunks, k0 = ptid / kRowChunks;
 #pragma unroll
       for (int it = 0; it < kPer; ++it) {
-        const int k = k0 + it * (kProducers / kRowChunks), kr = k & 7;
+        const int k = k0 + it * (kProducers / kRowChunks);
         const int r = r0 + k;
-        const uint32_t off = off0 + (uint32_t)((k >> 3) * 1024 + kr * 128 + (((c & 7) ^ kr) << 4));
+        const uint32_t off = off0 + mn_chunk_offset<kEB>(c, k);
         const void *src = nullptr;
         if (valid && r < r_end)
           src = op.at(rc[0], op.col(r, z));
@@ -598,12 +613,16 @@ __global__ void __launch_bounds__(kThreads, BN <= 128 ? 2 : 1)
         mbar_wait(&full_bar[s], ph);
         tc_fence_after();
         const uint32_t a_addr = smem_u32(tiles + s * kStage), b_addr = a_addr + kATile;
-        // MN-major: LBO = bytes between the 64-row (bf16) / 32-row (tf32) atoms = one k-block of
-        // 8-index groups; one UMMA (K = 16 bf16 / 8 tf32) spans 2 / 1 of those 1024-byte groups
-        constexpr uint32_t kLboMN = (uint32_t)(BK / 8) * 1024u;
-        constexpr int kUmmaK = 32 / kEB, kAdvMN = (kUmmaK / 8) * 1024 / 16;
-        const uint64_t adesc = make_smem_desc(a_addr, AOp::kMN ? kLboMN : 16u, 1024u);
-        const uint64_t bdesc = make_smem_desc(b_addr, BOp::kMN ? kLboMN : 16u, 1024u);
+        // MN-major (see mn_chunk_offset): bf16 LBO 8192 / SBO 1024 / SWIZZLE_128B, one UMMA (K = 16)
+        // = two 8-index groups = 2048 B; tf32 LBO 4096 / SBO 512 / SWIZZLE_128B_BASE32B, one UMMA
+        // (K = 8) = two 4-index groups = 1024 B.  K-major: SBO 1024, SWIZZLE_128B, 32 B per UMMA.
+        constexpr uint32_t kLboMN = kEB == 2 ? 8192u : 4096u, kSboMN = kEB == 2 ? 1024u : 512u;
+        constexpr uint32_t kTypeMN = kEB == 2 ? 2u : 1u;
+        constexpr int kUmmaK = 32 / kEB, kAdvMN = (kEB == 2 ? 2048 : 1024) / 16;
+        const uint64_t adesc = AOp::kMN ? make_smem_desc(a_addr, kLboMN, kSboMN, kTypeMN)
+                                        : make_smem_desc(a_addr, 16u, 1024u);
+        const uint64_t bdesc = BOp::kMN ? make_smem_desc(b_addr, kLboMN, kSboMN, kTypeMN)
+                                        : make_smem_desc(b_addr, 16u, 1024u);
 #pragma unroll
         for (int kk = 0; kk < BK / kUmmaK; ++kk) {
           const uint64_t ad = adesc + (uint64_t)(kk * (AOp::kMN ? kAdvMN : 2));

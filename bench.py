@@ -206,7 +206,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="v0", choices=list(WORKLOADS))
-    ap.add_argument("--math", default=os.environ.get("ALEGPU_MATH", "bf16"), choices=["fp32", "bf16"])
+    ap.add_argument("--math", default=os.environ.get("ALEGPU_MATH", "bf16"), choices=["fp32", "bf16", "tf32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
     args = ap.parse_args()
@@ -237,7 +237,7 @@ def main():
     E, T, H, epochs, nmb, A = w["E"], w["T"], w["H"], w["epochs"], w["nmb"], 4
     N = E * T
     mb = N // nmb
-    math = alegpu.MATH_BF16 if args.math == "bf16" else alegpu.MATH_FP32
+    math = {"bf16": alegpu.MATH_BF16, "tf32": alegpu.MATH_TF32, "fp32": alegpu.MATH_FP32}[args.math]
 
     # ---- synthetic inputs (seeded; different env slice per rank) ------------------------------
     s, pool = synth_inputs(w, seed=42 + rank)
@@ -454,7 +454,7 @@ def main():
     line = {"metric": METRIC, "value": value, "unit": "agent-steps/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16" if math == alegpu.MATH_BF16 else "f32", "data": "synthetic",
+            "dtype": {"bf16": "bf16", "tf32": "tf32", "fp32": "f32"}[args.math], "data": "synthetic",
             "config": {"workload": args.workload, "envs_per_gpu": E, "horizon": T, "hidden_size": H,
                        "num_epochs": epochs, "num_mini_batches": nmb, "mini_batch_per_gpu": mb,
                        "cuda_graph": use_graph, "math": args.math,

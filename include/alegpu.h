@@ -171,6 +171,50 @@ int alegpu_trace_end(char *out, size_t out_bytes);
 /* a fresh 128-byte ncclUniqueId (rank 0 creates it, the host broadcasts it) */
 int alegpu_nccl_unique_id(void *out128);
 
+/* ---- configs/<name>.yaml: Config + load_config — src/bin/train.cc:33-60, 108-136 -------------------
+ * The reference's flat YAML schema, key for key, with its inline defaults (:111-134).  size_t keys
+ * are int64 here, bools are int.  action_size is in the shipped files but never read by the
+ * reference (`const size_t action_size = 4`, :36): it is accepted and forced to 4.  The last four
+ * members are this library's opt-in extras (absent keys = reference semantics). */
+typedef struct {
+  int64_t total_environments; /* 512    */
+  int64_t hidden_size;        /* 512    */
+  int64_t horizon;            /* 128    */
+  int64_t max_steps;          /* 108000 */
+  int64_t frame_stack;        /* 4      */
+  double learning_rate;       /* 2.5e-4 */
+  float clip_param;           /* 0.1    */
+  float value_loss_coef;      /* 0.5    */
+  float entropy_coef;         /* 0.01   */
+  int64_t num_epochs;         /* 1      */
+  int64_t mini_batch_size;    /* 2048   */
+  int64_t num_mini_batches;   /* 32     */
+  float gae_discount;         /* 0.99   */
+  float gae_lambda;           /* 0.95   */
+  float max_gradient_norm;    /* 0.5    */
+  int64_t num_rollouts;       /* 7000   */
+  int64_t num_workers;        /* 16     */
+  int64_t worker_batch_size;  /* 32     */
+  int64_t frame_skip;         /* 4      */
+  float max_return;           /* -1     */
+  int record_observation, record_video, cuda_graph, deterministic; /* false */
+  int64_t action_size;        /* always 4 */
+  int normalize_advantages;   /* extra (alegpu_train_options), default 0 */
+  int clip_value_loss;        /* extra (alegpu_train_options), default 0 */
+  int shuffle;                /* extra: the host passes a randperm per epoch as options.indices */
+  int64_t num_gpus;           /* extra: ranks the envs are sharded over, default 1 */
+} alegpu_config;
+int alegpu_config_defaults(alegpu_config *config);
+/* load_config(path): a missing file or a scalar that does not convert -> ALEGPU_RUNTIME_ERROR
+ * (YAML::BadFile / YAML::BadConversion are std::runtime_error); unknown keys are ignored. */
+int alegpu_config_load(const char *path, alegpu_config *config);
+int alegpu_config_parse(const char *yaml_text, alegpu_config *config);
+/* What the reference leaves unchecked: `mini_batch_size` only sizes its Metrics tensors
+ * (src/bin/train.cc:383-387) while train() slices E*T / num_mini_batches rows (train.h:139-151).
+ * mini_batch_size * num_mini_batches != total_environments * horizon -> ALEGPU_INVALID_ARGUMENT;
+ * E*T not divisible by num_mini_batches -> ALEGPU_RUNTIME_ERROR (train.h:140-143). */
+int alegpu_config_validate(const alegpu_config *config);
+
 /* ---- the learner: policy + optimiser + trainer ----------------------------------------- */
 typedef struct alegpu_learner alegpu_learner;
 typedef struct alegpu_rollout alegpu_rollout;
@@ -212,6 +256,9 @@ typedef struct {
   const float *returns;           /* [N] */
   const uint8_t *masks;           /* [N] */
   int64_t size;                   /* N */
+  const float *values;            /* [N] values stored at collection time (ai::buffer::Batch.values,
+                                     src/ai/buffer.h:11; prepare_batch drops them, src/bin/train.cc:272-283):
+                                     read only when alegpu_train_options.clip_value_loss; may be NULL */
 } alegpu_batch;
 
 /* ai::ppo::train::Metrics — src/ai/ppo/train.h:64-109: [epochs,nmb,mb] f32 (masks 1-byte),
@@ -368,14 +415,19 @@ int alegpu_learner_train(alegpu_learner *learner, const alegpu_batch *batch,
  *   indices: DEVICE [num_epochs * N] int64; minibatch k of epoch e trains on rows
  *            indices[e*N + k*mb .. e*N + (k+1)*mb) (one randperm(N) per epoch gives the usual PPO
  *            shuffle), gathered by one HBM-bound kernel (2 x 28 224 + 45 B per row).  The per-sample
- *            metrics at [e,k,:] then describe the gathered rows.  An index outside [0,N) makes the
- *            NEXT shuffled train call fail with ALEGPU_OUT_OF_RANGE (checked on the device).
+ *            metrics at [e,k,:] then describe the gathered rows.  An index outside [0,N) makes THIS
+ *            call fail with ALEGPU_OUT_OF_RANGE before anything is trained (one validation pass over
+ *            the index vector and a 4-byte read-back: shuffled calls synchronise once).
  *   normalize_advantages: A' = (A - mean) / (std + 1e-8) per minibatch, mean and unbiased std over
  *            the minibatch's UNMASKED rows (over all ranks when world_size > 1); Metrics.advantages
- *            stays the raw value. */
+ *            stays the raw value.
+ *   clip_value_loss: value loss = 0.5 max((v-R)^2, (v_old + clamp(v-v_old, -clip_param, clip_param) - R)^2)
+ *            with v_old = batch.values (north_star's "clipped value" loss; the reference has
+ *            the plain 0.5 (v-R)^2, src/ai/ppo/losses.cc:15).  Metrics.value_losses holds the clipped form. */
 typedef struct {
   const int64_t *indices;
   int normalize_advantages;
+  int clip_value_loss;
 } alegpu_train_options;
 int alegpu_learner_train_ex(alegpu_learner *learner, const alegpu_batch *batch,
                             const alegpu_metrics *metrics, int64_t num_epochs,

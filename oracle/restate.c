@@ -154,11 +154,15 @@ void rs_log_softmax(const float *logits, int64_t n, int64_t A, float *out) { /* 
  * Outputs per sample: clipped (surrogate), value_losses, entropies, total_losses, ratio;
  * scalar loss = sum(mask*total)/sum(mask) (losses.cc:19); dlogits/dvalues = d loss / d(raw
  * logits, value).  inv_count_override > 0 replaces 1/sum(mask) (multi-GPU global count). */
-int rs_loss(const float *logits, const float *old_log_probs, const int64_t *actions,
-            const float *advantages, const float *values, const float *returns,
-            const uint8_t *masks, int64_t n, int64_t A, float clip, float vcoef, float ecoef,
-            float *loss, float *clipped, float *value_losses, float *entropies,
-            float *total_losses, float *ratio, float *dlogits, float *dvalues) {
+/* old_values != NULL: the opt-in clipped value loss (NOT in the reference, losses.cc:15 is the plain
+ * form; north_star / SURVEY D3): vl = 0.5 max((v-R)^2, (v_old + clamp(v-v_old, -clip, clip) - R)^2),
+ * backward with torch semantics (max -> larger branch, ties 1/2 + 1/2; clamp passes on the closed range) */
+int rs_loss_ex(const float *logits, const float *old_log_probs, const int64_t *actions,
+               const float *advantages, const float *values, const float *returns,
+               const uint8_t *masks, int64_t n, int64_t A, float clip, float vcoef, float ecoef,
+               float *loss, float *clipped, float *value_losses, float *entropies,
+               float *total_losses, float *ratio, float *dlogits, float *dvalues,
+               const float *old_values) {
   float *logp = (float *)malloc(sizeof(float) * (size_t)(n * A));
   rs_log_softmax(logits, n, A, logp);
   double count = 0.0;
@@ -175,7 +179,17 @@ int rs_loss(const float *logits, const float *old_log_probs, const int64_t *acti
     const float un = rho * adv, cl = crho * adv;                       /* losses.cc:36-37 */
     const float surr = un < cl ? un : cl;                              /* losses.cc:38 */
     const float dv = values[i] - returns[i];
-    const float vl = 0.5f * (dv * dv);                                 /* losses.cc:15 */
+    float vl = 0.5f * (dv * dv);                                       /* losses.cc:15 */
+    float dvl = dv;
+    if (old_values) {
+      const float d0 = values[i] - old_values[i];
+      const float cd = d0 < -clip ? -clip : (d0 > clip ? clip : d0);
+      const float dc = old_values[i] + cd - returns[i];
+      const float lu = dv * dv, lc = dc * dc;
+      const float gc = (d0 >= -clip && d0 <= clip) ? dc : 0.0f;
+      vl = 0.5f * (lu > lc ? lu : lc);
+      dvl = lu > lc ? dv : (lu < lc ? gc : 0.5f * dv + 0.5f * gc);
+    }
     float ent = 0.0f;
     for (int64_t j = 0; j < A; ++j)
       ent += expf(lp[j]) * lp[j];
@@ -206,7 +220,7 @@ int rs_loss(const float *logits, const float *old_log_probs, const int64_t *acti
         dlogits[i * A + j] = (g[j] - expf(lp[j]) * gsum) * scale; /* log-softmax backward */
     }
     if (dvalues)
-      dvalues[i] = vcoef * dv * scale;
+      dvalues[i] = vcoef * dvl * scale;
   }
   if (loss)
     *loss = (float)(acc / count);
@@ -406,16 +420,26 @@ float rs_clip_adam(float *params, float *grads, float *m, float *v, int64_t hidd
   return total;
 }
 
+int rs_loss(const float *logits, const float *old_log_probs, const int64_t *actions,
+            const float *advantages, const float *values, const float *returns,
+            const uint8_t *masks, int64_t n, int64_t A, float clip, float vcoef, float ecoef,
+            float *loss, float *clipped, float *value_losses, float *entropies,
+            float *total_losses, float *ratio, float *dlogits, float *dvalues) {
+  return rs_loss_ex(logits, old_log_probs, actions, advantages, values, returns, masks, n, A, clip,
+                    vcoef, ecoef, loss, clipped, value_losses, entropies, total_losses, ratio, dlogits,
+                    dvalues, NULL);
+}
+
 /* ---- train(): src/ai/ppo/train.h:114-157 ------------------------------------------------
  * Contiguous minibatch slices (the randperm at :146 is never consumed). metrics are
  * [epochs,nmb,mb] (m_gradnorm [epochs,nmb]); `step` in/out is the Adam step counter. */
-int rs_train(float *params, float *m, float *v, int64_t *step, int64_t hidden, int64_t actions,
-             const uint8_t *obs, const int64_t *act, const float *log_probs,
-             const float *advantages, const float *returns, const uint8_t *masks, int64_t N,
-             int64_t epochs, int64_t nmb, float clip, float vcoef, float ecoef, float max_norm,
-             double lr, float *m_loss, float *m_clipped, float *m_value, float *m_entropy,
-             float *m_ratio, float *m_total, float *m_adv, float *m_ret, uint8_t *m_masks,
-             float *m_gradnorm) {
+int rs_train_ex(float *params, float *m, float *v, int64_t *step, int64_t hidden, int64_t actions,
+                const uint8_t *obs, const int64_t *act, const float *log_probs,
+                const float *advantages, const float *returns, const uint8_t *masks, int64_t N,
+                int64_t epochs, int64_t nmb, float clip, float vcoef, float ecoef, float max_norm,
+                double lr, float *m_loss, float *m_clipped, float *m_value, float *m_entropy,
+                float *m_ratio, float *m_total, float *m_adv, float *m_ret, uint8_t *m_masks,
+                float *m_gradnorm, const float *old_values /* NULL = reference value loss */) {
   if (nmb <= 0 || N % nmb != 0)
     return RS_RUNTIME_ERROR; /* train.h:140-143 */
   const int64_t mb = N / nmb, P = rs_param_count(hidden, actions);
@@ -431,10 +455,11 @@ int rs_train(float *params, float *m, float *v, int64_t *step, int64_t hidden, i
       const int64_t s = k * mb, o = (ep * nmb + k) * mb;
       float loss;
       rs_net_forward(params, hidden, actions, obs + s * A0, mb, logits, vals, acts);
-      rs_loss(logits, log_probs + s * actions, act + s, advantages + s, vals, returns + s,
-              masks + s, mb, actions, clip, vcoef, ecoef, &loss, m_clipped ? m_clipped + o : NULL,
-              m_value ? m_value + o : NULL, m_entropy ? m_entropy + o : NULL,
-              m_total ? m_total + o : NULL, m_ratio ? m_ratio + o : NULL, dlog, dval);
+      rs_loss_ex(logits, log_probs + s * actions, act + s, advantages + s, vals, returns + s,
+                 masks + s, mb, actions, clip, vcoef, ecoef, &loss, m_clipped ? m_clipped + o : NULL,
+                 m_value ? m_value + o : NULL, m_entropy ? m_entropy + o : NULL,
+                 m_total ? m_total + o : NULL, m_ratio ? m_ratio + o : NULL, dlog, dval,
+                 old_values ? old_values + s : NULL);
       rs_net_backward(params, hidden, actions, acts, mb, dlog, dval, grads);
       *step += 1;
       const float tn = rs_clip_adam(params, grads, m, v, hidden, actions, *step, lr, max_norm);
@@ -448,4 +473,16 @@ int rs_train(float *params, float *m, float *v, int64_t *step, int64_t hidden, i
     }
   free(acts); free(logits); free(vals); free(dlog); free(dval); free(grads);
   return RS_OK;
+}
+
+int rs_train(float *params, float *m, float *v, int64_t *step, int64_t hidden, int64_t actions,
+             const uint8_t *obs, const int64_t *act, const float *log_probs,
+             const float *advantages, const float *returns, const uint8_t *masks, int64_t N,
+             int64_t epochs, int64_t nmb, float clip, float vcoef, float ecoef, float max_norm,
+             double lr, float *m_loss, float *m_clipped, float *m_value, float *m_entropy,
+             float *m_ratio, float *m_total, float *m_adv, float *m_ret, uint8_t *m_masks,
+             float *m_gradnorm) {
+  return rs_train_ex(params, m, v, step, hidden, actions, obs, act, log_probs, advantages, returns,
+                     masks, N, epochs, nmb, clip, vcoef, ecoef, max_norm, lr, m_loss, m_clipped,
+                     m_value, m_entropy, m_ratio, m_total, m_adv, m_ret, m_masks, m_gradnorm, NULL);
 }

@@ -112,7 +112,10 @@ def log_softmax(logits):
     return out
 
 
-def loss(logits, old_log_probs, actions, advantages, values, returns, masks, clip, vcoef, ecoef):
+def loss(logits, old_log_probs, actions, advantages, values, returns, masks, clip, vcoef, ecoef,
+         old_values=None):
+    """old_values: the opt-in clipped value loss (not in the reference; see restate.c rs_loss_ex)."""
+    ov = _c(old_values, np.float32) if old_values is not None else None
     z, ol = _c(logits, np.float32), _c(old_log_probs, np.float32)
     a = _c(actions, np.int64)
     adv, v, ret = (_c(x, np.float32) for x in (advantages, values, returns))
@@ -122,11 +125,12 @@ def loss(logits, old_log_probs, actions, advantages, values, returns, masks, cli
            ("clipped_losses", "value_losses", "entropies", "total_losses", "ratio", "dvalues")}
     out["dlogits"] = np.zeros((n, A), np.float32)
     ls = np.zeros(1, np.float32)
-    _check(lib().rs_loss(_f(z), _f(ol), _i(a), _f(adv), _f(v), _f(ret), _u(mk), C.c_int64(n),
-                         C.c_int64(A), C.c_float(clip), C.c_float(vcoef), C.c_float(ecoef),
-                         _f(ls), _f(out["clipped_losses"]), _f(out["value_losses"]),
-                         _f(out["entropies"]), _f(out["total_losses"]), _f(out["ratio"]),
-                         _f(out["dlogits"]), _f(out["dvalues"])))
+    _check(lib().rs_loss_ex(_f(z), _f(ol), _i(a), _f(adv), _f(v), _f(ret), _u(mk), C.c_int64(n),
+                            C.c_int64(A), C.c_float(clip), C.c_float(vcoef), C.c_float(ecoef),
+                            _f(ls), _f(out["clipped_losses"]), _f(out["value_losses"]),
+                            _f(out["entropies"]), _f(out["total_losses"]), _f(out["ratio"]),
+                            _f(out["dlogits"]), _f(out["dvalues"]),
+                            _f(ov) if ov is not None else None))
     out["loss"] = float(ls[0])
     return out
 
@@ -166,7 +170,8 @@ def clip_adam(params, grads, m, v, hidden, step, lr, max_norm, actions=4):
 
 
 def train(params, m, v, step, hidden, obs, actions_taken, log_probs, advantages, returns, masks,
-          epochs, nmb, clip, vcoef, ecoef, max_norm, lr, actions=4):
+          epochs, nmb, clip, vcoef, ecoef, max_norm, lr, actions=4, old_values=None):
+    ov = _c(old_values, np.float32) if old_values is not None else None
     p, m_, v_ = (_c(x, np.float32).copy() for x in (params, m, v))
     o, a = _c(obs, np.uint8), _c(actions_taken, np.int64)
     lp, adv, ret = (_c(x, np.float32) for x in (log_probs, advantages, returns))
@@ -181,13 +186,14 @@ def train(params, m, v, step, hidden, obs, actions_taken, log_probs, advantages,
     met["masks"] = np.zeros((epochs, nmb, mb), np.uint8)
     met["clipped_gradients"] = np.zeros((epochs, nmb), np.float32)
     st = C.c_int64(step)
-    _check(lib().rs_train(_f(p), _f(m_), _f(v_), C.byref(st), C.c_int64(hidden), C.c_int64(actions),
+    _check(lib().rs_train_ex(_f(p), _f(m_), _f(v_), C.byref(st), C.c_int64(hidden), C.c_int64(actions),
                           _u(o), _i(a), _f(lp), _f(adv), _f(ret), _u(mk), C.c_int64(N),
                           C.c_int64(epochs), C.c_int64(nmb), C.c_float(clip), C.c_float(vcoef),
                           C.c_float(ecoef), C.c_float(max_norm), C.c_double(lr), _f(met["loss"]),
                           _f(met["clipped_losses"]), _f(met["value_losses"]), _f(met["entropies"]),
                           _f(met["ratio"]), _f(met["total_losses"]), _f(met["advantages"]),
-                          _f(met["returns"]), _u(met["masks"]), _f(met["clipped_gradients"])))
+                          _f(met["returns"]), _u(met["masks"]), _f(met["clipped_gradients"]),
+                          _f(ov) if ov is not None else None))
     return p, m_, v_, int(st.value), met
 
 

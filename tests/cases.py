@@ -118,3 +118,32 @@ def train_case(N=16, A=4, seed=109):
 
 def sample_idx(P, k=4096, seed=1):
     return np.sort(np.random.default_rng(seed).choice(P, size=min(k, P), replace=False))
+
+
+# ---- the benchmarked shapes (bench.py workloads; hyper-parameters of configs/v0.yaml / v1.yaml) ----
+BENCH_SHAPES = {
+    # whole train(): configs/v0.yaml — 8 envs x 128 steps, 4 epochs x 4 minibatches of 256
+    "v0_train": dict(n=1024, epochs=4, nmb=4, clip=0.1, vcoef=0.5, ecoef=0.01, pseed=42, dseed=201),
+    # one minibatch of configs/v1.yaml (4096 x 5 / 16 = 1280 rows)
+    "v1_mb": dict(n=1280, clip=0.2, vcoef=0.4, ecoef=0.01, pseed=42, dseed=203),
+    # one per-GPU minibatch of the 4096 x 128 sweep on 8 GPUs (16 384 / 8 = 2048 rows)
+    "sweep_mb": dict(n=2048, clip=0.1, vcoef=0.5, ecoef=0.01, pseed=42, dseed=205),
+}
+
+
+def bench_shape_case(name):
+    """(params, train_case) of a BENCH_SHAPES entry: the reference's orthogonal init (seed 42) and a
+    seeded batch of the shape's row count, H = 512."""
+    c = BENCH_SHAPES[name]
+    return synth.orthogonal_params(512, 4, seed=c["pseed"]), train_case(c["n"], seed=c["dseed"])
+
+
+def tensor_samples(P_offsets, k=2048, seed=7):
+    """per-tensor sample indices (all of a tensor if it has <= k elements) into the flat vector"""
+    rng = np.random.default_rng(seed)
+    out = []
+    for i in range(len(P_offsets) - 1):
+        lo, hi = int(P_offsets[i]), int(P_offsets[i + 1])
+        n = hi - lo
+        out.append(lo + (np.arange(n) if n <= k else np.sort(rng.choice(n, k, replace=False))))
+    return out

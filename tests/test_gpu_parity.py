@@ -133,6 +133,66 @@ def test_preprocess_rollout_equals_step_by_step():
     assert np.array_equal(got_carry, stack)
 
 
+@pytest.mark.parametrize("ring_slots", [None, 2, 4])
+def test_rollout_ingest_equals_step_by_step(ring_slots, monkeypatch):
+    """alegpu_rollout_ingest (the hand-off the e2e bench number runs through): pinned host frames ->
+    copy stream -> device ring -> preprocess.  Both branches — the rollout-deep ring (one copy, one
+    fused kernel) and the per-step ring with slot reuse (ALEGPU_RING_SLOTS < T) — over THREE
+    consecutive rollouts with the carry stack alternating, bit-exact against T calls of
+    alegpu_preprocess_step and against the oracle restatement."""
+    import ctypes as C
+    if ring_slots is not None:
+        monkeypatch.setenv("ALEGPU_RING_SLOTS", str(ring_slots))
+    E, T = 5, 7
+    lib = alegpu.lib()
+    buf = alegpu.Buffer(E, T, 4)
+    slab = E * 2 * alegpu.FRAME_BYTES
+    hptr = C.c_void_p()
+    alegpu._check(lib.alegpu_host_alloc(C.byref(hptr), C.c_size_t(T * slab)))
+    host = np.ctypeslib.as_array(C.cast(hptr, C.POINTER(C.c_uint8)), shape=(T * slab,))
+    host = host.reshape(T, E, 2, 210, 160, 3)
+    stream = C.c_void_p()
+    alegpu._check(lib.alegpu_stream_create(C.byref(stream)))
+    carry0 = synth.observations(E, seed=61)
+    buf.carry.view(0, (E, 4, 84, 84)).copy_from(carry0)
+    stack = carry0.copy()          # oracle-side carried stack
+    step_src = DA.from_numpy(carry0)
+    for it in range(3):
+        s = synth.rollout_scalars(E, T, seed=70 + it)
+        starts = s["episode_starts"].copy()
+        starts[1, 2] = 1; starts[1, 3] = 1; starts[2, T - 1] = 1
+        frames = synth.frames(T * E, seed=80 + it, kind="ale" if it % 2 else "uniform")
+        host[...] = frames.reshape(T, E, 2, 210, 160, 3)
+        buf.episode_starts.copy_from(starts)
+        alegpu._check(lib.alegpu_rollout_ingest(buf.h, hptr, C.c_int(it % 2), stream))
+        alegpu.synchronize(stream.value)
+        got = buf.observations.numpy()
+        got_carry = buf.carry.numpy()[1 - it % 2]
+        # (a) the oracle restatement
+        for t in range(T):
+            assert np.array_equal(got[:, t], stack), (it, t)
+            _, q = restate.preprocess(host[t, :, 0], host[t, :, 1])
+            stack = restate.stack_update(stack, q, starts[:, t])
+        assert np.array_equal(got_carry, stack), it
+        # (b) T calls of alegpu_preprocess_step on device-resident frames
+        dframes, dstarts = DA.from_numpy(host), DA.from_numpy(starts)
+        for t in range(T):
+            dst = DA.zeros((E, 4, 84, 84), np.uint8)
+            fa = dframes.view(t * slab, (E, 210, 160, 3))
+            alegpu._check(lib.alegpu_preprocess_step_strided(  # frames interleaved [E,2,...]
+                C.c_void_p(fa.ptr), C.c_void_p(fa.ptr + alegpu.FRAME_BYTES),
+                C.c_int64(2 * alegpu.FRAME_BYTES), C.c_void_p(dstarts.ptr + t), C.c_int64(T),
+                C.c_void_p(step_src.ptr), C.c_int64(alegpu.STACK_BYTES), C.c_void_p(dst.ptr),
+                C.c_int64(alegpu.STACK_BYTES), C.c_int64(E), None))
+            alegpu.synchronize()
+            step_src = dst
+            want_next = got[:, t + 1] if t + 1 < T else got_carry
+            assert np.array_equal(dst.numpy(), want_next), (it, t)
+    alegpu._check(lib.alegpu_stream_destroy(stream))
+    del buf
+    alegpu._check(lib.alegpu_host_free(hptr))
+
+
 def test_preprocess_full_size_properties():
     # v0 step count (1024 frame pairs): max is commutative, and a pair (f,f) is idempotent
     E, T = 8, 16
@@ -400,6 +460,68 @@ def test_train_shuffle_and_advantage_normalisation(shuffle, norm):
         np.testing.assert_array_equal(m["masks"].ravel().astype(bool), msk.astype(bool))
 
 
+@pytest.mark.parametrize("shuffle", [False, True])
+def test_train_clipped_value_loss(shuffle):
+    """alegpu_train_options.clip_value_loss (needs batch.values) == the oracle's train() with the
+    clipped value loss restated (pinned against torch autograd in test_oracle_golden.py)."""
+    H, N, nmb = 32, 64, 4
+    mb = N // nmb
+    params = cases.net_params(H)
+    tc = cases.train_case(N, seed=43)
+    old_v = (tc["returns"] + 0.3 * np.random.default_rng(2).standard_normal(N)).astype(np.float32)
+    perm = np.random.default_rng(5).permutation(N).astype(np.int64) if shuffle else np.arange(N)
+    obs, act, lp, adv, ret, msk, ov = restate.gather_minibatches(
+        perm, tc["obs"], tc["actions"], tc["log_probs"], tc["advantages"], tc["returns"], tc["masks"],
+        old_v)
+    z = np.zeros_like(params)
+    want_p, _, _, _, want_m = restate.train(params, z, z, 0, H, obs, act, lp, adv, ret, msk, 1, nmb,
+                                            cases.CLIP, cases.VCOEF, cases.ECOEF, cases.MAX_NORM,
+                                            cases.LR, old_values=ov)
+    plain_p = restate.train(params, z, z, 0, H, obs, act, lp, adv, ret, msk, 1, nmb, cases.CLIP,
+                            cases.VCOEF, cases.ECOEF, cases.MAX_NORM, cases.LR)[0]
+    assert not np.array_equal(want_p, plain_p)  # the option changes the update
+    met = alegpu.Metrics(1, nmb, mb)
+    batch = alegpu.Batch(tc["obs"], tc["actions"], tc["log_probs"], tc["advantages"], tc["returns"],
+                         tc["masks"], values=old_v)
+    hp = alegpu.Hyperparameters(cases.CLIP, cases.VCOEF, cases.ECOEF, cases.MAX_NORM)
+    for graph in (False, True):
+        L = alegpu.Learner(H, 4, mb, alegpu.MATH_FP32, cases.LR)
+        L.set_params(params)
+        L.train(batch, met, 1, nmb, hp, cuda_graph=graph, indices=perm if shuffle else None,
+                clip_value_loss=True)
+        got = L.get_params()
+        err = np.linalg.norm((got - want_p).astype(np.float64)) / np.linalg.norm(want_p)
+        assert err < 1e-4, (err, graph)
+        m = met.numpy()
+        # minibatches 1.. see weights that already took Adam steps (sign-like for near-zero gradients):
+        # exact for minibatch 0, 5e-3 after
+        np.testing.assert_allclose(m["value_losses"][0, 0], want_m["value_losses"][0, 0], rtol=1e-5, atol=1e-7)
+        np.testing.assert_allclose(m["value_losses"], want_m["value_losses"], rtol=5e-3, atol=1e-5)
+        np.testing.assert_allclose(m["loss"], want_m["loss"], rtol=1e-3, atol=1e-5)
+    with pytest.raises(ValueError):  # the option without the stored values
+        L.train(alegpu.Batch(tc["obs"], tc["actions"], tc["log_probs"], tc["advantages"],
+                             tc["returns"], tc["masks"]), met, 1, nmb, hp, clip_value_loss=True)
+
+
+def test_train_action_out_of_range_is_reported():
+    """An action index outside [0, A) (the reference's gather at losses.cc:12 would throw) is flagged
+    on the device through a mapped host flag and reported by the next learner call."""
+    H, N = 32, 16
+    tc = cases.train_case(N, seed=3)
+    L = alegpu.Learner(H, 4, N, alegpu.MATH_FP32, cases.LR)
+    L.set_params(cases.net_params(H))
+    acts = tc["actions"].copy()
+    acts[5] = 4
+    hp = alegpu.Hyperparameters(cases.CLIP, cases.VCOEF, cases.ECOEF, cases.MAX_NORM)
+    bad = alegpu.Batch(tc["obs"], acts, tc["log_probs"], tc["advantages"], tc["returns"], tc["masks"])
+    good = alegpu.Batch(tc["obs"], tc["actions"], tc["log_probs"], tc["advantages"], tc["returns"],
+                        tc["masks"])
+    L.train(bad, None, 1, 1, hp)
+    with pytest.raises(IndexError):
+        L.train(good, None, 1, 1, hp)
+    L.train(good, None, 1, 1, hp)  # the flag was cleared
+
+
 def test_train_shuffle_index_out_of_range():
     H, N = 32, 16
     tc = cases.train_case(N, seed=2)
@@ -410,10 +532,12 @@ def test_train_shuffle_index_out_of_range():
     hp = alegpu.Hyperparameters(cases.CLIP, cases.VCOEF, cases.ECOEF, cases.MAX_NORM)
     bad = np.arange(N, dtype=np.int64)
     bad[3] = N  # torch index_select would throw (std::out_of_range family)
-    L.train(batch, None, 1, 1, hp, indices=bad)
-    with pytest.raises(IndexError):  # std::out_of_range
-        L.train(batch, None, 1, 1, hp, indices=np.arange(N, dtype=np.int64))
+    before = L.get_params()
+    with pytest.raises(IndexError):  # std::out_of_range, from the SAME call, before anything trains
+        L.train(batch, None, 1, 1, hp, indices=bad)
+    assert np.array_equal(L.get_params(), before) and L.get_adam()[2] == 0
     L.train(batch, None, 1, 1, hp, indices=np.arange(N, dtype=np.int64))  # flag was cleared
+    assert L.get_adam()[2] == 1
 
 
 # ---- N3: on-device reduction of Metrics for the logging feed (src/bin/train.cc:163-210) ---------

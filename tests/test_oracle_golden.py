@@ -189,6 +189,42 @@ def test_normalize_advantages_matches_torch_std():
     np.testing.assert_allclose(got, want.numpy(), rtol=1e-5, atol=1e-6)
 
 
+def test_clipped_value_loss_matches_torch_autograd():
+    """The opt-in clipped value loss (north_star / SURVEY D3; NOT in the reference) pinned against the
+    CleanRL expression under torch autograd: value, total loss, d/dlogits and d/dvalues."""
+    torch = pytest.importorskip("torch")
+    c = cases.loss_case(n=193, seed=9)
+    rng = np.random.default_rng(4)
+    old_v = (c["values"] + 0.15 * rng.standard_normal(193)).astype(np.float32)
+    old_v[:5] = c["values"][:5]  # inside the clamp range: both branches equal (a tie)
+    clip, vc, ec = 0.1, 0.5, 0.01
+    got = restate.loss(c["logits"], c["old_log_probs"], c["actions"], c["advantages"], c["values"],
+                       c["returns"], c["masks"], clip, vc, ec, old_values=old_v)
+    t = lambda k, **kw: torch.tensor(c[k], **kw)
+    z, v = t("logits", requires_grad=True), t("values", requires_grad=True)
+    lp = torch.log_softmax(z, -1)
+    a = t("actions")
+    ratio = torch.exp(lp.gather(-1, a[:, None])[:, 0] - t("old_log_probs").gather(-1, a[:, None])[:, 0])
+    adv, ret, ov = t("advantages"), t("returns"), torch.tensor(old_v)
+    surr = torch.min(ratio * adv, torch.clamp(ratio, 1 - clip, 1 + clip) * adv)
+    v_clipped = ov + torch.clamp(v - ov, -clip, clip)
+    vl = 0.5 * torch.max((v - ret) ** 2, (v_clipped - ret) ** 2)
+    ent = -(lp.exp() * lp).sum(-1)
+    total = -surr + vc * vl - ec * ent
+    mask = t("masks").bool()
+    loss = (total * mask).sum() / mask.sum()
+    loss.backward()
+    np.testing.assert_allclose(got["value_losses"], vl.detach().numpy(), rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(got["loss"], float(loss), rtol=1e-5)
+    np.testing.assert_allclose(got["dvalues"], v.grad.numpy(), rtol=1e-4, atol=1e-8)
+    np.testing.assert_allclose(got["dlogits"], z.grad.numpy(), rtol=1e-4, atol=1e-8)
+    # and off by default == the reference form
+    ref = restate.loss(c["logits"], c["old_log_probs"], c["actions"], c["advantages"], c["values"],
+                       c["returns"], c["masks"], clip, vc, ec)
+    np.testing.assert_array_equal(ref["value_losses"],
+                                  (0.5 * (c["values"] - c["returns"]) ** 2).astype(np.float32))
+
+
 # ---- live-path resize (stb restated; PARITY UNPINNED — no reference vector exists) ---------------
 def test_stb_resize_restatement_properties():
     # hand-derived known answer of the stated rules: Mitchell at scale 1/2 on [0,0,255,255]:

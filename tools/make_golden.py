@@ -86,8 +86,50 @@ def main():
     np.savez(os.path.join(OUT, "train_h32.npz"), params=pf[idx],
              param_norms=np.array([np.linalg.norm(pf[offs[i]:offs[i + 1]].astype(np.float64))
                                    for i in range(12)]), **met)
+    bench_shapes()
     print("wrote", sorted(os.listdir(OUT)))
 
 
+def bench_shapes():
+    """7. the benchmarked shapes through the reference's own code (H = 512): a whole v0 train() and
+    one v1 / one sweep minibatch (forward, loss, backward).  The fixtures keep per-tensor norms and
+    2048 samples per tensor (a full gradient is 6.7 MB)."""
+    ref.set_num_threads(os.cpu_count() or 1)
+    offs = cases.param_offsets(512)
+    samp = cases.tensor_samples(offs)
+    flat_idx = np.concatenate(samp)
+    out = {}
+    for name, c in cases.BENCH_SHAPES.items():
+        params, tc = cases.bench_shape_case(name)
+        L = ref.Learner(512, 4, 42, cases.LR)
+        L.set_params(params)
+        if "epochs" in c:
+            met = L.train(tc["obs"], tc["actions"], tc["log_probs"], tc["advantages"], tc["returns"],
+                          tc["masks"], c["epochs"], c["nmb"], c["clip"], c["vcoef"], c["ecoef"],
+                          cases.MAX_NORM)
+            pf = L.get_params()
+            out[name + ".params"] = pf[flat_idx]
+            out[name + ".update"] = (pf - params)[flat_idx]
+            out[name + ".update_norms"] = np.array(
+                [np.linalg.norm((pf - params)[offs[i]:offs[i + 1]].astype(np.float64)) for i in range(12)])
+            out[name + ".loss"] = met["loss"][:, :, 0]
+            out[name + ".clipped_gradients"] = met["clipped_gradients"]
+            for k in ("clipped_losses", "value_losses", "entropies", "ratio"):
+                out[name + "." + k] = met[k][:, :, :32]
+        else:
+            g, loss, lg, v = L.grads(tc["obs"], tc["actions"], tc["log_probs"], tc["advantages"],
+                                     tc["returns"], tc["masks"], c["clip"], c["vcoef"], c["ecoef"])
+            out[name + ".grads"] = g[flat_idx]
+            out[name + ".grad_norms"] = np.array(
+                [np.linalg.norm(g[offs[i]:offs[i + 1]].astype(np.float64)) for i in range(12)])
+            out[name + ".loss"] = np.float32(loss)
+            out[name + ".logits"], out[name + ".values"] = lg, v
+    np.savez_compressed(os.path.join(OUT, "bench_shapes.npz"), **out)
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "bench_shapes":
+        assert ref.available(), "build oracle/_ref first: make -C oracle ref"
+        bench_shapes()
+    else:
+        main()
