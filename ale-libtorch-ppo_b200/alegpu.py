@@ -644,6 +644,29 @@ class Learner:
         return int(lib().alegpu_learner_last_launch_count(self.h))
 
 
+# ---- env -> GPU mapping of the data-parallel path -------------------------------------
+def shard_rows(N, num_mini_batches, world_size, rank):
+    """Rows of the flat [N] batch that rank `rank` owns so that ITS minibatch k is its share of the
+    reference's minibatch k = rows [k*mb, (k+1)*mb) (src/ai/ppo/train.h:149-151): for every k the
+    slice [k*mb + rank*mb/G, k*mb + (rank+1)*mb/G).  With this mapping G GPUs train on exactly the
+    minibatches one GPU would (up to fp32 summation order)."""
+    mb = N // num_mini_batches
+    assert N % num_mini_batches == 0 and mb % world_size == 0, "mb must divide over the ranks"
+    per = mb // world_size
+    return np.concatenate([np.arange(k * mb + rank * per, k * mb + (rank + 1) * per)
+                           for k in range(num_mini_batches)])
+
+
+def shard_envs(E, T, num_mini_batches, world_size, rank):
+    """The same mapping in env units (rows are env-major, row = e*T + t): valid when the reference's
+    minibatches are whole envs (num_mini_batches * world_size divides E; v1: 4096/(16*8) = 32, sweep:
+    4096/(32*8) = 16): rank g owns envs [k*E/nmb + g*E/(nmb*G), k*E/nmb + (g+1)*E/(nmb*G)) for every k."""
+    assert E % (num_mini_batches * world_size) == 0, "nmb * world_size must divide E"
+    per_mb, per = E // num_mini_batches, E // (num_mini_batches * world_size)
+    return np.concatenate([np.arange(k * per_mb + rank * per, k * per_mb + (rank + 1) * per)
+                           for k in range(num_mini_batches)])
+
+
 def selftest_tc_gemm(A, B, M, N, R, a_mn=False, b_mn=False, bn=64, splits=1, use_async=False,
                      tf32=False):
     """C[M,N] = A . B^T through the tcgen05/TMEM engine (alegpu_selftest_tc_gemm).  A is

@@ -672,7 +672,16 @@ extern "C" int alegpu_learner_destroy(alegpu_learner *L) {
     return ALEGPU_OK;
   cudaSetDevice(L->cfg.device);
   cudaStreamSynchronize(L->stream);
+  // A captured graph that holds NCCL kernel nodes keeps a reference on its communicator (NCCL hangs a
+  // cudaUserObject on the graph) and ncclCommDestroy waits for that reference to drop: the graph
+  // must die FIRST.  (Destroying the communicators first was the teardown hang of round 1.)
+  if (L->graph_exec) {
+    cudaGraphExecDestroy(L->graph_exec);
+    L->graph_exec = nullptr;
+  }
 #ifdef ALEGPU_WITH_NCCL
+  if (L->comm_stream)
+    cudaStreamSynchronize(L->comm_stream);
   if (L->comm2)
     nccl().CommDestroy(L->comm2);
   if (L->comm)
