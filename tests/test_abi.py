@@ -128,19 +128,42 @@ def test_bench_reference_arm_line_contract():
 
 
 def test_bench_clock_summary_flags_throttle_reasons():
-    """The clocks object of the bench line: median SM clock under load, reasons seen in ANY sample;
-    a run without a single sample says so instead of reporting a clean run."""
+    """The clocks object of the bench line: median SM clock of the samples that fall INSIDE a timed
+    region, reasons seen in any of them; a run without a single such sample says so instead of
+    reporting a clean run.  (The sampler is a separate process that appends lines to a file.)"""
     import sys
     sys.path.insert(0, ROOT)
     import bench
-    c = bench.ClockSampler(0)
+    c = bench.ClockSampler(0, mode="none")
     assert c.summary()["reasons"] == ["unsampled"]
-    idle = ["Not Active"] * 4
-    c.samples = [["1965", "1965"] + idle, ["1800", "1965", "Not Active", "Active", "Not Active", "Active"],
-                 ["1950", "1965"] + idle]
+    with open(c.path, "w") as f:
+        f.write("# nvml\n")
+        f.write("99.0 1200 1965 1 0 0 0\n")        # outside every timed window: ignored
+        f.write("100.5 1965 1965 0 0 0 0\n")
+        f.write("101.0 1800 1965 0 1 0 1\n")
+        f.write("101.5 1950 1965 0 0 0 0\n")
+        f.write("250.0 300 1965 0 0 1 0\n")        # idle, after the run: ignored
+    c.window(100.0, 102.0)
     s = c.summary()
+    os.remove(c.path)
     assert s["sm_mhz"] == 1950.0 and s["sm_max_mhz"] == 1965.0 and s["samples"] == 3
-    assert s["reasons"] == ["hw_thermal_slowdown", "sw_power_cap"]
+    assert s["reasons"] == ["hw_thermal_slowdown", "sw_power_cap"] and s["source"] == "nvml"
+
+
+def test_bench_sampler_process_writes_samples_or_says_why(tmp_path):
+    """`bench.py --_sampler` (the separate clock-sampling process) starts, writes its source header
+    (nvml, or the nvidia-smi fallback with the reason) and dies on terminate()."""
+    import subprocess
+    import sys
+    import time
+    path = str(tmp_path / "clocks.txt")
+    p = subprocess.Popen([sys.executable, os.path.join(ROOT, "bench.py"), "--_sampler", "0", path])
+    t0 = time.time()
+    while time.time() - t0 < 20 and not (os.path.exists(path) and os.path.getsize(path) > 0):
+        time.sleep(0.1)
+    p.terminate()
+    p.wait(timeout=10)
+    assert open(path).readline().startswith("#")
 
 
 def test_bench_product_arm_fails_loudly_without_device():
