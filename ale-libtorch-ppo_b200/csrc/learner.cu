@@ -246,7 +246,19 @@ int allreduce_grads(alegpu_learner *L) {
   return ALEGPU_OK;
 }
 
-int clip_and_step(alegpu_learner *L, float max_norm, float *total_norm_out) {
+int clip_and_step(alegpu_learner *L, float max_norm, float *total_norm_out,
+                  const float *count = nullptr, float *m_loss = nullptr, int64_t mb = 0) {
+  static const bool no_fused = getenv("ALEGPU_NO_FUSED_ADAM") != nullptr; // A/B: the two-kernel form
+  if (!no_fused && adam_fused_fits(L->Ppad)) {
+    L->host_step += 1;
+    return launch_adam_fused(L->params, L->grads, L->m, L->v, use_tc(L) ? L->tc.w_shadow : nullptr,
+                             use_tc(L) ? L->tc.c1w_perm : nullptr, use_tc(L) ? L->tc.elem_bytes : 0,
+                             L->Ppad, L->P, L->norm_partials, L->opt, max_norm, total_norm_out,
+                             L->grads + L->P, count, m_loss, mb, L->stream);
+  }
+  if (m_loss)
+    if (int rc = finalize_metrics(L->grads + L->P, count, m_loss, mb, nullptr, L->stream))
+      return rc;
   // the padding behind the P parameters carries the loss sum (see enqueue_train): not part of the norm
   if (int rc = launch_grad_sumsq(L->grads, L->Ppad, L->P, L->norm_partials, L->opt, max_norm,
                                  total_norm_out, L->stream))
@@ -381,13 +393,12 @@ int enqueue_train(alegpu_learner *L, const alegpu_batch &b, const alegpu_metrics
         return rc;
       if (int rc = allreduce_grads(L))
         return rc;
+      // norm + clip + Adam + the Metrics.loss broadcast (train.h:98): one launch
       if (int rc = clip_and_step(L, hp.max_gradient_norm,
                                  mt.clipped_gradients ? mt.clipped_gradients + ep * nmb + k
-                                                      : L->scalars))
+                                                      : L->scalars,
+                                 count, mt.loss ? mt.loss + o : nullptr, mb))
         return rc;
-      if (mt.loss)
-        if (int rc = finalize_metrics(L->grads + L->P, count, mt.loss + o, mb, nullptr, L->stream))
-          return rc;
     }
   return ALEGPU_OK;
 }

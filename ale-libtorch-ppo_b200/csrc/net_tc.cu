@@ -877,13 +877,17 @@ __global__ void bf16_to_f32_kernel(const bf16 *__restrict__ src, float *__restri
 template <class T>
 __global__ void __launch_bounds__(256)
     obs_to_s2d_kernel(const uint8_t *__restrict__ obs, T *__restrict__ out, int64_t total) {
-  // total = n * 84 * 21 work items (n, y, x4)
+  // total = n * 21 * 84 work items (n, Y, x4, y & 3) with y & 3 fastest: four neighbouring threads write
+  // the four 16-channel groups of ONE 64-channel block, so a warp writes 8 whole blocks = 1 KB (bf16) /
+  // 2 KB (fp32) of contiguous output (the first version ran x4 fastest: 32- / 64-byte pieces with a
+  // 128- / 256-byte stride, 0.58 of the copy roofline)
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t row = i / 21; // n*84 + y
-    const int x4 = (int)(i - row * 21);
-    const int64_t n = row / 84;
-    const int y = (int)(row - n * 84);
+    const int64_t blk = i / 84; // n*21 + Y
+    const int j = (int)(i - blk * 84);
+    const int x4 = j >> 2;
+    const int64_t n = blk / 21;
+    const int y = (int)(blk - n * 21) * 4 + (j & 3);
     const uint8_t *src = obs + n * 28224 + (size_t)y * 84 + x4 * 4;
     uint32_t w[4];
 #pragma unroll
@@ -1227,17 +1231,24 @@ int backward_impl(const NetParams &P, const NetParams &G, TcState &S, const uint
   if (int rc = heads_wgrad(G, A, n, S.ws_heads, S.ws_heads_n, w))
     return rc;
   {
-    const int64_t tiles = ceil_div(H, tc::BM) * ceil_div(3137, 128);
-    const size_t per = (size_t)H * 3137;
-    int splits, rps;
-    plan_splits(n, tiles, per, S.ws_fc_n, &splits, &rps);
-    if (n <= 1024)
-      splits = 1, rps = 0; // 100 output tiles already fill the chip; skip the partial round trip
-    if (splits == 1) { // [H][3136 | bias] = dfc^T . [act3 | 1]
+    // [H][3136 | bias] = dfc^T . [act3 | 1], stored directly (no split partials, no reduction pass).
+    // Up to 1024 rows 128-wide tiles (100 CTAs) are the fastest; above, 64-wide tiles give 200 CTAs each
+    // walking the whole reduction (measured at 1280 rows: 2 splits of 128-wide tiles + the 16.8 us
+    // reduction of 2 x 6.4 MB partials = 58.7 us in bf16; ALEGPU_FC_WGRAD_SPLIT=1 keeps that form for A/B)
+    static const bool split_ab = getenv("ALEGPU_FC_WGRAD_SPLIT") != nullptr;
+    if (n <= 1024) {
       if (int rc = tc::launch_gemm_tc<128, 3>(ColsMN<T>{dfcT, H}, ColsMN<T>{act3, 3136},
                                               EpiWgradDirect{G.fcw, G.fcb, 3136}, H, 3137, n, 1, 0, w))
         return rc;
+    } else if (!split_ab) {
+      if (int rc = tc::launch_gemm_tc<64, 4>(ColsMN<T>{dfcT, H}, ColsMN<T>{act3, 3136},
+                                             EpiWgradDirect{G.fcw, G.fcb, 3136}, H, 3137, n, 1, 0, w))
+        return rc;
     } else {
+      const int64_t tiles = ceil_div(H, tc::BM) * ceil_div(3137, 128);
+      const size_t per = (size_t)H * 3137;
+      int splits, rps;
+      plan_splits(n, tiles, per, S.ws_fc_n, &splits, &rps);
       if (int rc = tc::launch_gemm_tc<128, 3>(ColsMN<T>{dfcT, H}, ColsMN<T>{act3, 3136},
                                               EpiPartial{S.ws_fc, H, 3137}, H, 3137, n, splits, rps, w))
         return rc;

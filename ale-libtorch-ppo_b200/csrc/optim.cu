@@ -160,6 +160,147 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
+// ---- one launch: ||g||^2 -> grid barrier -> clip + Adam (+ Metrics.loss broadcast) ---------------------
+// kNormBlocks CTAs (2 per SM, all co-resident) each own a fixed slice of the flat buffer; a thread keeps
+// its <= kCache float4 of the gradient IN REGISTERS across the barrier, so the gradient is read once
+// (28 B per parameter in total, no 4 B/param norm pass), and its p / m / v loads are issued BEFORE it
+// waits, so they are in flight while the last CTA forms the clip coefficient.  The barrier: every CTA
+// reads the step counter, publishes its partial and arrives on done_count; the last one sums the
+// partials in index order (bit-reproducible), writes coef / step_size / bc2_sqrt and then advances
+// st->step, which is what the others spin on.  Used when the buffer fits the register cache
+// (P <= kCache * 4 * 296 * 256 = 1.8 M floats: every shipped config); larger nets take the two kernels.
+constexpr int kCache = 6;
+template <class ST>
+__global__ void __launch_bounds__(kThreads, 2)
+    adam_fused_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m,
+                      float *__restrict__ v, ST *__restrict__ shadow, ST *__restrict__ c1w_perm,
+                      int64_t n4, int64_t n_valid, float *__restrict__ partials, OptState *st,
+                      float max_norm, float *__restrict__ total_norm_out,
+                      const float *__restrict__ loss_sum, const float *__restrict__ count,
+                      float *__restrict__ m_loss, int64_t mb) {
+  __shared__ float red[kThreads / 32];
+  __shared__ bool s_last;
+  float4 *p4 = reinterpret_cast<float4 *>(p);
+  const float4 *g4 = reinterpret_cast<const float4 *>(g);
+  float4 *m4 = reinterpret_cast<float4 *>(m);
+  float4 *v4 = reinterpret_cast<float4 *>(v);
+  const int64_t stride = (int64_t)gridDim.x * kThreads;
+  const int64_t i0 = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 gg[kCache], pp[kCache], mm[kCache], vv[kCache];
+  float acc = 0.0f;
+#pragma unroll
+  for (int c = 0; c < kCache; ++c) {
+    const int64_t i = i0 + c * stride;
+    gg[c] = i < n4 ? __ldcg(g4 + i) : zero4;
+    float4 x = gg[c];
+    if (4 * i + 3 >= n_valid) { // the padding behind the last parameter is not part of the norm
+      x.x = 4 * i < n_valid ? x.x : 0.0f;
+      x.y = 4 * i + 1 < n_valid ? x.y : 0.0f;
+      x.z = 4 * i + 2 < n_valid ? x.z : 0.0f;
+      x.w = 0.0f;
+    }
+    acc += x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
+  }
+  const long long step0 = *reinterpret_cast<volatile long long *>(&st->step);
+  acc = block_sum<float, kThreads>(acc, red);
+  if (threadIdx.x == 0) {
+    partials[blockIdx.x] = acc;
+    __threadfence();
+    s_last = atomicAdd(&st->done_count, 1u) == gridDim.x - 1;
+  }
+#pragma unroll
+  for (int c = 0; c < kCache; ++c) { // in flight while this CTA waits at the barrier
+    const int64_t i = i0 + c * stride;
+    pp[c] = i < n4 ? p4[i] : zero4;
+    mm[c] = i < n4 ? m4[i] : zero4;
+    vv[c] = i < n4 ? v4[i] : zero4;
+  }
+  __syncthreads();
+  if (s_last) {
+    if (threadIdx.x < 32) {
+      __threadfence();
+      double s = 0.0;
+      for (int i = threadIdx.x; i < (int)gridDim.x; i += 32)
+        s += (double)__ldcg(partials + i);
+      s = warp_sum(s);
+      if (threadIdx.x == 0) {
+        const float total = (float)sqrt(s);
+        const float coef = (float)((double)max_norm / ((double)total + 1e-6)); // train.cc:39
+        st->coef = fminf(coef, 1.0f);                                          // train.cc:40-41
+        const double t = (double)(step0 + 1); // Adam's counter counts minibatch updates (train.h:129)
+        const double bc1 = 1.0 - pow(0.9, t), bc2 = 1.0 - pow(0.999, t);
+        st->step_size = (float)(st->lr / bc1);
+        st->bc2_sqrt = (float)sqrt(bc2);
+        st->done_count = 0u;
+        if (total_norm_out)
+          *total_norm_out = total; // the PRE-clip norm (train.h:104)
+        __threadfence();
+        *reinterpret_cast<volatile long long *>(&st->step) = step0 + 1; // releases the other CTAs
+      }
+    }
+  } else if (threadIdx.x == 0) {
+    while (*reinterpret_cast<volatile long long *>(&st->step) == step0)
+      __nanosleep(40);
+    __threadfence();
+  }
+  __syncthreads();
+  const float coef = __ldcg(&st->coef), step_size = __ldcg(&st->step_size), bc2_sqrt = __ldcg(&st->bc2_sqrt);
+  const float b1 = 0.9f, b2 = 0.999f, omb1 = (float)(1.0 - 0.9), omb2 = (float)(1.0 - 0.999);
+  const float eps = 1e-5f;
+#pragma unroll
+  for (int c = 0; c < kCache; ++c) {
+    const int64_t i = i0 + c * stride;
+    if (i >= n4)
+      continue;
+    float *pa = &pp[c].x, *ga = &gg[c].x, *ma = &mm[c].x, *va = &vv[c].x;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float gc = ga[k] * coef; // train.cc:42-44 (the scaled gradient is consumed here only)
+      ma[k] = ma[k] * b1 + gc * omb1;
+      va[k] = va[k] * b2 + (gc * gc) * omb2;
+      const float denom = sqrtf(va[k]) / bc2_sqrt + eps;
+      pa[k] = pa[k] - step_size * (ma[k] / denom);
+    }
+    p4[i] = pp[c];
+    m4[i] = mm[c];
+    v4[i] = vv[c];
+    if (shadow) {
+      if constexpr (sizeof(ST) == 2) {
+        __nv_bfloat162 lo = __floats2bfloat162_rn(pp[c].x, pp[c].y), hi = __floats2bfloat162_rn(pp[c].z, pp[c].w);
+        uint2 pk;
+        pk.x = *reinterpret_cast<uint32_t *>(&lo);
+        pk.y = *reinterpret_cast<uint32_t *>(&hi);
+        reinterpret_cast<uint2 *>(shadow)[i] = pk;
+      } else {
+        reinterpret_cast<float4 *>(shadow)[i] = make_float4(round_tf32(pp[c].x), round_tf32(pp[c].y),
+                                                            round_tf32(pp[c].z), round_tf32(pp[c].w));
+      }
+      if (c1w_perm && i < 32 * 256 / 4) { // conv1 weights also in the space-to-depth k' order (see adam_clip_kernel)
+        const int idx = (int)i * 4, co = idx >> 8, k = idx & 255;
+        const int ch = k >> 6, ky = (k >> 3) & 7, kx = k & 7;
+        ST *o = c1w_perm + co * 256 + ((ky >> 2) * 2 + (kx >> 2)) * 64 + (ky & 3) * 16 + (kx & 3) * 4 + ch;
+        if constexpr (sizeof(ST) == 2) {
+          o[0] = __float2bfloat16_rn(pp[c].x);
+          o[4] = __float2bfloat16_rn(pp[c].y);
+          o[8] = __float2bfloat16_rn(pp[c].z);
+          o[12] = __float2bfloat16_rn(pp[c].w);
+        } else {
+          o[0] = round_tf32(pp[c].x);
+          o[4] = round_tf32(pp[c].y);
+          o[8] = round_tf32(pp[c].z);
+          o[12] = round_tf32(pp[c].w);
+        }
+      }
+    }
+  }
+  if (m_loss) { // Metrics.loss[epoch,k,:] = the scalar loss broadcast over mb (train.h:98); losses.cc:19
+    const float loss = loss_sum[0] / count[0];
+    for (int64_t i = i0; i < mb; i += stride)
+      m_loss[i] = loss;
+  }
+}
+
 __global__ void f32_to_bf16_kernel(const float *__restrict__ src, __nv_bfloat16 *__restrict__ dst,
                                    int64_t n) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
@@ -189,6 +330,26 @@ int launch_adam_clip(float *params, float *grads, float *m, float *v, void *shad
     adam_clip_kernel<__nv_bfloat16><<<blocks, kThreads, 0, s>>>(
         params, grads, m, v, static_cast<__nv_bfloat16 *>(shadow),
         static_cast<__nv_bfloat16 *>(c1w_perm), n_padded / 4, st);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}
+
+bool adam_fused_fits(int64_t n_padded) { return n_padded / 4 <= (int64_t)kCache * kNormBlocks * kThreads; }
+
+int launch_adam_fused(float *params, float *grads, float *m, float *v, void *shadow, void *c1w_perm,
+                      int shadow_elem_bytes, int64_t n_padded, int64_t n_valid, float *partials,
+                      OptState *st, float max_norm, float *total_norm_out, const float *loss_sum,
+                      const float *count, float *m_loss, int64_t mb, cudaStream_t s) {
+  ALEGPU_REQUIRE(adam_fused_fits(n_padded), ALEGPU_RUNTIME_ERROR, "adam_fused: buffer exceeds the register cache");
+  if (shadow && shadow_elem_bytes == 4)
+    adam_fused_kernel<float><<<kNormBlocks, kThreads, 0, s>>>(
+        params, grads, m, v, static_cast<float *>(shadow), static_cast<float *>(c1w_perm), n_padded / 4,
+        n_valid, partials, st, max_norm, total_norm_out, loss_sum, count, m_loss, mb);
+  else
+    adam_fused_kernel<__nv_bfloat16><<<kNormBlocks, kThreads, 0, s>>>(
+        params, grads, m, v, static_cast<__nv_bfloat16 *>(shadow), static_cast<__nv_bfloat16 *>(c1w_perm),
+        n_padded / 4, n_valid, partials, st, max_norm, total_norm_out, loss_sum, count, m_loss, mb);
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
   return ALEGPU_OK;

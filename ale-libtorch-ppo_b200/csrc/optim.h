@@ -27,6 +27,13 @@ int launch_grad_sumsq(const float *grads, int64_t n_padded, int64_t n_valid, flo
 // in the space-to-depth k' order
 int launch_adam_clip(float *params, float *grads, float *m, float *v, void *shadow, void *c1w_perm,
                      int shadow_elem_bytes, int64_t n_padded, const OptState *st, cudaStream_t s);
+// ONE launch for norm + clip + Adam (+ the Metrics.loss broadcast when m_loss != nullptr): the gradient
+// stays in registers across a grid barrier (optim.cu).  Only when adam_fused_fits(n_padded).
+bool adam_fused_fits(int64_t n_padded);
+int launch_adam_fused(float *params, float *grads, float *m, float *v, void *shadow, void *c1w_perm,
+                      int shadow_elem_bytes, int64_t n_padded, int64_t n_valid, float *partials,
+                      OptState *st, float max_norm, float *total_norm_out, const float *loss_sum,
+                      const float *count, float *m_loss, int64_t mb, cudaStream_t s);
 int launch_f32_to_bf16(const float *src, void *dst, int64_t n, cudaStream_t s);
 
 } // namespace alegpu

@@ -6,7 +6,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "ale-libtorch-ppo_b200"), os.path.join(ROOT, "tests")]
 import numpy as np
 import alegpu, cases, synth
-from bench import HP
+from bench import load_workload
+HP = load_workload("v0", 1)  # configs/v0.yaml hyper-parameters
 H, nmb, epochs = 512, 4, 4
 hp = alegpu.Hyperparameters(HP["clip"], HP["vcoef"], HP["ecoef"], HP["max_norm"])
 for mb in (8, 32, 64, 128, 256, 512, 1024):

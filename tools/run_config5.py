@@ -13,7 +13,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "ale-libtorch-ppo_b200"), os.path.join(ROOT, "tests")]
 import alegpu  # noqa: E402
 import synth  # noqa: E402
-from bench import HP  # noqa: E402
+from bench import load_workload  # noqa: E402
+HP = load_workload("v0", 1)  # configs/v0.yaml hyper-parameters
 
 E = int(sys.argv[1]) if len(sys.argv) > 1 else 64
 T = int(sys.argv[2]) if len(sys.argv) > 2 else 128

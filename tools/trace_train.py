@@ -12,10 +12,11 @@ sys.path[:0] = [ROOT, os.path.join(ROOT, "ale-libtorch-ppo_b200"), os.path.join(
 import alegpu  # noqa: E402
 import cases  # noqa: E402
 import synth  # noqa: E402
-from bench import WORKLOADS, HP  # noqa: E402
+from bench import load_workload  # noqa: E402
 
-w = WORKLOADS[sys.argv[1] if len(sys.argv) > 1 else "v0"]
-math = alegpu.MATH_BF16 if (len(sys.argv) < 3 or sys.argv[2] == "bf16") else alegpu.MATH_FP32
+w = load_workload(sys.argv[1] if len(sys.argv) > 1 else "v0", 1)
+HP = w
+math = {"bf16": alegpu.MATH_BF16, "tf32": alegpu.MATH_TF32, "fp32": alegpu.MATH_FP32}[sys.argv[2] if len(sys.argv) > 2 else "bf16"]
 E, T, H, epochs, nmb = w["E"], w["T"], w["H"], w["epochs"], w["nmb"]
 N, mb = E * T, E * T // nmb
 tc = cases.train_case(N, seed=5)
