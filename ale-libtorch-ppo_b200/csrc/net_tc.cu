@@ -31,6 +31,7 @@
 #include "net_tc.h"
 #include "optim.h"
 #include "tc_gemm.cuh"
+#include "tc_shift.cuh"
 
 namespace alegpu {
 namespace {
@@ -952,7 +953,9 @@ template <class T> Shadow<T> shadow_view(const TcState &S, const NetParams &P) {
 // kMapObsAll.. : one slot per (re)allocation of obs16_all, used round-robin, so a descriptor that an
 // earlier kernel may still have cached is never rewritten in place
 enum TmaSlot { kMapAct1 = 0, kMapAct2, kMapDact3, kMapDact2, kMapObsMb, kMapObsAll, kMapObsAllSlots = 16,
-               kMapCount = kMapObsAll + kMapObsAllSlots };
+               // plain [rows x 64] tiled maps of the same buffers for the shift convolutions (tc_shift.cuh)
+               kMapAct2Rows = kMapObsAll + kMapObsAllSlots, kMapObsMbRows, kMapObsAllRows,
+               kMapCount = kMapObsAllRows + kMapObsAllSlots };
 using EncodeIm2colFn = CUresult (*)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
                                     const cuuint64_t *, const cuuint64_t *, const int *, const int *,
                                     cuuint32_t, cuuint32_t, const cuuint32_t *, CUtensorMapInterleave,
@@ -989,6 +992,41 @@ int set_im2col_map(TcState &T, int slot, void *base, int H, int W, int64_t N, in
                         CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   ALEGPU_REQUIRE(r == CUDA_SUCCESS, ALEGPU_RUNTIME_ERROR,
                  "cuTensorMapEncodeIm2col failed: " + std::to_string((int)r));
+  ALEGPU_CUDA_CHECK(cudaMemcpy((CUtensorMap *)T.tmaps + slot, &m, sizeof(m), cudaMemcpyHostToDevice));
+  return ALEGPU_OK;
+}
+using EncodeTiledFn = CUresult (*)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                   CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                   CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = [] {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return (EncodeTiledFn)p;
+  }();
+  return fn;
+}
+// map slot <- the [rows x 64] matrix view of an NHWC buffer with 64 channels per pixel: boxes of
+// kShiftStageRows rows x one 128-byte channel panel, 128-byte swizzle, zeros past the last row
+int set_rows_map(TcState &T, int slot, void *base, int64_t rows) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  ALEGPU_REQUIRE(fn != nullptr, ALEGPU_RUNTIME_ERROR, "cuTensorMapEncodeTiled is not available");
+  alignas(64) CUtensorMap m;
+  const cuuint64_t eb = (cuuint64_t)T.elem_bytes;
+  const cuuint64_t dims[2] = {64, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {64 * eb};
+  const cuuint32_t box[2] = {(cuuint32_t)(128 / eb), (cuuint32_t)tc::kShiftStageRows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = fn(&m, eb == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                        base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  ALEGPU_REQUIRE(r == CUDA_SUCCESS, ALEGPU_RUNTIME_ERROR,
+                 "cuTensorMapEncodeTiled failed: " + std::to_string((int)r));
   ALEGPU_CUDA_CHECK(cudaMemcpy((CUtensorMap *)T.tmaps + slot, &m, sizeof(m), cudaMemcpyHostToDevice));
   return ALEGPU_OK;
 }
@@ -1053,7 +1091,17 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
     if (int rc = set_im2col_map(T, kMapDact3, T.dact3, 7, 7, cap, -2, 0)) return rc; // 3x3, padding 2
     if (int rc = set_im2col_map(T, kMapDact2, T.dact2, 9, 9, cap, -1, 0)) return rc; // 2x2, padding 1
     if (int rc = set_im2col_map(T, kMapObsMb, T.obs16_mb, 21, 21, cap, 0, -1)) return rc; // 2x2 taps
+    if (int rc = set_rows_map(T, kMapAct2Rows, T.act2, cap * 81)) return rc;
+    if (int rc = set_rows_map(T, kMapObsMbRows, T.obs16_mb, cap * 441)) return rc;
   }
+  env = getenv("ALEGPU_NO_SHIFT"); // A/B: conv1 / conv3 forward through the im2col engine instead
+  T.use_shift = T.use_tma && !(env && env[0] == '1');
+  // the matrix-base-offset field of the row-shifted descriptors stays 0: measured on B200, the 128-byte
+  // swizzle is a function of the absolute shared-memory address, so a descriptor may start at any
+  // 128-byte row of a 1024-byte aligned panel as it is (setting (start >> 7) & 7 there gives wrong
+  // products; ALEGPU_SHIFT_BASE_OFFSET=1 reproduces that)
+  env = getenv("ALEGPU_SHIFT_BASE_OFFSET");
+  T.shift_base_offset = env && env[0] == '1';
   return ALEGPU_OK;
 }
 
@@ -1115,6 +1163,8 @@ int net_tc_reserve_obs(TcState &T, int64_t n) {
   T.obs16_all_rows = n;
   if (T.use_tma) {
     T.obs_all_map = (T.obs_all_map + 1) % kMapObsAllSlots;
+    if (int rc = set_rows_map(T, kMapObsAllRows + T.obs_all_map, T.obs16_all, n * 441))
+      return rc;
     return set_im2col_map(T, kMapObsAll + T.obs_all_map, T.obs16_all, 21, 21, n, 0, -1);
   }
   return ALEGPU_OK;
@@ -1155,7 +1205,14 @@ int forward_impl(const NetParams &P, TcState &S, const uint8_t *obs, int64_t n, 
     }
     const T *x16 = (const T *)obs16, *all = (const T *)S.obs16_all;
     const bool in_all = all && x16 >= all && x16 < all + (size_t)S.obs16_all_rows * 28224;
-    if (S.use_tma && (x16 == (const T *)S.obs16_mb || in_all)) {
+    if (S.use_shift && (x16 == (const T *)S.obs16_mb || in_all)) {
+      // shift convolution: the 2x2 taps are row-shifted views of one staged copy of the s2d rows
+      if (int rc = tc::launch_conv_shift<T, 32, 2, 2, 21, 21, 20, 20, 3>(
+              tmap(S, in_all ? kMapObsAllRows + S.obs_all_map : kMapObsMbRows),
+              in_all ? (int64_t)((x16 - all) / 28224) * 441 : 0, (const T *)S.c1w_perm,
+              EpiBiasRelu<T>{act1, P.c1b, 32, 1.0f / 255.0f}, n, s, S.shift_base_offset))
+        return rc;
+    } else if (S.use_tma && (x16 == (const T *)S.obs16_mb || in_all)) {
       const Col1Tma<T> a{tmap(S, in_all ? kMapObsAll + S.obs_all_map : kMapObsMb),
                          in_all ? (int)((x16 - all) / 28224) : 0};
       if (int rc = tc::launch_gemm_tc<32, 4>(a, RowsK<T>{(const T *)S.c1w_perm, 256},
@@ -1177,7 +1234,12 @@ int forward_impl(const NetParams &P, TcState &S, const uint8_t *obs, int64_t n, 
                                                 EpiBiasRelu<T>{act2, P.c2b, 64, 1.0f}, n * 81, 64,
                                                 512, 1, 0, s))
     return rc;
-  if (S.use_tma) {
+  if (S.use_shift) { // 3x3 taps = 9 row-shifted views of one staged copy of act2's rows
+    if (int rc = tc::launch_conv_shift<T, 64, 3, 3, 9, 9, 7, 7, (sizeof(T) == 4 ? 2 : 3)>(
+            tmap(S, kMapAct2Rows), 0, W.c3w, EpiBiasRelu<T>{act3, P.c3b, 64, 1.0f}, n, s,
+            S.shift_base_offset))
+      return rc;
+  } else if (S.use_tma) {
     if (int rc = tc::launch_gemm_tc<64, 4>(Col3Tma<T>{tmap(S, kMapAct2), 0}, RowsK<T>{W.c3w, 576},
                                            EpiBiasRelu<T>{act3, P.c3b, 64, 1.0f}, n * 49, 64, 576,
                                            1, 0, s))

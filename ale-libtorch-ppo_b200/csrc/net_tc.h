@@ -30,6 +30,8 @@ struct TcState {
   void *tmaps = nullptr;
   int obs_all_map = 0;       // which of the round-robin obs16_all descriptor slots is current
   bool use_tma = true;       // ALEGPU_NO_TMA=1: gather conv operands with cp.async instead (A/B)
+  bool use_shift = true;     // ALEGPU_NO_SHIFT=1: conv1 / conv3 forward through the im2col engine (A/B)
+  bool shift_base_offset = false; // experiment switch, see net_tc_init: the field must stay 0
   bool serial = false;       // ALEGPU_TC_SERIAL=1: keep everything on one stream (profiling)
   bool conv1_u8 = false;     // ALEGPU_CONV1_U8=1: conv1 forward reads the u8 observations (A/B)
   bool conv1_wgrad_u8 = false; // ALEGPU_CONV1_WGRAD_U8=1: conv1 wgrad in im2col form over the u8 observations (A/B)

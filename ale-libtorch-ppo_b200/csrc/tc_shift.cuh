@@ -1,0 +1,223 @@
+// tc_shift.cuh — stride-1 convolutions as "shift GEMMs": the input is staged ONCE per output tile and
+// every filter tap is a shifted view of that one staged copy.
+//
+// The im2col engine (tc_gemm.cuh) feeds the tensor core one [128 pixels x 64 channels] box per tap, so
+// a KHxKW convolution pulls every input pixel KH*KW times L2 -> SM (conv3: 9x, conv1 on the
+// space-to-depth observations: 4x) and re-fetches the weights for every tile; the conv layers of this
+// network sit on that L2 -> SM path, not on the tensor core.  Here the output is
+// computed on the INPUT's pixel grid: rows r = image*G + gy*GW + gx run over all G = GH*GW input
+// pixels of every image, and
+//       out(r)[co] = sum_{tap (ky,kx)} sum_c X[r + ky*GW + kx][c] * W[co][(ky*KW+kx)*64 + c]
+// which equals the convolution wherever (gy, gx) is a valid output position (gy < OH, gx < OW); the
+// other rows are computed and dropped (conv3: 81 grid rows per 49 outputs, conv1: 441 per 400 — tensor
+// work the kernel has to spare).  So the A operand of EVERY tap is the same 128 + (KH-1)*GW + KW-1 rows
+// of the plain [rows x 64] input matrix: one tiled TMA load per 128-byte channel panel stages them in the
+// 128-byte-swizzled K-major layout, and the UMMA shared-memory descriptor of tap (ky,kx) simply starts
+// (ky*GW + kx) rows = (ky*GW + kx)*128 bytes further in.  The weights (<= 147 KB) are loaded once per
+// CTA and stay resident; a CTA walks its tiles with a double-buffered TMEM accumulator.  Per tile the SM
+// ingests 19 KB (bf16) / 38 KB (tf32) instead of 147 / 295 KB (+ 74 / 147 KB of weights) for conv3.
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2-5 =
+// epilogue (TMEM lane quarter = warp & 3).
+#pragma once
+#include "tc_gemm.cuh"
+
+namespace alegpu {
+namespace tc {
+
+__device__ __forceinline__ void tma_tile_2d(uint32_t dst, const void *map, int c0, int c1,
+                                            uint64_t *bar) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+               " [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+               "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+               : "memory");
+}
+// the producer's single arrival on a stage's full barrier, carrying the bytes its TMA loads will deliver
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+// K-major SWIZZLE_128B descriptor whose start address is any 128-byte row of a 1024-byte aligned panel.
+// Measured on B200: the swizzle XOR is a function of the absolute shared-memory address (as TMA's is),
+// so the shifted start needs NO matrix-base-offset (bits 49-51 stay 0); use_base_offset puts
+// (start >> 7) & 7 there and gives wrong products — kept only as the experiment that showed it
+__device__ __forceinline__ uint64_t make_smem_desc_row(uint32_t smem_addr, bool use_base_offset) {
+  uint64_t d = make_smem_desc(smem_addr, 16u, 1024u);
+  if (use_base_offset)
+    d |= (uint64_t)((smem_addr >> 7) & 7u) << 49;
+  return d;
+}
+
+constexpr int kShiftThreads = 192;
+constexpr int kShiftStageRows = 152; // 128 + the largest tap shift of the layers built on it (22), to 8
+
+template <class T, int BN, int KH, int KW, int GW> struct ShiftGeom {
+  static constexpr int kEB = (int)sizeof(T);
+  static constexpr int kBKE = 128 / kEB;       // elements of one 128-byte panel row
+  static constexpr int kCP = 64 / kBKE;        // panels per 64-channel pixel (bf16 1, tf32 2)
+  static constexpr int kTaps = KH * KW;
+  static constexpr int kK = kTaps * 64;        // reduction length
+  static constexpr int kNKB = kTaps * kCP;     // 128-byte k-blocks
+  static constexpr int kMaxShift = (KH - 1) * GW + KW - 1;
+  static_assert(128 + kMaxShift <= kShiftStageRows, "stage too short for this filter");
+  static constexpr int kPanel = kShiftStageRows * 128;
+  static constexpr int kStage = kCP * kPanel;
+  static constexpr int kBPanel = BN * 128;
+  static constexpr int kBBytes = kNKB * kBPanel;
+  static constexpr int smem(int stages) { return kBBytes + stages * kStage + 1024; }
+};
+
+// Epi(i_out, j0, v, 0) receives 16 consecutive output channels of OUTPUT pixel row i_out (image-major
+// OHxOW), as the epilogues of tc_gemm.cuh do.
+template <class T, int BN, int KH, int KW, int GH, int GW, int OH, int OW, int STAGES, class Epi>
+__global__ void __launch_bounds__(kShiftThreads, 1)
+    conv_shift_kernel(const void *xmap, int row_base, const T *__restrict__ w, const Epi epi,
+                      int64_t grid_rows, int use_base_offset) {
+  using Geo = ShiftGeom<T, BN, KH, KW, GW>;
+  constexpr int G = GH * GW;
+  constexpr uint32_t kIdesc = make_idesc(BN, false, false, Geo::kEB);
+  constexpr uint32_t kCols = tmem_cols(BN);
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], acc_full[2], acc_empty[2];
+  __shared__ uint32_t tmem_slot;
+  uint8_t *base = reinterpret_cast<uint8_t *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const uint32_t b_s = smem_u32(base), st_s = b_s + Geo::kBBytes;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tiles = (int)((grid_rows + BM - 1) / BM);
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&acc_full[b], 1);
+      mbar_init(&acc_empty[b], 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1)
+    tmem_alloc(&tmem_slot, 2 * kCols);
+  // the whole weight matrix [BN][K] (K-major) -> resident 128-byte-swizzled panels, one per k-block
+  {
+    constexpr int kRowChunks = Geo::kK * Geo::kEB / 16;
+    for (int q = threadIdx.x; q < BN * kRowChunks; q += kShiftThreads) {
+      const int j = q / kRowChunks, kcg = q - j * kRowChunks, kb = kcg >> 3, kc = kcg & 7;
+      const uint32_t dst = b_s + (uint32_t)(kb * Geo::kBPanel + j * 128 + ((kc ^ (j & 7)) << 4));
+      cp_async16(dst, w + (size_t)j * Geo::kK + kcg * (16 / Geo::kEB), w);
+    }
+    cp_async_commit();
+    cp_async_wait<0>();
+    fence_proxy_async_smem();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) { // ===== TMA producer: one staged copy of the input rows per tile
+      int it = 0;
+      for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
+        const int s = it % STAGES;
+        mbar_wait(&empty_bar[s], (((uint32_t)(it / STAGES)) & 1u) ^ 1u);
+        mbar_arrive_expect_tx(&full_bar[s], (uint32_t)Geo::kStage);
+#pragma unroll
+        for (int cp = 0; cp < Geo::kCP; ++cp)
+          tma_tile_2d(st_s + (uint32_t)(s * Geo::kStage + cp * Geo::kPanel), xmap, cp * Geo::kBKE,
+                      row_base + tile * BM, &full_bar[s]);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) { // ===== MMA issuer: every tap is a row-shifted view of the staged rows
+      int it = 0;
+      for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
+        const int s = it % STAGES, buf = it & 1;
+        if (it >= 2)
+          mbar_wait(&acc_empty[buf], (((uint32_t)(it >> 1)) & 1u) ^ 1u);
+        mbar_wait(&full_bar[s], ((uint32_t)(it / STAGES)) & 1u);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + (uint32_t)(buf * kCols);
+        const uint32_t stage = st_s + (uint32_t)(s * Geo::kStage);
+#pragma unroll
+        for (int t = 0; t < Geo::kTaps; ++t) {
+          const int shift = (t / KW) * GW + (t % KW);
+#pragma unroll
+          for (int cp = 0; cp < Geo::kCP; ++cp) {
+            const uint64_t adesc = make_smem_desc_row(stage + (uint32_t)(cp * Geo::kPanel + shift * 128),
+                                                      use_base_offset != 0);
+            const uint64_t bdesc =
+                make_smem_desc(b_s + (uint32_t)((t * Geo::kCP + cp) * Geo::kBPanel), 16u, 1024u);
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+              const uint32_t acc = (uint32_t)((t | cp | kk) != 0);
+              if constexpr (Geo::kEB == 4)
+                umma_tf32(tmem_d, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), kIdesc, acc);
+              else
+                umma_bf16(tmem_d, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), kIdesc, acc);
+            }
+          }
+        }
+        umma_commit(&empty_bar[s]); // the stage is free once these UMMAs have read it
+        umma_commit(&acc_full[buf]);
+      }
+    }
+  } else { // ===== epilogue: warps 2..5, TMEM lane quarter = warp & 3
+    const int quarter = warp & 3;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
+      const int buf = it & 1;
+      mbar_wait(&acc_full[buf], ((uint32_t)(it >> 1)) & 1u);
+      tc_fence_after();
+      const int64_t r = (int64_t)tile * BM + quarter * 32 + lane;
+      const int64_t img = r / G;
+      const int q = (int)(r - img * G), gy = q / GW, gx = q - gy * GW;
+      const bool valid = r < grid_rows && gy < OH && gx < OW;
+      const int64_t i_out = (img * OH + gy) * OW + gx;
+#pragma unroll
+      for (int c = 0; c < BN; c += 16) {
+        float v[16];
+        tmem_ld16(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * kCols + c), v);
+        if (valid)
+          epi((int)i_out, c, v, 0);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0)
+        mbar_arrive(&acc_empty[buf]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1)
+    tmem_dealloc(tmem_base, 2 * kCols);
+}
+
+template <class T, int BN, int KH, int KW, int GH, int GW, int OH, int OW, int STAGES, class Epi>
+int launch_conv_shift(const void *xmap, int64_t row_base, const T *w, const Epi &e, int64_t images,
+                      cudaStream_t s, bool use_base_offset) {
+  if (images <= 0)
+    return ALEGPU_OK;
+  using Geo = ShiftGeom<T, BN, KH, KW, GW>;
+  auto kern = conv_shift_kernel<T, BN, KH, KW, GH, GW, OH, OW, STAGES, Epi>;
+  constexpr int kSmem = Geo::smem(STAGES);
+  static_assert(kSmem <= 227 * 1024, "shift conv: shared memory over budget");
+  static bool configured = false; // per template instantiation
+  if (!configured) {
+    ALEGPU_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+    configured = true;
+  }
+  const int64_t grid_rows = images * GH * GW, tiles = ceil_div(grid_rows, BM);
+  ALEGPU_REQUIRE(row_base + grid_rows + kShiftStageRows < ((int64_t)1 << 31), ALEGPU_INVALID_ARGUMENT,
+                 "shift conv: row coordinate exceeds the TMA range");
+  const unsigned grid = (unsigned)std::min<int64_t>(tiles, kNumSMs);
+  kern<<<grid, kShiftThreads, kSmem, s>>>(xmap, (int)row_base, w, e, grid_rows, use_base_offset ? 1 : 0);
+  ALEGPU_COUNT_LAUNCH_NAMED(__PRETTY_FUNCTION__);
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}
+
+} // namespace tc
+} // namespace alegpu

@@ -300,3 +300,25 @@ def test_tma_descriptor_follows_a_regrown_observation_copy(monkeypatch):
         outs.append(L.get_params())
     assert np.array_equal(outs[0], outs[1])
     assert not np.array_equal(outs[0], params)
+
+
+@pytest.mark.parametrize("n", [37, 256])
+@pytest.mark.parametrize("math", [alegpu.MATH_BF16, alegpu.MATH_TF32], ids=["bf16", "tf32"])
+def test_shift_convolutions_match_the_im2col_engine(math, n, monkeypatch):
+    """conv1 / conv3 forward as shift GEMMs (tc_shift.cuh: the input staged once per tile, every tap a
+    row-shifted shared-memory descriptor, weights resident) against the im2col engine
+    (ALEGPU_NO_SHIFT=1): the same products accumulated in the same tap-major order."""
+    H = 64
+    params = cases.net_params(H, seed=5)
+    tc = cases.train_case(n, seed=19)
+    outs = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("ALEGPU_NO_SHIFT", flag)
+        L = alegpu.Learner(H, 4, n, math, cases.LR)
+        L.set_params(params)
+        grads, loss, logits, values = L.grads(_batch(tc), hp())
+        outs[flag] = (grads, logits, values) + tuple(L.activations(n))
+    names = ("grads", "logits", "values", "act1", "act2", "act3", "fc")
+    for name, a, b in zip(names, outs["0"], outs["1"]):
+        err = rel_l2(a, b)
+        assert err <= 1e-6, (name, err)
