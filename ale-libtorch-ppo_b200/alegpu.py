@@ -43,6 +43,8 @@ def lib():
         _lib.alegpu_version.restype = C.c_char_p
         _lib.alegpu_learner_param_count.restype = C.c_int64
         _lib.alegpu_learner_param_count.argtypes = [C.c_void_p]
+        _lib.alegpu_learner_comm_mode.restype = C.c_char_p
+        _lib.alegpu_learner_comm_mode.argtypes = [C.c_void_p]
         _lib.alegpu_learner_stream.restype = C.c_void_p
         _lib.alegpu_learner_stream.argtypes = [C.c_void_p]
         _lib.alegpu_learner_last_launch_count.restype = C.c_int64
@@ -509,6 +511,10 @@ class Learner:
         self.hidden_size, self.action_size, self.max_minibatch = hidden_size, action_size, max_minibatch
         self.P = int(lib().alegpu_learner_param_count(self.h))
         self.stream = lib().alegpu_learner_stream(self.h)
+
+    def comm_mode(self):
+        """'single', 'fused-nvlink' or 'nccl' (alegpu_learner_comm_mode)."""
+        return lib().alegpu_learner_comm_mode(self.h).decode()
 
     def close(self):
         """Destroy the learner now (NCCL communicator included); with world_size > 1 every rank

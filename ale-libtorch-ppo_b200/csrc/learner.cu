@@ -35,6 +35,7 @@ struct NcclApi {
   ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
   ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
                             cudaStream_t) = nullptr;
+  ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
   ncclResult_t (*CommSplit)(ncclComm_t, int, int, ncclComm_t *, ncclConfig_t *) = nullptr;
   const char *(*GetErrorString)(ncclResult_t) = nullptr;
@@ -50,6 +51,7 @@ static NcclApi &nccl() {
       api.GetUniqueId = (decltype(api.GetUniqueId))dlsym(h, "ncclGetUniqueId");
       api.CommInitRank = (decltype(api.CommInitRank))dlsym(h, "ncclCommInitRank");
       api.AllReduce = (decltype(api.AllReduce))dlsym(h, "ncclAllReduce");
+      api.AllGather = (decltype(api.AllGather))dlsym(h, "ncclAllGather");
       api.CommDestroy = (decltype(api.CommDestroy))dlsym(h, "ncclCommDestroy");
       api.CommSplit = (decltype(api.CommSplit))dlsym(h, "ncclCommSplit");
       api.GetErrorString = (decltype(api.GetErrorString))dlsym(h, "ncclGetErrorString");
@@ -129,6 +131,13 @@ struct alegpu_learner {
   cudaStream_t comm_stream = nullptr;
   cudaEvent_t ev_comm = nullptr;
 #endif
+  // fused NVLink gradient exchange (optim.cu: adam_fused_allreduce_kernel): peers' gradient /
+  // exchange / signal buffers mapped through CUDA IPC; false = the ncclAllReduce path
+  bool fused_ar = false;
+  ArParams ar{};
+  void *xchg = nullptr;            // [ArSignals | reduced slice]
+  std::vector<void *> ipc_opened;  // peer mappings to close
+  std::string comm_mode = "single";
   std::vector<float> host_tmp;
 };
 
@@ -198,7 +207,10 @@ bool use_tc(const alegpu_learner *L) {
 // an input error a kernel of an EARLIER call reported through the mapped flag (no synchronisation)
 int learner_input_error(alegpu_learner *L) {
   if (L->err_host && *(volatile int *)L->err_host) {
+    const int code = *(volatile int *)L->err_host;
     *(volatile int *)L->err_host = 0;
+    if (code == 2)
+      return fail(ALEGPU_RUNTIME_ERROR, "train: a peer rank did not reach the gradient exchange in time");
     return fail(ALEGPU_OUT_OF_RANGE, "train: an action index was outside [0, action_size)");
   }
   return ALEGPU_OK;
@@ -247,8 +259,17 @@ int allreduce_grads(alegpu_learner *L) {
 }
 
 int clip_and_step(alegpu_learner *L, float max_norm, float *total_norm_out,
-                  const float *count = nullptr, float *m_loss = nullptr, int64_t mb = 0) {
+                  const float *count = nullptr, float *m_loss = nullptr, int64_t mb = 0,
+                  bool exchange = false) {
   static const bool no_fused = getenv("ALEGPU_NO_FUSED_ADAM") != nullptr; // A/B: the two-kernel form
+  if (exchange && L->fused_ar) { // gradient exchange over NVLink inside the optimiser kernel
+    L->host_step += 1;
+    return launch_adam_fused_allreduce(L->params, L->m, L->v, use_tc(L) ? L->tc.w_shadow : nullptr,
+                                       use_tc(L) ? L->tc.c1w_perm : nullptr,
+                                       use_tc(L) ? L->tc.elem_bytes : 0, L->Ppad, L->P, L->norm_partials,
+                                       L->opt, max_norm, total_norm_out, count, m_loss, mb, L->ar,
+                                       L->stream);
+  }
   if (!no_fused && adam_fused_fits(L->Ppad)) {
     L->host_step += 1;
     return launch_adam_fused(L->params, L->grads, L->m, L->v, use_tc(L) ? L->tc.w_shadow : nullptr,
@@ -391,17 +412,106 @@ int enqueue_train(alegpu_learner *L, const alegpu_batch &b, const alegpu_metrics
         return rc;
       if (int rc = backward(L, obs, mb, obs16))
         return rc;
-      if (int rc = allreduce_grads(L))
-        return rc;
+      if (!L->fused_ar) // (the fused path sums the gradient inside the optimiser kernel below)
+        if (int rc = allreduce_grads(L))
+          return rc;
       // norm + clip + Adam + the Metrics.loss broadcast (train.h:98): one launch
       if (int rc = clip_and_step(L, hp.max_gradient_norm,
                                  mt.clipped_gradients ? mt.clipped_gradients + ep * nmb + k
                                                       : L->scalars,
-                                 count, mt.loss ? mt.loss + o : nullptr, mb))
+                                 count, mt.loss ? mt.loss + o : nullptr, mb, /*exchange=*/true))
         return rc;
     }
   return ALEGPU_OK;
 }
+
+#ifdef ALEGPU_WITH_NCCL
+// Map every peer's flat buffer and exchange buffer (CUDA IPC; the 2 x 64-byte handles travel through
+// one ncclAllGather) so the optimiser kernel can pull gradients over NVLink.  Any rank that cannot
+// (no peer access, IPC refused, net too large for the register-cached kernel) makes ALL ranks keep the
+// ncclAllReduce path: the decision is an all-reduced minimum.  ALEGPU_NO_FUSED_AR=1 forces that path.
+int setup_fused_allreduce(alegpu_learner *L) {
+  const int world = L->cfg.world_size, rank = L->cfg.rank;
+  L->comm_mode = "nccl";
+  int ok = 1;
+  if (getenv("ALEGPU_NO_FUSED_AR") || getenv("ALEGPU_NO_FUSED_ADAM") || !nccl().AllGather ||
+      world > kArMaxRanks || !adam_fused_fits(L->Ppad))
+    ok = 0;
+  const int64_t slice4 = ceil_div(L->Ppad / 4, world);
+  const size_t xbytes = 1024 + (size_t)slice4 * 16;
+  struct Handles {
+    cudaIpcMemHandle_t flat, xchg;
+  } mine{};
+  static_assert(sizeof(Handles) == 128, "two 64-byte IPC handles");
+  if (ok) {
+    ALEGPU_CUDA_CHECK(cudaMalloc(&L->xchg, xbytes));
+    ALEGPU_CUDA_CHECK(cudaMemset(L->xchg, 0, xbytes));
+    if (cudaIpcGetMemHandle(&mine.flat, L->flat) != cudaSuccess ||
+        cudaIpcGetMemHandle(&mine.xchg, L->xchg) != cudaSuccess) {
+      cudaGetLastError();
+      ok = 0;
+    }
+  }
+  char *d_buf = nullptr; // [mine | all ranks | ok flag]
+  ALEGPU_CUDA_CHECK(cudaMalloc(&d_buf, 128 * (size_t)(world + 1) + 16));
+  ALEGPU_CUDA_CHECK(cudaMemcpyAsync(d_buf, &mine, 128, cudaMemcpyHostToDevice, L->stream));
+  ncclResult_t r = nccl().AllGather(d_buf, d_buf + 128, 128, ncclChar, L->comm, L->stream);
+  if (r != ncclSuccess)
+    return fail(ALEGPU_CUDA_ERROR, std::string("ncclAllGather: ") + nccl().GetErrorString(r));
+  std::vector<Handles> all((size_t)world);
+  ALEGPU_CUDA_CHECK(cudaMemcpyAsync(all.data(), d_buf + 128, 128 * (size_t)world, cudaMemcpyDeviceToHost,
+                                    L->stream));
+  ALEGPU_CUDA_CHECK(cudaStreamSynchronize(L->stream));
+  ArParams ar{};
+  ar.world = world;
+  ar.rank = rank;
+  ar.slice4 = slice4;
+  ar.error_flag = L->err_dev;
+  for (int p = 0; p < world && ok; ++p) {
+    void *flat = L->flat, *xchg = L->xchg;
+    if (p != rank) {
+      if (cudaIpcOpenMemHandle(&flat, all[(size_t)p].flat, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+        cudaGetLastError();
+        ok = 0;
+        break;
+      }
+      L->ipc_opened.push_back(flat);
+      if (cudaIpcOpenMemHandle(&xchg, all[(size_t)p].xchg, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+        cudaGetLastError();
+        ok = 0;
+        break;
+      }
+      L->ipc_opened.push_back(xchg);
+    }
+    ar.grads[p] = static_cast<float *>(flat) + L->Ppad; // params | grads | m | v
+    ar.sig[p] = static_cast<ArSignals *>(xchg);
+    ar.xbuf[p] = reinterpret_cast<float *>(static_cast<char *>(xchg) + 1024);
+  }
+  float *d_ok = reinterpret_cast<float *>(d_buf + 128 * (size_t)(world + 1));
+  const float okf = (float)ok;
+  ALEGPU_CUDA_CHECK(cudaMemcpyAsync(d_ok, &okf, sizeof(float), cudaMemcpyHostToDevice, L->stream));
+  r = nccl().AllReduce(d_ok, d_ok, 1, ncclFloat, ncclMin, L->comm, L->stream);
+  if (r != ncclSuccess)
+    return fail(ALEGPU_CUDA_ERROR, std::string("ncclAllReduce: ") + nccl().GetErrorString(r));
+  float all_ok = 0.0f;
+  ALEGPU_CUDA_CHECK(cudaMemcpyAsync(&all_ok, d_ok, sizeof(float), cudaMemcpyDeviceToHost, L->stream));
+  ALEGPU_CUDA_CHECK(cudaStreamSynchronize(L->stream));
+  cudaFree(d_buf);
+  if (all_ok >= 1.0f) {
+    L->ar = ar;
+    L->fused_ar = true;
+    L->comm_mode = "fused-nvlink";
+  } else {
+    for (void *q : L->ipc_opened)
+      cudaIpcCloseMemHandle(q);
+    L->ipc_opened.clear();
+    if (L->xchg)
+      cudaFree(L->xchg);
+    L->xchg = nullptr;
+  }
+  return ALEGPU_OK;
+}
+#endif
 
 template <typename T> void key_push(std::vector<uint64_t> &k, T v) {
   uint64_t x = 0;
@@ -667,6 +777,8 @@ extern "C" int alegpu_learner_create(const alegpu_learner_config *config, alegpu
       ALEGPU_CUDA_CHECK(cudaStreamCreateWithFlags(&L->comm_stream, cudaStreamNonBlocking));
       ALEGPU_CUDA_CHECK(cudaEventCreateWithFlags(&L->ev_comm, cudaEventDisableTiming));
     }
+    if (int rc = setup_fused_allreduce(L.get()))
+      return rc;
   }
 #else
   ALEGPU_REQUIRE(L->cfg.world_size == 1, ALEGPU_RUNTIME_ERROR,
@@ -693,6 +805,17 @@ extern "C" int alegpu_learner_destroy(alegpu_learner *L) {
 #ifdef ALEGPU_WITH_NCCL
   if (L->comm_stream)
     cudaStreamSynchronize(L->comm_stream);
+  if (L->fused_ar) {
+    // a peer's last optimiser kernel may still be pulling this rank's exchange buffer: every rank
+    // reaches this point with ITS stream drained, so one tiny collective is the handshake after which
+    // the mappings can go
+    nccl().AllReduce(L->counts, L->counts, 1, ncclFloat, ncclSum, L->comm, L->stream);
+    cudaStreamSynchronize(L->stream);
+    for (void *q : L->ipc_opened)
+      cudaIpcCloseMemHandle(q);
+    L->ipc_opened.clear();
+    // (freeing the exported exchange buffer happens below, after the communicators are gone)
+  }
   if (L->comm2)
     nccl().CommDestroy(L->comm2);
   if (L->comm)
@@ -714,6 +837,8 @@ extern "C" int alegpu_learner_destroy(alegpu_learner *L) {
     cudaFree(L->opt);
   if (L->loss_done)
     cudaFree(L->loss_done);
+  if (L->xchg)
+    cudaFree(L->xchg);
   if (L->err_host)
     cudaFreeHost(L->err_host);
   net_tc_destroy(L->tc);
@@ -729,6 +854,9 @@ extern "C" int alegpu_learner_destroy(alegpu_learner *L) {
 }
 
 extern "C" int64_t alegpu_learner_param_count(const alegpu_learner *L) { return L ? L->P : 0; }
+extern "C" const char *alegpu_learner_comm_mode(const alegpu_learner *L) {
+  return L ? L->comm_mode.c_str() : "";
+}
 extern "C" void *alegpu_learner_stream(alegpu_learner *L) { return L ? L->stream : nullptr; }
 
 extern "C" int alegpu_learner_set_params(alegpu_learner *L, const float *params_host) {

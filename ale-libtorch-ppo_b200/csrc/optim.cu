@@ -301,6 +301,221 @@ __global__ void __launch_bounds__(kThreads, 2)
   }
 }
 
+// ---- multi-GPU: gradient exchange + norm + clip + Adam in ONE kernel over NVLink peer memory ----------
+// Two-shot all-reduce by PULL, fused into the optimiser step (replaces ncclAllReduce x2 + grad_sumsq +
+// adam_clip + finalize_metrics per minibatch):
+//   0. announce "my local gradient of step e is complete" in every peer's signal block; wait for all.
+//   1. reduce-scatter: this rank sums ITS slice over all ranks' raw gradients (16-byte volatile loads
+//      over NVLink, ranks added in index order -> bit-reproducible, identical on every rank), stores it
+//      in its exchange buffer and accumulates the slice's sum of squares; grid barrier; the last CTA
+//      publishes the slice's sum of squares and "slice e reduced" to every peer.
+//   2. wait for all slices; total norm = sqrt(sum of the per-rank partials, rank order) — the same
+//      bits on every rank; clip coefficient and bias corrections.
+//   3. all-gather fused into Adam's gradient load: element i's gradient comes from its owner's
+//      exchange buffer (local for the own slice, a volatile NVLink load otherwise); p / m / v were
+//      prefetched before step 2's wait.  Parameters stay replicated and bit-identical on all ranks.
+// Reuse hazards are closed by the protocol itself: a peer overwrites its raw gradient (next backward) only
+// after it passed step 2, i.e. after this rank published its slice, i.e. after this rank finished reading;
+// an exchange buffer is rewritten in step 1 of e+1, after every peer announced e+1, i.e. finished e.
+__device__ __forceinline__ float4 ld_peer_f4(const float *p) {
+  float4 r;
+  asm volatile("ld.volatile.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ unsigned long long ld_flag(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_flag(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// spin until *p >= e (bounded: ~seconds; a missing peer raises the error flag instead of hanging the GPU)
+__device__ __forceinline__ void wait_flag(const unsigned long long *p, unsigned long long e, int *err) {
+  for (long long spins = 0; ld_flag(p) < e; ++spins) {
+    __nanosleep(64);
+    if (spins > (1ll << 25)) {
+      if (err)
+        atomicExch(err, 2);
+      break;
+    }
+  }
+}
+
+template <class ST>
+__global__ void __launch_bounds__(kThreads, 2)
+    adam_fused_allreduce_kernel(float *__restrict__ p, float *__restrict__ m, float *__restrict__ v,
+                                ST *__restrict__ shadow, ST *__restrict__ c1w_perm, int64_t n4,
+                                int64_t n_valid, float *__restrict__ partials, OptState *st,
+                                float max_norm, float *__restrict__ total_norm_out,
+                                const float *__restrict__ count, float *__restrict__ m_loss, int64_t mb,
+                                const ArParams ar) {
+  __shared__ float red[kThreads / 32];
+  __shared__ bool s_last;
+  __shared__ float s_coef[3];
+  float4 *p4 = reinterpret_cast<float4 *>(p);
+  float4 *m4 = reinterpret_cast<float4 *>(m);
+  float4 *v4 = reinterpret_cast<float4 *>(v);
+  const int64_t stride = (int64_t)gridDim.x * kThreads;
+  const int64_t i0 = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  const long long step0 = *reinterpret_cast<volatile long long *>(&st->step);
+  const unsigned long long e = (unsigned long long)(step0 + 1);
+  ArSignals *mine = ar.sig[ar.rank];
+  // ---- 0: announce, wait for every rank's gradient
+  if (blockIdx.x == 0 && threadIdx.x < ar.world) {
+    __threadfence_system();
+    st_flag(&ar.sig[threadIdx.x]->ready[ar.rank], e);
+  }
+  if (threadIdx.x < ar.world)
+    wait_flag(&mine->ready[threadIdx.x], e, ar.error_flag);
+  __syncthreads();
+  __threadfence_system();
+  // ---- 1: reduce-scatter of this rank's slice
+  const int64_t lo4 = ar.slice4 * ar.rank;
+  const int64_t hi4 = lo4 + ar.slice4 < n4 ? lo4 + ar.slice4 : n4;
+  float4 *xmine = reinterpret_cast<float4 *>(ar.xbuf[ar.rank]);
+  float acc = 0.0f;
+  for (int64_t i = lo4 + i0; i < hi4; i += stride) {
+    float4 s = zero4;
+    for (int r = 0; r < ar.world; ++r) { // fixed rank order: the same bits whoever computes the slice
+      const float4 x = ld_peer_f4(ar.grads[r] + 4 * i);
+      s.x += x.x; s.y += x.y; s.z += x.z; s.w += x.w;
+    }
+    xmine[i - lo4] = s;
+    float4 x = s;
+    if (4 * i + 3 >= n_valid) { // the padding behind the last parameter (the loss sum) is not part of the norm
+      x.x = 4 * i < n_valid ? x.x : 0.0f;
+      x.y = 4 * i + 1 < n_valid ? x.y : 0.0f;
+      x.z = 4 * i + 2 < n_valid ? x.z : 0.0f;
+      x.w = 0.0f;
+    }
+    acc += x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
+  }
+  acc = block_sum<float, kThreads>(acc, red);
+  if (threadIdx.x == 0) {
+    partials[blockIdx.x] = acc;
+    __threadfence_system(); // this CTA's slice stores before its arrival
+    s_last = atomicAdd(&st->done_count, 1u) == gridDim.x - 1;
+  }
+  // p / m / v of this thread's Adam elements: in flight across the waits below
+  float4 pp[kCache], mm[kCache], vv[kCache];
+#pragma unroll
+  for (int c = 0; c < kCache; ++c) {
+    const int64_t i = i0 + c * stride;
+    pp[c] = i < n4 ? p4[i] : zero4;
+    mm[c] = i < n4 ? m4[i] : zero4;
+    vv[c] = i < n4 ? v4[i] : zero4;
+  }
+  __syncthreads();
+  if (s_last && threadIdx.x < 32) { // every CTA of this rank has stored its part of the slice
+    __threadfence();
+    double s = 0.0;
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += 32)
+      s += (double)__ldcg(partials + i);
+    s = warp_sum(s);
+    if (threadIdx.x == 0)
+      st->done_count = 0u;
+    if (threadIdx.x < ar.world) {
+      ar.sig[threadIdx.x]->partial[ar.rank] = s;
+      __threadfence_system();
+      st_flag(&ar.sig[threadIdx.x]->reduced[ar.rank], e);
+    }
+  }
+  // ---- 2: all slices reduced; the global norm from the per-rank partials (rank order)
+  if (threadIdx.x < ar.world)
+    wait_flag(&mine->reduced[threadIdx.x], e, ar.error_flag);
+  __syncthreads();
+  __threadfence_system();
+  if (threadIdx.x == 0) {
+    double s = 0.0;
+    for (int r = 0; r < ar.world; ++r)
+      s += *reinterpret_cast<volatile double *>(&mine->partial[r]);
+    const float total = (float)sqrt(s);
+    const float coef = fminf((float)((double)max_norm / ((double)total + 1e-6)), 1.0f); // train.cc:39-41
+    const double t = (double)(step0 + 1);
+    const double bc1 = 1.0 - pow(0.9, t), bc2 = 1.0 - pow(0.999, t);
+    s_coef[0] = coef;
+    s_coef[1] = (float)(*reinterpret_cast<volatile double *>(&st->lr) / bc1);
+    s_coef[2] = (float)sqrt(bc2);
+    if (blockIdx.x == 0) { // every CTA derives the same three numbers; one records them
+      st->coef = s_coef[0];
+      st->step_size = s_coef[1];
+      st->bc2_sqrt = s_coef[2];
+      if (total_norm_out)
+        *total_norm_out = total; // the PRE-clip norm of the GLOBAL gradient (train.h:104)
+    }
+  }
+  __syncthreads();
+  const float coef = s_coef[0], step_size = s_coef[1], bc2_sqrt = s_coef[2];
+  const float b1 = 0.9f, b2 = 0.999f, omb1 = (float)(1.0 - 0.9), omb2 = (float)(1.0 - 0.999);
+  const float eps = 1e-5f;
+  // ---- 3: all-gather fused into Adam's gradient load
+#pragma unroll
+  for (int c = 0; c < kCache; ++c) {
+    const int64_t i = i0 + c * stride;
+    if (i >= n4)
+      continue;
+    const int owner = (int)(i / ar.slice4);
+    const float *src = ar.xbuf[owner] + 4 * (i - ar.slice4 * owner);
+    float4 gg = owner == ar.rank ? *reinterpret_cast<const float4 *>(src) : ld_peer_f4(src);
+    float *pa = &pp[c].x, *ga = &gg.x, *ma = &mm[c].x, *va = &vv[c].x;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float gc = ga[k] * coef;
+      ma[k] = ma[k] * b1 + gc * omb1;
+      va[k] = va[k] * b2 + (gc * gc) * omb2;
+      const float denom = sqrtf(va[k]) / bc2_sqrt + eps;
+      pa[k] = pa[k] - step_size * (ma[k] / denom);
+    }
+    p4[i] = pp[c];
+    m4[i] = mm[c];
+    v4[i] = vv[c];
+    if (shadow) {
+      if constexpr (sizeof(ST) == 2) {
+        __nv_bfloat162 lo = __floats2bfloat162_rn(pp[c].x, pp[c].y), hi = __floats2bfloat162_rn(pp[c].z, pp[c].w);
+        uint2 pk;
+        pk.x = *reinterpret_cast<uint32_t *>(&lo);
+        pk.y = *reinterpret_cast<uint32_t *>(&hi);
+        reinterpret_cast<uint2 *>(shadow)[i] = pk;
+      } else {
+        reinterpret_cast<float4 *>(shadow)[i] = make_float4(round_tf32(pp[c].x), round_tf32(pp[c].y),
+                                                            round_tf32(pp[c].z), round_tf32(pp[c].w));
+      }
+      if (c1w_perm && i < 32 * 256 / 4) {
+        const int idx = (int)i * 4, co = idx >> 8, k = idx & 255;
+        const int ch = k >> 6, ky = (k >> 3) & 7, kx = k & 7;
+        ST *o = c1w_perm + co * 256 + ((ky >> 2) * 2 + (kx >> 2)) * 64 + (ky & 3) * 16 + (kx & 3) * 4 + ch;
+        if constexpr (sizeof(ST) == 2) {
+          o[0] = __float2bfloat16_rn(pp[c].x);
+          o[4] = __float2bfloat16_rn(pp[c].y);
+          o[8] = __float2bfloat16_rn(pp[c].z);
+          o[12] = __float2bfloat16_rn(pp[c].w);
+        } else {
+          o[0] = round_tf32(pp[c].x);
+          o[4] = round_tf32(pp[c].y);
+          o[8] = round_tf32(pp[c].z);
+          o[12] = round_tf32(pp[c].w);
+        }
+      }
+    }
+  }
+  if (m_loss) { // Metrics.loss: the GLOBAL loss sum rode in the first padding slot of the gradient
+    const int64_t li = n_valid, l4 = li / 4;
+    const int owner = (int)(l4 / ar.slice4);
+    const float *src = ar.xbuf[owner] + (li - 4 * ar.slice4 * owner);
+    const float loss = *reinterpret_cast<const volatile float *>(src) / count[0];
+    for (int64_t i = i0; i < mb; i += stride)
+      m_loss[i] = loss;
+  }
+  // the step counter advances once every CTA has read it (all CTAs arrived before `reduced` was published)
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    *reinterpret_cast<volatile long long *>(&st->step) = step0 + 1;
+}
+
 __global__ void f32_to_bf16_kernel(const float *__restrict__ src, __nv_bfloat16 *__restrict__ dst,
                                    int64_t n) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
@@ -350,6 +565,26 @@ int launch_adam_fused(float *params, float *grads, float *m, float *v, void *sha
     adam_fused_kernel<__nv_bfloat16><<<kNormBlocks, kThreads, 0, s>>>(
         params, grads, m, v, static_cast<__nv_bfloat16 *>(shadow), static_cast<__nv_bfloat16 *>(c1w_perm),
         n_padded / 4, n_valid, partials, st, max_norm, total_norm_out, loss_sum, count, m_loss, mb);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}
+
+int launch_adam_fused_allreduce(float *params, float *m, float *v, void *shadow, void *c1w_perm,
+                                int shadow_elem_bytes, int64_t n_padded, int64_t n_valid,
+                                float *partials, OptState *st, float max_norm, float *total_norm_out,
+                                const float *count, float *m_loss, int64_t mb, const ArParams &ar,
+                                cudaStream_t s) {
+  ALEGPU_REQUIRE(adam_fused_fits(n_padded), ALEGPU_RUNTIME_ERROR,
+                 "adam_fused_allreduce: buffer exceeds the register cache");
+  if (shadow && shadow_elem_bytes == 4)
+    adam_fused_allreduce_kernel<float><<<kNormBlocks, kThreads, 0, s>>>(
+        params, m, v, static_cast<float *>(shadow), static_cast<float *>(c1w_perm), n_padded / 4, n_valid,
+        partials, st, max_norm, total_norm_out, count, m_loss, mb, ar);
+  else
+    adam_fused_allreduce_kernel<__nv_bfloat16><<<kNormBlocks, kThreads, 0, s>>>(
+        params, m, v, static_cast<__nv_bfloat16 *>(shadow), static_cast<__nv_bfloat16 *>(c1w_perm),
+        n_padded / 4, n_valid, partials, st, max_norm, total_norm_out, count, m_loss, mb, ar);
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
   return ALEGPU_OK;

@@ -34,6 +34,28 @@ int launch_adam_fused(float *params, float *grads, float *m, float *v, void *sha
                       int shadow_elem_bytes, int64_t n_padded, int64_t n_valid, float *partials,
                       OptState *st, float max_norm, float *total_norm_out, const float *loss_sum,
                       const float *count, float *m_loss, int64_t mb, cudaStream_t s);
+// ---- multi-GPU: the gradient exchange fused into the same kernel (no separate collective launch) ----
+// Every rank maps its peers' gradient buffers, exchange buffers and signal blocks (CUDA IPC, set up
+// once by the learner).  Rank r owns the r-th contiguous slice of the flat buffer.
+constexpr int kArMaxRanks = 16;
+struct ArSignals { // lives in every rank's exchange allocation; peers write their slot over NVLink
+  unsigned long long ready[kArMaxRanks];   // [p]: rank p's local gradient of step e is complete
+  unsigned long long reduced[kArMaxRanks]; // [p]: rank p's slice of step e is summed and published
+  double partial[kArMaxRanks];             // [p]: sum of squares of rank p's reduced slice
+};
+struct ArParams {
+  int world = 1, rank = 0;
+  int64_t slice4 = 0;               // float4 elements per rank slice (the last slice may be shorter)
+  float *grads[kArMaxRanks] = {};   // every rank's raw local gradient (flat, n_padded floats)
+  float *xbuf[kArMaxRanks] = {};    // every rank's reduced slice (slice4 float4)
+  ArSignals *sig[kArMaxRanks] = {}; // every rank's signal block
+  int *error_flag = nullptr;        // mapped host int: 2 = a peer did not show up in time
+};
+int launch_adam_fused_allreduce(float *params, float *m, float *v, void *shadow, void *c1w_perm,
+                                int shadow_elem_bytes, int64_t n_padded, int64_t n_valid,
+                                float *partials, OptState *st, float max_norm, float *total_norm_out,
+                                const float *count, float *m_loss, int64_t mb, const ArParams &ar,
+                                cudaStream_t s);
 int launch_f32_to_bf16(const float *src, void *dst, int64_t n, cudaStream_t s);
 
 } // namespace alegpu

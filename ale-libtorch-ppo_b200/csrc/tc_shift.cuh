@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(kShiftThreads, 1)
   constexpr uint32_t kIdesc = make_idesc(BN, false, false, Geo::kEB);
   constexpr uint32_t kCols = tmem_cols(BN);
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], acc_full[2], acc_empty[2];
+  __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], acc_full[2], acc_empty[2], b_ready;
   __shared__ uint32_t tmem_slot;
   uint8_t *base = reinterpret_cast<uint8_t *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const uint32_t b_s = smem_u32(base), st_s = b_s + Geo::kBBytes;
@@ -96,22 +96,11 @@ __global__ void __launch_bounds__(kShiftThreads, 1)
       mbar_init(&acc_full[b], 1);
       mbar_init(&acc_empty[b], 4);
     }
+    mbar_init(&b_ready, 4);
     fence_barrier_init();
   }
   if (warp == 1)
     tmem_alloc(&tmem_slot, 2 * kCols);
-  // the whole weight matrix [BN][K] (K-major) -> resident 128-byte-swizzled panels, one per k-block
-  {
-    constexpr int kRowChunks = Geo::kK * Geo::kEB / 16;
-    for (int q = threadIdx.x; q < BN * kRowChunks; q += kShiftThreads) {
-      const int j = q / kRowChunks, kcg = q - j * kRowChunks, kb = kcg >> 3, kc = kcg & 7;
-      const uint32_t dst = b_s + (uint32_t)(kb * Geo::kBPanel + j * 128 + ((kc ^ (j & 7)) << 4));
-      cp_async16(dst, w + (size_t)j * Geo::kK + kcg * (16 / Geo::kEB), w);
-    }
-    cp_async_commit();
-    cp_async_wait<0>();
-    fence_proxy_async_smem();
-  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -132,6 +121,7 @@ __global__ void __launch_bounds__(kShiftThreads, 1)
     }
   } else if (warp == 1) {
     if (lane == 0) { // ===== MMA issuer: every tap is a row-shifted view of the staged rows
+      mbar_wait(&b_ready, 0u); // the resident weights have landed
       int it = 0;
       for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
         const int s = it % STAGES, buf = it & 1;
@@ -165,6 +155,22 @@ __global__ void __launch_bounds__(kShiftThreads, 1)
       }
     }
   } else { // ===== epilogue: warps 2..5, TMEM lane quarter = warp & 3
+    // first: the whole weight matrix [BN][K] (K-major) -> resident 128-byte-swizzled panels, one per
+    // k-block, while the producer warp already streams the first input stages in
+    {
+      constexpr int kRowChunks = Geo::kK * Geo::kEB / 16;
+      for (int q = threadIdx.x - 64; q < BN * kRowChunks; q += 128) {
+        const int j = q / kRowChunks, kcg = q - j * kRowChunks, kb = kcg >> 3, kc = kcg & 7;
+        const uint32_t dst = b_s + (uint32_t)(kb * Geo::kBPanel + j * 128 + ((kc ^ (j & 7)) << 4));
+        cp_async16(dst, w + (size_t)j * Geo::kK + kcg * (16 / Geo::kEB), w);
+      }
+      cp_async_commit();
+      cp_async_wait<0>();
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0)
+        mbar_arrive(&b_ready);
+    }
     const int quarter = warp & 3;
     int it = 0;
     for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {

@@ -619,6 +619,7 @@ def main():
         run.L.set_params(synth.orthogonal_params(w["H"], 4, seed=42))
         run.stream = run.L.stream
     res = H.measure(run, args.steps, args.warmup, min_s=args.min_seconds)
+    comm_mode = run.L.comm_mode()
     run.close()
 
     # extras at N = 1: the other tensor-core precision on the headline workload, and the other two
@@ -643,7 +644,7 @@ def main():
         os._exit(0)
     roof, roof_hbm = rooflines(w, args.math, res)
     cfg = shape_config(w, world)
-    cfg.update({"cuda_graph": use_graph, "math": args.math,
+    cfg.update({"cuda_graph": use_graph, "math": args.math, "gradient_exchange": comm_mode,
                 "l2": "inputs larger than L2 (raw frames %.0f MB per step)" % (w["T"] * run.slab / 1e6)})
     line = {"metric": METRIC, "value": res["value"], "unit": "agent-steps/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": res["ms_per_step"],

@@ -346,6 +346,11 @@ int alegpu_learner_create(const alegpu_learner_config *config, alegpu_learner **
 int alegpu_learner_destroy(alegpu_learner *learner);
 int64_t alegpu_learner_param_count(const alegpu_learner *learner);
 void *alegpu_learner_stream(alegpu_learner *learner);
+/* how gradients are exchanged (no reference counterpart: the reference is single-device):
+ * "single" (world_size 1), "fused-nvlink" (every rank maps its peers' gradient buffers through CUDA
+ * IPC and the optimiser kernel pulls, sums and applies them over NVLink in one launch per minibatch), or
+ * "nccl" (ncclAllReduce per minibatch: ALEGPU_NO_FUSED_AR=1, or when peer mapping is not possible) */
+const char *alegpu_learner_comm_mode(const alegpu_learner *learner);
 
 /* Weights in the reference's `parameters()` order and native tensor layouts (host arrays of
  * param_count floats) — needed to start from the oracle's orthogonal init

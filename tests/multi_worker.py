@@ -57,7 +57,7 @@ def main():
     m = met.numpy()
     np.savez(os.path.join(work, f"rank{rank}.npz"), params=L.get_params(), loss=m["loss"],
              clipped_gradients=m["clipped_gradients"], total_losses=m["total_losses"],
-             step=L.get_adam()[2])
+             step=L.get_adam()[2], comm_mode=L.comm_mode())
     L.close()  # graceful NCCL teardown on every rank
     print(f"rank {rank} done", flush=True)
 

@@ -79,6 +79,12 @@ def test_multi_gpu_train_equals_single_gpu(tmp_path, math, graph, env):
         pytest.skip("needs >= 2 GPUs")
     H, N, nmb, epochs = 64, 256, 2, 2  # minibatch 128 rows = 128/G per rank
     ranks = run_ranks(tmp_path, G, math, graph, H, N, nmb, epochs, env=env)
+    # the default exchanges gradients inside the optimiser kernel over NVLink peer mappings; the other
+    # two environments are the ncclAllReduce path (with / without the overlapped FC bucket)
+    want_mode = "nccl" if "ALEGPU_NO_FUSED_AR" in env else "fused-nvlink"
+    if "ALEGPU_NO_COMM_OVERLAP" in env:
+        want_mode = str(ranks[0]["comm_mode"])  # overlap only matters on the NCCL path
+    assert all(str(r["comm_mode"]) == want_mode for r in ranks), [str(r["comm_mode"]) for r in ranks]
     for r in ranks[1:]:  # replicated parameters stay bit-identical on every rank
         assert np.array_equal(r["params"], ranks[0]["params"])
         assert np.array_equal(r["loss"], ranks[0]["loss"])  # the GLOBAL minibatch loss on every rank
@@ -88,7 +94,7 @@ def test_multi_gpu_train_equals_single_gpu(tmp_path, math, graph, env):
     p1, m1, (params, tc, _) = single_gpu(math, graph, H, N, nmb, epochs)
     tol = {alegpu.MATH_FP32: 1e-5, alegpu.MATH_TF32: 1e-4, alegpu.MATH_BF16: 1e-3}[math]
     err = rel_l2(ranks[0]["params"], p1)
-    print(f"G={G} {NAMES[math]} graph={graph} {env}: params rel-L2 vs 1 GPU {err:.2e}")
+    print(f"G={G} {NAMES[math]} graph={graph} {env} [{ranks[0]['comm_mode']}]: params rel-L2 vs 1 GPU {err:.2e}")
     assert err <= tol, err
     mt = 1e-4 if math == alegpu.MATH_FP32 else 2e-2
     np.testing.assert_allclose(ranks[0]["loss"][:, :, 0], m1["loss"][:, :, 0], rtol=mt, atol=1e-5)
