@@ -954,7 +954,7 @@ template <class T> Shadow<T> shadow_view(const TcState &S, const NetParams &P) {
 // earlier kernel may still have cached is never rewritten in place
 enum TmaSlot { kMapAct1 = 0, kMapAct2, kMapDact3, kMapDact2, kMapObsMb, kMapObsAll, kMapObsAllSlots = 16,
                // plain [rows x 64] tiled maps of the same buffers for the shift convolutions (tc_shift.cuh)
-               kMapAct2Rows = kMapObsAll + kMapObsAllSlots, kMapObsMbRows, kMapObsAllRows,
+               kMapAct2Rows = kMapObsAll + kMapObsAllSlots, kMapAct1Rows, kMapObsMbRows, kMapObsAllRows,
                kMapCount = kMapObsAllRows + kMapObsAllSlots };
 using EncodeIm2colFn = CUresult (*)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
                                     const cuuint64_t *, const cuuint64_t *, const int *, const int *,
@@ -1092,6 +1092,7 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
     if (int rc = set_im2col_map(T, kMapDact2, T.dact2, 9, 9, cap, -1, 0)) return rc; // 2x2, padding 1
     if (int rc = set_im2col_map(T, kMapObsMb, T.obs16_mb, 21, 21, cap, 0, -1)) return rc; // 2x2 taps
     if (int rc = set_rows_map(T, kMapAct2Rows, T.act2, cap * 81)) return rc;
+    if (int rc = set_rows_map(T, kMapAct1Rows, T.act1, cap * 200)) return rc; // pixel pairs [n,20,10,64]
     if (int rc = set_rows_map(T, kMapObsMbRows, T.obs16_mb, cap * 441)) return rc;
   }
   env = getenv("ALEGPU_NO_SHIFT"); // A/B: conv1 / conv3 forward through the im2col engine instead
@@ -1207,7 +1208,7 @@ int forward_impl(const NetParams &P, TcState &S, const uint8_t *obs, int64_t n, 
     const bool in_all = all && x16 >= all && x16 < all + (size_t)S.obs16_all_rows * 28224;
     if (S.use_shift && (x16 == (const T *)S.obs16_mb || in_all)) {
       // shift convolution: the 2x2 taps are row-shifted views of one staged copy of the s2d rows
-      if (int rc = tc::launch_conv_shift<T, 32, 2, 2, 21, 21, 20, 20, 3>(
+      if (int rc = tc::launch_conv_shift<T, 32, 2, 2, 21, 21, 20, 20, 1, 3>(
               tmap(S, in_all ? kMapObsAllRows + S.obs_all_map : kMapObsMbRows),
               in_all ? (int64_t)((x16 - all) / 28224) * 441 : 0, (const T *)S.c1w_perm,
               EpiBiasRelu<T>{act1, P.c1b, 32, 1.0f / 255.0f}, n, s, S.shift_base_offset))
@@ -1225,7 +1226,17 @@ int forward_impl(const NetParams &P, TcState &S, const uint8_t *obs, int64_t n, 
                                                   n * 400, 32, 256, 1, 0, s))
       return rc;
   }
-  if (S.use_tma) {
+  // conv2 (stride 2) as a shift convolution runs on 200 grid rows per 81 outputs; measured at 1280 rows
+  // (tf32): 44.1 us against 40.4 us for the im2col form — the shift kernels are bound by the UMMA issue
+  // rate of 128 x 64 x 8 instructions (operands stream from shared memory per instruction), so 2.5x
+  // the tensor work costs more than the 8x less L2 traffic saves.  ALEGPU_SHIFT_CONV2=1 selects it.
+  static const bool shift_conv2 = getenv("ALEGPU_SHIFT_CONV2") != nullptr;
+  if (S.use_shift && shift_conv2) { // 4 (ky) x 2 (pixel pairs) taps over act1's pair grid, outputs on its even rows
+    if (int rc = tc::launch_conv_shift<T, 64, 4, 2, 20, 10, 9, 9, 2, (sizeof(T) == 4 ? 2 : 3)>(
+            tmap(S, kMapAct1Rows), 0, W.c2w, EpiBiasRelu<T>{act2, P.c2b, 64, 1.0f}, n, s,
+            S.shift_base_offset))
+      return rc;
+  } else if (S.use_tma) {
     if (int rc = tc::launch_gemm_tc<64, 4>(Col2Tma<T>{tmap(S, kMapAct1), 0}, RowsK<T>{W.c2w, 512},
                                            EpiBiasRelu<T>{act2, P.c2b, 64, 1.0f}, n * 81, 64, 512,
                                            1, 0, s))
@@ -1235,7 +1246,7 @@ int forward_impl(const NetParams &P, TcState &S, const uint8_t *obs, int64_t n, 
                                                 512, 1, 0, s))
     return rc;
   if (S.use_shift) { // 3x3 taps = 9 row-shifted views of one staged copy of act2's rows
-    if (int rc = tc::launch_conv_shift<T, 64, 3, 3, 9, 9, 7, 7, (sizeof(T) == 4 ? 2 : 3)>(
+    if (int rc = tc::launch_conv_shift<T, 64, 3, 3, 9, 9, 7, 7, 1, (sizeof(T) == 4 ? 2 : 3)>(
             tmap(S, kMapAct2Rows), 0, W.c3w, EpiBiasRelu<T>{act3, P.c3b, 64, 1.0f}, n, s,
             S.shift_base_offset))
       return rc;

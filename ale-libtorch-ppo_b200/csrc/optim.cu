@@ -380,11 +380,19 @@ __global__ void __launch_bounds__(kThreads, 2)
   float4 *xmine = reinterpret_cast<float4 *>(ar.xbuf[ar.rank]);
   float acc = 0.0f;
   for (int64_t i = lo4 + i0; i < hi4; i += stride) {
+    // all ranks' loads are issued before the first one is consumed (NVLink round trips overlap instead
+    // of adding up), then summed in fixed rank order: the same bits whoever computes the slice
+    float4 xr[kArMaxRanks];
+#pragma unroll
+    for (int r = 0; r < kArMaxRanks; ++r)
+      if (r < ar.world)
+        xr[r] = ld_peer_f4(ar.grads[r] + 4 * i);
     float4 s = zero4;
-    for (int r = 0; r < ar.world; ++r) { // fixed rank order: the same bits whoever computes the slice
-      const float4 x = ld_peer_f4(ar.grads[r] + 4 * i);
-      s.x += x.x; s.y += x.y; s.z += x.z; s.w += x.w;
-    }
+#pragma unroll
+    for (int r = 0; r < kArMaxRanks; ++r)
+      if (r < ar.world) {
+        s.x += xr[r].x; s.y += xr[r].y; s.z += xr[r].z; s.w += xr[r].w;
+      }
     xmine[i - lo4] = s;
     float4 x = s;
     if (4 * i + 3 >= n_valid) { // the padding behind the last parameter (the loss sum) is not part of the norm
@@ -453,16 +461,24 @@ __global__ void __launch_bounds__(kThreads, 2)
   const float coef = s_coef[0], step_size = s_coef[1], bc2_sqrt = s_coef[2];
   const float b1 = 0.9f, b2 = 0.999f, omb1 = (float)(1.0 - 0.9), omb2 = (float)(1.0 - 0.999);
   const float eps = 1e-5f;
-  // ---- 3: all-gather fused into Adam's gradient load
+  // ---- 3: all-gather fused into Adam's gradient load (every pull issued before the first is used)
+  float4 gq[kCache];
+#pragma unroll
+  for (int c = 0; c < kCache; ++c) {
+    const int64_t i = i0 + c * stride;
+    gq[c] = zero4;
+    if (i < n4) {
+      const int owner = (int)(i / ar.slice4);
+      const float *src = ar.xbuf[owner] + 4 * (i - ar.slice4 * owner);
+      gq[c] = owner == ar.rank ? *reinterpret_cast<const float4 *>(src) : ld_peer_f4(src);
+    }
+  }
 #pragma unroll
   for (int c = 0; c < kCache; ++c) {
     const int64_t i = i0 + c * stride;
     if (i >= n4)
       continue;
-    const int owner = (int)(i / ar.slice4);
-    const float *src = ar.xbuf[owner] + 4 * (i - ar.slice4 * owner);
-    float4 gg = owner == ar.rank ? *reinterpret_cast<const float4 *>(src) : ld_peer_f4(src);
-    float *pa = &pp[c].x, *ga = &gg.x, *ma = &mm[c].x, *va = &vv[c].x;
+    float *pa = &pp[c].x, *ga = &gq[c].x, *ma = &mm[c].x, *va = &vv[c].x;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const float gc = ga[k] * coef;

@@ -9,8 +9,10 @@
 // pixels of every image, and
 //       out(r)[co] = sum_{tap (ky,kx)} sum_c X[r + ky*GW + kx][c] * W[co][(ky*KW+kx)*64 + c]
 // which equals the convolution wherever (gy, gx) is a valid output position (gy < OH, gx < OW); the
-// other rows are computed and dropped (conv3: 81 grid rows per 49 outputs, conv1: 441 per 400 — tensor
-// work the kernel has to spare).  So the A operand of EVERY tap is the same 128 + (KH-1)*GW + KW-1 rows
+// other rows are computed and dropped (conv3: 81 grid rows per 49 outputs, conv1: 441 per 400; conv2,
+// stride 2, runs on act1's pixel-PAIR grid [20 x 10] where a 4x4 stride-2 filter is a 4x2 stride-(2,1)
+// one: outputs sit on the even grid rows, 200 grid rows per 81 outputs — tensor work the kernel has to
+// spare).  So the A operand of EVERY tap is the same 128 + (KH-1)*GW + KW-1 rows
 // of the plain [rows x 64] input matrix: one tiled TMA load per 128-byte channel panel stages them in the
 // 128-byte-swizzled K-major layout, and the UMMA shared-memory descriptor of tap (ky,kx) simply starts
 // (ky*GW + kx) rows = (ky*GW + kx)*128 bytes further in.  The weights (<= 147 KB) are loaded once per
@@ -49,7 +51,7 @@ __device__ __forceinline__ uint64_t make_smem_desc_row(uint32_t smem_addr, bool 
 }
 
 constexpr int kShiftThreads = 192;
-constexpr int kShiftStageRows = 152; // 128 + the largest tap shift of the layers built on it (22), to 8
+constexpr int kShiftStageRows = 160; // 128 + the largest tap shift of the layers built on it (conv2: 31), to 8
 
 template <class T, int BN, int KH, int KW, int GW> struct ShiftGeom {
   static constexpr int kEB = (int)sizeof(T);
@@ -69,7 +71,7 @@ template <class T, int BN, int KH, int KW, int GW> struct ShiftGeom {
 
 // Epi(i_out, j0, v, 0) receives 16 consecutive output channels of OUTPUT pixel row i_out (image-major
 // OHxOW), as the epilogues of tc_gemm.cuh do.
-template <class T, int BN, int KH, int KW, int GH, int GW, int OH, int OW, int STAGES, class Epi>
+template <class T, int BN, int KH, int KW, int GH, int GW, int OH, int OW, int SY, int STAGES, class Epi>
 __global__ void __launch_bounds__(kShiftThreads, 1)
     conv_shift_kernel(const void *xmap, int row_base, const T *__restrict__ w, const Epi epi,
                       int64_t grid_rows, int use_base_offset) {
@@ -180,8 +182,9 @@ __global__ void __launch_bounds__(kShiftThreads, 1)
       const int64_t r = (int64_t)tile * BM + quarter * 32 + lane;
       const int64_t img = r / G;
       const int q = (int)(r - img * G), gy = q / GW, gx = q - gy * GW;
-      const bool valid = r < grid_rows && gy < OH && gx < OW;
-      const int64_t i_out = (img * OH + gy) * OW + gx;
+      // SY = 2: a stride-2 layer on its input grid — only every second grid row is an output row
+      const bool valid = r < grid_rows && (gy % SY) == 0 && gy / SY < OH && gx < OW;
+      const int64_t i_out = (img * OH + gy / SY) * OW + gx;
 #pragma unroll
       for (int c = 0; c < BN; c += 16) {
         float v[16];
@@ -201,13 +204,13 @@ __global__ void __launch_bounds__(kShiftThreads, 1)
     tmem_dealloc(tmem_base, 2 * kCols);
 }
 
-template <class T, int BN, int KH, int KW, int GH, int GW, int OH, int OW, int STAGES, class Epi>
+template <class T, int BN, int KH, int KW, int GH, int GW, int OH, int OW, int SY, int STAGES, class Epi>
 int launch_conv_shift(const void *xmap, int64_t row_base, const T *w, const Epi &e, int64_t images,
                       cudaStream_t s, bool use_base_offset) {
   if (images <= 0)
     return ALEGPU_OK;
   using Geo = ShiftGeom<T, BN, KH, KW, GW>;
-  auto kern = conv_shift_kernel<T, BN, KH, KW, GH, GW, OH, OW, STAGES, Epi>;
+  auto kern = conv_shift_kernel<T, BN, KH, KW, GH, GW, OH, OW, SY, STAGES, Epi>;
   constexpr int kSmem = Geo::smem(STAGES);
   static_assert(kSmem <= 227 * 1024, "shift conv: shared memory over budget");
   static bool configured = false; // per template instantiation
