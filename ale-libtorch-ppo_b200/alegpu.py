@@ -226,6 +226,27 @@ class vision:
         return (res, f32.numpy()) if return_f32 else res
 
 
+def vision_resize_area(planes):
+    """interpolate(size 84x84, mode area) over [..., 210, 160] float planes (alegpu_vision_resize_area:
+    resize_grayscale_image / resize_frame_stacked_{grayscale,rgb}_images, src/ai/vision.cc:12-48)."""
+    x = np.ascontiguousarray(planes, np.float32)
+    lead = x.shape[:-2]
+    n = int(np.prod(lead)) if lead else 1
+    d, out = DeviceArray.from_numpy(x), DeviceArray((n, 84, 84), np.float32)
+    _check(lib().alegpu_vision_resize_area(_p(d), C.c_int64(n), _p(out), None))
+    return out.numpy().reshape(lead + (84, 84))
+
+
+def vision_rgb_to_grayscale(images):
+    """rgb_to_grayscale_frame_stacked_images (src/ai/vision.cc:71-84): [..., 3, 84, 84] -> [..., 84, 84]."""
+    x = np.ascontiguousarray(images, np.float32)
+    lead = x.shape[:-3]
+    n = int(np.prod(lead)) if lead else 1
+    d, out = DeviceArray.from_numpy(x), DeviceArray((n, 84, 84), np.float32)
+    _check(lib().alegpu_vision_rgb_to_grayscale(_p(d), C.c_int64(n), _p(out), None))
+    return out.numpy().reshape(lead + (84, 84))
+
+
 def preprocess_gray_step(frames_a, frames_b, starts, src_stack, dst_stack, frame_env_stride=210 * 160,
                          starts_stride=1, src_env_stride=STACK_BYTES, dst_env_stride=STACK_BYTES,
                          E=None, stream=None):

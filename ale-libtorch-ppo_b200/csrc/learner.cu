@@ -138,6 +138,7 @@ struct alegpu_learner {
   void *xchg = nullptr;            // [ArSignals | reduced slice]
   std::vector<void *> ipc_opened;  // peer mappings to close
   std::string comm_mode = "single";
+  cudaEvent_t ev_bridge_in = nullptr, ev_bridge_out = nullptr; // alegpu_learner_wait_stream / _stream_wait_learner
   std::vector<float> host_tmp;
 };
 
@@ -837,6 +838,9 @@ extern "C" int alegpu_learner_destroy(alegpu_learner *L) {
     cudaFree(L->opt);
   if (L->loss_done)
     cudaFree(L->loss_done);
+  for (cudaEvent_t e : {L->ev_bridge_in, L->ev_bridge_out})
+    if (e)
+      cudaEventDestroy(e);
   if (L->xchg)
     cudaFree(L->xchg);
   if (L->err_host)
@@ -854,6 +858,28 @@ extern "C" int alegpu_learner_destroy(alegpu_learner *L) {
 }
 
 extern "C" int64_t alegpu_learner_param_count(const alegpu_learner *L) { return L ? L->P : 0; }
+extern "C" int alegpu_learner_wait_stream(alegpu_learner *L, void *stream) {
+  ALEGPU_REQUIRE(L, ALEGPU_INVALID_ARGUMENT, "learner_wait_stream: null learner");
+  if (as_stream(stream) == L->stream)
+    return ALEGPU_OK;
+  ALEGPU_CUDA_CHECK(cudaSetDevice(L->cfg.device));
+  if (!L->ev_bridge_in)
+    ALEGPU_CUDA_CHECK(cudaEventCreateWithFlags(&L->ev_bridge_in, cudaEventDisableTiming));
+  ALEGPU_CUDA_CHECK(cudaEventRecord(L->ev_bridge_in, as_stream(stream)));
+  ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(L->stream, L->ev_bridge_in, 0));
+  return ALEGPU_OK;
+}
+extern "C" int alegpu_stream_wait_learner(alegpu_learner *L, void *stream) {
+  ALEGPU_REQUIRE(L, ALEGPU_INVALID_ARGUMENT, "stream_wait_learner: null learner");
+  if (as_stream(stream) == L->stream)
+    return ALEGPU_OK;
+  ALEGPU_CUDA_CHECK(cudaSetDevice(L->cfg.device));
+  if (!L->ev_bridge_out)
+    ALEGPU_CUDA_CHECK(cudaEventCreateWithFlags(&L->ev_bridge_out, cudaEventDisableTiming));
+  ALEGPU_CUDA_CHECK(cudaEventRecord(L->ev_bridge_out, L->stream));
+  ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(as_stream(stream), L->ev_bridge_out, 0));
+  return ALEGPU_OK;
+}
 extern "C" const char *alegpu_learner_comm_mode(const alegpu_learner *L) {
   return L ? L->comm_mode.c_str() : "";
 }

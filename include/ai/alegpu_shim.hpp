@@ -86,6 +86,69 @@ inline void resize_grayscale_image(const alegpu_shim::U8 &image, int width, int 
   check(alegpu_resize_grayscale(image.data, n, width, height, new_width, new_height, out.data,
                                 nullptr, current_stream()));
 }
+// The libtorch overloads of src/ai/vision.h:6-13 over device views of FLOAT planes (the header's own
+// note: "when using the GPU, the dtype must be a float"); `out` is caller-owned, shapes as the reference
+// returns them.  All are interpolate(size 84x84, mode area) / a matmul with the grayscale weights.
+inline void resize_grayscale_image(const alegpu_shim::F32 &image, alegpu_shim::F32 &out) { // vision.cc:12-20
+  using namespace alegpu_shim;
+  if (image.sizes != std::vector<int64_t>{210, 160} || out.numel() != 84 * 84)
+    throw std::invalid_argument("image must be [210,160], out [84,84]");
+  check(alegpu_vision_resize_area(image.data, 1, out.data, current_stream()));
+}
+inline void resize_frame_stacked_grayscale_images(const alegpu_shim::F32 &images, // vision.cc:22-32
+                                                  alegpu_shim::F32 &out) {
+  using namespace alegpu_shim;
+  if (images.sizes.size() != 4 || images.size(2) != 210 || images.size(3) != 160 ||
+      out.numel() != images.size(0) * images.size(1) * 84 * 84)
+    throw std::invalid_argument("images must be [B,F,210,160], out [B,F,84,84]");
+  check(alegpu_vision_resize_area(images.data, images.size(0) * images.size(1), out.data, current_stream()));
+}
+inline void resize_frame_stacked_rgb_images(const alegpu_shim::F32 &images, // vision.cc:38-48
+                                            alegpu_shim::F32 &out) {
+  using namespace alegpu_shim;
+  if (images.sizes.size() != 5 || images.size(2) != 3 || images.size(3) != 210 || images.size(4) != 160 ||
+      out.numel() != images.size(0) * images.size(1) * 3 * 84 * 84)
+    throw std::invalid_argument("images must be [B,F,3,210,160], out [B,F,3,84,84]");
+  check(alegpu_vision_resize_area(images.data, images.size(0) * images.size(1) * 3, out.data,
+                                  current_stream()));
+}
+inline void rgb_to_grayscale_frame_stacked_images(const alegpu_shim::F32 &images, // vision.cc:71-84
+                                                  alegpu_shim::F32 &out) {
+  using namespace alegpu_shim;
+  if (images.sizes.size() != 5 || images.size(2) != 3 || images.size(3) != 84 || images.size(4) != 84 ||
+      out.numel() != images.size(0) * images.size(1) * 84 * 84)
+    throw std::invalid_argument("images must be [B,F,3,84,84], out [B,F,84,84]");
+  check(alegpu_vision_rgb_to_grayscale(images.data, images.size(0) * images.size(1), out.data,
+                                       current_stream()));
+}
+#ifdef ALEGPU_WITH_TORCH
+// the reference's exact signatures (src/ai/vision.h:6-13): CUDA float tensors in, new tensors out;
+// torch only allocates the result
+inline torch::Tensor resize_grayscale_image(const torch::Tensor &image) {
+  auto out = torch::empty({84, 84}, image.options());
+  alegpu_shim::F32 o(out);
+  resize_grayscale_image(alegpu_shim::F32(image.contiguous()), o);
+  return out;
+}
+inline torch::Tensor resize_frame_stacked_grayscale_images(const torch::Tensor &images) {
+  auto out = torch::empty({images.size(0), images.size(1), 84, 84}, images.options());
+  alegpu_shim::F32 o(out);
+  resize_frame_stacked_grayscale_images(alegpu_shim::F32(images.contiguous()), o);
+  return out;
+}
+inline torch::Tensor resize_frame_stacked_rgb_images(const torch::Tensor &images) {
+  auto out = torch::empty({images.size(0), images.size(1), 3, 84, 84}, images.options());
+  alegpu_shim::F32 o(out);
+  resize_frame_stacked_rgb_images(alegpu_shim::F32(images.contiguous()), o);
+  return out;
+}
+inline torch::Tensor rgb_to_grayscale_frame_stacked_images(const torch::Tensor &images) {
+  auto out = torch::empty({images.size(0), images.size(1), 84, 84}, images.options());
+  alegpu_shim::F32 o(out);
+  rgb_to_grayscale_frame_stacked_images(alegpu_shim::F32(images.contiguous()), o);
+  return out;
+}
+#endif
 } // namespace vision
 
 // ---- src/ai/gae.h:4-7 -----------------------------------------------------------------------------
@@ -108,6 +171,18 @@ inline void gae(alegpu_shim::F32 &advantages, const alegpu_shim::F32 &rewards,
                    truncations.data, episode_starts.data, rewards.size(0), rewards.size(1), gamma,
                    lambda, current_stream()));
 }
+#ifdef ALEGPU_WITH_TORCH
+// the reference's exact signature (src/ai/gae.h:4-7); bool tensors are 1-byte, as the C ABI expects
+inline void gae(torch::Tensor &advantages, const torch::Tensor &rewards, const torch::Tensor &values,
+                const torch::Tensor &next_values, const torch::Tensor &terminals,
+                const torch::Tensor &truncations, const torch::Tensor &episode_starts, float gamma,
+                float lambda) {
+  alegpu_shim::F32 a(advantages);
+  gae(a, alegpu_shim::F32(rewards), alegpu_shim::F32(values), alegpu_shim::F32(next_values),
+      alegpu_shim::U8(terminals), alegpu_shim::U8(truncations), alegpu_shim::U8(episode_starts), gamma,
+      lambda);
+}
+#endif
 } // namespace gae
 
 // ---- src/ai/buffer.h:5-58 ---------------------------------------------------------------------------
@@ -201,6 +276,34 @@ inline void compute(Metrics &out, const alegpu_shim::F32 &logits,
                     out.clipped_losses.data, out.value_losses.data, out.entropies.data,
                     out.total_losses.data, out.ratio.data, dlogits, dvalues, current_stream()));
 }
+#ifdef ALEGPU_WITH_TORCH
+// the reference's signature and return type (losses.h:6-37): tensors in, a Metrics of NEW tensors out.
+// (log-softmax is idempotent, so passing the already normalised log-probabilities, as the reference's
+// caller does at train.h:118-124, gives the same numbers as passing raw logits.)
+struct TensorMetrics { // losses.h:6-13
+  torch::Tensor loss, clipped_losses, value_losses, entropies, ratio, total_losses;
+};
+inline TensorMetrics compute(const torch::Tensor &log_probabilities,
+                             const torch::Tensor &old_log_probabilities, const torch::Tensor &actions,
+                             const torch::Tensor &advantages, const torch::Tensor &values,
+                             const torch::Tensor &returns, const torch::Tensor &masks, float clip_param,
+                             float value_loss_coef, float entropy_coef) {
+  const auto f = log_probabilities.options();
+  const int64_t n = actions.numel();
+  TensorMetrics t{torch::empty({}, f),  torch::empty({n}, f), torch::empty({n}, f),
+                  torch::empty({n}, f), torch::empty({n}, f), torch::empty({n}, f)};
+  Metrics m{alegpu_shim::F32(t.loss),      alegpu_shim::F32(t.clipped_losses),
+            alegpu_shim::F32(t.value_losses), alegpu_shim::F32(t.entropies),
+            alegpu_shim::F32(t.ratio),     alegpu_shim::F32(t.total_losses)};
+  const auto mk = masks.to(torch::kUInt8); // bool tensors are 1 byte; make the dtype explicit
+  compute(m, alegpu_shim::F32(log_probabilities.contiguous()),
+          alegpu_shim::F32(old_log_probabilities.contiguous()), alegpu_shim::I64(actions.contiguous()),
+          alegpu_shim::F32(advantages.contiguous()), alegpu_shim::F32(values.contiguous()),
+          alegpu_shim::F32(returns.contiguous()), alegpu_shim::U8(mk), clip_param, value_loss_coef,
+          entropy_coef);
+  return t;
+}
+#endif
 } // namespace losses
 
 // ---- src/ai/ppo/train.h:27-157 ----------------------------------------------------------------------
@@ -250,9 +353,32 @@ public:
     return flat;
   }
   void set_learning_rate(double lr) { alegpu_shim::check(alegpu_learner_set_lr(h_, lr)); } // :424-428
+  // Stream contract (include/alegpu.h): the learner works on its own stream; every call made through
+  // this shim is ordered after what the shim's current stream holds (Buffer::add / get, gae, ...) and
+  // the current stream is ordered after it, as if everything ran on the reference's single current stream.
+  void enter() { alegpu_shim::check(alegpu_learner_wait_stream(h_, alegpu_shim::current_stream())); }
+  void leave() { alegpu_shim::check(alegpu_stream_wait_learner(h_, alegpu_shim::current_stream())); }
+  // NetworkImpl::forward (src/bin/train.cc:255-265): logits [n,A], values [n] (caller-owned views)
+  void forward(const alegpu_shim::U8 &observations, alegpu_shim::F32 &logits, alegpu_shim::F32 &values) {
+    enter();
+    alegpu_shim::check(alegpu_learner_forward(h_, observations.data, observations.size(0), logits.data,
+                                              values.data));
+    leave();
+  }
 
 private:
   alegpu_learner *h_ = nullptr;
+};
+// The two objects the reference's train() takes (train.h:133-136): a NetworkModel and an optimizer.
+// Both are views of the one Learner that owns the flat parameter / Adam buffers.
+struct Network { // satisfies the NetworkModel shape of train.h:12-25 where the trainer needs it
+  Learner &learner;
+  Network *operator->() { return this; }
+  void train() {} // train.h:138: train mode (no dropout / batch-norm in this network)
+};
+struct Adam { // torch::optim::Adam(lr, eps = 1e-5), src/bin/train.cc:360-362
+  Learner &learner;
+  void set_lr(double lr) { learner.set_learning_rate(lr); } // :424-428
 };
 
 // train(network, optimizer, metrics, indices, batch, num_epochs, num_mini_batches, hp) —
@@ -263,7 +389,7 @@ inline void train(Learner &learner, Metrics &metrics, alegpu_shim::I64 & /*indic
   using namespace alegpu_shim;
   alegpu_batch b{batch.observations.data, batch.actions.data,  batch.log_probabilities.data,
                  batch.advantages.data,   batch.returns.data,  batch.masks.data,
-                 batch.actions.numel()};
+                 batch.actions.numel(),   nullptr};
   alegpu_metrics m{metrics.loss.data,       metrics.clipped_losses.data, metrics.value_losses.data,
                    metrics.entropies.data,  metrics.ratio.data,          metrics.total_losses.data,
                    metrics.advantages.data, metrics.returns.data,        metrics.masks.data,
@@ -271,8 +397,18 @@ inline void train(Learner &learner, Metrics &metrics, alegpu_shim::I64 & /*indic
   alegpu_hyperparameters h{hp.clip_param, hp.value_loss_coef, hp.entropy_coef, hp.max_gradient_norm};
   if (num_mini_batches == 0 || b.size % (int64_t)num_mini_batches != 0) // train.h:140-143
     throw std::runtime_error("Batch size must be divisible by num_mini_batches");
+  learner.enter(); // after the Buffer::get / prepare_batch work on the caller's stream
   check(alegpu_learner_train(learner.handle(), &b, &m, (int64_t)num_epochs,
                              (int64_t)num_mini_batches, &h, cuda_graph ? 1 : 0));
+  learner.leave(); // a Metrics read on the caller's stream sees the finished update
+}
+// the reference's argument list (train.h:133-136):
+//   train(network, optimizer, metrics, indices, batch, num_epochs, num_mini_batches, hyperparameters)
+inline void train(Network &network, Adam &optimizer, Metrics &metrics, alegpu_shim::I64 &indices,
+                  Batch &batch, size_t num_epochs, size_t num_mini_batches, Hyperparameters &hp) {
+  if (&network.learner != &optimizer.learner)
+    throw std::invalid_argument("network and optimizer must belong to the same Learner");
+  train(network.learner, metrics, indices, batch, num_epochs, num_mini_batches, hp);
 }
 } // namespace train
 } // namespace ppo

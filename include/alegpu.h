@@ -137,6 +137,17 @@ int alegpu_preprocess_gray_step(const uint8_t *frames_a, const uint8_t *frames_b
                                 int64_t src_env_stride, uint8_t *dst_stack,
                                 int64_t dst_env_stride, int64_t E, void *stream);
 
+/* The stand-alone libtorch vision operators of src/ai/vision.h:6-13 (the preprocess oracle's own
+ * interface; the learner path itself uses the fused alegpu_preprocess_step):
+ * resize_grayscale_image(Tensor [210,160]) (vision.cc:12-20, planes = 1),
+ * resize_frame_stacked_grayscale_images ([B,F,210,160], :22-32, planes = B*F) and
+ * resize_frame_stacked_rgb_images ([B,F,3,210,160], :38-48, planes = B*F*3) are all
+ * interpolate(size 84x84, mode area) over float planes: images [planes,210,160] f32 -> out [planes,84,84]. */
+int alegpu_vision_resize_area(const float *images, int64_t planes, float *out, void *stream);
+/* rgb_to_grayscale_frame_stacked_images — vision.cc:71-84: [n = B*F, 3, 84, 84] f32 -> [n, 84, 84] f32,
+ * matmul with (0.2125, 0.7154, 0.0721) over the channel axis (:51). */
+int alegpu_vision_rgb_to_grayscale(const float *images, int64_t n, float *out, void *stream);
+
 /* ai::ppo::losses::normalize_logits — src/ai/ppo/losses.cc:45-47. [n,A] -> [n,A]. */
 int alegpu_normalize_logits(const float *logits, int64_t n, int64_t A, float *out,
                             void *stream);
@@ -346,6 +357,18 @@ int alegpu_learner_create(const alegpu_learner_config *config, alegpu_learner **
 int alegpu_learner_destroy(alegpu_learner *learner);
 int64_t alegpu_learner_param_count(const alegpu_learner *learner);
 void *alegpu_learner_stream(alegpu_learner *learner);
+/* Stream contract.  Every learner entry point (train, act, forward, grads, set_lr) enqueues on the
+ * learner's OWN non-blocking stream (alegpu_learner_stream) and returns without waiting; the stateless
+ * operators and the rollout buffer enqueue on the stream they are given.  A caller that mixes the two on
+ * different streams (the reference does everything on the current stream, SURVEY §8b "Threading") orders
+ * them with these two calls, which record / wait an event and never block the host:
+ *   alegpu_learner_wait_stream(L, s): work the learner enqueues from now on starts after everything
+ *                                     already enqueued on s (e.g. Buffer::add / get of this rollout);
+ *   alegpu_stream_wait_learner(L, s): work enqueued on s from now on starts after everything the
+ *                                     learner has enqueued so far (e.g. a Metrics read after train()).
+ * include/ai/alegpu_shim.hpp brackets every Learner call with them on the shim's current stream. */
+int alegpu_learner_wait_stream(alegpu_learner *learner, void *stream);
+int alegpu_stream_wait_learner(alegpu_learner *learner, void *stream);
 /* how gradients are exchanged (no reference counterpart: the reference is single-device):
  * "single" (world_size 1), "fused-nvlink" (every rank maps its peers' gradient buffers through CUDA
  * IPC and the optimiser kernel pulls, sums and applies them over NVLink in one launch per minibatch), or

@@ -98,6 +98,34 @@ def preprocess(frames_a, frames_b):
     return g, q
 
 
+def resize_area(planes):
+    """interpolate(size=84x84, mode=area) of src/ai/vision.cc:8-10 over [..., 210, 160] float planes:
+    output (oy, ox) = mean of input rows [floor(oy*210/84), ceil((oy+1)*210/84)) x columns
+    [floor(ox*160/84), ceil((ox+1)*160/84)), fp32 sum (rows, then columns) / count."""
+    x = np.asarray(planes, np.float32)
+    lead = x.shape[:-2]
+    x = x.reshape(-1, 210, 160)
+    out = np.zeros((x.shape[0], 84, 84), np.float32)
+    for oy in range(84):
+        y0, y1 = (oy * 210) // 84, -((-(oy + 1) * 210) // 84)
+        for ox in range(84):
+            x0, x1 = (ox * 160) // 84, -((-(ox + 1) * 160) // 84)
+            s = np.zeros(x.shape[0], np.float32)
+            for y in range(y0, y1):
+                for xx in range(x0, x1):
+                    s = s + x[:, y, xx]
+            out[:, oy, ox] = s / np.float32((y1 - y0) * (x1 - x0))
+    return out.reshape(lead + (84, 84))
+
+
+def rgb_to_grayscale(images):
+    """rgb_to_grayscale_frame_stacked_images (src/ai/vision.cc:71-84): [..., 3, 84, 84] -> [..., 84, 84],
+    matmul with (0.2125, 0.7154, 0.0721) over the channel axis."""
+    x = np.asarray(images, np.float32)
+    f = np.float32
+    return ((x[..., 0, :, :] * f(0.2125) + x[..., 1, :, :] * f(0.7154)) + x[..., 2, :, :] * f(0.0721)).astype(f)
+
+
 def stack_update(stack, frames, starts):
     s = _c(stack, np.uint8).copy()
     f, st = _c(frames, np.uint8), _c(starts, np.uint8)

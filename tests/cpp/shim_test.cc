@@ -112,6 +112,76 @@ int main(int argc, char **argv) {
       std::printf("gpu vision: resize ok\n");
     }
   }
+  if (argc > 1 && std::strcmp(argv[1], "gpu") == 0) {
+    // The reference's call sequence with NO manual synchronisation between the caller's stream (legacy
+    // default here, as in the reference) and the learner's own stream: Buffer::add x T, Buffer::get,
+    // train(network, optimizer, ...), then a Metrics read on the caller's stream.  Run twice from the
+    // same start: identical losses, finite, and the Adam step counter moved — the stream bridge of
+    // ai::ppo::train::Learner orders the two streams.
+    const int64_t E = 4, T = 8, A = 4, N = E * T, nmb = 2, mb = N / nmb;
+    float loss_runs[2][2];
+    for (int run = 0; run < 2; ++run) {
+      ai::buffer::Buffer buf(E, T, {4, 84, 84}, A);
+      std::vector<int64_t> act(E);
+      std::vector<float> rew(E), lg(E * A), val(E), nv(E, 0.25f);
+      std::vector<uint8_t> z(E, 0), st(E, 0);
+      int64_t *d_act; float *d_rew, *d_lg, *d_val, *d_nv; uint8_t *d_z, *d_st;
+      check(alegpu_malloc((void **)&d_act, E * 8)); check(alegpu_malloc((void **)&d_rew, E * 4));
+      check(alegpu_malloc((void **)&d_lg, E * A * 4)); check(alegpu_malloc((void **)&d_val, E * 4));
+      check(alegpu_malloc((void **)&d_nv, E * 4)); check(alegpu_malloc((void **)&d_z, E));
+      check(alegpu_malloc((void **)&d_st, E));
+      check(alegpu_memcpy_h2d(d_nv, nv.data(), E * 4, nullptr));
+      check(alegpu_memcpy_h2d(d_z, z.data(), E, nullptr));
+      for (int64_t t = 0; t < T; ++t) {
+        for (int64_t e = 0; e < E; ++e) {
+          act[e] = (e + t) % A; rew[e] = (float)((e * 7 + t) % 3); val[e] = 0.1f * (float)(e - t);
+          st[e] = t == 0; for (int64_t a = 0; a < A; ++a) lg[e * A + a] = 0.01f * (float)(a * (t + 1) - e);
+        }
+        check(alegpu_memcpy_h2d(d_act, act.data(), E * 8, nullptr));
+        check(alegpu_memcpy_h2d(d_rew, rew.data(), E * 4, nullptr));
+        check(alegpu_memcpy_h2d(d_lg, lg.data(), E * A * 4, nullptr));
+        check(alegpu_memcpy_h2d(d_val, val.data(), E * 4, nullptr));
+        check(alegpu_memcpy_h2d(d_st, st.data(), E, nullptr));
+        check(alegpu_stream_synchronize(nullptr)); // the host arrays above are reused next step
+        buf.add(U8(nullptr, {}), I64(d_act, {E}), F32(d_rew, {E}), U8(d_z, {E}), U8(d_z, {E}),
+                U8(d_st, {E}), F32(d_lg, {E, A}), F32(d_val, {E}));
+      }
+      ai::buffer::Batch rb = buf.get(F32(d_nv, {E}), 0.99f, 0.95f);
+      ai::ppo::train::Learner learner(32, A, mb, 2.5e-4, ALEGPU_MATH_FP32);
+      std::vector<float> w((size_t)learner.parameter_count());
+      for (size_t i = 0; i < w.size(); ++i)
+        w[i] = 0.02f * (float)((int)(i * 2654435761u % 201) - 100) / 100.0f;
+      learner.load_parameters(w);
+      ai::ppo::train::Network network{learner};
+      ai::ppo::train::Adam optimizer{learner};
+      ai::ppo::train::Batch tb;
+      tb.observations = U8(rb.observations.data, {N, 4, 84, 84});
+      tb.actions = I64(rb.actions.data, {N});
+      tb.log_probabilities = F32(rb.log_probabilities.data, {N, A});
+      tb.advantages = F32(rb.advantages.data, {N});
+      tb.returns = F32(rb.returns.data, {N});
+      tb.masks = U8(rb.masks.data, {N});
+      float *d_loss, *d_gn;
+      check(alegpu_malloc((void **)&d_loss, nmb * mb * 4)); check(alegpu_malloc((void **)&d_gn, nmb * 4));
+      ai::ppo::train::Metrics met;
+      met.loss = F32(d_loss, {1, nmb, mb});
+      met.clipped_gradients = F32(d_gn, {1, nmb});
+      ai::ppo::train::Hyperparameters hp{0.1f, 0.5f, 0.01f, 0.5f};
+      I64 indices;
+      ai::ppo::train::train(network, optimizer, met, indices, tb, 1, nmb, hp); // train.h:133-136
+      std::vector<float> h_loss(nmb * mb);
+      check(alegpu_memcpy_d2h(h_loss.data(), d_loss, nmb * mb * 4, nullptr)); // caller's stream, no manual sync
+      check(alegpu_stream_synchronize(nullptr));
+      loss_runs[run][0] = h_loss[0];
+      loss_runs[run][1] = h_loss[mb];
+      EXPECT(std::isfinite(h_loss[0]) && std::isfinite(h_loss[mb]) && h_loss[0] != 0.0f);
+      int64_t step = 0;
+      check(alegpu_learner_get_adam(learner.handle(), nullptr, nullptr, &step));
+      EXPECT(step == nmb);
+    }
+    EXPECT(loss_runs[0][0] == loss_runs[1][0] && loss_runs[0][1] == loss_runs[1][1]);
+    std::printf("gpu train via shim: loss %.6f %.6f\n", loss_runs[0][0], loss_runs[0][1]);
+  }
   std::printf("shim ok\n");
   return 0;
 }

@@ -112,6 +112,24 @@ def test_preprocess_matches_oracle_and_golden():
     assert np.abs(diff).max() <= 1 and (diff != 0).mean() <= 1e-3
 
 
+def test_vision_operators_match_oracle():
+    """The stand-alone vision operators of src/ai/vision.h:6-13 (alegpu_vision_*): bit-exact against the
+    restatement (same fp32 order), which is pinned to libtorch in test_oracle_golden.py; chained they
+    reproduce the fused preprocess kernel's un-quantised grayscale to 1e-3."""
+    rng = np.random.default_rng(8)
+    x = (rng.integers(0, 256, (2, 2, 3, 210, 160))).astype(np.float32)
+    small = alegpu.vision_resize_area(x)
+    assert small.shape == (2, 2, 3, 84, 84)
+    assert np.array_equal(small, restate.resize_area(x))
+    gray = alegpu.vision_rgb_to_grayscale(small)
+    assert np.array_equal(gray, restate.rgb_to_grayscale(small))
+    for v in (0.0, 17.0, 255.0):  # test/ai/vision-test.cc:5-30
+        assert np.all(alegpu.vision_resize_area(np.full((3, 210, 160), v, np.float32)) == v)
+    hwc = np.ascontiguousarray(x[:, 0].transpose(0, 2, 3, 1)).astype(np.uint8)  # [2,210,160,3]
+    fused_gray, _ = restate.preprocess(hwc, hwc)
+    np.testing.assert_allclose(gray[:, 0], fused_gray, atol=1e-3, rtol=0)
+
+
 def test_preprocess_rollout_equals_step_by_step():
     E, T = 3, 9
     s = synth.rollout_scalars(E, T, seed=4)

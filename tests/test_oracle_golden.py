@@ -189,6 +189,23 @@ def test_normalize_advantages_matches_torch_std():
     np.testing.assert_allclose(got, want.numpy(), rtol=1e-5, atol=1e-6)
 
 
+def test_vision_restatements_match_libtorch():
+    """restate.resize_area / rgb_to_grayscale against the expressions of src/ai/vision.cc:8-84 in torch
+    (interpolate(mode=area), matmul with the grayscale weights) and the constant-image cases of
+    test/ai/vision-test.cc:5-30."""
+    torch = pytest.importorskip("torch")
+    rng = np.random.default_rng(3)
+    x = (rng.random((2, 3, 210, 160)) * 255).astype(np.float32)
+    want = torch.nn.functional.interpolate(torch.from_numpy(x), size=(84, 84), mode="area").numpy()
+    got = restate.resize_area(x)
+    np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-4)
+    w = torch.tensor([0.2125, 0.7154, 0.0721])
+    g = torch.matmul(torch.from_numpy(want).permute(0, 2, 3, 1), w).numpy()
+    np.testing.assert_allclose(restate.rgb_to_grayscale(want), g, rtol=1e-5, atol=1e-4)
+    for v in (0.0, 1.0, 255.0):
+        assert np.all(restate.resize_area(np.full((1, 210, 160), v, np.float32)) == v)
+
+
 def test_clipped_value_loss_matches_torch_autograd():
     """The opt-in clipped value loss (north_star / SURVEY D3; NOT in the reference) pinned against the
     CleanRL expression under torch autograd: value, total loss, d/dlogits and d/dvalues."""
