@@ -847,9 +847,13 @@ int conv1_wgrad_s2d(const T *s2d, const T *dy, int64_t n, float scale, float *gw
   ALEGPU_REQUIRE(ws_floats >= per + bias_floats, ALEGPU_RUNTIME_ERROR, "conv1 wgrad: workspace too small");
   float *bp = ws + (ws_floats - bias_floats);
   int splits, rps;
-  // one output tile: up to 148 splits (one CTA per SM).  Measured per iteration, v0 / v1: 296 splits
-  // 2.41 / 6.84 ms, 148 splits 2.32 / 6.82 ms, 74 splits 2.36 / 6.90 ms, 37 splits 2.58 / 8.07 ms
-  plan_splits(n * 441, 2, per, ws_floats - bias_floats, &splits, &rps);
+  // one output tile: bf16 up to 148 splits (one CTA per SM).  Measured per iteration, v0 / v1, bf16: 296
+  // splits 2.41 / 6.84 ms, 148 splits 2.32 / 6.82 ms, 74 splits 2.36 / 6.90 ms, 37 splits 2.58 / 8.07 ms
+  // tf32 (twice the operand bytes per reduction row, HBM-bound): 296 splits = two CTAs per SM measured
+  // 8.76 -> 8.30 ms per v1 train(); bf16 keeps 148.  ALEGPU_C1_WGRAD_TILES=1|2 overrides (A/B).
+  static const int tiles_ab = getenv("ALEGPU_C1_WGRAD_TILES") ? atoi(getenv("ALEGPU_C1_WGRAD_TILES")) : 0;
+  plan_splits(n * 441, tiles_ab > 0 ? tiles_ab : (sizeof(T) == 4 ? 1 : 2), per, ws_floats - bias_floats,
+              &splits, &rps);
   c1_bias_partial_kernel<T><<<kBiasParts, 256, 0, w>>>(dy, n * 400, bp);
   ALEGPU_COUNT_LAUNCH();
   if (join)
@@ -1011,15 +1015,15 @@ EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 // map slot <- the [rows x 64] matrix view of an NHWC buffer with 64 channels per pixel: boxes of
-// kShiftStageRows rows x one 128-byte channel panel, 128-byte swizzle, zeros past the last row
-int set_rows_map(TcState &T, int slot, void *base, int64_t rows) {
+// box_rows rows (the layer's stage height) x one 128-byte channel panel, 128-byte swizzle, zeros past the last row
+int set_rows_map(TcState &T, int slot, void *base, int64_t rows, int box_rows) {
   EncodeTiledFn fn = encode_tiled_fn();
   ALEGPU_REQUIRE(fn != nullptr, ALEGPU_RUNTIME_ERROR, "cuTensorMapEncodeTiled is not available");
   alignas(64) CUtensorMap m;
   const cuuint64_t eb = (cuuint64_t)T.elem_bytes;
   const cuuint64_t dims[2] = {64, (cuuint64_t)rows};
   const cuuint64_t strides[1] = {64 * eb};
-  const cuuint32_t box[2] = {(cuuint32_t)(128 / eb), (cuuint32_t)tc::kShiftStageRows};
+  const cuuint32_t box[2] = {(cuuint32_t)(128 / eb), (cuuint32_t)box_rows};
   const cuuint32_t estr[2] = {1, 1};
   const CUresult r = fn(&m, eb == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
                         base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -1067,7 +1071,7 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
   T.ws_fc_n = (size_t)hidden * 3137 * 2;
   T.ws_c3_n = (size_t)577 * 64 * 64;
   T.ws_c2_n = (size_t)513 * 64 * 64;
-  T.ws_c1_n = (size_t)128 * 64 * 148 + (size_t)296 * 32; // conv1 wgrad: <= 148 split partials + bias partials
+  T.ws_c1_n = (size_t)128 * 64 * 296 + (size_t)296 * 32; // conv1 wgrad: <= 296 split partials + bias partials
   if (int rc = alloc((void **)&T.ws_heads, sizeof(float) * T.ws_heads_n)) return rc;
   if (int rc = alloc((void **)&T.ws_fc, sizeof(float) * T.ws_fc_n)) return rc;
   if (int rc = alloc((void **)&T.ws_c3, sizeof(float) * T.ws_c3_n)) return rc;
@@ -1091,9 +1095,9 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
     if (int rc = set_im2col_map(T, kMapDact3, T.dact3, 7, 7, cap, -2, 0)) return rc; // 3x3, padding 2
     if (int rc = set_im2col_map(T, kMapDact2, T.dact2, 9, 9, cap, -1, 0)) return rc; // 2x2, padding 1
     if (int rc = set_im2col_map(T, kMapObsMb, T.obs16_mb, 21, 21, cap, 0, -1)) return rc; // 2x2 taps
-    if (int rc = set_rows_map(T, kMapAct2Rows, T.act2, cap * 81)) return rc;
-    if (int rc = set_rows_map(T, kMapAct1Rows, T.act1, cap * 200)) return rc; // pixel pairs [n,20,10,64]
-    if (int rc = set_rows_map(T, kMapObsMbRows, T.obs16_mb, cap * 441)) return rc;
+    if (int rc = set_rows_map(T, kMapAct2Rows, T.act2, cap * 81, tc::shift_stage_rows(3, 3, 9))) return rc;
+    if (int rc = set_rows_map(T, kMapAct1Rows, T.act1, cap * 200, tc::shift_stage_rows(4, 2, 10))) return rc; // pixel pairs [n,20,10,64]
+    if (int rc = set_rows_map(T, kMapObsMbRows, T.obs16_mb, cap * 441, tc::shift_stage_rows(2, 2, 21))) return rc;
   }
   env = getenv("ALEGPU_NO_SHIFT"); // A/B: conv1 / conv3 forward through the im2col engine instead
   T.use_shift = T.use_tma && !(env && env[0] == '1');
@@ -1164,7 +1168,7 @@ int net_tc_reserve_obs(TcState &T, int64_t n) {
   T.obs16_all_rows = n;
   if (T.use_tma) {
     T.obs_all_map = (T.obs_all_map + 1) % kMapObsAllSlots;
-    if (int rc = set_rows_map(T, kMapObsAllRows + T.obs_all_map, T.obs16_all, n * 441))
+    if (int rc = set_rows_map(T, kMapObsAllRows + T.obs_all_map, T.obs16_all, n * 441, tc::shift_stage_rows(2, 2, 21)))
       return rc;
     return set_im2col_map(T, kMapObsAll + T.obs_all_map, T.obs16_all, 21, 21, n, 0, -1);
   }
@@ -1208,7 +1212,7 @@ int forward_impl(const NetParams &P, TcState &S, const uint8_t *obs, int64_t n, 
     const bool in_all = all && x16 >= all && x16 < all + (size_t)S.obs16_all_rows * 28224;
     if (S.use_shift && (x16 == (const T *)S.obs16_mb || in_all)) {
       // shift convolution: the 2x2 taps are row-shifted views of one staged copy of the s2d rows
-      if (int rc = tc::launch_conv_shift<T, 32, 2, 2, 21, 21, 20, 20, 1, 3>(
+      if (int rc = tc::launch_conv_shift<T, 32, 2, 2, 21, 21, 20, 20, 1, 3, 1>(
               tmap(S, in_all ? kMapObsAllRows + S.obs_all_map : kMapObsMbRows),
               in_all ? (int64_t)((x16 - all) / 28224) * 441 : 0, (const T *)S.c1w_perm,
               EpiBiasRelu<T>{act1, P.c1b, 32, 1.0f / 255.0f}, n, s, S.shift_base_offset))
@@ -1232,7 +1236,7 @@ int forward_impl(const NetParams &P, TcState &S, const uint8_t *obs, int64_t n, 
   // the tensor work costs more than the 8x less L2 traffic saves.  ALEGPU_SHIFT_CONV2=1 selects it.
   static const bool shift_conv2 = getenv("ALEGPU_SHIFT_CONV2") != nullptr;
   if (S.use_shift && shift_conv2) { // 4 (ky) x 2 (pixel pairs) taps over act1's pair grid, outputs on its even rows
-    if (int rc = tc::launch_conv_shift<T, 64, 4, 2, 20, 10, 9, 9, 2, (sizeof(T) == 4 ? 2 : 3)>(
+    if (int rc = tc::launch_conv_shift<T, 64, 4, 2, 20, 10, 9, 9, 2, (sizeof(T) == 4 ? 2 : 3), 1>(
             tmap(S, kMapAct1Rows), 0, W.c2w, EpiBiasRelu<T>{act2, P.c2b, 64, 1.0f}, n, s,
             S.shift_base_offset))
       return rc;
@@ -1246,7 +1250,7 @@ int forward_impl(const NetParams &P, TcState &S, const uint8_t *obs, int64_t n, 
                                                 512, 1, 0, s))
     return rc;
   if (S.use_shift) { // 3x3 taps = 9 row-shifted views of one staged copy of act2's rows
-    if (int rc = tc::launch_conv_shift<T, 64, 3, 3, 9, 9, 7, 7, 1, (sizeof(T) == 4 ? 2 : 3)>(
+    if (int rc = tc::launch_conv_shift<T, 64, 3, 3, 9, 9, 7, 7, 1, (sizeof(T) == 4 ? 2 : 3), 1>(
             tmap(S, kMapAct2Rows), 0, W.c3w, EpiBiasRelu<T>{act3, P.c3b, 64, 1.0f}, n, s,
             S.shift_base_offset))
       return rc;

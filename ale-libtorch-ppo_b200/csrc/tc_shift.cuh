@@ -51,7 +51,10 @@ __device__ __forceinline__ uint64_t make_smem_desc_row(uint32_t smem_addr, bool 
 }
 
 constexpr int kShiftThreads = 192;
-constexpr int kShiftStageRows = 160; // 128 + the largest tap shift of the layers built on it (conv2: 31), to 8
+// rows one staged copy holds: 128 + the filter's largest tap shift, rounded up to 8 (the TMA box height)
+__host__ __device__ constexpr int shift_stage_rows(int kh, int kw, int gw) {
+  return ((128 + (kh - 1) * gw + kw - 1 + 7) / 8) * 8;
+}
 
 template <class T, int BN, int KH, int KW, int GW> struct ShiftGeom {
   static constexpr int kEB = (int)sizeof(T);
@@ -60,9 +63,9 @@ template <class T, int BN, int KH, int KW, int GW> struct ShiftGeom {
   static constexpr int kTaps = KH * KW;
   static constexpr int kK = kTaps * 64;        // reduction length
   static constexpr int kNKB = kTaps * kCP;     // 128-byte k-blocks
-  static constexpr int kMaxShift = (KH - 1) * GW + KW - 1;
-  static_assert(128 + kMaxShift <= kShiftStageRows, "stage too short for this filter");
-  static constexpr int kPanel = kShiftStageRows * 128;
+  static constexpr int kRows = shift_stage_rows(KH, KW, GW);
+  static_assert(kRows <= 256, "TMA box height");
+  static constexpr int kPanel = kRows * 128;
   static constexpr int kStage = kCP * kPanel;
   static constexpr int kBPanel = BN * 128;
   static constexpr int kBBytes = kNKB * kBPanel;
@@ -71,8 +74,9 @@ template <class T, int BN, int KH, int KW, int GW> struct ShiftGeom {
 
 // Epi(i_out, j0, v, 0) receives 16 consecutive output channels of OUTPUT pixel row i_out (image-major
 // OHxOW), as the epilogues of tc_gemm.cuh do.
-template <class T, int BN, int KH, int KW, int GH, int GW, int OH, int OW, int SY, int STAGES, class Epi>
-__global__ void __launch_bounds__(kShiftThreads, 1)
+template <class T, int BN, int KH, int KW, int GH, int GW, int OH, int OW, int SY, int STAGES, int OCC,
+          class Epi>
+__global__ void __launch_bounds__(kShiftThreads, OCC)
     conv_shift_kernel(const void *xmap, int row_base, const T *__restrict__ w, const Epi epi,
                       int64_t grid_rows, int use_base_offset) {
   using Geo = ShiftGeom<T, BN, KH, KW, GW>;
@@ -204,24 +208,26 @@ __global__ void __launch_bounds__(kShiftThreads, 1)
     tmem_dealloc(tmem_base, 2 * kCols);
 }
 
-template <class T, int BN, int KH, int KW, int GH, int GW, int OH, int OW, int SY, int STAGES, class Epi>
+// OCC = CTAs per SM the shared-memory footprint allows (the HBM-bound conv1 wants 2 for latency hiding)
+template <class T, int BN, int KH, int KW, int GH, int GW, int OH, int OW, int SY, int STAGES, int OCC,
+          class Epi>
 int launch_conv_shift(const void *xmap, int64_t row_base, const T *w, const Epi &e, int64_t images,
                       cudaStream_t s, bool use_base_offset) {
   if (images <= 0)
     return ALEGPU_OK;
   using Geo = ShiftGeom<T, BN, KH, KW, GW>;
-  auto kern = conv_shift_kernel<T, BN, KH, KW, GH, GW, OH, OW, SY, STAGES, Epi>;
+  auto kern = conv_shift_kernel<T, BN, KH, KW, GH, GW, OH, OW, SY, STAGES, OCC, Epi>;
   constexpr int kSmem = Geo::smem(STAGES);
-  static_assert(kSmem <= 227 * 1024, "shift conv: shared memory over budget");
+  static_assert(OCC * (kSmem + 1024) <= 228 * 1024, "shift conv: shared memory over budget");
   static bool configured = false; // per template instantiation
   if (!configured) {
     ALEGPU_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
     configured = true;
   }
   const int64_t grid_rows = images * GH * GW, tiles = ceil_div(grid_rows, BM);
-  ALEGPU_REQUIRE(row_base + grid_rows + kShiftStageRows < ((int64_t)1 << 31), ALEGPU_INVALID_ARGUMENT,
+  ALEGPU_REQUIRE(row_base + grid_rows + Geo::kRows < ((int64_t)1 << 31), ALEGPU_INVALID_ARGUMENT,
                  "shift conv: row coordinate exceeds the TMA range");
-  const unsigned grid = (unsigned)std::min<int64_t>(tiles, kNumSMs);
+  const unsigned grid = (unsigned)std::min<int64_t>(tiles, (int64_t)kNumSMs * OCC);
   kern<<<grid, kShiftThreads, kSmem, s>>>(xmap, (int)row_base, w, e, grid_rows, use_base_offset ? 1 : 0);
   ALEGPU_COUNT_LAUNCH_NAMED(__PRETTY_FUNCTION__);
   ALEGPU_LAUNCH_CHECK();

@@ -30,7 +30,7 @@ __global__ void __launch_bounds__(256)
   float s = 0.0f;
   for (int y = y0; y < y1; ++y)
     for (int x = x0; x < x1; ++x)
-      s += __ldg(src + y * kInW + x);
+      s = __fadd_rn(s, __ldg(src + y * kInW + x));
   out[i] = s / (float)((y1 - y0) * (x1 - x0));
 }
 
@@ -43,7 +43,9 @@ __global__ void __launch_bounds__(256)
   const int o = (int)(i - n * kOut * kOut);
   const float *src = in + n * 3 * kOut * kOut + o;
   // matmul over the channel axis, weights of vision.cc:51
-  out[i] = (src[0] * 0.2125f + src[kOut * kOut] * 0.7154f) + src[2 * kOut * kOut] * 0.0721f;
+  // (no FMA contraction: the restatement's fp32 operation order, bit for bit)
+  out[i] = __fadd_rn(__fadd_rn(__fmul_rn(src[0], 0.2125f), __fmul_rn(src[kOut * kOut], 0.7154f)),
+                     __fmul_rn(src[2 * kOut * kOut], 0.0721f));
 }
 
 } // namespace
