@@ -598,6 +598,41 @@ template <class T> struct EpiReluMask { // out[i][j] = y[i][j] > 0 ? acc : 0 -> 
     store_x16(out + o, v);
   }
 };
+// FC data gradient: dact3 = relu'(act3) * acc into BOTH layouts — compact [n,7,7,64] (conv3's weight
+// gradient reads it) and zero-bordered [n,10,10,64] (the shift-convolution form of conv3's data gradient:
+// the untouched columns / rows 7..9 are the padding)
+template <class T> struct EpiReluMaskFcPad {
+  T *out, *out_pad;
+  const T *y;
+  __device__ void operator()(int i, int j0, float (&v)[16], int) const {
+    const size_t o = (size_t)i * 3136 + j0;
+    float yy[16];
+    load_x16(y + o, yy);
+#pragma unroll
+    for (int t = 0; t < 16; ++t)
+      v[t] = yy[t] > 0.0f ? v[t] : 0.0f;
+    store_x16(out + o, v);
+    const int p = j0 >> 6, py = p / 7, px = p - py * 7;
+    store_x16(out_pad + ((size_t)i * 100 + py * 10 + px) * 64 + (j0 & 63), v);
+  }
+};
+// conv3 data gradient as a shift convolution: row i of the compact [n,9,9,64] layout (conv2's weight
+// gradient reads it), row r of the zero-bordered [n,10,10,64] grid it was computed on (conv2's data
+// gradient reads that)
+template <class T> struct EpiReluMaskPad {
+  T *out, *out_pad;
+  const T *y;
+  __device__ void operator()(int i, int j0, float (&v)[16], int r) const {
+    const size_t o = (size_t)i * 64 + j0;
+    float yy[16];
+    load_x16(y + o, yy);
+#pragma unroll
+    for (int t = 0; t < 16; ++t)
+      v[t] = yy[t] > 0.0f ? v[t] : 0.0f;
+    store_x16(out + o, v);
+    store_x16(out_pad + (size_t)r * 64 + j0, v);
+  }
+};
 template <class T> struct EpiReluMaskConv2 { // scatter parity class z back into NHWC [n,20,20,32]
   T *out;
   const T *y;
@@ -958,7 +993,8 @@ template <class T> Shadow<T> shadow_view(const TcState &S, const NetParams &P) {
 // earlier kernel may still have cached is never rewritten in place
 enum TmaSlot { kMapAct1 = 0, kMapAct2, kMapDact3, kMapDact2, kMapObsMb, kMapObsAll, kMapObsAllSlots = 16,
                // plain [rows x 64] tiled maps of the same buffers for the shift convolutions (tc_shift.cuh)
-               kMapAct2Rows = kMapObsAll + kMapObsAllSlots, kMapAct1Rows, kMapObsMbRows, kMapObsAllRows,
+               kMapAct2Rows = kMapObsAll + kMapObsAllSlots, kMapAct1Rows, kMapDact3PadRows, kMapDact2PadRows,
+               kMapObsMbRows, kMapObsAllRows,
                kMapCount = kMapObsAllRows + kMapObsAllSlots };
 using EncodeIm2colFn = CUresult (*)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
                                     const cuuint64_t *, const cuuint64_t *, const int *, const int *,
@@ -1065,6 +1101,10 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
   if (int rc = alloc(&T.dact1, eb * (size_t)cap * 12800)) return rc;
   if (int rc = alloc(&T.dact2, eb * (size_t)cap * 5184)) return rc;
   if (int rc = alloc(&T.dact3, eb * (size_t)cap * 3136)) return rc;
+  // zero-bordered [n,10,10,64] copies of dact3 / dact2 for the shift-convolution data gradients: only
+  // the valid 7x7 / 9x9 positions are ever written, the rest stays the zero it was allocated as
+  if (int rc = alloc(&T.dact3p, eb * (size_t)cap * 6400)) return rc;
+  if (int rc = alloc(&T.dact2p, eb * (size_t)cap * 6400)) return rc;
   if (elem_bytes == 2) // tf32: the tensor core reads the (tf32-rounded) fp32 dfc itself
     if (int rc = alloc(&T.dfc16, eb * (size_t)cap * hidden)) return rc;
   T.ws_heads_n = (size_t)(actions + 1) * (hidden + 1) * 2 * kNumSMs;
@@ -1097,10 +1137,20 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
     if (int rc = set_im2col_map(T, kMapObsMb, T.obs16_mb, 21, 21, cap, 0, -1)) return rc; // 2x2 taps
     if (int rc = set_rows_map(T, kMapAct2Rows, T.act2, cap * 81, tc::shift_stage_rows(3, 3, 9))) return rc;
     if (int rc = set_rows_map(T, kMapAct1Rows, T.act1, cap * 200, tc::shift_stage_rows(4, 2, 10))) return rc; // pixel pairs [n,20,10,64]
+    if (int rc = set_rows_map(T, kMapDact3PadRows, T.dact3p, cap * 100, tc::shift_stage_rows(3, 3, 10))) return rc;
+    if (int rc = set_rows_map(T, kMapDact2PadRows, T.dact2p, cap * 100, tc::shift_stage_rows(2, 2, 10))) return rc;
     if (int rc = set_rows_map(T, kMapObsMbRows, T.obs16_mb, cap * 441, tc::shift_stage_rows(2, 2, 21))) return rc;
   }
   env = getenv("ALEGPU_NO_SHIFT"); // A/B: conv1 / conv3 forward through the im2col engine instead
   T.use_shift = T.use_tma && !(env && env[0] == '1');
+  // conv3 / conv2 data gradients as shift convolutions over zero-bordered gradient copies: measured at
+  // 1280 rows, bf16 28.4 -> 26.5 us and 40.8 -> 38.9 us (train() 5.44 -> 5.24 ms); tf32 47.4 -> 49.1 us
+  // and 67.5 -> 63.9 us with the extra bordered stores costing more than that (8.30 -> 8.51 ms): in tf32
+  // these kernels are bound by the tensor core's operand fetch from shared memory (a K = 8 UMMA of
+  // 128 x 64 moves 6 KB for 65 k MACs, half the bf16 ratio), not by L2 traffic.  So: on for bf16, off
+  // for tf32; ALEGPU_SHIFT_DGRAD=0|1 overrides (A/B).
+  env = getenv("ALEGPU_SHIFT_DGRAD");
+  T.use_shift_dgrad = T.use_shift && (env ? env[0] == '1' : elem_bytes == 2);
   // the matrix-base-offset field of the row-shifted descriptors stays 0: measured on B200, the 128-byte
   // swizzle is a function of the absolute shared-memory address, so a descriptor may start at any
   // 128-byte row of a 1024-byte aligned panel as it is (setting (start >> 7) & 7 there gives wrong
@@ -1111,7 +1161,7 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
 }
 
 void net_tc_destroy(TcState &T) {
-  for (void *p : {T.c1w_perm, T.obs16_mb, T.obs16_all, T.w_shadow, T.act1, T.act2, T.act3, T.dact1, T.dact2, T.dact3, T.fc16, T.dfc16,
+  for (void *p : {T.c1w_perm, T.obs16_mb, T.obs16_all, T.w_shadow, T.act1, T.act2, T.act3, T.dact1, T.dact2, T.dact3, T.dact3p, T.dact2p, T.fc16, T.dfc16,
                   T.wt, T.tmaps, (void *)T.stage, (void *)T.ws_heads, (void *)T.ws_fc, (void *)T.ws_c3,
                   (void *)T.ws_c2, (void *)T.ws_c1})
     if (p)
@@ -1212,9 +1262,9 @@ int forward_impl(const NetParams &P, TcState &S, const uint8_t *obs, int64_t n, 
     const bool in_all = all && x16 >= all && x16 < all + (size_t)S.obs16_all_rows * 28224;
     if (S.use_shift && (x16 == (const T *)S.obs16_mb || in_all)) {
       // shift convolution: the 2x2 taps are row-shifted views of one staged copy of the s2d rows
-      if (int rc = tc::launch_conv_shift<T, 32, 2, 2, 21, 21, 20, 20, 1, 3, 1>(
+      if (int rc = tc::launch_conv_shift<T, 32, 2, 2, 21, 21, 20, 20, 1, 3, 1, false>(
               tmap(S, in_all ? kMapObsAllRows + S.obs_all_map : kMapObsMbRows),
-              in_all ? (int64_t)((x16 - all) / 28224) * 441 : 0, (const T *)S.c1w_perm,
+              in_all ? (int64_t)((x16 - all) / 28224) * 441 : 0, tc::WKMajor<T>{(const T *)S.c1w_perm, 256},
               EpiBiasRelu<T>{act1, P.c1b, 32, 1.0f / 255.0f}, n, s, S.shift_base_offset))
         return rc;
     } else if (S.use_tma && (x16 == (const T *)S.obs16_mb || in_all)) {
@@ -1236,8 +1286,8 @@ int forward_impl(const NetParams &P, TcState &S, const uint8_t *obs, int64_t n, 
   // the tensor work costs more than the 8x less L2 traffic saves.  ALEGPU_SHIFT_CONV2=1 selects it.
   static const bool shift_conv2 = getenv("ALEGPU_SHIFT_CONV2") != nullptr;
   if (S.use_shift && shift_conv2) { // 4 (ky) x 2 (pixel pairs) taps over act1's pair grid, outputs on its even rows
-    if (int rc = tc::launch_conv_shift<T, 64, 4, 2, 20, 10, 9, 9, 2, (sizeof(T) == 4 ? 2 : 3), 1>(
-            tmap(S, kMapAct1Rows), 0, W.c2w, EpiBiasRelu<T>{act2, P.c2b, 64, 1.0f}, n, s,
+    if (int rc = tc::launch_conv_shift<T, 64, 4, 2, 20, 10, 9, 9, 2, (sizeof(T) == 4 ? 2 : 3), 1, false>(
+            tmap(S, kMapAct1Rows), 0, tc::WKMajor<T>{W.c2w, 512}, EpiBiasRelu<T>{act2, P.c2b, 64, 1.0f}, n, s,
             S.shift_base_offset))
       return rc;
   } else if (S.use_tma) {
@@ -1250,8 +1300,8 @@ int forward_impl(const NetParams &P, TcState &S, const uint8_t *obs, int64_t n, 
                                                 512, 1, 0, s))
     return rc;
   if (S.use_shift) { // 3x3 taps = 9 row-shifted views of one staged copy of act2's rows
-    if (int rc = tc::launch_conv_shift<T, 64, 3, 3, 9, 9, 7, 7, 1, (sizeof(T) == 4 ? 2 : 3), 1>(
-            tmap(S, kMapAct2Rows), 0, W.c3w, EpiBiasRelu<T>{act3, P.c3b, 64, 1.0f}, n, s,
+    if (int rc = tc::launch_conv_shift<T, 64, 3, 3, 9, 9, 7, 7, 1, (sizeof(T) == 4 ? 2 : 3), 1, false>(
+            tmap(S, kMapAct2Rows), 0, tc::WKMajor<T>{W.c3w, 576}, EpiBiasRelu<T>{act3, P.c3b, 64, 1.0f}, n, s,
             S.shift_base_offset))
       return rc;
   } else if (S.use_tma) {
@@ -1338,7 +1388,17 @@ int backward_impl(const NetParams &P, const NetParams &G, TcState &S, const uint
   if (!S.serial) // the FC + heads gradients (95 % of the bytes) can already be exchanged
     ALEGPU_CUDA_CHECK(cudaEventRecord(S.ev_fcw, w));
   // ---- main: FC dgrad: dact3 = (dfc . fcw) * relu'(act3)
-  if (ceil_div(n, tc::BM) * 25 < kNumSMs) { // small minibatch: narrower tiles, twice the CTAs
+  T *dact3p = (T *)S.dact3p, *dact2p = (T *)S.dact2p;
+  if (S.use_shift_dgrad) { // also the zero-bordered copy the shift-convolution conv3 dgrad stages
+    if (ceil_div(n, tc::BM) * 25 < kNumSMs) {
+      if (int rc = tc::launch_gemm_tc<64, 4>(RowsK<T>{dfcT, H}, ColsMN<T>{W.fcw, 3136},
+                                             EpiReluMaskFcPad<T>{dact3, dact3p, act3}, n, 3136, H, 1, 0, s))
+        return rc;
+    } else if (int rc = tc::launch_gemm_tc<128, 3>(RowsK<T>{dfcT, H}, ColsMN<T>{W.fcw, 3136},
+                                                   EpiReluMaskFcPad<T>{dact3, dact3p, act3}, n, 3136, H,
+                                                   1, 0, s))
+      return rc;
+  } else if (ceil_div(n, tc::BM) * 25 < kNumSMs) { // small minibatch: narrower tiles, twice the CTAs
     if (int rc = tc::launch_gemm_tc<64, 4>(RowsK<T>{dfcT, H}, ColsMN<T>{W.fcw, 3136},
                                            EpiReluMask<T>{dact3, act3, 3136}, n, 3136, H, 1, 0, s))
       return rc;
@@ -1355,7 +1415,12 @@ int backward_impl(const NetParams &P, const NetParams &G, TcState &S, const uint
                                                S.ws_c3, S.ws_c3_n, w))
     return rc;
   // ---- main: conv3 dgrad
-  if (S.use_tma) {
+  if (S.use_shift_dgrad) { // 9 flipped taps = row-shifted views of one staged copy of the bordered dact3
+    if (int rc = tc::launch_conv_shift<T, 64, 3, 3, 10, 10, 9, 9, 1, (sizeof(T) == 4 ? 2 : 3), 1, true>(
+            tmap(S, kMapDact3PadRows), 0, tc::WMNView<W3T<T>>{W3T<T>{W.c3w}},
+            EpiReluMaskPad<T>{dact2, dact2p, act2}, n, s, S.shift_base_offset))
+      return rc;
+  } else if (S.use_tma) {
     if (int rc = tc::launch_gemm_tc<64, 4>(DCol3Tma<T>{tmap(S, kMapDact3), 0}, W3T<T>{W.c3w},
                                            EpiReluMask<T>{dact2, act2, 64}, n * 81, 64, 576, 1, 0, s))
       return rc;
@@ -1375,7 +1440,12 @@ int backward_impl(const NetParams &P, const NetParams &G, TcState &S, const uint
     ALEGPU_CUDA_CHECK(cudaEventRecord(S.ev_join, w));
   // ---- main: conv2 dgrad (the 4 parity classes of the stride-2 transposed convolution as 128 output
   // columns of ONE GEMM over the TMA-fetched 2x2-tap walk of dact2; cp.async fallback: 4 z-slices)
-  if (S.use_tma) {
+  if (S.use_shift_dgrad) { // 2x2 flipped taps over the bordered dact2, all four parity classes as 128 columns
+    if (int rc = tc::launch_conv_shift<T, 128, 2, 2, 10, 10, 10, 10, 1, (sizeof(T) == 4 ? 2 : 3), 1, true>(
+            tmap(S, kMapDact2PadRows), 0, tc::WMNView<W2TAll<T>>{W2TAll<T>{W.c2w}},
+            EpiReluMaskConv2All<T>{dact1, act1}, n, s, S.shift_base_offset))
+      return rc;
+  } else if (S.use_tma) {
     if (int rc = tc::launch_gemm_tc<128, 3>(DCol2Tma<T>{tmap(S, kMapDact2), 0}, W2TAll<T>{W.c2w},
                                             EpiReluMaskConv2All<T>{dact1, act1}, n * 100, 128, 256, 1, 0,
                                             s))

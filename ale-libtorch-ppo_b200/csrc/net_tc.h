@@ -14,7 +14,8 @@ struct TcState {
   void *obs16_mb = nullptr, *obs16_all = nullptr;
   int64_t obs16_all_rows = 0;
   void *act1 = nullptr, *act2 = nullptr, *act3 = nullptr;    // bf16 NHWC activations
-  void *dact1 = nullptr, *dact2 = nullptr, *dact3 = nullptr; // bf16 NHWC activation grads
+  void *dact1 = nullptr, *dact2 = nullptr, *dact3 = nullptr; // NHWC activation grads (operand type)
+  void *dact3p = nullptr, *dact2p = nullptr; // zero-bordered [n,10,10,64] copies (shift-convolution data gradients)
   void *fc16 = nullptr, *dfc16 = nullptr;                    // bf16 copies of fc in/out grads
   void *wt = nullptr;        // bf16 re-laid-out weights for dgrad
   float *stage = nullptr;    // fp32 staging for get_activations
@@ -30,6 +31,7 @@ struct TcState {
   void *tmaps = nullptr;
   int obs_all_map = 0;       // which of the round-robin obs16_all descriptor slots is current
   bool use_tma = true;       // ALEGPU_NO_TMA=1: gather conv operands with cp.async instead (A/B)
+  bool use_shift_dgrad = true; // conv3 / conv2 data gradients as shift convolutions (default: bf16 only; ALEGPU_SHIFT_DGRAD=0|1)
   bool use_shift = true;     // ALEGPU_NO_SHIFT=1: conv1 / conv3 forward through the im2col engine (A/B)
   bool shift_base_offset = false; // experiment switch, see net_tc_init: the field must stay 0
   bool serial = false;       // ALEGPU_TC_SERIAL=1: keep everything on one stream (profiling)

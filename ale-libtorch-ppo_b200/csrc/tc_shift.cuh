@@ -72,16 +72,42 @@ template <class T, int BN, int KH, int KW, int GW> struct ShiftGeom {
   static constexpr int smem(int stages) { return kBBytes + stages * kStage + 1024; }
 };
 
-// Epi(i_out, j0, v, 0) receives 16 consecutive output channels of OUTPUT pixel row i_out (image-major
-// OHxOW), as the epilogues of tc_gemm.cuh do.
+// Where the resident weights come from.  WKMajor: a plain [BN][K] matrix, reduction index contiguous
+// (forward layers).  WMNView<Op>: one of the transposed-weight views of net_tc.cu (row(j0) / col(k, 0) /
+// at(rc, cc): 16-byte chunks contiguous along the OUTPUT index j), stored MN-major (data gradients).
+template <class T> struct WKMajor {
+  static constexpr bool kMN = false;
+  const T *w;
+  int K;
+  __device__ __forceinline__ const void *chunk(int j, int kcg) const { // row j, 16-byte chunk kcg of its K
+    return w + (size_t)j * K + kcg * (16 / (int)sizeof(T));
+  }
+  __device__ __forceinline__ const void *anchor() const { return w; }
+};
+template <class Op> struct WMNView {
+  static constexpr bool kMN = true;
+  Op op;
+  __device__ __forceinline__ const void *chunk(int c, int k) const { // rows c*EPC.., reduction index k
+    return op.at(op.row(c * (16 / Op::kElemBytes)), op.col(k, 0));
+  }
+  __device__ __forceinline__ const void *anchor() const { return op.anchor(); }
+};
+
+// Epi(i_out, j0, v, r) receives 16 consecutive output channels of OUTPUT pixel row i_out (image-major
+// OHxOW), as the epilogues of tc_gemm.cuh do; r = the row on the computation grid (image*G + gy*GW + gx).
+//
+// kFlip = the data-gradient walk: out(r) = sum_taps X[r - (ky*GW + kx)] W_tap.  The input X then is a
+// zero-bordered copy of the output gradient on the OUTPUT's grid pitch GW (trailing zero columns / rows
+// double as the left / top padding of the next row / image), written by the producing layer's epilogue.
 template <class T, int BN, int KH, int KW, int GH, int GW, int OH, int OW, int SY, int STAGES, int OCC,
-          class Epi>
+          bool kFlip, class WSrc, class Epi>
 __global__ void __launch_bounds__(kShiftThreads, OCC)
-    conv_shift_kernel(const void *xmap, int row_base, const T *__restrict__ w, const Epi epi,
-                      int64_t grid_rows, int use_base_offset) {
+    conv_shift_kernel(const void *xmap, int row_base, const WSrc w, const Epi epi, int64_t grid_rows,
+                      int use_base_offset) {
   using Geo = ShiftGeom<T, BN, KH, KW, GW>;
   constexpr int G = GH * GW;
-  constexpr uint32_t kIdesc = make_idesc(BN, false, false, Geo::kEB);
+  constexpr int kMaxShift = (KH - 1) * GW + KW - 1;
+  constexpr uint32_t kIdesc = make_idesc(BN, false, WSrc::kMN, Geo::kEB);
   constexpr uint32_t kCols = tmem_cols(BN);
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], acc_full[2], acc_empty[2], b_ready;
@@ -122,7 +148,7 @@ __global__ void __launch_bounds__(kShiftThreads, OCC)
 #pragma unroll
         for (int cp = 0; cp < Geo::kCP; ++cp)
           tma_tile_2d(st_s + (uint32_t)(s * Geo::kStage + cp * Geo::kPanel), xmap, cp * Geo::kBKE,
-                      row_base + tile * BM, &full_bar[s]);
+                      row_base + tile * BM - (kFlip ? kMaxShift : 0), &full_bar[s]); // (rows < 0: zeros)
       }
     }
   } else if (warp == 1) {
@@ -139,20 +165,26 @@ __global__ void __launch_bounds__(kShiftThreads, OCC)
         const uint32_t stage = st_s + (uint32_t)(s * Geo::kStage);
 #pragma unroll
         for (int t = 0; t < Geo::kTaps; ++t) {
-          const int shift = (t / KW) * GW + (t % KW);
+          const int tap_shift = (t / KW) * GW + (t % KW);
+          const int shift = kFlip ? kMaxShift - tap_shift : tap_shift; // row of the stage the tap starts at
+          // MN-major resident weights: the layouts / descriptor constants of tc_gemm.cuh (mn_chunk_offset)
+          constexpr uint32_t kLboMN = Geo::kEB == 2 ? 8192u : 4096u, kSboMN = Geo::kEB == 2 ? 1024u : 512u;
+          constexpr uint32_t kTypeMN = Geo::kEB == 2 ? 2u : 1u;
+          constexpr int kAdvB = WSrc::kMN ? (Geo::kEB == 2 ? 2048 : 1024) / 16 : 2;
 #pragma unroll
           for (int cp = 0; cp < Geo::kCP; ++cp) {
             const uint64_t adesc = make_smem_desc_row(stage + (uint32_t)(cp * Geo::kPanel + shift * 128),
                                                       use_base_offset != 0);
-            const uint64_t bdesc =
-                make_smem_desc(b_s + (uint32_t)((t * Geo::kCP + cp) * Geo::kBPanel), 16u, 1024u);
+            const uint32_t b_addr = b_s + (uint32_t)((t * Geo::kCP + cp) * Geo::kBPanel);
+            const uint64_t bdesc = WSrc::kMN ? make_smem_desc(b_addr, kLboMN, kSboMN, kTypeMN)
+                                             : make_smem_desc(b_addr, 16u, 1024u);
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk) {
               const uint32_t acc = (uint32_t)((t | cp | kk) != 0);
               if constexpr (Geo::kEB == 4)
-                umma_tf32(tmem_d, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), kIdesc, acc);
+                umma_tf32(tmem_d, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * kAdvB), kIdesc, acc);
               else
-                umma_bf16(tmem_d, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), kIdesc, acc);
+                umma_bf16(tmem_d, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * kAdvB), kIdesc, acc);
             }
           }
         }
@@ -164,11 +196,20 @@ __global__ void __launch_bounds__(kShiftThreads, OCC)
     // first: the whole weight matrix [BN][K] (K-major) -> resident 128-byte-swizzled panels, one per
     // k-block, while the producer warp already streams the first input stages in
     {
-      constexpr int kRowChunks = Geo::kK * Geo::kEB / 16;
-      for (int q = threadIdx.x - 64; q < BN * kRowChunks; q += 128) {
-        const int j = q / kRowChunks, kcg = q - j * kRowChunks, kb = kcg >> 3, kc = kcg & 7;
-        const uint32_t dst = b_s + (uint32_t)(kb * Geo::kBPanel + j * 128 + ((kc ^ (j & 7)) << 4));
-        cp_async16(dst, w + (size_t)j * Geo::kK + kcg * (16 / Geo::kEB), w);
+      if constexpr (!WSrc::kMN) {
+        constexpr int kRowChunks = Geo::kK * Geo::kEB / 16;
+        for (int q = threadIdx.x - 64; q < BN * kRowChunks; q += 128) {
+          const int j = q / kRowChunks, kcg = q - j * kRowChunks, kb = kcg >> 3, kc = kcg & 7;
+          const uint32_t dst = b_s + (uint32_t)(kb * Geo::kBPanel + j * 128 + ((kc ^ (j & 7)) << 4));
+          cp_async16(dst, w.chunk(j, kcg), w.anchor());
+        }
+      } else { // one [BN x BKE] MN-major panel per k-block: chunk c = 16 bytes of consecutive output indices
+        constexpr int kEPC = 16 / Geo::kEB, kRowChunks = BN / kEPC;
+        for (int q = threadIdx.x - 64; q < kRowChunks * Geo::kK; q += 128) {
+          const int k = q / kRowChunks, c = q - k * kRowChunks, kb = k / Geo::kBKE, kl = k - kb * Geo::kBKE;
+          const uint32_t dst = b_s + (uint32_t)(kb * Geo::kBPanel) + mn_chunk_offset<Geo::kEB>(c, kl);
+          cp_async16(dst, w.chunk(c, k), w.anchor());
+        }
       }
       cp_async_commit();
       cp_async_wait<0>();
@@ -194,7 +235,7 @@ __global__ void __launch_bounds__(kShiftThreads, OCC)
         float v[16];
         tmem_ld16(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * kCols + c), v);
         if (valid)
-          epi((int)i_out, c, v, 0);
+          epi((int)i_out, c, v, (int)r);
       }
       tc_fence_before();
       __syncwarp();
@@ -208,15 +249,15 @@ __global__ void __launch_bounds__(kShiftThreads, OCC)
     tmem_dealloc(tmem_base, 2 * kCols);
 }
 
-// OCC = CTAs per SM the shared-memory footprint allows (the HBM-bound conv1 wants 2 for latency hiding)
+// OCC = CTAs per SM the shared-memory footprint allows
 template <class T, int BN, int KH, int KW, int GH, int GW, int OH, int OW, int SY, int STAGES, int OCC,
-          class Epi>
-int launch_conv_shift(const void *xmap, int64_t row_base, const T *w, const Epi &e, int64_t images,
+          bool kFlip, class WSrc, class Epi>
+int launch_conv_shift(const void *xmap, int64_t row_base, const WSrc &w, const Epi &e, int64_t images,
                       cudaStream_t s, bool use_base_offset) {
   if (images <= 0)
     return ALEGPU_OK;
   using Geo = ShiftGeom<T, BN, KH, KW, GW>;
-  auto kern = conv_shift_kernel<T, BN, KH, KW, GH, GW, OH, OW, SY, STAGES, OCC, Epi>;
+  auto kern = conv_shift_kernel<T, BN, KH, KW, GH, GW, OH, OW, SY, STAGES, OCC, kFlip, WSrc, Epi>;
   constexpr int kSmem = Geo::smem(STAGES);
   static_assert(OCC * (kSmem + 1024) <= 228 * 1024, "shift conv: shared memory over budget");
   static bool configured = false; // per template instantiation

@@ -305,13 +305,15 @@ def test_tma_descriptor_follows_a_regrown_observation_copy(monkeypatch):
 @pytest.mark.parametrize("n", [37, 256])
 @pytest.mark.parametrize("math", [alegpu.MATH_BF16, alegpu.MATH_TF32], ids=["bf16", "tf32"])
 def test_shift_convolutions_match_the_im2col_engine(math, n, monkeypatch):
-    """conv1 / conv3 forward as shift GEMMs (tc_shift.cuh: the input staged once per tile, every tap a
-    row-shifted shared-memory descriptor, weights resident) against the im2col engine
-    (ALEGPU_NO_SHIFT=1): the same products accumulated in the same tap-major order."""
+    """conv1 / conv3 forward and conv3 / conv2 data gradients as shift GEMMs (tc_shift.cuh: the input
+    staged once per tile, every tap a row-shifted shared-memory descriptor, weights resident; the data
+    gradients over zero-bordered gradient copies with flipped taps and MN-major resident weights) against
+    the im2col engine (ALEGPU_NO_SHIFT=1): the same products accumulated in the same tap-major order."""
     H = 64
     params = cases.net_params(H, seed=5)
     tc = cases.train_case(n, seed=19)
     outs = {}
+    monkeypatch.setenv("ALEGPU_SHIFT_DGRAD", "1")  # also the data-gradient forms (default: bf16 only)
     for flag in ("1", "0"):
         monkeypatch.setenv("ALEGPU_NO_SHIFT", flag)
         L = alegpu.Learner(H, 4, n, math, cases.LR)
