@@ -11,6 +11,8 @@
 // lane per env in EXACTLY the reference's operation order (no fma contraction, so results are
 // bit-identical to a sequential fp32 evaluation), and all threads write advantages / returns
 // / clamped rewards / masks back coalesced.  23 algorithmic bytes per (env, step).
+#include <mutex>
+
 #include "common.cuh"
 
 namespace alegpu {
@@ -86,11 +88,22 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
-int *g_error_flag = nullptr; // lazily allocated device int for the stateless entry points
+// The stateless entry points need a device int for the flag-exclusivity check.  One per DEVICE (a
+// process may drive several GPUs), created under a lock; the calls that use it end with a stream
+// synchronise (the reference's `.any().item()`), so two host threads on the same device must not run
+// them concurrently on different streams — documented in alegpu.h (the reference is single-threaded here).
+std::mutex g_flag_mutex;
+int *g_error_flags[64] = {};
+thread_local int *g_error_flag = nullptr; // the current device's flag, set by ensure_flag()
 
 int ensure_flag() {
-  if (!g_error_flag)
-    ALEGPU_CUDA_CHECK(cudaMalloc(&g_error_flag, sizeof(int)));
+  int dev = 0;
+  ALEGPU_CUDA_CHECK(cudaGetDevice(&dev));
+  ALEGPU_REQUIRE(dev >= 0 && dev < 64, ALEGPU_RUNTIME_ERROR, "gae: device ordinal out of range");
+  std::lock_guard<std::mutex> lock(g_flag_mutex);
+  if (!g_error_flags[dev])
+    ALEGPU_CUDA_CHECK(cudaMalloc(&g_error_flags[dev], sizeof(int)));
+  g_error_flag = g_error_flags[dev];
   return ALEGPU_OK;
 }
 

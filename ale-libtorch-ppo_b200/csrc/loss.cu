@@ -5,6 +5,8 @@
 // sum, per-sample metrics, dlogits, dvalues.  102 algorithmic bytes per sample.
 // Reductions are deterministic: warp shuffles, a fixed tree per block, block partials summed
 // in index order by one warp.
+#include <mutex>
+
 #include "loss.cuh"
 
 namespace alegpu {
@@ -100,21 +102,33 @@ __global__ void loss_finalize_kernel(const float *__restrict__ partials, int npa
     loss[0] = s / count[0];
 }
 
+// scratch of the stateless alegpu_loss (count, loss, per-block partials): one per DEVICE, grown under a
+// lock.  alegpu_loss is not re-entrant per device (two streams would share count / partials) and may
+// allocate, so it must not be called inside a stream capture — documented in alegpu.h; the learner's own
+// loss path (heads.cu) uses per-learner buffers and has neither restriction.
 struct Scratch {
   float *buf = nullptr;
   size_t cap = 0;
 };
-Scratch g_scratch;
+std::mutex g_scratch_mutex;
+Scratch g_scratches[64];
+thread_local Scratch g_scratch; // the current device's scratch after ensure_scratch()
 
 int ensure_scratch(size_t floats) {
-  if (g_scratch.cap < floats) {
-    if (g_scratch.buf)
-      cudaFree(g_scratch.buf);
-    g_scratch.buf = nullptr;
-    g_scratch.cap = 0;
-    ALEGPU_CUDA_CHECK(cudaMalloc(&g_scratch.buf, floats * sizeof(float)));
-    g_scratch.cap = floats;
+  int dev = 0;
+  ALEGPU_CUDA_CHECK(cudaGetDevice(&dev));
+  ALEGPU_REQUIRE(dev >= 0 && dev < 64, ALEGPU_RUNTIME_ERROR, "loss: device ordinal out of range");
+  std::lock_guard<std::mutex> lock(g_scratch_mutex);
+  Scratch &sc = g_scratches[dev];
+  if (sc.cap < floats) {
+    if (sc.buf)
+      cudaFree(sc.buf);
+    sc.buf = nullptr;
+    sc.cap = 0;
+    ALEGPU_CUDA_CHECK(cudaMalloc(&sc.buf, floats * sizeof(float)));
+    sc.cap = floats;
   }
+  g_scratch = sc;
   return ALEGPU_OK;
 }
 

@@ -156,7 +156,9 @@ int alegpu_normalize_logits(const float *logits, int64_t n, int64_t A, float *ou
  * autograd produces for mini_batch_update (train.h:118-126) w.r.t. the RAW logits and the
  * values.  logits [n,A] raw network outputs, old_log_probs [n,A] normalised, actions [n]
  * int64, masks [n] 1-byte.  Outputs (any may be NULL): loss [1], per-sample clipped_losses,
- * value_losses, entropies, total_losses, ratio [n], dlogits [n,A], dvalues [n]. A <= 32. */
+ * value_losses, entropies, total_losses, ratio [n], dlogits [n,A], dvalues [n]. A <= 32.
+ * Uses a per-device scratch buffer: not re-entrant on one device (call it from one thread / stream at a
+ * time) and it may allocate, so not inside a stream capture — alegpu_learner_train has neither limit. */
 int alegpu_loss(const float *logits, const float *old_log_probs, const int64_t *actions,
                 const float *advantages, const float *values, const float *returns,
                 const uint8_t *masks, int64_t n, int64_t A, float clip_param,
