@@ -1194,7 +1194,10 @@ int convert_obs(const TcState &T, const uint8_t *obs, int64_t n, void *out, cuda
   const int64_t total = n * 84 * 21;
   if (total == 0)
     return ALEGPU_OK;
-  const int blocks = (int)std::min<int64_t>(ceil_div(total, 256), (int64_t)kNumSMs * 16);
+  // one work item per thread, no grid-stride cap: measured per v1 train() (tf32) 722 us at 148 x 16 blocks,
+  // 665 at x64, 646 at x256, 636 uncapped (0.70 of the copy peak); ALEGPU_S2D_BLOCKS caps it for the A/B
+  static const int64_t cap_ab = getenv("ALEGPU_S2D_BLOCKS") ? atoll(getenv("ALEGPU_S2D_BLOCKS")) : ((int64_t)1 << 30);
+  const int blocks = (int)std::min<int64_t>(ceil_div(total, 256), cap_ab);
   if (T.elem_bytes == 4)
     obs_to_s2d_kernel<float><<<blocks, 256, 0, s>>>(obs, (float *)out, total);
   else
