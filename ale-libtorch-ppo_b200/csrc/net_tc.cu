@@ -332,6 +332,30 @@ template <class T> struct ColsMN {
     return rc >= 0 ? (const void *)(cc + rc) : ones_chunk_ptr<kElemBytes>();
   }
 };
+// The same transposed view of a plain [rows r][64 channels] matrix as ColsMN, fetched by TMA: an MN-major
+// operand tile is, per 128-byte group of channels, just BK consecutive matrix rows of 128 bytes (bf16: one
+// 64-channel x 64-row box, SWIZZLE_128B; tf32: two 32-channel x 32-row boxes 4096 B apart, and the tensor
+// map's SWIZZLE_128B_ATOM_32B is the BASE32B pattern the tf32 MN-major descriptor expects).  One elected
+// thread, one or two bulk loads per k-block instead of 512 cp.async copies.  Rows past the split's r_end
+// arrive as data (or zeros past the tensor) — harmless: the OTHER operand zero-fills them.
+template <class T> struct ColsMNTma {
+  ALEGPU_RAW_BF16
+  static constexpr int kElemBytes = (int)sizeof(T);
+  static constexpr bool kMN = true;
+  static constexpr bool kAsync = true;
+  static constexpr bool kTma = true;
+  const void *map; // CUtensorMap (tiled, 2-d) in global memory
+  int row_base;    // matrix row of reduction index 0
+  struct TileCtx {
+    int c0;
+  };
+  __device__ __forceinline__ TileCtx tile(int n0) const { return TileCtx{n0}; }
+  __device__ __forceinline__ void tma(const TileCtx &t, uint32_t dst, int r0, int, uint64_t *bar) const {
+    tc::tma_tile_2d(dst, map, t.c0, row_base + r0, bar);
+    if constexpr (sizeof(T) == 4)
+      tc::tma_tile_2d(dst + 4096u, map, t.c0 + 32, row_base + r0, bar);
+  }
+};
 // conv1 wgrad on the space-to-depth layout, A operand (MN-major): row m = tap*32 + oc (tap = a*2+b),
 // reduction index r = s2d block (n, Y, X) of 21x21.  Element = dact1[n, Y-a, X-b, oc] or 0 outside
 // 20x20: the FOUR TAPS ARE FOUR SHIFTED VIEWS OF THE (small) OUTPUT GRADIENT, so the observation
@@ -853,14 +877,19 @@ void plan_splits(int64_t R, int64_t tiles, size_t per_split_floats, size_t ws_fl
 // conv weight gradient: ws[z][k][co] partials of  sum_m col(m,k) * dY[m][co], then fixed-order sum
 template <class T, class Col, int K, int C>
 int conv_wgrad(const Col &col, const T *dy, int64_t Mtot, float scale, float *gw, float *gb,
-               float *ws, size_t ws_floats, cudaStream_t s, bool conv1_perm = false) {
+               float *ws, size_t ws_floats, cudaStream_t s, bool conv1_perm = false,
+               const void *dy_map = nullptr /* TMA map of dy's [rows x 64] view, or nullptr = cp.async */) {
   const int64_t mtiles = ceil_div(K + 1, tc::BM);
   const size_t per = (size_t)(K + 1) * C;
   ALEGPU_REQUIRE(ws_floats >= per, ALEGPU_RUNTIME_ERROR, "wgrad: workspace too small");
   int splits, rps;
   plan_splits(Mtot, mtiles, per, ws_floats, &splits, &rps);
-  if (int rc = tc::launch_gemm_tc<64, 4>(ColMN<Col, K>{col}, ColsMN<T>{dy, C},
-                                         EpiPartial{ws, K + 1, C}, K + 1, C, Mtot, splits, rps, s))
+  if (dy_map && C == 64) {
+    if (int rc = tc::launch_gemm_tc<64, 4>(ColMN<Col, K>{col}, ColsMNTma<T>{dy_map, 0},
+                                           EpiPartial{ws, K + 1, C}, K + 1, C, Mtot, splits, rps, s))
+      return rc;
+  } else if (int rc = tc::launch_gemm_tc<64, 4>(ColMN<Col, K>{col}, ColsMN<T>{dy, C},
+                                                EpiPartial{ws, K + 1, C}, K + 1, C, Mtot, splits, rps, s))
     return rc;
   static_assert(C % 32 == 0, "channel count must be a multiple of 32");
   reduce_wgrad_t_kernel<<<dim3(K + 1, C / 32), dim3(32, 8), 0, s>>>(
@@ -876,7 +905,8 @@ int conv_wgrad(const Col &col, const T *dy, int64_t Mtot, float scale, float *gw
 // null when w == s) is recorded after them and awaited before the final reduction.
 template <class T>
 int conv1_wgrad_s2d(const T *s2d, const T *dy, int64_t n, float scale, float *gw, float *gb,
-                    float *ws, size_t ws_floats, cudaStream_t s, cudaStream_t w, cudaEvent_t join) {
+                    float *ws, size_t ws_floats, cudaStream_t s, cudaStream_t w, cudaEvent_t join,
+                    const void *s2d_map = nullptr, int s2d_row_base = 0) {
   constexpr size_t per = 128 * 64;
   const size_t bias_floats = (size_t)kBiasParts * 32;
   ALEGPU_REQUIRE(ws_floats >= per + bias_floats, ALEGPU_RUNTIME_ERROR, "conv1 wgrad: workspace too small");
@@ -893,8 +923,12 @@ int conv1_wgrad_s2d(const T *s2d, const T *dy, int64_t n, float scale, float *gw
   ALEGPU_COUNT_LAUNCH();
   if (join)
     ALEGPU_CUDA_CHECK(cudaEventRecord(join, w));
-  if (int rc = tc::launch_gemm_tc<64, 4>(DYShift<T>{dy}, ColsMN<T>{s2d, 64}, EpiPartial{ws, 128, 64}, 128,
-                                         64, n * 441, splits, rps, s))
+  if (s2d_map) { // the observation operand (read once, un-expanded) through TMA
+    if (int rc = tc::launch_gemm_tc<64, 4>(DYShift<T>{dy}, ColsMNTma<T>{s2d_map, s2d_row_base},
+                                           EpiPartial{ws, 128, 64}, 128, 64, n * 441, splits, rps, s))
+      return rc;
+  } else if (int rc = tc::launch_gemm_tc<64, 4>(DYShift<T>{dy}, ColsMN<T>{s2d, 64}, EpiPartial{ws, 128, 64},
+                                                128, 64, n * 441, splits, rps, s))
     return rc;
   if (join)
     ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(s, join, 0));
@@ -994,6 +1028,8 @@ template <class T> Shadow<T> shadow_view(const TcState &S, const NetParams &P) {
 enum TmaSlot { kMapAct1 = 0, kMapAct2, kMapDact3, kMapDact2, kMapObsMb, kMapObsAll, kMapObsAllSlots = 16,
                // plain [rows x 64] tiled maps of the same buffers for the shift convolutions (tc_shift.cuh)
                kMapAct2Rows = kMapObsAll + kMapObsAllSlots, kMapAct1Rows, kMapDact3PadRows, kMapDact2PadRows,
+               kMapDact3MN, kMapDact2MN, kMapObsMbMN, kMapObsAllMN, // [rows x 64] boxes of one k-block of rows (ColsMNTma)
+               kMapObsAllMNEnd = kMapObsAllMN + kMapObsAllSlots - 1,
                kMapObsMbRows, kMapObsAllRows,
                kMapCount = kMapObsAllRows + kMapObsAllSlots };
 using EncodeIm2colFn = CUresult (*)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
@@ -1052,7 +1088,7 @@ EncodeTiledFn encode_tiled_fn() {
 }
 // map slot <- the [rows x 64] matrix view of an NHWC buffer with 64 channels per pixel: boxes of
 // box_rows rows (the layer's stage height) x one 128-byte channel panel, 128-byte swizzle, zeros past the last row
-int set_rows_map(TcState &T, int slot, void *base, int64_t rows, int box_rows) {
+int set_rows_map(TcState &T, int slot, void *base, int64_t rows, int box_rows, bool mn_operand = false) {
   EncodeTiledFn fn = encode_tiled_fn();
   ALEGPU_REQUIRE(fn != nullptr, ALEGPU_RUNTIME_ERROR, "cuTensorMapEncodeTiled is not available");
   alignas(64) CUtensorMap m;
@@ -1063,7 +1099,9 @@ int set_rows_map(TcState &T, int slot, void *base, int64_t rows, int box_rows) {
   const cuuint32_t estr[2] = {1, 1};
   const CUresult r = fn(&m, eb == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
                         base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        // an MN-major tf32 operand tile is swizzled in 32-byte units (UMMA SWIZZLE_128B_BASE32B)
+                        mn_operand && eb == 4 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   ALEGPU_REQUIRE(r == CUDA_SUCCESS, ALEGPU_RUNTIME_ERROR,
                  "cuTensorMapEncodeTiled failed: " + std::to_string((int)r));
@@ -1139,8 +1177,14 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
     if (int rc = set_rows_map(T, kMapAct1Rows, T.act1, cap * 200, tc::shift_stage_rows(4, 2, 10))) return rc; // pixel pairs [n,20,10,64]
     if (int rc = set_rows_map(T, kMapDact3PadRows, T.dact3p, cap * 100, tc::shift_stage_rows(3, 3, 10))) return rc;
     if (int rc = set_rows_map(T, kMapDact2PadRows, T.dact2p, cap * 100, tc::shift_stage_rows(2, 2, 10))) return rc;
+    const int bk = 128 / elem_bytes; // rows of one k-block
+    if (int rc = set_rows_map(T, kMapDact3MN, T.dact3, cap * 49, bk, true)) return rc;
+    if (int rc = set_rows_map(T, kMapDact2MN, T.dact2, cap * 81, bk, true)) return rc;
+    if (int rc = set_rows_map(T, kMapObsMbMN, T.obs16_mb, cap * 441, bk, true)) return rc;
     if (int rc = set_rows_map(T, kMapObsMbRows, T.obs16_mb, cap * 441, tc::shift_stage_rows(2, 2, 21))) return rc;
   }
+  env = getenv("ALEGPU_NO_TMA_WGRAD"); // A/B: the weight gradients' plain-matrix operand through cp.async
+  T.use_tma_wgrad = T.use_tma && !(env && env[0] == '1');
   env = getenv("ALEGPU_NO_SHIFT"); // A/B: conv1 / conv3 forward through the im2col engine instead
   T.use_shift = T.use_tma && !(env && env[0] == '1');
   // conv3 / conv2 data gradients as shift convolutions over zero-bordered gradient copies: measured at
@@ -1222,6 +1266,8 @@ int net_tc_reserve_obs(TcState &T, int64_t n) {
   if (T.use_tma) {
     T.obs_all_map = (T.obs_all_map + 1) % kMapObsAllSlots;
     if (int rc = set_rows_map(T, kMapObsAllRows + T.obs_all_map, T.obs16_all, n * 441, tc::shift_stage_rows(2, 2, 21)))
+      return rc;
+    if (int rc = set_rows_map(T, kMapObsAllMN + T.obs_all_map, T.obs16_all, n * 441, 128 / T.elem_bytes, true))
       return rc;
     return set_im2col_map(T, kMapObsAll + T.obs_all_map, T.obs16_all, 21, 21, n, 0, -1);
   }
@@ -1415,7 +1461,8 @@ int backward_impl(const NetParams &P, const NetParams &G, TcState &S, const uint
   }
   // ---- side: conv3 wgrad (needs dact3)
   if (int rc = conv_wgrad<T, Col3<T>, 576, 64>(Col3<T>{act2}, dact3, n * 49, 1.0f, G.c3w, G.c3b,
-                                               S.ws_c3, S.ws_c3_n, w))
+                                               S.ws_c3, S.ws_c3_n, w, false,
+                                               S.use_tma_wgrad ? tmap(S, kMapDact3MN) : nullptr))
     return rc;
   // ---- main: conv3 dgrad
   if (S.use_shift_dgrad) { // 9 flipped taps = row-shifted views of one staged copy of the bordered dact3
@@ -1437,7 +1484,8 @@ int backward_impl(const NetParams &P, const NetParams &G, TcState &S, const uint
   }
   // ---- side: conv2 wgrad (needs dact2)
   if (int rc = conv_wgrad<T, Col2<T>, 512, 64>(Col2<T>{act1}, dact2, n * 81, 1.0f, G.c2w, G.c2b,
-                                               S.ws_c2, S.ws_c2_n, w))
+                                               S.ws_c2, S.ws_c2_n, w, false,
+                                               S.use_tma_wgrad ? tmap(S, kMapDact2MN) : nullptr))
     return rc;
   if (!S.serial)
     ALEGPU_CUDA_CHECK(cudaEventRecord(S.ev_join, w));
@@ -1480,8 +1528,16 @@ int backward_impl(const NetParams &P, const NetParams &G, TcState &S, const uint
       ALEGPU_CUDA_CHECK(cudaEventRecord(S.ev_d1, s));
       ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(w, S.ev_d1, 0));
     }
+    const T *all = (const T *)S.obs16_all;
+    const bool in_all = all && x16 >= all && x16 < all + (size_t)S.obs16_all_rows * 28224;
+    const void *xmap = nullptr;
+    int xbase = 0;
+    if (S.use_tma_wgrad && (in_all || x16 == (const T *)S.obs16_mb)) {
+      xmap = tmap(S, in_all ? kMapObsAllMN + S.obs_all_map : kMapObsMbMN);
+      xbase = in_all ? (int)((x16 - all) / 28224) * 441 : 0;
+    }
     if (int rc = conv1_wgrad_s2d<T>(x16, dact1, n, 1.0f / 255.0f, G.c1w, G.c1b, S.ws_c1, S.ws_c1_n,
-                                    s, fork ? w : s, fork ? S.ev_join : nullptr))
+                                    s, fork ? w : s, fork ? S.ev_join : nullptr, xmap, xbase))
       return rc;
   }
   if (!S.serial)
