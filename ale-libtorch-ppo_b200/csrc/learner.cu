@@ -757,7 +757,7 @@ extern "C" int alegpu_learner_create(const alegpu_learner_config *config, alegpu
   ALEGPU_CUDA_CHECK(cudaHostGetDevicePointer(&L->err_dev, L->err_host, 0));
   if (tc)
     if (int rc = net_tc_init(L->tc, H, A, cap, L->Ppad, config->math == ALEGPU_MATH_TF32 ? 4 : 2,
-                             L->stream))
+                             a.dfc, L->stream))
       return rc;
   a.dfc16 = L->tc.dfc16; // bf16 mode: the heads kernel also emits dfc in bf16 for the tensor-core backward
   a.dfc_round_tf32 = config->math == ALEGPU_MATH_TF32; // tf32 mode: it rounds dfc itself to tf32

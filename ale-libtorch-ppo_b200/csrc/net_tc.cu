@@ -338,12 +338,14 @@ template <class T> struct ColsMN {
 // map's SWIZZLE_128B_ATOM_32B is the BASE32B pattern the tf32 MN-major descriptor expects).  One elected
 // thread, one or two bulk loads per k-block instead of 512 cp.async copies.  Rows past the split's r_end
 // arrive as data (or zeros past the tensor) — harmless: the OTHER operand zero-fills them.
-template <class T> struct ColsMNTma {
+template <class T, int ROWS = 64> struct ColsMNTma {
   ALEGPU_RAW_BF16
   static constexpr int kElemBytes = (int)sizeof(T);
   static constexpr bool kMN = true;
   static constexpr bool kAsync = true;
   static constexpr bool kTma = true;
+  static constexpr int kAtomRows = 128 / kElemBytes;              // matrix columns per 128-byte group
+  static constexpr uint32_t kLbo = kElemBytes == 2 ? 8192u : 4096u; // bytes between the groups of one tile
   const void *map; // CUtensorMap (tiled, 2-d) in global memory
   int row_base;    // matrix row of reduction index 0
   struct TileCtx {
@@ -351,9 +353,28 @@ template <class T> struct ColsMNTma {
   };
   __device__ __forceinline__ TileCtx tile(int n0) const { return TileCtx{n0}; }
   __device__ __forceinline__ void tma(const TileCtx &t, uint32_t dst, int r0, int, uint64_t *bar) const {
-    tc::tma_tile_2d(dst, map, t.c0, row_base + r0, bar);
-    if constexpr (sizeof(T) == 4)
-      tc::tma_tile_2d(dst + 4096u, map, t.c0 + 32, row_base + r0, bar);
+#pragma unroll
+    for (int a = 0; a < ROWS / kAtomRows; ++a) // columns past the matrix arrive as zeros
+      tc::tma_tile_2d(dst + (uint32_t)a * kLbo, map, t.c0 + a * kAtomRows, row_base + r0, bar);
+  }
+};
+// K-major view of a plain [rows][ld] matrix (RowsK) fetched by TMA: ROWS/64 boxes of 64 rows x one
+// 128-byte k-block, SWIZZLE_128B.  Rows past the matrix are zeros, rows past M are masked by the epilogue.
+template <class T, int ROWS> struct RowsKTma {
+  ALEGPU_RAW_BF16
+  static constexpr int kElemBytes = (int)sizeof(T);
+  static constexpr bool kMN = false;
+  static constexpr bool kAsync = true;
+  static constexpr bool kTma = true;
+  const void *map;
+  struct TileCtx {
+    int row0;
+  };
+  __device__ __forceinline__ TileCtx tile(int i0) const { return TileCtx{i0}; }
+  __device__ __forceinline__ void tma(const TileCtx &t, uint32_t dst, int r0, int, uint64_t *bar) const {
+#pragma unroll
+    for (int h = 0; h < ROWS / 64; ++h)
+      tc::tma_tile_2d(dst + (uint32_t)h * 8192u, map, r0, t.row0 + h * 64, bar);
   }
 };
 // conv1 wgrad on the space-to-depth layout, A operand (MN-major): row m = tap*32 + oc (tap = a*2+b),
@@ -1028,7 +1049,7 @@ template <class T> Shadow<T> shadow_view(const TcState &S, const NetParams &P) {
 enum TmaSlot { kMapAct1 = 0, kMapAct2, kMapDact3, kMapDact2, kMapObsMb, kMapObsAll, kMapObsAllSlots = 16,
                // plain [rows x 64] tiled maps of the same buffers for the shift convolutions (tc_shift.cuh)
                kMapAct2Rows = kMapObsAll + kMapObsAllSlots, kMapAct1Rows, kMapDact3PadRows, kMapDact2PadRows,
-               kMapDact3MN, kMapDact2MN, kMapObsMbMN, kMapObsAllMN, // [rows x 64] boxes of one k-block of rows (ColsMNTma)
+               kMapDact3MN, kMapDact2MN, kMapDfcK, kMapAct3K, kMapFcwK, kMapFcwMN, kMapObsMbMN, kMapObsAllMN, // [rows x 64] boxes of one k-block of rows (ColsMNTma)
                kMapObsAllMNEnd = kMapObsAllMN + kMapObsAllSlots - 1,
                kMapObsMbRows, kMapObsAllRows,
                kMapCount = kMapObsAllRows + kMapObsAllSlots };
@@ -1088,13 +1109,14 @@ EncodeTiledFn encode_tiled_fn() {
 }
 // map slot <- the [rows x 64] matrix view of an NHWC buffer with 64 channels per pixel: boxes of
 // box_rows rows (the layer's stage height) x one 128-byte channel panel, 128-byte swizzle, zeros past the last row
-int set_rows_map(TcState &T, int slot, void *base, int64_t rows, int box_rows, bool mn_operand = false) {
+int set_rows_map(TcState &T, int slot, void *base, int64_t rows, int box_rows, bool mn_operand = false,
+                 int64_t cols = 64) {
   EncodeTiledFn fn = encode_tiled_fn();
   ALEGPU_REQUIRE(fn != nullptr, ALEGPU_RUNTIME_ERROR, "cuTensorMapEncodeTiled is not available");
   alignas(64) CUtensorMap m;
   const cuuint64_t eb = (cuuint64_t)T.elem_bytes;
-  const cuuint64_t dims[2] = {64, (cuuint64_t)rows};
-  const cuuint64_t strides[1] = {64 * eb};
+  const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)cols * eb};
   const cuuint32_t box[2] = {(cuuint32_t)(128 / eb), (cuuint32_t)box_rows};
   const cuuint32_t estr[2] = {1, 1};
   const CUresult r = fn(&m, eb == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
@@ -1114,7 +1136,7 @@ const void *tmap(const TcState &T, int slot) { return (const CUtensorMap *)T.tma
 
 // ---- public (net_tc.h) ----------------------------------------------------------------------------
 int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_t Ppad,
-                int elem_bytes, cudaStream_t) {
+                int elem_bytes, float *dfc_f32, cudaStream_t) {
   ALEGPU_REQUIRE(hidden % 16 == 0, ALEGPU_INVALID_ARGUMENT,
                  "the tensor-core path needs hidden_size % 16 == 0");
   ALEGPU_REQUIRE(elem_bytes == 2 || elem_bytes == 4, ALEGPU_INVALID_ARGUMENT,
@@ -1181,8 +1203,21 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
     if (int rc = set_rows_map(T, kMapDact3MN, T.dact3, cap * 49, bk, true)) return rc;
     if (int rc = set_rows_map(T, kMapDact2MN, T.dact2, cap * 81, bk, true)) return rc;
     if (int rc = set_rows_map(T, kMapObsMbMN, T.obs16_mb, cap * 441, bk, true)) return rc;
+    // the FC layers' plain matrices: dfc [cap][H], act3 [cap][3136], the fc weight shadow [H][3136] (K-major
+    // 64-row boxes, and the transposed MN-major view the data gradient reads)
+    void *dfc = elem_bytes == 2 ? T.dfc16 : (void *)dfc_f32;
+    char *fcw = (char *)T.w_shadow + eb * (size_t)(32 * 256 + 32 + 64 * 512 + 64 + 64 * 576 + 64);
+    T.fc_tma = dfc != nullptr;
+    if (T.fc_tma) {
+      if (int rc = set_rows_map(T, kMapDfcK, dfc, cap, 64, false, hidden)) return rc;
+      if (int rc = set_rows_map(T, kMapAct3K, T.act3, cap, 64, false, 3136)) return rc;
+      if (int rc = set_rows_map(T, kMapFcwK, fcw, hidden, 64, false, 3136)) return rc;
+      if (int rc = set_rows_map(T, kMapFcwMN, fcw, hidden, bk, true, 3136)) return rc;
+    }
     if (int rc = set_rows_map(T, kMapObsMbRows, T.obs16_mb, cap * 441, tc::shift_stage_rows(2, 2, 21))) return rc;
   }
+  env = getenv("ALEGPU_NO_TMA_FC"); // A/B: the FC forward / data-gradient operands through cp.async
+  T.fc_tma = T.fc_tma && T.use_tma && !(env && env[0] == '1');
   env = getenv("ALEGPU_NO_TMA_WGRAD"); // A/B: the weight gradients' plain-matrix operand through cp.async
   T.use_tma_wgrad = T.use_tma && !(env && env[0] == '1');
   env = getenv("ALEGPU_NO_SHIFT"); // A/B: conv1 / conv3 forward through the im2col engine instead
@@ -1371,8 +1406,13 @@ int forward_impl(const NetParams &P, TcState &S, const uint8_t *obs, int64_t n, 
     splits = std::max(splits, 1);
     const int rps = (int)(ceil_div(ceil_div(3136, splits), tc::BK) * tc::BK);
     splits = (int)ceil_div(3136, rps);
-    if (int rc = tc::launch_gemm_tc<64, 4>(RowsK<T>{act3, 3136}, RowsK<T>{W.fcw, 3136},
-                                           EpiPartial{A.fc_ws, (int)n, H}, n, H, 3136, splits, rps, s))
+    if (S.fc_tma) { // both plain matrices through TMA (K-major 64-row boxes)
+      if (int rc = tc::launch_gemm_tc<64, 4>(RowsKTma<T, 128>{tmap(S, kMapAct3K)},
+                                             RowsKTma<T, 64>{tmap(S, kMapFcwK)},
+                                             EpiPartial{A.fc_ws, (int)n, H}, n, H, 3136, splits, rps, s))
+        return rc;
+    } else if (int rc = tc::launch_gemm_tc<64, 4>(RowsK<T>{act3, 3136}, RowsK<T>{W.fcw, 3136},
+                                                  EpiPartial{A.fc_ws, (int)n, H}, n, H, 3136, splits, rps, s))
       return rc;
     const int64_t total4 = n * H / 4;
     reduce_fc_kernel<<<(unsigned)std::min<int64_t>(ceil_div(total4, 256), 2 * kNumSMs), 256, 0, s>>>(
@@ -1382,6 +1422,9 @@ int forward_impl(const NetParams &P, TcState &S, const uint8_t *obs, int64_t n, 
     ALEGPU_LAUNCH_CHECK();
     return ALEGPU_OK;
   }
+  if (S.fc_tma)
+    return tc::launch_gemm_tc<128, 3>(RowsKTma<T, 128>{tmap(S, kMapAct3K)}, RowsKTma<T, 128>{tmap(S, kMapFcwK)},
+                                      EpiBiasF32{A.fc, P.fcb, H}, n, H, 3136, 1, 0, s);
   return tc::launch_gemm_tc<128, 3>(RowsK<T>{act3, 3136}, RowsK<T>{W.fcw, 3136},
                                     EpiBiasF32{A.fc, P.fcb, H}, n, H, 3136, 1, 0, s);
 }
@@ -1438,23 +1481,29 @@ int backward_impl(const NetParams &P, const NetParams &G, TcState &S, const uint
     ALEGPU_CUDA_CHECK(cudaEventRecord(S.ev_fcw, w));
   // ---- main: FC dgrad: dact3 = (dfc . fcw) * relu'(act3)
   T *dact3p = (T *)S.dact3p, *dact2p = (T *)S.dact2p;
-  if (S.use_shift_dgrad) { // also the zero-bordered copy the shift-convolution conv3 dgrad stages
-    if (ceil_div(n, tc::BM) * 25 < kNumSMs) {
-      if (int rc = tc::launch_gemm_tc<64, 4>(RowsK<T>{dfcT, H}, ColsMN<T>{W.fcw, 3136},
-                                             EpiReluMaskFcPad<T>{dact3, dact3p, act3}, n, 3136, H, 1, 0, s))
+  {
+    // operands: dfc [n][H] K-major, fcw^T MN-major — through TMA (S.fc_tma) or cp.async; epilogue: relu'
+    // mask into dact3, plus the zero-bordered copy when conv3's data gradient runs as a shift convolution;
+    // small minibatches take 64-wide tiles (twice the CTAs)
+    const bool small = ceil_div(n, tc::BM) * 25 < kNumSMs;
+    auto run = [&](auto epi) -> int {
+      if (S.fc_tma) {
+        if (small)
+          return tc::launch_gemm_tc<64, 4>(RowsKTma<T, 128>{tmap(S, kMapDfcK)},
+                                           ColsMNTma<T, 64>{tmap(S, kMapFcwMN), 0}, epi, n, 3136, H, 1, 0, s);
+        return tc::launch_gemm_tc<128, 3>(RowsKTma<T, 128>{tmap(S, kMapDfcK)},
+                                          ColsMNTma<T, 128>{tmap(S, kMapFcwMN), 0}, epi, n, 3136, H, 1, 0, s);
+      }
+      if (small)
+        return tc::launch_gemm_tc<64, 4>(RowsK<T>{dfcT, H}, ColsMN<T>{W.fcw, 3136}, epi, n, 3136, H, 1, 0, s);
+      return tc::launch_gemm_tc<128, 3>(RowsK<T>{dfcT, H}, ColsMN<T>{W.fcw, 3136}, epi, n, 3136, H, 1, 0, s);
+    };
+    if (S.use_shift_dgrad) {
+      if (int rc = run(EpiReluMaskFcPad<T>{dact3, dact3p, act3}))
         return rc;
-    } else if (int rc = tc::launch_gemm_tc<128, 3>(RowsK<T>{dfcT, H}, ColsMN<T>{W.fcw, 3136},
-                                                   EpiReluMaskFcPad<T>{dact3, dact3p, act3}, n, 3136, H,
-                                                   1, 0, s))
+    } else if (int rc = run(EpiReluMask<T>{dact3, act3, 3136}))
       return rc;
-  } else if (ceil_div(n, tc::BM) * 25 < kNumSMs) { // small minibatch: narrower tiles, twice the CTAs
-    if (int rc = tc::launch_gemm_tc<64, 4>(RowsK<T>{dfcT, H}, ColsMN<T>{W.fcw, 3136},
-                                           EpiReluMask<T>{dact3, act3, 3136}, n, 3136, H, 1, 0, s))
-      return rc;
-  } else if (int rc = tc::launch_gemm_tc<128, 3>(RowsK<T>{dfcT, H}, ColsMN<T>{W.fcw, 3136},
-                                                 EpiReluMask<T>{dact3, act3, 3136}, n, 3136, H, 1,
-                                                 0, s))
-    return rc;
+  }
   if (!S.serial) {
     ALEGPU_CUDA_CHECK(cudaEventRecord(S.ev_d3, s));
     ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(w, S.ev_d3, 0));

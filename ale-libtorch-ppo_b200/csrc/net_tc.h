@@ -31,6 +31,7 @@ struct TcState {
   void *tmaps = nullptr;
   int obs_all_map = 0;       // which of the round-robin obs16_all descriptor slots is current
   bool use_tma = true;       // ALEGPU_NO_TMA=1: gather conv operands with cp.async instead (A/B)
+  bool fc_tma = false;       // FC forward / data-gradient operands through tiled TMA (ALEGPU_NO_TMA_FC=1: cp.async)
   bool use_tma_wgrad = true; // ALEGPU_NO_TMA_WGRAD=1: the weight gradients' plain-matrix operand via cp.async (A/B)
   bool use_shift_dgrad = true; // conv3 / conv2 data gradients as shift convolutions (default: bf16 only; ALEGPU_SHIFT_DGRAD=0|1)
   bool use_shift = true;     // ALEGPU_NO_SHIFT=1: conv1 / conv3 forward through the im2col engine (A/B)
@@ -40,8 +41,9 @@ struct TcState {
   bool conv1_wgrad_u8 = false; // ALEGPU_CONV1_WGRAD_U8=1: conv1 wgrad in im2col form over the u8 observations (A/B)
 };
 
+// dfc_f32: the learner's fp32 dfc buffer [cap][hidden] (the tf32 path's FC data-gradient operand)
 int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_t Ppad,
-                int elem_bytes, cudaStream_t s);
+                int elem_bytes, float *dfc_f32, cudaStream_t s);
 void net_tc_destroy(TcState &T);
 int net_tc_refresh_weights(TcState &T, const float *params, int64_t Ppad, cudaStream_t s);
 // obs16 = the rows' bf16 NHWC copy when the caller already made one (net_tc_prepare_obs); nullptr:
