@@ -377,6 +377,44 @@ template <class T, int ROWS> struct RowsKTma {
       tc::tma_tile_2d(dst + (uint32_t)h * 8192u, map, r0, t.row0 + h * 64, bar);
   }
 };
+// The transposed conv weights of the data gradients (W3T, W2TAll) through 3-d tiled TMA.  Both views read,
+// for one filter tap and a run of BK output channels co (the k-block), 128-byte groups of consecutive
+// input-channel elements — boxes {128 bytes, 1 tap, BK co} of the weight tensor seen as [co][tap'][128 B]:
+//   conv3 (W3T):    c3w [64 co][9 taps][64 ci]       -> group g = ci / (128 B), tap' = tap
+//   conv2 (W2TAll): c2w [64 co][16 taps][32 ci]; output row j = cls*32 + ci with cls = (py,px) and the
+//                   tap of (cls, t = (ty,tx)) = (py+2ty)*4 + px+2tx: bf16 groups of 64 rows are the two
+//                   px of one py = two NEIGHBOURING taps (tap' = tap pair), tf32 groups of 32 rows one tap
+template <class T, int NGROUPS, bool kConv2> struct WTapTma {
+  ALEGPU_RAW_BF16
+  static constexpr int kElemBytes = (int)sizeof(T);
+  static constexpr bool kMN = true;
+  static constexpr bool kAsync = true;
+  static constexpr bool kTma = true;
+  static constexpr int kAtomRows = 128 / kElemBytes;
+  static constexpr uint32_t kLbo = kElemBytes == 2 ? 8192u : 4096u;
+  const void *map;
+  struct TileCtx {
+    int n0;
+  };
+  __device__ __forceinline__ TileCtx tile(int n0) const { return TileCtx{n0}; }
+  __device__ __forceinline__ void tma(const TileCtx &, uint32_t dst, int r0, int, uint64_t *bar) const {
+    const int t = r0 >> 6, co0 = r0 & 63;
+#pragma unroll
+    for (int g = 0; g < NGROUPS; ++g) {
+      int c0 = 0, tap = t;
+      if constexpr (!kConv2) {
+        c0 = g * kAtomRows; // conv3: group g = input channels [g*atom, (g+1)*atom) of tap t
+      } else {
+        const int ty = t >> 1, tx = t & 1;
+        if constexpr (sizeof(T) == 2)
+          tap = (g + 2 * ty) * 2 + tx; // bf16: group g = py, tap pair index ((py+2ty)*4 + 2tx) / 2
+        else
+          tap = ((g >> 1) + 2 * ty) * 4 + (g & 1) + 2 * tx; // tf32: group g = cls = (py, px)
+      }
+      tc::tma_tile_3d(dst + (uint32_t)g * kLbo, map, c0, tap, co0, bar);
+    }
+  }
+};
 // conv1 wgrad on the space-to-depth layout, A operand (MN-major): row m = tap*32 + oc (tap = a*2+b),
 // reduction index r = s2d block (n, Y, X) of 21x21.  Element = dact1[n, Y-a, X-b, oc] or 0 outside
 // 20x20: the FOUR TAPS ARE FOUR SHIFTED VIEWS OF THE (small) OUTPUT GRADIENT, so the observation
@@ -1049,7 +1087,7 @@ template <class T> Shadow<T> shadow_view(const TcState &S, const NetParams &P) {
 enum TmaSlot { kMapAct1 = 0, kMapAct2, kMapDact3, kMapDact2, kMapObsMb, kMapObsAll, kMapObsAllSlots = 16,
                // plain [rows x 64] tiled maps of the same buffers for the shift convolutions (tc_shift.cuh)
                kMapAct2Rows = kMapObsAll + kMapObsAllSlots, kMapAct1Rows, kMapDact3PadRows, kMapDact2PadRows,
-               kMapDact3MN, kMapDact2MN, kMapDfcK, kMapAct3K, kMapFcwK, kMapFcwMN, kMapObsMbMN, kMapObsAllMN, // [rows x 64] boxes of one k-block of rows (ColsMNTma)
+               kMapDact3MN, kMapDact2MN, kMapDfcK, kMapAct3K, kMapFcwK, kMapFcwMN, kMapC2wK, kMapC3wTap, kMapC2wTap, kMapObsMbMN, kMapObsAllMN, // [rows x 64] boxes of one k-block of rows (ColsMNTma)
                kMapObsAllMNEnd = kMapObsAllMN + kMapObsAllSlots - 1,
                kMapObsMbRows, kMapObsAllRows,
                kMapCount = kMapObsAllRows + kMapObsAllSlots };
@@ -1130,6 +1168,26 @@ int set_rows_map(TcState &T, int slot, void *base, int64_t rows, int box_rows, b
   ALEGPU_CUDA_CHECK(cudaMemcpy((CUtensorMap *)T.tmaps + slot, &m, sizeof(m), cudaMemcpyHostToDevice));
   return ALEGPU_OK;
 }
+// map slot <- a weight tensor seen as [co][taps'][group elements]: boxes {128 bytes, 1, one k-block of co},
+// swizzled as an MN-major operand tile
+int set_wtap_map(TcState &T, int slot, void *base, int group_elems_total, int taps, int co) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  ALEGPU_REQUIRE(fn != nullptr, ALEGPU_RUNTIME_ERROR, "cuTensorMapEncodeTiled is not available");
+  alignas(64) CUtensorMap m;
+  const cuuint64_t eb = (cuuint64_t)T.elem_bytes;
+  const cuuint64_t dims[3] = {(cuuint64_t)group_elems_total, (cuuint64_t)taps, (cuuint64_t)co};
+  const cuuint64_t strides[2] = {(cuuint64_t)group_elems_total * eb, (cuuint64_t)group_elems_total * taps * eb};
+  const cuuint32_t box[3] = {(cuuint32_t)(128 / eb), 1, (cuuint32_t)(128 / eb)};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  const CUresult r = fn(&m, eb == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3,
+                        base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        eb == 4 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  ALEGPU_REQUIRE(r == CUDA_SUCCESS, ALEGPU_RUNTIME_ERROR,
+                 "cuTensorMapEncodeTiled (weights) failed: " + std::to_string((int)r));
+  ALEGPU_CUDA_CHECK(cudaMemcpy((CUtensorMap *)T.tmaps + slot, &m, sizeof(m), cudaMemcpyHostToDevice));
+  return ALEGPU_OK;
+}
 const void *tmap(const TcState &T, int slot) { return (const CUtensorMap *)T.tmaps + slot; }
 
 } // namespace
@@ -1205,6 +1263,13 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
     if (int rc = set_rows_map(T, kMapObsMbMN, T.obs16_mb, cap * 441, bk, true)) return rc;
     // the FC layers' plain matrices: dfc [cap][H], act3 [cap][3136], the fc weight shadow [H][3136] (K-major
     // 64-row boxes, and the transposed MN-major view the data gradient reads)
+    // conv weights of the shadow: c2w [64][512] K-major rows (conv2 forward), and the per-tap views the data
+    // gradients read (conv3: [64 co][9][64 ci]; conv2: [64 co][8 tap pairs][64] in bf16, [64 co][16 taps][32] in tf32)
+    char *c2w = (char *)T.w_shadow + eb * (size_t)(32 * 256 + 32);
+    char *c3w = c2w + eb * (size_t)(64 * 512 + 64);
+    if (int rc = set_rows_map(T, kMapC2wK, c2w, 64, 64, false, 512)) return rc;
+    if (int rc = set_wtap_map(T, kMapC3wTap, c3w, 64, 9, 64)) return rc;
+    if (int rc = set_wtap_map(T, kMapC2wTap, c2w, elem_bytes == 2 ? 64 : 32, elem_bytes == 2 ? 8 : 16, 64)) return rc;
     void *dfc = elem_bytes == 2 ? T.dfc16 : (void *)dfc_f32;
     char *fcw = (char *)T.w_shadow + eb * (size_t)(32 * 256 + 32 + 64 * 512 + 64 + 64 * 576 + 64);
     T.fc_tma = dfc != nullptr;
@@ -1216,6 +1281,8 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
     }
     if (int rc = set_rows_map(T, kMapObsMbRows, T.obs16_mb, cap * 441, tc::shift_stage_rows(2, 2, 21))) return rc;
   }
+  env = getenv("ALEGPU_NO_TMA_WEIGHTS"); // A/B: conv2 forward / conv3, conv2 data-gradient weights via cp.async
+  T.use_tma_weights = T.use_tma && !(env && env[0] == '1');
   env = getenv("ALEGPU_NO_TMA_FC"); // A/B: the FC forward / data-gradient operands through cp.async
   T.fc_tma = T.fc_tma && T.use_tma && !(env && env[0] == '1');
   env = getenv("ALEGPU_NO_TMA_WGRAD"); // A/B: the weight gradients' plain-matrix operand through cp.async
@@ -1374,6 +1441,11 @@ int forward_impl(const NetParams &P, TcState &S, const uint8_t *obs, int64_t n, 
             tmap(S, kMapAct1Rows), 0, tc::WKMajor<T>{W.c2w, 512}, EpiBiasRelu<T>{act2, P.c2b, 64, 1.0f}, n, s,
             S.shift_base_offset))
       return rc;
+  } else if (S.use_tma && S.use_tma_weights) { // both operands by TMA: im2col boxes and the weight rows
+    if (int rc = tc::launch_gemm_tc<64, 4>(Col2Tma<T>{tmap(S, kMapAct1), 0}, RowsKTma<T, 64>{tmap(S, kMapC2wK)},
+                                           EpiBiasRelu<T>{act2, P.c2b, 64, 1.0f}, n * 81, 64, 512,
+                                           1, 0, s))
+      return rc;
   } else if (S.use_tma) {
     if (int rc = tc::launch_gemm_tc<64, 4>(Col2Tma<T>{tmap(S, kMapAct1), 0}, RowsK<T>{W.c2w, 512},
                                            EpiBiasRelu<T>{act2, P.c2b, 64, 1.0f}, n * 81, 64, 512,
@@ -1519,6 +1591,11 @@ int backward_impl(const NetParams &P, const NetParams &G, TcState &S, const uint
             tmap(S, kMapDact3PadRows), 0, tc::WMNView<W3T<T>>{W3T<T>{W.c3w}},
             EpiReluMaskPad<T>{dact2, dact2p, act2}, n, s, S.shift_base_offset))
       return rc;
+  } else if (S.use_tma && S.use_tma_weights) {
+    if (int rc = tc::launch_gemm_tc<64, 4>(DCol3Tma<T>{tmap(S, kMapDact3), 0},
+                                           WTapTma<T, (sizeof(T) == 2 ? 1 : 2), false>{tmap(S, kMapC3wTap)},
+                                           EpiReluMask<T>{dact2, act2, 64}, n * 81, 64, 576, 1, 0, s))
+      return rc;
   } else if (S.use_tma) {
     if (int rc = tc::launch_gemm_tc<64, 4>(DCol3Tma<T>{tmap(S, kMapDact3), 0}, W3T<T>{W.c3w},
                                            EpiReluMask<T>{dact2, act2, 64}, n * 81, 64, 576, 1, 0, s))
@@ -1544,6 +1621,12 @@ int backward_impl(const NetParams &P, const NetParams &G, TcState &S, const uint
     if (int rc = tc::launch_conv_shift<T, 128, 2, 2, 10, 10, 10, 10, 1, (sizeof(T) == 4 ? 2 : 3), 1, true>(
             tmap(S, kMapDact2PadRows), 0, tc::WMNView<W2TAll<T>>{W2TAll<T>{W.c2w}},
             EpiReluMaskConv2All<T>{dact1, act1}, n, s, S.shift_base_offset))
+      return rc;
+  } else if (S.use_tma && S.use_tma_weights) {
+    if (int rc = tc::launch_gemm_tc<128, 3>(DCol2Tma<T>{tmap(S, kMapDact2), 0},
+                                            WTapTma<T, (sizeof(T) == 2 ? 2 : 4), true>{tmap(S, kMapC2wTap)},
+                                            EpiReluMaskConv2All<T>{dact1, act1}, n * 100, 128, 256, 1, 0,
+                                            s))
       return rc;
   } else if (S.use_tma) {
     if (int rc = tc::launch_gemm_tc<128, 3>(DCol2Tma<T>{tmap(S, kMapDact2), 0}, W2TAll<T>{W.c2w},

@@ -31,6 +31,7 @@ struct TcState {
   void *tmaps = nullptr;
   int obs_all_map = 0;       // which of the round-robin obs16_all descriptor slots is current
   bool use_tma = true;       // ALEGPU_NO_TMA=1: gather conv operands with cp.async instead (A/B)
+  bool use_tma_weights = true; // conv weights (conv2 forward, conv3 / conv2 data gradients) through TMA (ALEGPU_NO_TMA_WEIGHTS=1: cp.async)
   bool fc_tma = false;       // FC forward / data-gradient operands through tiled TMA (ALEGPU_NO_TMA_FC=1: cp.async)
   bool use_tma_wgrad = true; // ALEGPU_NO_TMA_WGRAD=1: the weight gradients' plain-matrix operand via cp.async (A/B)
   bool use_shift_dgrad = true; // conv3 / conv2 data gradients as shift convolutions (default: bf16 only; ALEGPU_SHIFT_DGRAD=0|1)

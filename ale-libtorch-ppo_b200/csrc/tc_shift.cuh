@@ -34,6 +34,13 @@ __device__ __forceinline__ void tma_tile_2d(uint32_t dst, const void *map, int c
                "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
                : "memory");
 }
+__device__ __forceinline__ void tma_tile_3d(uint32_t dst, const void *map, int c0, int c1, int c2,
+                                            uint64_t *bar) {
+  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+               " [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst),
+               "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
 // the producer's single arrival on a stage's full barrier, carrying the bytes its TMA loads will deliver
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)

@@ -242,7 +242,8 @@ def test_train_bf16_vs_oracle_and_determinism():
     assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[1], outs[2])  # bit-reproducible
 
 
-def test_tma_im2col_operands_equal_the_gather_operands(monkeypatch):
+@pytest.mark.parametrize("shift_dgrad", ["1", "0"])
+def test_tma_im2col_operands_equal_the_gather_operands(monkeypatch, shift_dgrad):
     """The TMA im2col producers (conv1/2/3 forward, conv3/conv2 data gradients; conv2's four parity
     classes as one GEMM) against the cp.async gather producers they replace (ALEGPU_NO_TMA=1): the same
     bf16 products summed in the same k order, so the results must agree to the bit.  37 rows: every
@@ -251,6 +252,8 @@ def test_tma_im2col_operands_equal_the_gather_operands(monkeypatch):
     params = cases.net_params(H, seed=5)
     tc = cases.train_case(n, seed=19)
     outs = {}
+    # shift_dgrad = 0: the data gradients take the im2col engine with TMA-fetched weight taps (WTapTma) too
+    monkeypatch.setenv("ALEGPU_SHIFT_DGRAD", shift_dgrad)
     for flag in ("1", "0"):
         monkeypatch.setenv("ALEGPU_NO_TMA", flag)
         L = alegpu.Learner(H, 4, n, alegpu.MATH_BF16, cases.LR)
