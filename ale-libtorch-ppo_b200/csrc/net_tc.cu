@@ -451,6 +451,29 @@ template <class T> struct DYShift {
     return p ? ldg16(p) : zero16();
   }
 };
+// DYShift through TMA (tf32 only: a tap's 32 output channels are exactly one 128-byte MN group; in bf16 a
+// group would span two taps).  Per k-block of 32 space-to-depth blocks r = (n, Y, X) and per tap (a, b) ONE
+// im2col load of 32 pixels x 32 channels of dact1 [n,20,20,32]: base pixel (X-1, Y-1) on the map's 21-wide
+// traversal grid (lower corner -1, upper corner 0), tap offsets (1-b, 1-a); pixels outside 20x20 are zeros.
+struct DYShiftTma {
+  ALEGPU_RAW_BF16
+  static constexpr int kElemBytes = 4;
+  static constexpr bool kMN = true;
+  static constexpr bool kAsync = true;
+  static constexpr bool kTma = true;
+  const void *map;
+  struct TileCtx {
+    int m0;
+  };
+  __device__ __forceinline__ TileCtx tile(int m0) const { return TileCtx{m0}; }
+  __device__ __forceinline__ void tma(const TileCtx &, uint32_t dst, int r0, int, uint64_t *bar) const {
+    const int n = r0 / 441, pix = r0 - n * 441, Y = pix / 21, X = pix - Y * 21;
+#pragma unroll
+    for (int tap = 0; tap < 4; ++tap)
+      tc::tma_im2col_4d(dst + (uint32_t)tap * 4096u, map, 0, X - 1, Y - 1, n, (uint16_t)(1 - (tap & 1)),
+                        (uint16_t)(1 - (tap >> 1)), bar);
+  }
+};
 struct ColsMNF32 {
   ALEGPU_RAW_F32
   static constexpr bool kMN = true;
@@ -965,7 +988,8 @@ int conv_wgrad(const Col &col, const T *dy, int64_t Mtot, float scale, float *gw
 template <class T>
 int conv1_wgrad_s2d(const T *s2d, const T *dy, int64_t n, float scale, float *gw, float *gb,
                     float *ws, size_t ws_floats, cudaStream_t s, cudaStream_t w, cudaEvent_t join,
-                    const void *s2d_map = nullptr, int s2d_row_base = 0) {
+                    const void *s2d_map = nullptr, int s2d_row_base = 0,
+                    const void *dy_shift_map = nullptr /* tf32: DYShiftTma's im2col map of dact1 */) {
   constexpr size_t per = 128 * 64;
   const size_t bias_floats = (size_t)kBiasParts * 32;
   ALEGPU_REQUIRE(ws_floats >= per + bias_floats, ALEGPU_RUNTIME_ERROR, "conv1 wgrad: workspace too small");
@@ -982,7 +1006,17 @@ int conv1_wgrad_s2d(const T *s2d, const T *dy, int64_t n, float scale, float *gw
   ALEGPU_COUNT_LAUNCH();
   if (join)
     ALEGPU_CUDA_CHECK(cudaEventRecord(join, w));
-  if (s2d_map) { // the observation operand (read once, un-expanded) through TMA
+  bool launched = false;
+  if constexpr (sizeof(T) == 4) {
+    if (s2d_map && dy_shift_map) { // both operands by TMA: no producer warp issues a copy
+      if (int rc = tc::launch_gemm_tc<64, 4>(DYShiftTma{dy_shift_map}, ColsMNTma<T>{s2d_map, s2d_row_base},
+                                             EpiPartial{ws, 128, 64}, 128, 64, n * 441, splits, rps, s))
+        return rc;
+      launched = true;
+    }
+  }
+  if (launched) {
+  } else if (s2d_map) { // the observation operand (read once, un-expanded) through TMA
     if (int rc = tc::launch_gemm_tc<64, 4>(DYShift<T>{dy}, ColsMNTma<T>{s2d_map, s2d_row_base},
                                            EpiPartial{ws, 128, 64}, 128, 64, n * 441, splits, rps, s))
       return rc;
@@ -1087,7 +1121,7 @@ template <class T> Shadow<T> shadow_view(const TcState &S, const NetParams &P) {
 enum TmaSlot { kMapAct1 = 0, kMapAct2, kMapDact3, kMapDact2, kMapObsMb, kMapObsAll, kMapObsAllSlots = 16,
                // plain [rows x 64] tiled maps of the same buffers for the shift convolutions (tc_shift.cuh)
                kMapAct2Rows = kMapObsAll + kMapObsAllSlots, kMapAct1Rows, kMapDact3PadRows, kMapDact2PadRows,
-               kMapDact3MN, kMapDact2MN, kMapDfcK, kMapAct3K, kMapFcwK, kMapFcwMN, kMapC2wK, kMapC3wTap, kMapC2wTap, kMapObsMbMN, kMapObsAllMN, // [rows x 64] boxes of one k-block of rows (ColsMNTma)
+               kMapDact3MN, kMapDact2MN, kMapDfcK, kMapAct3K, kMapFcwK, kMapFcwMN, kMapC2wK, kMapC3wTap, kMapC2wTap, kMapDact1Shift, kMapObsMbMN, kMapObsAllMN, // [rows x 64] boxes of one k-block of rows (ColsMNTma)
                kMapObsAllMNEnd = kMapObsAllMN + kMapObsAllSlots - 1,
                kMapObsMbRows, kMapObsAllRows,
                kMapCount = kMapObsAllRows + kMapObsAllSlots };
@@ -1270,6 +1304,21 @@ int net_tc_init(TcState &T, int64_t hidden, int64_t actions, int64_t cap, int64_
     if (int rc = set_rows_map(T, kMapC2wK, c2w, 64, 64, false, 512)) return rc;
     if (int rc = set_wtap_map(T, kMapC3wTap, c3w, 64, 9, 64)) return rc;
     if (int rc = set_wtap_map(T, kMapC2wTap, c2w, elem_bytes == 2 ? 64 : 32, elem_bytes == 2 ? 8 : 16, 64)) return rc;
+    if (elem_bytes == 4) { // dact1 [n,20,20,32] fp32 for DYShiftTma: 32-pixel x 32-channel boxes, MN-major swizzle
+      EncodeIm2colFn fn = encode_im2col_fn();
+      ALEGPU_REQUIRE(fn != nullptr, ALEGPU_RUNTIME_ERROR, "cuTensorMapEncodeIm2col is not available");
+      alignas(64) CUtensorMap m;
+      const cuuint64_t dims[4] = {32, 20, 20, (cuuint64_t)cap};
+      const cuuint64_t strides[3] = {128, 20 * 128, 400 * 128};
+      const int lo[2] = {-1, -1}, hi[2] = {0, 0};
+      const cuuint32_t estr[4] = {1, 1, 1, 1};
+      const CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, T.dact1, dims, strides, lo, hi, 32, 32, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B,
+                            CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      ALEGPU_REQUIRE(r == CUDA_SUCCESS, ALEGPU_RUNTIME_ERROR,
+                     "cuTensorMapEncodeIm2col (dact1) failed: " + std::to_string((int)r));
+      ALEGPU_CUDA_CHECK(cudaMemcpy((CUtensorMap *)T.tmaps + kMapDact1Shift, &m, sizeof(m), cudaMemcpyHostToDevice));
+    }
     void *dfc = elem_bytes == 2 ? T.dfc16 : (void *)dfc_f32;
     char *fcw = (char *)T.w_shadow + eb * (size_t)(32 * 256 + 32 + 64 * 512 + 64 + 64 * 576 + 64);
     T.fc_tma = dfc != nullptr;
@@ -1669,7 +1718,10 @@ int backward_impl(const NetParams &P, const NetParams &G, TcState &S, const uint
       xbase = in_all ? (int)((x16 - all) / 28224) * 441 : 0;
     }
     if (int rc = conv1_wgrad_s2d<T>(x16, dact1, n, 1.0f / 255.0f, G.c1w, G.c1b, S.ws_c1, S.ws_c1_n,
-                                    s, fork ? w : s, fork ? S.ev_join : nullptr, xmap, xbase))
+                                    s, fork ? w : s, fork ? S.ev_join : nullptr, xmap, xbase,
+                                    S.use_tma_wgrad && S.elem_bytes == 4 && !getenv("ALEGPU_NO_TMA_DYSHIFT")
+                                        ? tmap(S, kMapDact1Shift)
+                                        : nullptr))
       return rc;
   }
   if (!S.serial)
