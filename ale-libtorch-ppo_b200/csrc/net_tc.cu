@@ -865,13 +865,15 @@ __global__ void reduce_wgrad_kernel(const float *__restrict__ ws, int splits, in
 
 // conv1 wgrad (space-to-depth form): gw[oc*256 + k] = scale * sum_z ws[z][(tap,oc)][ch] with
 // k = conv1_k_of_kprime(tap*64 + ch); gb[oc] = sum over the column-sum partials bp[g][oc].
-// block (32, 8): 32 outputs, the 8 thread rows sum interleaved z subsets that are then combined in
-// fixed order (deterministic).  grid = 256 blocks of weights + 1 block of biases.
-__global__ void __launch_bounds__(256)
+// grid = 256 blocks of weights + 1 block of biases.
+__global__ void __launch_bounds__(1024)
     reduce_c1_s2d_kernel(const float *__restrict__ ws, int splits, float scale,
                          const float *__restrict__ bp, int bias_parts, float *__restrict__ gw,
                          float *__restrict__ gb) {
-  __shared__ float part[8][32];
+  // block (32, 32): 32 outputs x 32 interleaved z subsets (up to 296 splits: <= 10 loads per thread, all
+  // independent), combined in fixed order -> deterministic.  (8 subsets of 37 dependent loads took 19.7 us
+  // at 296 splits; this form is latency-shallow.)
+  __shared__ float part[32][33];
   const int ty = threadIdx.y, tx = threadIdx.x;
   const bool bias = blockIdx.x == 256;
   const int idx = blockIdx.x * 32 + tx;
@@ -880,9 +882,9 @@ __global__ void __launch_bounds__(256)
   const int count = bias ? bias_parts : splits;
   float s0 = 0.0f, s1 = 0.0f;
   int z = ty;
-  for (; z + 8 < count; z += 16) { // two independent chains per thread
+  for (; z + 32 < count; z += 64) { // two independent chains per thread
     s0 += p[(size_t)z * stride];
-    s1 += p[(size_t)(z + 8) * stride];
+    s1 += p[(size_t)(z + 32) * stride];
   }
   if (z < count)
     s0 += p[(size_t)z * stride];
@@ -891,7 +893,7 @@ __global__ void __launch_bounds__(256)
   if (ty == 0) {
     float t = part[0][tx];
 #pragma unroll
-    for (int g = 1; g < 8; ++g)
+    for (int g = 1; g < 32; ++g)
       t += part[g][tx];
     if (bias) {
       gb[tx] = t;
@@ -1025,7 +1027,7 @@ int conv1_wgrad_s2d(const T *s2d, const T *dy, int64_t n, float scale, float *gw
     return rc;
   if (join)
     ALEGPU_CUDA_CHECK(cudaStreamWaitEvent(s, join, 0));
-  reduce_c1_s2d_kernel<<<257, dim3(32, 8), 0, s>>>(ws, splits, scale, bp, kBiasParts, gw, gb);
+  reduce_c1_s2d_kernel<<<257, dim3(32, 32), 0, s>>>(ws, splits, scale, bp, kBiasParts, gw, gb);
   ALEGPU_COUNT_LAUNCH();
   ALEGPU_LAUNCH_CHECK();
   return ALEGPU_OK;
