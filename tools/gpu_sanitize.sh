@@ -1,4 +1,5 @@
 #!/bin/bash
+# NOTE: compute-sanitizer is CLOSED on this pool (profiles/r02_sanitizer_unavailable.txt); the script is kept for a pool where it runs.
 # compute-sanitizer evidence (SURVEY §5 race-detection row): memcheck over the tensor-core engine
 # (mbarrier / TMEM / TMA / shift convolutions), the preprocess pipe and one train(); racecheck over the
 # shared-memory CUDA-core kernels (preprocess, GAE, heads / loss, optimiser).  Summaries -> gpurun_out/.
