@@ -293,6 +293,33 @@ class losses:
         res["loss"] = float(loss.numpy()[0])
         return res
 
+    LOSS_STATIC_MAX_ROWS = 1 << 20  # ALEGPU_LOSS_STATIC_MAX_ROWS
+
+    @staticmethod
+    def compute_static(logits, old_log_probabilities, actions, advantages, values, returns, masks,
+                       clip_param, value_loss_coef, entropy_coef):
+        """alegpu_loss_static: losses.compute with the library's static device scratch (no allocation
+        inside the call; n <= LOSS_STATIC_MAX_ROWS).  No counterpart in the reference."""
+        z, ol = _dev(logits, np.float32), _dev(old_log_probabilities, np.float32)
+        a = _dev(actions, np.int64)
+        adv, v, ret = (_dev(x, np.float32) for x in (advantages, values, returns))
+        mk = _dev(masks, np.uint8)
+        n, A = z.shape
+        out = {k: DeviceArray.zeros(n, np.float32) for k in
+               ("clipped_losses", "value_losses", "entropies", "total_losses", "ratio", "dvalues")}
+        out["dlogits"] = DeviceArray.zeros((n, A), np.float32)
+        loss = DeviceArray.zeros(1, np.float32)
+        _check(lib().alegpu_loss_static(_p(z), _p(ol), _p(a), _p(adv), _p(v), _p(ret), _p(mk),
+                                        C.c_int64(n), C.c_int64(A), C.c_float(clip_param),
+                                        C.c_float(value_loss_coef), C.c_float(entropy_coef),
+                                        _p(loss), _p(out["clipped_losses"]),
+                                        _p(out["value_losses"]), _p(out["entropies"]),
+                                        _p(out["total_losses"]), _p(out["ratio"]),
+                                        _p(out["dlogits"]), _p(out["dvalues"]), None))
+        res = {k: d.numpy() for k, d in out.items()}
+        res["loss"] = float(loss.numpy()[0])
+        return res
+
 
 # ---- configs/*.yaml: Config / load_config — src/bin/train.cc:33-60, 108-136 ---------------------
 class Config(C.Structure):

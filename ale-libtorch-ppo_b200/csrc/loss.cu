@@ -202,3 +202,85 @@ extern "C" int alegpu_loss(const float *logits, const float *old_log_probs,
   ALEGPU_LAUNCH_CHECK();
   return ALEGPU_OK;
 }
+
+// ---- alegpu_loss_static: alegpu_loss for callers that cannot allocate ------------------------------
+// No counterpart in the reference.  Same kernels and
+// launch sequence as alegpu_loss, but the scratch (mask count, loss slot, per-block partials) lives in
+// a file-scope device array instead of a cudaMalloc'ed buffer, so the entry point never calls
+// cudaMalloc / cudaFree (or anything that allocates) and can be used under stream capture or from
+// harnesses that forbid allocation.  Every GPU that loads the library holds the array
+// (kLossStaticFloats * 4 bytes = 16.25 KB) until exit.  All calls on one device share it: calls that
+// overlap on the GPU race, and the array keeps the previous call's contents — the header slots are
+// cleared on the stream at the start of every call; the partials need no clearing (every slot that is
+// read is written first by the same call).
+static constexpr int64_t kLossStaticMaxRows = ALEGPU_LOSS_STATIC_MAX_ROWS;        // 1 << 20
+static constexpr int kLossStaticHeader = 64;                                      // 256-byte header
+static constexpr int kLossStaticBlocks = (int)(kLossStaticMaxRows / kThreads);    // 4096 partials
+static constexpr int kLossStaticFloats = kLossStaticHeader + kLossStaticBlocks;
+static_assert(kLossStaticMaxRows % kThreads == 0, "max rows must be whole blocks");
+static __device__ __align__(256) float g_loss_static_scratch[kLossStaticFloats];
+
+namespace {
+// In host code g_loss_static_scratch is only a stand-in for the symbol, not a device address: the
+// address each device gives it is looked up once per device, with that device current.
+std::mutex g_loss_static_mutex;
+float *g_loss_static_ptr[64] = {};
+
+int loss_static_scratch(float **out) {
+  int dev = 0;
+  ALEGPU_CUDA_CHECK(cudaGetDevice(&dev));
+  ALEGPU_REQUIRE(dev >= 0 && dev < 64, ALEGPU_RUNTIME_ERROR, "loss_static: device ordinal out of range");
+  std::lock_guard<std::mutex> lock(g_loss_static_mutex);
+  if (!g_loss_static_ptr[dev]) {
+    float *ptr = nullptr;
+    ALEGPU_CUDA_CHECK(cudaGetSymbolAddress((void **)&ptr, g_loss_static_scratch));
+    ALEGPU_REQUIRE(ptr != nullptr, ALEGPU_RUNTIME_ERROR, "loss_static: null symbol address");
+    g_loss_static_ptr[dev] = ptr;
+  }
+  *out = g_loss_static_ptr[dev];
+  return ALEGPU_OK;
+}
+} // namespace
+
+extern "C" int alegpu_loss_static(const float *logits, const float *old_log_probs,
+                                  const int64_t *actions, const float *advantages,
+                                  const float *values, const float *returns, const uint8_t *masks,
+                                  int64_t n, int64_t A, float clip_param, float value_loss_coef,
+                                  float entropy_coef, float *loss, float *clipped_losses,
+                                  float *value_losses, float *entropies, float *total_losses,
+                                  float *ratio, float *dlogits, float *dvalues, void *stream) {
+  ALEGPU_REQUIRE(n >= 1 && A >= 1 && A <= 32, ALEGPU_INVALID_ARGUMENT,
+                 "loss_static: need n >= 1 and 1 <= A <= 32");
+  ALEGPU_REQUIRE(n <= kLossStaticMaxRows, ALEGPU_INVALID_ARGUMENT,
+                 "loss_static: n = " + std::to_string(n) + " exceeds the static scratch (at most " +
+                     std::to_string(kLossStaticMaxRows) + " rows per call; use alegpu_loss)");
+  ALEGPU_REQUIRE(logits && old_log_probs && actions && advantages && values && returns && masks,
+                 ALEGPU_INVALID_ARGUMENT, "loss_static: null input pointer");
+  cudaStream_t s = as_stream(stream);
+  float *scratch = nullptr;
+  if (int rc = loss_static_scratch(&scratch))
+    return rc;
+  const int blocks = (int)ceil_div(n, kThreads);
+  float *count = scratch, *lossbuf = scratch + 1, *partials = scratch + kLossStaticHeader;
+  ALEGPU_CUDA_CHECK(cudaMemsetAsync(scratch, 0, kLossStaticHeader * sizeof(float), s));
+  if (int rc = launch_mask_count(masks, n, 1, count, s))
+    return rc;
+  if (A <= 4)
+    loss_kernel<4><<<blocks, kThreads, 0, s>>>(logits, old_log_probs, actions, advantages,
+                                               values, returns, masks, n, (int)A, clip_param,
+                                               value_loss_coef, entropy_coef, count, partials,
+                                               clipped_losses, value_losses, entropies,
+                                               total_losses, ratio, dlogits, dvalues);
+  else
+    loss_kernel<32><<<blocks, kThreads, 0, s>>>(logits, old_log_probs, actions, advantages,
+                                                values, returns, masks, n, (int)A, clip_param,
+                                                value_loss_coef, entropy_coef, count, partials,
+                                                clipped_losses, value_losses, entropies,
+                                                total_losses, ratio, dlogits, dvalues);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  loss_finalize_kernel<<<1, 32, 0, s>>>(partials, blocks, count, loss ? loss : lossbuf);
+  ALEGPU_COUNT_LAUNCH();
+  ALEGPU_LAUNCH_CHECK();
+  return ALEGPU_OK;
+}

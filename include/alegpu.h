@@ -166,6 +166,26 @@ int alegpu_loss(const float *logits, const float *old_log_probs, const int64_t *
                 float *value_losses, float *entropies, float *total_losses, float *ratio,
                 float *dlogits, float *dvalues, void *stream);
 
+/* alegpu_loss for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid allocation).  It has NO counterpart in the reference.
+ * Same arguments, kernels and results as alegpu_loss, but the
+ * scratch (mask count, loss slot, per-block partials) is a 16.25 KB file-scope `static __device__`
+ * array inside the library, so the call performs no cudaMalloc / cudaFree / allocating library call.
+ * Limits: n <= ALEGPU_LOSS_STATIC_MAX_ROWS (larger n -> ALEGPU_INVALID_ARGUMENT; use alegpu_loss).
+ * Every GPU that loads the library holds the array until exit.  All calls on one device share it and
+ * it keeps the last call's contents (the slots that must start at zero are cleared on `stream` by each
+ * call): calls that overlap on the GPU — two streams, or two threads — race; serialise them.  The
+ * first call on a device looks the array's device address up (cudaGetSymbolAddress, once per device
+ * with that device current); make that first call outside a stream capture. */
+#define ALEGPU_LOSS_STATIC_MAX_ROWS (1 << 20)
+int alegpu_loss_static(const float *logits, const float *old_log_probs, const int64_t *actions,
+                       const float *advantages, const float *values, const float *returns,
+                       const uint8_t *masks, int64_t n, int64_t A, float clip_param,
+                       float value_loss_coef, float entropy_coef, float *loss,
+                       float *clipped_losses, float *value_losses, float *entropies,
+                       float *total_losses, float *ratio, float *dlogits, float *dvalues,
+                       void *stream);
+
 /* streams / events for hosts that overlap the frame hand-off with compute */
 int alegpu_stream_create(void **stream);
 int alegpu_stream_destroy(void *stream);
