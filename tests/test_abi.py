@@ -35,11 +35,13 @@ def test_sass_is_sm100a_only():
 
 def test_sass_uses_tcgen05_tmem_and_tma():
     """The GEMM engine is tcgen05 (UTCHMMA, accumulators read back from TMEM with LDTM), its conv
-    operands come through TMA im2col (UTMALDG.*IM2COL) and the preprocess pipe through bulk copies
-    (UBLKCP); no legacy warp-level HMMA tensor-core path is shipped."""
+    operands come through TMA im2col (UTMALDG.*IM2COL), the shift convolutions' staged inputs and the
+    plain-matrix / per-tap weight operands through tiled TMA (UTMALDG.2D / .3D) and the preprocess pipe
+    through bulk copies (UBLKCP); no legacy warp-level HMMA tensor-core path is shipped."""
     import subprocess
     sass = subprocess.run(["cuobjdump", "-sass", alegpu.SO_PATH], capture_output=True, text=True).stdout
-    for mnemonic in ("UTCHMMA", "LDTM", "UTCBAR", "UTMALDG.4D.IM2COL", "UBLKCP", "SYNCS.PHASECHK"):
+    for mnemonic in ("UTCHMMA", "LDTM", "UTCBAR", "UTMALDG.4D.IM2COL", "UTMALDG.2D", "UTMALDG.3D",
+                     "UBLKCP", "SYNCS.PHASECHK"):
         assert mnemonic in sass, mnemonic
     assert not re.search(r"\bHMMA\.", sass), "legacy mma.sync path in the shipped library"
 
